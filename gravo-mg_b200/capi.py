@@ -1,0 +1,238 @@
+"""ctypes binding of the C ABI (include/gravomg_b200.h) -- the host-side mirror of the reference's
+entry points, one method per reference function with the same argument meaning:
+
+    reference (namespace GravoMG)            here (class Context)
+    toEdgeDistanceMatrix(matrix, points)     to_edge_distance_matrix(colptr, rowidx, points)
+    extractEdges(matrix)                     extract_edges(colptr, rowidx, val)
+    averageEdgeLength(positions, neighbors)  average_edge_length(points, edges)
+    fastDiscSample(pos, edge_matrix, radius) fast_disc_sample(points, colptr, rowidx, radius)
+    assignParents(...)                       assign_parents(points, colptr, rowidx, samples)
+    extractCoarseEdges(...)                  extract_coarse_edges(colptr, rowidx, val, m, parents)
+    coarseFromMeanOfFineChildren(...)        coarse_from_mean_of_fine_children(points, colptr, rowidx, parents, m)
+    constructVoronoiTriangles(...)           construct_voronoi_triangles(points, colptr, rowidx, val)
+    constructProlongation(...)               construct_prolongation(fine, coarse, c_colptr, c_rowidx, c_val, parents, weighting)
+    projectedPoints(weights, coarse_points)  projected_points(rowptr, colidx, val, coarse_points)
+
+There is no CPU fallback: if the CUDA library is missing or no GPU is usable, construction raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgravomg_b200.so")
+
+BARYCENTRIC, UNIFORM, INVDIST = 0, 1, 2
+SAMPLER_EXACT, SAMPLER_PARALLEL = 0, 1
+
+STATUS_NAMES = {0: "GMG_OK", 1: "GMG_ERR_CUDA", 2: "GMG_ERR_INVALID", 3: "GMG_ERR_FALLBACK_RATIO",
+                4: "GMG_ERR_ZERO_LENGTH_EDGE", 5: "GMG_ERR_ASYMMETRIC", 6: "GMG_ERR_STATE", 7: "GMG_ERR_NCCL"}
+
+_i32p, _i64p, _f64p = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+
+
+class GmgError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"{STATUS_NAMES.get(status, status)}: {message}")
+        self.status = status
+
+
+class ProlongationStats(C.Structure):
+    _fields_ = [("no_triangle_found", C.c_int64), ("edges_found", C.c_int64), ("fallback_count", C.c_int64)]
+
+
+_lib = None
+
+
+def load_library():
+    """Load the CUDA library; raises if it has not been built (no fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(f"{LIB_PATH} is missing: run `python -m gravomg_b200.build` "
+                                    "(the product path has no CPU fallback)")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.gmg_last_error.restype = C.c_char_p
+        _lib.gmg_last_error.argtypes = [C.c_void_p]
+        _lib.gmg_last_kernel_ms.restype = C.c_double
+        _lib.gmg_last_kernel_ms.argtypes = [C.c_void_p]
+        _lib.gmg_launch_count.restype = C.c_int64
+        _lib.gmg_launch_count.argtypes = [C.c_void_p]
+        _lib.gmg_destroy.argtypes = [C.c_void_p]
+        _lib.gmg_destroy.restype = None
+    return _lib
+
+
+def _p(a, ty):
+    return a.ctypes.data_as(ty)
+
+
+def _pts(a):
+    a = np.asarray(a, dtype=np.float64)
+    if a.ndim != 2 or a.shape[1] != 3:
+        raise ValueError("points must have shape (n, 3)")
+    return np.asfortranarray(a)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Context:
+    """One CUDA stream worth of state; one calling thread at a time."""
+
+    def __init__(self, device=0, stream=None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.gmg_create(C.c_int(device), C.c_void_p(stream or 0), C.byref(h))
+        if rc != 0:
+            raise GmgError(rc, self.lib.gmg_last_error(None).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.gmg_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc != 0:
+            raise GmgError(rc, self.lib.gmg_last_error(self.h).decode())
+
+    @property
+    def last_kernel_ms(self):
+        return float(self.lib.gmg_last_kernel_ms(self.h))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.gmg_launch_count(self.h))
+
+    # ---- reference entry points ---------------------------------------------------------------
+    def to_edge_distance_matrix(self, colptr, rowidx, points):
+        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
+        n = pts.shape[0]
+        out = np.empty(rowidx.shape[0], dtype=np.float64)
+        self._check(self.lib.gmg_to_edge_distance_matrix(self.h, C.c_int64(n), _p(colptr, _i32p), _p(rowidx, _i32p),
+                                                         _p(pts, _f64p), C.c_int64(n), _p(out, _f64p)))
+        return out
+
+    def extract_edges(self, colptr, rowidx, val):
+        colptr, rowidx, val = _i32(colptr), _i32(rowidx), _f64(val)
+        n, nnz = colptr.shape[0] - 1, rowidx.shape[0]
+        edges = np.empty((nnz, 2), dtype=np.int32, order="F")
+        values = np.empty(nnz, dtype=np.float64)
+        self._check(self.lib.gmg_extract_edges(self.h, C.c_int64(n), _p(colptr, _i32p), _p(rowidx, _i32p),
+                                               _p(val, _f64p), _p(edges, _i32p), _p(values, _f64p)))
+        return edges, values
+
+    def average_edge_length(self, points, edges):
+        pts = _pts(points)
+        edges = np.asfortranarray(edges, dtype=np.int32)
+        out = C.c_double()
+        self._check(self.lib.gmg_average_edge_length(self.h, C.c_int64(pts.shape[0]), _p(pts, _f64p),
+                                                     C.c_int64(pts.shape[0]), C.c_int64(edges.shape[0]),
+                                                     _p(edges, _i32p), C.byref(out)))
+        return out.value
+
+    def fast_disc_sample(self, points, colptr, rowidx, radius, mode=SAMPLER_EXACT, seed=42):
+        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
+        n = pts.shape[0]
+        sel = np.empty(max(n, 1), dtype=np.int64)
+        m = C.c_int64()
+        self._check(self.lib.gmg_fast_disc_sample(self.h, C.c_int64(n), _p(pts, _f64p), C.c_int64(n),
+                                                  _p(colptr, _i32p), _p(rowidx, _i32p), C.c_double(radius),
+                                                  C.c_int(mode), C.c_uint64(seed), _p(sel, _i64p), C.byref(m)))
+        return sel[:m.value].copy()
+
+    def assign_parents(self, points, colptr, rowidx, samples):
+        pts, colptr, rowidx, samples = _pts(points), _i32(colptr), _i32(rowidx), _i64(samples)
+        n = pts.shape[0]
+        par = np.empty(n, dtype=np.int64)
+        self._check(self.lib.gmg_assign_parents(self.h, C.c_int64(n), _p(pts, _f64p), C.c_int64(n), _p(colptr, _i32p),
+                                                _p(rowidx, _i32p), C.c_int64(samples.shape[0]), _p(samples, _i64p),
+                                                _p(par, _i64p)))
+        return par
+
+    def _fetch_sparse(self, nnz):
+        inner = np.empty(nnz, dtype=np.int32)
+        val = np.empty(nnz, dtype=np.float64)
+        self._check(self.lib.gmg_fetch_sparse(self.h, _p(inner, _i32p), _p(val, _f64p)))
+        return inner, val
+
+    def extract_coarse_edges(self, colptr, rowidx, val, m, parents):
+        colptr, rowidx, val, parents = _i32(colptr), _i32(rowidx), _f64(val), _i64(parents)
+        n = colptr.shape[0] - 1
+        ocp = np.empty(m + 1, dtype=np.int32)
+        nnz = C.c_int64()
+        self._check(self.lib.gmg_extract_coarse_edges(self.h, C.c_int64(n), _p(colptr, _i32p), _p(rowidx, _i32p),
+                                                      _p(val, _f64p), C.c_int64(m), _p(parents, _i64p),
+                                                      _p(ocp, _i32p), C.byref(nnz)))
+        ri, va = self._fetch_sparse(nnz.value)
+        return ocp, ri, va
+
+    def coarse_from_mean_of_fine_children(self, points, colptr, rowidx, parents, m):
+        pts, colptr, rowidx, parents = _pts(points), _i32(colptr), _i32(rowidx), _i64(parents)
+        n = pts.shape[0]
+        out = np.empty((m, 3), dtype=np.float64, order="F")
+        self._check(self.lib.gmg_coarse_from_mean_of_fine_children(
+            self.h, C.c_int64(n), _p(pts, _f64p), C.c_int64(n), _p(colptr, _i32p), _p(rowidx, _i32p),
+            _p(parents, _i64p), C.c_int64(m), _p(out, _f64p), C.c_int64(max(m, 1))))
+        return out
+
+    def construct_voronoi_triangles(self, points, colptr, rowidx, val):
+        pts, colptr, rowidx, val = _pts(points), _i32(colptr), _i32(rowidx), _f64(val)
+        m = pts.shape[0]
+        T = C.c_int64()
+        fan_ptr = np.empty(m + 1, dtype=np.int64)
+        self._check(self.lib.gmg_construct_voronoi_triangles(self.h, C.c_int64(m), _p(pts, _f64p), C.c_int64(m),
+                                                             _p(colptr, _i32p), _p(rowidx, _i32p), _p(val, _f64p),
+                                                             C.byref(T), _p(fan_ptr, _i64p)))
+        T = T.value
+        tri = np.empty((T, 3), dtype=np.int64)
+        nrm = np.empty((T, 3), dtype=np.float64)
+        fan = np.empty(3 * T, dtype=np.int64)
+        self._check(self.lib.gmg_fetch_triangles(self.h, _p(tri, _i64p), _p(nrm, _f64p), _p(fan, _i64p)))
+        return tri, nrm, fan_ptr, fan
+
+    def construct_prolongation(self, fine_points, coarse_points, c_colptr, c_rowidx, c_val, parents,
+                               weighting=BARYCENTRIC, return_stats=False):
+        fp, cp = _pts(fine_points), _pts(coarse_points)
+        c_colptr, c_rowidx, c_val, parents = _i32(c_colptr), _i32(c_rowidx), _f64(c_val), _i64(parents)
+        n, m = fp.shape[0], cp.shape[0]
+        rowptr = np.empty(n + 1, dtype=np.int32)
+        nnz = C.c_int64()
+        st = ProlongationStats()
+        self._check(self.lib.gmg_construct_prolongation(
+            self.h, C.c_int64(n), _p(fp, _f64p), C.c_int64(n), C.c_int64(m), _p(cp, _f64p), C.c_int64(max(m, 1)),
+            _p(c_colptr, _i32p), _p(c_rowidx, _i32p), _p(c_val, _f64p), _p(parents, _i64p), C.c_int(weighting),
+            _p(rowptr, _i32p), C.byref(nnz), C.byref(st)))
+        ci, va = self._fetch_sparse(nnz.value)
+        if return_stats:
+            return rowptr, ci, va, dict(no_triangle_found=st.no_triangle_found, edges_found=st.edges_found,
+                                        fallback_count=st.fallback_count)
+        return rowptr, ci, va
+
+    def projected_points(self, rowptr, colidx, val, coarse_points):
+        cp, rowptr, colidx, val = _pts(coarse_points), _i32(rowptr), _i32(colidx), _f64(val)
+        n, m = rowptr.shape[0] - 1, cp.shape[0]
+        out = np.empty((n, 3), dtype=np.float64, order="F")
+        self._check(self.lib.gmg_projected_points(self.h, C.c_int64(n), C.c_int64(m), _p(rowptr, _i32p),
+                                                  _p(colidx, _i32p), _p(val, _f64p), _p(cp, _f64p),
+                                                  C.c_int64(max(m, 1)), _p(out, _f64p), C.c_int64(max(n, 1))))
+        return out

@@ -1,0 +1,161 @@
+// Shared device/host plumbing for the gravomg_b200 kernels: error handling, the context, stream-
+// ordered device buffers, a work-efficient exclusive scan, and the 3-vector arithmetic whose
+// association order matches the oracle (oracle/eigen_shim/Eigen/Core): (x+y)+z, no FMA.
+//
+// The whole library is compiled with -fmad=false: every floating-point result on this path either
+// feeds a comparison that decides an integer output or must agree with the reference to 1e-12.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cooperative_groups.h>
+
+#include <cfloat>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/gravomg_b200.h"
+
+namespace gmg {
+
+namespace cg = cooperative_groups;
+
+struct Error {
+    int status;
+    std::string what;
+};
+
+#define GMG_CUDA(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t e__ = (expr);                                                                   \
+        if (e__ != cudaSuccess)                                                                     \
+            throw ::gmg::Error{GMG_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__) +  \
+                                                 " (" __FILE__ ":" + std::to_string(__LINE__) + ")"}; \
+    } while (0)
+
+#define GMG_REQUIRE(cond, status, msg)                                \
+    do {                                                              \
+        if (!(cond)) throw ::gmg::Error{status, std::string(msg)};    \
+    } while (0)
+
+constexpr int kBlock = 256;
+
+inline int div_up(int64_t a, int64_t b) { return int((a + b - 1) / b); }
+
+}  // namespace gmg
+
+// The context owns the stream, timing events and the retained variable-size result.
+struct gmg_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    std::string last_error;
+    double last_kernel_ms = 0.0;
+    int64_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // retained result of the last two-call function (device memory, released on the next call)
+    void* keep[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int64_t keep_n[6] = {0, 0, 0, 0, 0, 0};
+    int keep_kind = 0;  // 0 none, 1 sparse (inner,val), 2 triangles (tri,normal,fan)
+};
+
+namespace gmg {
+
+// Stream-ordered device buffer (cudaMallocAsync pool): allocation and release cost no device sync.
+template <typename T> struct DevBuf {
+    T* p = nullptr;
+    int64_t n = 0;
+    cudaStream_t s = nullptr;
+    DevBuf() {}
+    DevBuf(gmg_ctx* c, int64_t count) { alloc(c, count); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n), s(o.s) { o.p = nullptr; o.n = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; s = o.s; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void alloc(gmg_ctx* c, int64_t count) {
+        release();
+        s = c->stream; n = count;
+        GMG_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&p), sizeof(T) * size_t(count > 0 ? count : 1), s));
+    }
+    void release() {
+        if (p) cudaFreeAsync(p, s);
+        p = nullptr; n = 0;
+    }
+    T* detach() { T* q = p; p = nullptr; n = 0; return q; }
+    void upload(const T* host, int64_t count) {
+        if (count > 0) GMG_CUDA(cudaMemcpyAsync(p, host, sizeof(T) * size_t(count), cudaMemcpyHostToDevice, s));
+    }
+    void download(T* host, int64_t count) const {
+        if (count > 0) GMG_CUDA(cudaMemcpyAsync(host, p, sizeof(T) * size_t(count), cudaMemcpyDeviceToHost, s));
+    }
+    void zero() { GMG_CUDA(cudaMemsetAsync(p, 0, sizeof(T) * size_t(n > 0 ? n : 1), s)); }
+};
+
+template <typename T> DevBuf<T> to_device(gmg_ctx* c, const T* host, int64_t count) {
+    DevBuf<T> b(c, count);
+    b.upload(host, count);
+    return b;
+}
+
+// Column-major n x 3 points with leading dimension ld -> packed x|y|z on the device (ld = n).
+inline DevBuf<double> points_to_device(gmg_ctx* c, const double* host, int64_t n, int64_t ld) {
+    DevBuf<double> b(c, 3 * n);
+    for (int k = 0; k < 3; ++k)
+        if (n > 0)
+            GMG_CUDA(cudaMemcpyAsync(b.p + k * n, host + k * ld, sizeof(double) * size_t(n), cudaMemcpyHostToDevice,
+                                     c->stream));
+    return b;
+}
+inline void points_to_host(gmg_ctx* c, const double* dev, int64_t n, double* host, int64_t ld) {
+    for (int k = 0; k < 3; ++k)
+        if (n > 0)
+            GMG_CUDA(cudaMemcpyAsync(host + k * ld, dev + k * n, sizeof(double) * size_t(n), cudaMemcpyDeviceToHost,
+                                     c->stream));
+}
+
+inline void sync(gmg_ctx* c) { GMG_CUDA(cudaStreamSynchronize(c->stream)); }
+
+#define GMG_LAUNCH(ctx, kernel, grid, block, smem, ...)                         \
+    do {                                                                        \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);        \
+        GMG_CUDA(cudaGetLastError());                                           \
+        ++(ctx)->launches;                                                      \
+    } while (0)
+
+// Device-side exclusive scan of int32 counts (in place allowed); *total (device int64) receives the sum.
+void exclusive_scan_i32(gmg_ctx* c, const int32_t* in, int32_t* out, int64_t n, int64_t* d_total);
+
+// ---- 3-vector arithmetic: same association order as the oracle ---------------------------------
+struct V3 { double x, y, z; };
+__device__ __forceinline__ V3 ld3(const double* __restrict__ p, int64_t n, int64_t i) {
+    return V3{__ldg(p + i), __ldg(p + n + i), __ldg(p + 2 * n + i)};
+}
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return V3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, double s) { return V3{a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ double norm(V3 a) { return sqrt(dot(a, a)); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+    return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ V3 normalized(V3 a) {
+    double z = dot(a, a);
+    if (z > 0.0) { double s = sqrt(z); return V3{a.x / s, a.y / s, a.z / s}; }
+    return a;
+}
+
+// lower_bound of key in the ascending int32 range [lo, hi); returns hi when every entry is smaller
+__device__ __forceinline__ int32_t lower_bound_i32(const int32_t* __restrict__ a, int32_t lo, int32_t hi, int32_t key) {
+    while (lo < hi) {
+        int32_t mid = lo + ((hi - lo) >> 1);
+        if (__ldg(a + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+}  // namespace gmg

@@ -1,0 +1,260 @@
+// Streaming utility kernels: exclusive scan, edge lengths (GravoMG::toEdgeDistanceMatrix,
+// reference src/utility.cpp:50-56), edge-list flattening (extractEdges, src/utility.cpp:58-71),
+// mean edge length (averageEdgeLength, src/multigrid.cpp:127-133) and the pattern-symmetry check.
+#include "stages.h"
+
+namespace gmg {
+
+// ---------------------------------------------------------------------------------------------
+// Exclusive scan: reduce-then-scan over tiles of 2048 (256 threads x 8 items).
+// ---------------------------------------------------------------------------------------------
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kBlock * kScanItems;
+
+__device__ __forceinline__ int32_t block_exclusive_scan(int32_t v, int32_t& block_total) {
+    __shared__ int32_t warp_sums[kBlock / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int32_t w = lane < kBlock / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < kBlock / 32; d <<= 1) {
+            int32_t t = __shfl_up_sync(0xffffffffu, w, d);
+            if (lane >= d) w += t;
+        }
+        if (lane < kBlock / 32) warp_sums[lane] = w;
+    }
+    __syncthreads();
+    const int32_t warp_off = wid ? warp_sums[wid - 1] : 0;
+    block_total = warp_sums[kBlock / 32 - 1];
+    __syncthreads();
+    return warp_off + incl - v;
+}
+
+__global__ void __launch_bounds__(kBlock) scan_tile_sums(const int32_t* __restrict__ in, int64_t n,
+                                                         int32_t* __restrict__ tile_sums) {
+    const int64_t base = int64_t(blockIdx.x) * kScanTile;
+    int32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        int64_t i = base + k * kBlock + threadIdx.x;
+        if (i < n) s += in[i];
+    }
+    int32_t total;
+    block_exclusive_scan(s, total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+// One block scans up to any number of tile sums sequentially in chunks of kBlock.
+__global__ void __launch_bounds__(kBlock) scan_small(int32_t* __restrict__ a, int64_t n, int64_t* __restrict__ total) {
+    int64_t carry = 0;
+    for (int64_t base = 0; base < n; base += kBlock) {
+        int64_t i = base + threadIdx.x;
+        int32_t v = i < n ? a[i] : 0;
+        int32_t bt;
+        int32_t ex = block_exclusive_scan(v, bt);
+        if (i < n) a[i] = int32_t(carry + ex);
+        carry += bt;
+    }
+    if (threadIdx.x == 0 && total) *total = carry;
+}
+
+__global__ void __launch_bounds__(kBlock) scan_apply(const int32_t* __restrict__ in, int32_t* __restrict__ out,
+                                                     int64_t n, const int32_t* __restrict__ tile_offsets) {
+    // blocked arrangement: thread t owns items [t*8, t*8+8) of the tile, so the scan is in order
+    const int64_t base = int64_t(blockIdx.x) * kScanTile + int64_t(threadIdx.x) * kScanItems;
+    int32_t v[kScanItems];
+    int32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        s += v[k];
+    }
+    int32_t bt;
+    int32_t ex = block_exclusive_scan(s, bt) + tile_offsets[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanItems; ++k) {
+        if (base + k < n) out[base + k] = ex;
+        ex += v[k];
+    }
+}
+
+void exclusive_scan_i32(gmg_ctx* c, const int32_t* in, int32_t* out, int64_t n, int64_t* d_total) {
+    if (n <= 0) {
+        if (d_total) GMG_CUDA(cudaMemsetAsync(d_total, 0, sizeof(int64_t), c->stream));
+        return;
+    }
+    const int tiles = div_up(n, kScanTile);
+    DevBuf<int32_t> sums(c, tiles);
+    GMG_LAUNCH(c, scan_tile_sums, tiles, kBlock, 0, in, n, sums.p);
+    GMG_LAUNCH(c, scan_small, 1, kBlock, 0, sums.p, int64_t(tiles), d_total);
+    GMG_LAUNCH(c, scan_apply, tiles, kBlock, 0, in, out, n, sums.p);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K0 edge lengths: 8 lanes per column walk its stored entries; a warp covers 4 adjacent columns,
+// so index reads and length writes are contiguous. Position gathers are the irregular part.
+// Algorithmic bytes: 28n + 12nnz.
+// ---------------------------------------------------------------------------------------------
+constexpr int kGroup = 8;
+
+__global__ void __launch_bounds__(kBlock) edge_length_kernel(int32_t n, const int32_t* __restrict__ colptr,
+                                                             const int32_t* __restrict__ rowidx,
+                                                             const double* __restrict__ pts,
+                                                             double* __restrict__ out_len) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t col = int32_t(gid / kGroup);
+    const int sub = int(gid % kGroup);
+    if (col >= n) return;
+    const int32_t b = __ldg(colptr + col), e = __ldg(colptr + col + 1);
+    const V3 pc = ld3(pts, n, col);
+    for (int32_t k = b + sub; k < e; k += kGroup) {
+        const int32_t r = __ldg(rowidx + k);
+        out_len[k] = norm(ld3(pts, n, r) - pc);   // (points.row(row) - points.row(col)).norm()
+    }
+}
+
+void edge_lengths(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* pts,
+                  double* out_len) {
+    if (n == 0) return;
+    GMG_LAUNCH(c, edge_length_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, pts, out_len);
+}
+
+// extractEdges: edge e of column c, row r -> edges(e,0) = c, edges(e,1) = r; values copied.
+__global__ void __launch_bounds__(kBlock) extract_edges_kernel(int32_t n, const int32_t* __restrict__ colptr,
+                                                               const int32_t* __restrict__ rowidx,
+                                                               const double* __restrict__ val, int64_t nnz,
+                                                               int32_t* __restrict__ out_edges,
+                                                               double* __restrict__ out_values) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t col = int32_t(gid / kGroup);
+    const int sub = int(gid % kGroup);
+    if (col >= n) return;
+    const int32_t b = __ldg(colptr + col), e = __ldg(colptr + col + 1);
+    for (int32_t k = b + sub; k < e; k += kGroup) {
+        out_edges[k] = col;
+        out_edges[nnz + k] = __ldg(rowidx + k);
+        out_values[k] = __ldg(val + k);
+    }
+}
+
+void extract_edges_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                       int64_t nnz, int32_t* out_edges, double* out_values) {
+    if (n == 0) return;
+    GMG_LAUNCH(c, extract_edges_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, val, nnz,
+               out_edges, out_values);
+}
+
+// Mean edge length: fixed-shape deterministic reduction. Each block sums a contiguous slab with a
+// fixed tree; block partials are then summed by one block with the same tree.
+__device__ __forceinline__ double block_sum(double v) {
+    __shared__ double ws[kBlock / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+    if (lane == 0) ws[wid] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (wid == 0) {
+        r = lane < kBlock / 32 ? ws[lane] : 0.0;
+#pragma unroll
+        for (int d = 4; d > 0; d >>= 1) r += __shfl_down_sync(0xffffffffu, r, d);
+    }
+    __syncthreads();
+    return r;  // valid in thread 0
+}
+
+constexpr int kSumPerThread = 8;
+
+__global__ void __launch_bounds__(kBlock) edge_list_length_partial(int32_t n, const double* __restrict__ pts,
+                                                                   int64_t n_edges, const int32_t* __restrict__ edges,
+                                                                   double* __restrict__ partial) {
+    const int64_t base = int64_t(blockIdx.x) * kBlock * kSumPerThread;
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < kSumPerThread; ++k) {
+        const int64_t e = base + int64_t(k) * kBlock + threadIdx.x;
+        if (e < n_edges) s += norm(ld3(pts, n, __ldg(edges + n_edges + e)) - ld3(pts, n, __ldg(edges + e)));
+    }
+    s = block_sum(s);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+__global__ void __launch_bounds__(kBlock) sum_partials(const double* __restrict__ partial, int64_t count,
+                                                       double denom, double* __restrict__ out) {
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < count; i += kBlock) s += partial[i];
+    s = block_sum(s);
+    if (threadIdx.x == 0) *out = s / denom;
+}
+
+// Same reduction straight from the CSC arrays (used inside the hierarchy: no edge list is built).
+__global__ void __launch_bounds__(kBlock) length_partial(int64_t nnz, const double* __restrict__ len,
+                                                         double* __restrict__ partial) {
+    const int64_t base = int64_t(blockIdx.x) * kBlock * kSumPerThread;
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < kSumPerThread; ++k) {
+        const int64_t e = base + int64_t(k) * kBlock + threadIdx.x;
+        if (e < nnz) s += __ldg(len + e);
+    }
+    s = block_sum(s);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n_edges, const int32_t* edges,
+                             double* d_out) {
+    const int blocks = n_edges > 0 ? div_up(n_edges, int64_t(kBlock) * kSumPerThread) : 1;
+    DevBuf<double> partial(c, blocks);
+    if (n_edges > 0) GMG_LAUNCH(c, edge_list_length_partial, blocks, kBlock, 0, n, pts, n_edges, edges, partial.p);
+    else partial.zero();
+    GMG_LAUNCH(c, sum_partials, 1, kBlock, 0, partial.p, int64_t(blocks), double(n_edges - n), d_out);
+}
+
+void mean_length_dev(gmg_ctx* c, int64_t nnz, const double* len, double denom, double* d_out) {
+    const int blocks = nnz > 0 ? div_up(nnz, int64_t(kBlock) * kSumPerThread) : 1;
+    DevBuf<double> partial(c, blocks);
+    if (nnz > 0) GMG_LAUNCH(c, length_partial, blocks, kBlock, 0, nnz, len, partial.p);
+    else partial.zero();
+    GMG_LAUNCH(c, sum_partials, 1, kBlock, 0, partial.p, int64_t(blocks), denom, d_out);
+}
+
+// Pattern checks: row indices strictly ascending and in range; (r,c) stored => (c,r) stored.
+__global__ void __launch_bounds__(kBlock) check_pattern_kernel(int32_t n, const int32_t* __restrict__ colptr,
+                                                               const int32_t* __restrict__ rowidx,
+                                                               int32_t* __restrict__ flags) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t col = int32_t(gid / kGroup);
+    const int sub = int(gid % kGroup);
+    if (col >= n) return;
+    const int32_t b = __ldg(colptr + col), e = __ldg(colptr + col + 1);
+    if (e < b) { flags[0] = 1; return; }
+    for (int32_t k = b + sub; k < e; k += kGroup) {
+        const int32_t r = __ldg(rowidx + k);
+        if (r < 0 || r >= n || (k > b && __ldg(rowidx + k - 1) >= r)) { flags[0] = 1; continue; }
+        const int32_t rb = __ldg(colptr + r), re = __ldg(colptr + r + 1);
+        const int32_t pos = lower_bound_i32(rowidx, rb, re, col);
+        if (pos >= re || __ldg(rowidx + pos) != col) flags[1] = 1;
+    }
+}
+
+void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric) {
+    if (n == 0) return;
+    DevBuf<int32_t> flags(c, 2);
+    flags.zero();
+    GMG_LAUNCH(c, check_pattern_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, flags.p);
+    int32_t h[2];
+    flags.download(h, 2);
+    sync(c);
+    GMG_REQUIRE(h[0] == 0, GMG_ERR_INVALID, "edge matrix: row indices must be in range and strictly ascending per column");
+    GMG_REQUIRE(!need_symmetric || h[1] == 0, GMG_ERR_ASYMMETRIC, "edge matrix pattern is not symmetric");
+}
+
+}  // namespace gmg

@@ -1,0 +1,186 @@
+// Nearest-source (parent) assignment as a frontier-parallel sweep (GravoMG::assignParents,
+// reference src/multigrid.cpp:77-125, a multi-source Dijkstra with a (distance, index) min-heap).
+//
+// What the sequential code computes, and how it is reproduced bit-for-bit in parallel:
+//   1. dist[v] = min over source->v paths of the left-to-right sum fl(edge + path) (:107-108).
+//      Rounded addition is monotone, so a label-correcting sweep relaxing with the same
+//      fl(len + dist[u]) converges to the same bits. Non-negative doubles order like their bit
+//      patterns, so the relaxation is one atomicMin on a 64-bit word.
+//   2. parents[v] is inherited from the neighbour whose offer FIRST reached dist[v] (strict <, :111).
+//      When every edge strictly increases the path length, heap pops happen in lexicographic
+//      (dist, index) order, hence pred[v] = argmin_{u : fl(len_uv + dist[u]) == dist[v]} (dist[u], u).
+//      parents[v] = parents[pred[v]]; sources are roots. An edge with fl(len + d) == d (duplicate
+//      points) makes the pop order dynamic: detected and reported as GMG_ERR_ZERO_LENGTH_EDGE.
+//   3. Unreached vertices keep parent 0 (:82).
+// "Neighbours of v" are the stored rows of column v; with a symmetric pattern these are also the
+// vertices that relax INTO v.
+//
+// Algorithmic bytes: 40n + 4nnz + 4m (+ 8nnz for the cached lengths).
+#include "stages.h"
+
+namespace gmg {
+
+constexpr int kPLanes = 8;
+constexpr unsigned long long kInfBits = 0x7FEFFFFFFFFFFFFFull;  // DBL_MAX, src/multigrid.cpp:84
+
+struct ParentArgs {
+    int32_t n;
+    const int32_t* colptr;
+    const int32_t* rowidx;
+    const double* len;
+    unsigned long long* dist;  // bit patterns of non-negative doubles
+    int32_t* stamp;            // round in which a vertex was last queued
+    int32_t* q0;
+    int32_t* q1;
+    int32_t* counters;         // [0],[1] tails of q0,q1; [2] rounds
+};
+
+__global__ void __launch_bounds__(kBlock) parents_init_kernel(int32_t n, unsigned long long* __restrict__ dist,
+                                                              int32_t* __restrict__ stamp, int32_t* __restrict__ srcid) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n) { dist[i] = kInfBits; stamp[i] = 0; srcid[i] = -1; }
+}
+
+// Later sources overwrite earlier ones exactly like the loop at :89-93 (duplicates: last wins).
+__global__ void __launch_bounds__(kBlock) parents_seed_kernel(int32_t m, const int32_t* __restrict__ samples,
+                                                              unsigned long long* __restrict__ dist,
+                                                              int32_t* __restrict__ srcid, int32_t* __restrict__ q0,
+                                                              int32_t* __restrict__ counters) {
+    const int64_t cidx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (cidx >= m) return;
+    const int32_t v = samples[cidx];
+    dist[v] = 0ull;
+    atomicMax(srcid + v, int32_t(cidx));
+    q0[cidx] = v;
+    if (cidx == 0) counters[0] = m;
+}
+
+__global__ void __launch_bounds__(kBlock) parents_sweep_kernel(ParentArgs a) {
+    cg::grid_group grid = cg::this_grid();
+    const int64_t groups = int64_t(gridDim.x) * (kBlock / kPLanes);
+    const int64_t group = (int64_t(blockIdx.x) * kBlock + threadIdx.x) / kPLanes;
+    const int sub = threadIdx.x % kPLanes;
+    int32_t* cur = a.q0;
+    int32_t* nxt = a.q1;
+    int cur_c = 0;
+    int round = 1;
+    for (;;) {
+        const int32_t count = *(volatile int32_t*)(a.counters + cur_c);
+        if (count == 0) break;
+        for (int64_t q = group; q < count; q += groups) {
+            const int32_t u = cur[q];
+            const double du = __longlong_as_double((long long)*(volatile unsigned long long*)(a.dist + u));
+            const int32_t b = __ldg(a.colptr + u), e = __ldg(a.colptr + u + 1);
+            for (int32_t k = b + sub; k < e; k += kPLanes) {
+                const int32_t v = __ldg(a.rowidx + k);
+                const double cand = __ldg(a.len + k) + du;                      // edge + path, :108
+                const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
+                if (!(cand >= 0.0)) continue;                                   // NaN never wins a strict <
+                const unsigned long long old = atomicMin(a.dist + v, cb);
+                if (cb < old && atomicExch(a.stamp + v, round) != round)
+                    nxt[atomicAdd(a.counters + (cur_c ^ 1), 1)] = v;
+            }
+        }
+        grid.sync();
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[cur_c] = 0;
+        int32_t* t = cur; cur = nxt; nxt = t;
+        cur_c ^= 1;
+        ++round;
+        grid.sync();
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[2] = round - 1;
+}
+
+// pred[v] by the (dist, index) rule; also detects edges that do not increase the path length.
+__global__ void __launch_bounds__(kBlock) parents_pred_kernel(int32_t n, const int32_t* __restrict__ colptr,
+                                                              const int32_t* __restrict__ rowidx,
+                                                              const double* __restrict__ len,
+                                                              const unsigned long long* __restrict__ dist,
+                                                              const int32_t* __restrict__ srcid,
+                                                              int32_t* __restrict__ pred, int32_t* __restrict__ flags) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t v = int32_t(gid / kPLanes);
+    const int sub = int(gid % kPLanes);
+    if (v >= n) return;
+    const unsigned long long dvb = dist[v];
+    const bool is_source = srcid[v] >= 0;
+    unsigned long long best_d = ~0ull;
+    int32_t best_u = 0x7fffffff;
+    const int32_t b = __ldg(colptr + v), e = __ldg(colptr + v + 1);
+    for (int32_t k = b + sub; k < e; k += kPLanes) {
+        const int32_t u = __ldg(rowidx + k);
+        if (u == v) continue;
+        const unsigned long long dub = dist[u];
+        if (dub == kInfBits) continue;
+        const double du = __longlong_as_double((long long)dub);
+        const double cand = __ldg(len + k) + du;
+        if (!(cand > du)) flags[0] = 1;          // zero-length (or NaN) edge next to a reached vertex
+        const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
+        if (cb == dvb && (dub < best_d || (dub == best_d && u < best_u))) { best_d = dub; best_u = u; }
+    }
+#pragma unroll
+    for (int d = kPLanes / 2; d > 0; d >>= 1) {
+        const unsigned long long od = __shfl_xor_sync(0xffffffffu, best_d, d, kPLanes);
+        const int32_t ou = __shfl_xor_sync(0xffffffffu, best_u, d, kPLanes);
+        if (od < best_d || (od == best_d && ou < best_u)) { best_d = od; best_u = ou; }
+    }
+    if (sub == 0) {
+        // sources and unreached vertices are roots; a reached non-source always has an offerer
+        if (is_source || dvb == kInfBits) pred[v] = v;
+        else if (best_u == 0x7fffffff) { pred[v] = v; flags[1] = 1; }
+        else pred[v] = best_u;
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) parents_resolve_kernel(int32_t n, const int32_t* __restrict__ pred,
+                                                                 const int32_t* __restrict__ srcid,
+                                                                 int32_t* __restrict__ parents) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i >= n) return;
+    int32_t u = int32_t(i);
+    for (;;) {                       // dist strictly decreases along pred, so this walk ends at a root
+        const int32_t p = pred[u];
+        if (p == u) break;
+        u = p;
+    }
+    const int32_t s = srcid[u];
+    parents[i] = s >= 0 ? s : 0;     // unreached: value-initialised 0 (:82)
+}
+
+void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
+                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats) {
+    if (stats) stats->rounds = 0;
+    if (n == 0) return;
+    DevBuf<unsigned long long> dist(c, n);
+    DevBuf<int32_t> stamp(c, n), srcid(c, n), q0(c, n), q1(c, n), counters(c, 4), pred(c, n), flags(c, 2);
+    counters.zero();
+    flags.zero();
+    GMG_LAUNCH(c, parents_init_kernel, div_up(n, kBlock), kBlock, 0, n, dist.p, stamp.p, srcid.p);
+    if (m > 0) {
+        GMG_LAUNCH(c, parents_seed_kernel, div_up(m, kBlock), kBlock, 0, m, samples, dist.p, srcid.p, q0.p, counters.p);
+        ParentArgs a{n, colptr, rowidx, len, dist.p, stamp.p, q0.p, q1.p, counters.p};
+        int per_sm = 0;
+        GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parents_sweep_kernel, kBlock, 0));
+        GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "parent sweep kernel does not fit on an SM");
+        int grid = per_sm * c->sm_count;
+        const int needed = div_up(int64_t(n) * kPLanes, kBlock);
+        if (grid > needed) grid = needed;
+        void* args[] = {&a};
+        GMG_CUDA(cudaLaunchCooperativeKernel((void*)parents_sweep_kernel, dim3(grid), dim3(kBlock), args, 0, c->stream));
+        ++c->launches;
+    }
+    GMG_LAUNCH(c, parents_pred_kernel, div_up(int64_t(n) * kPLanes, kBlock), kBlock, 0, n, colptr, rowidx, len, dist.p,
+               srcid.p, pred.p, flags.p);
+    GMG_LAUNCH(c, parents_resolve_kernel, div_up(n, kBlock), kBlock, 0, n, pred.p, srcid.p, parents);
+    int32_t hf[2], hc[4];
+    flags.download(hf, 2);
+    counters.download(hc, 4);
+    sync(c);
+    if (stats) stats->rounds = hc[2];
+    GMG_REQUIRE(hf[0] == 0, GMG_ERR_ZERO_LENGTH_EDGE,
+                "assignParents: an edge does not increase the path length (duplicate points?); "
+                "the reference's heap order is then dynamic and is not reproduced");
+    GMG_REQUIRE(hf[1] == 0, GMG_ERR_ASYMMETRIC, "assignParents: a reached vertex has no offering neighbour (asymmetric pattern)");
+}
+
+}  // namespace gmg

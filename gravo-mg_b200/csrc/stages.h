@@ -1,0 +1,79 @@
+// Host-side stage functions over DEVICE arrays. The C ABI entry points (capi.cu) and the resident
+// hierarchy builder (hierarchy.cu) are both thin sequences of these calls.
+#pragma once
+
+#include "common.cuh"
+
+namespace gmg {
+
+// ---- k_basic.cu -------------------------------------------------------------------------------
+void edge_lengths(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* pts,
+                  double* out_len);
+void extract_edges_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                       int64_t nnz, int32_t* out_edges, double* out_values);
+void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n_edges, const int32_t* edges,
+                             double* d_out);
+void mean_length_dev(gmg_ctx* c, int64_t nnz, const double* len, double denom, double* d_out);
+void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric);
+
+// ---- k_sampler.cu -----------------------------------------------------------------------------
+// Greedy disc sampling in priority order (index order = the reference's set). `len` holds the
+// Euclidean length of every stored entry. Returns m; selection receives ascending fine indices.
+struct SamplerStats { int rounds; };
+int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
+                    double radius, int mode, uint64_t seed, DevBuf<int32_t>& selection, SamplerStats* stats);
+
+// ---- k_parents.cu -----------------------------------------------------------------------------
+struct ParentStats { int rounds; };
+void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
+                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats);
+
+// ---- k_cluster.cu -----------------------------------------------------------------------------
+struct Clusters {
+    DevBuf<int32_t> ptr;    // m+1
+    DevBuf<int32_t> child;  // n, ascending within each cluster
+};
+void build_clusters(gmg_ctx* c, int32_t n, int32_t m, const int32_t* parents, Clusters& out);
+
+struct DeviceCsc {
+    int32_t n = 0;
+    int64_t nnz = 0;
+    DevBuf<int32_t> colptr, rowidx;
+    DevBuf<double> val;
+};
+void coarse_edges(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val, int32_t m,
+                  const int32_t* parents, const Clusters& cl, DeviceCsc& out);
+void coarse_points(gmg_ctx* c, int32_t n, const double* pts, const int32_t* colptr, const int32_t* rowidx, int32_t m,
+                   const Clusters& cl, double* out_pts);
+
+// ---- k_triangles.cu ---------------------------------------------------------------------------
+struct Triangles {
+    int64_t T = 0;
+    DevBuf<int32_t> tri;      // 3T, row-major (v0,v1,v2) ascending triples in lexicographic order
+    DevBuf<double> normal;    // 3T, row-major
+    DevBuf<int32_t> fan_ptr;  // m+1
+    DevBuf<int32_t> fan_tri;  // 3T triangle ids, ascending per vertex
+    DevBuf<int32_t> fan_o1;   // 3T: second vertex after rotating the owner to the front
+    DevBuf<int32_t> fan_o2;   // 3T: third vertex after rotation
+};
+void voronoi_triangles(gmg_ctx* c, int32_t m, const double* pts, const int32_t* colptr, const int32_t* rowidx,
+                       const double* val, Triangles& out);
+
+// ---- k_prolong.cu -----------------------------------------------------------------------------
+struct DeviceCsr {
+    int32_t rows = 0, cols = 0;
+    int64_t nnz = 0;
+    DevBuf<int32_t> rowptr, colidx;
+    DevBuf<double> val;
+};
+void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, const double* coarse_pts,
+                  const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
+                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats);
+void projected_points_dev(gmg_ctx* c, int32_t n, int32_t m, const int32_t* rowptr, const int32_t* colidx,
+                          const double* val, const double* coarse_pts, double* out_pts);
+
+// index conversions at the ABI boundary (std::vector<Eigen::Index> is int64, device indices int32)
+void narrow_i64(gmg_ctx* c, const int64_t* in, int32_t* out, int64_t n, int64_t upper, int32_t* d_flag);
+void widen_i32(gmg_ctx* c, const int32_t* in, int64_t* out, int64_t n);
+
+}  // namespace gmg

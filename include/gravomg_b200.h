@@ -1,0 +1,131 @@
+/* gravomg_b200 -- C ABI of the B200-native Gravo MG hierarchy-construction path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types. Each entry point
+ * replaces one reference function (paths relative to the reference repository):
+ *
+ *   gmg_to_edge_distance_matrix        GravoMG::toEdgeDistanceMatrix        include/gravomg/utility.h:22,  src/utility.cpp:50-56
+ *   gmg_extract_edges                  GravoMG::extractEdges                include/gravomg/utility.h:24,  src/utility.cpp:58-71
+ *   gmg_average_edge_length            GravoMG::averageEdgeLength           include/gravomg/multigrid.h:36, src/multigrid.cpp:127-133
+ *   gmg_fast_disc_sample               GravoMG::fastDiscSample              include/gravomg/sampling.h:14-18, src/sampling.cpp:7-53
+ *   gmg_assign_parents                 GravoMG::assignParents               include/gravomg/multigrid.h:30-34, src/multigrid.cpp:77-125
+ *   gmg_extract_coarse_edges           GravoMG::extractCoarseEdges          include/gravomg/multigrid.h:38-43, src/multigrid.cpp:135-169
+ *   gmg_coarse_from_mean_of_fine_children  GravoMG::coarseFromMeanOfFineChildren  multigrid.h:45-50, src/multigrid.cpp:171-207
+ *   gmg_construct_voronoi_triangles    GravoMG::constructVoronoiTriangles   include/gravomg/multigrid.h:52-55, src/multigrid.cpp:209-263
+ *   gmg_construct_prolongation         GravoMG::constructProlongation       include/gravomg/multigrid.h:57-63, src/multigrid.cpp:265-498
+ *   gmg_projected_points               GravoMG::projectedPoints             include/gravomg/multigrid.h:65,  src/multigrid.cpp:500-510
+ *   gmg_hierarchy_*                    [not in reference] the per-level call order of test/main.cpp:68-121,
+ *                                      looped over levels with everything resident in HBM, plus the Galerkin
+ *                                      operator, SpMV and multicolour Gauss-Seidel BASELINE.json asks for.
+ *
+ * Data conventions (those of the reference's Eigen types, include/gravomg/utility.h:10-18):
+ *   points     column-major n x 3 doubles with leading dimension ld >= n  (Eigen::MatrixXd::data(), ld = rows())
+ *   edge matrix  compressed column-major: int32 colptr[n+1], int32 rowidx[nnz] ascending per column,
+ *              f64 val[nnz]   (Eigen::SparseMatrix<double>: outerIndexPtr / innerIndexPtr / valuePtr)
+ *   P          compressed row-major: int32 rowptr[n+1], int32 colidx[nnz] ascending per row, f64 val[nnz]
+ *   std::vector<Eigen::Index>  -> int64 pointer + length
+ * All pointers in the per-function entry points are HOST pointers; the library copies to and from
+ * the device inside the call. gmg_hierarchy_* keeps everything on the device between stages.
+ *
+ * Variable-size outputs use a two-call convention: the compute call returns the sizes and keeps
+ * the result in the context; gmg_fetch_* copies it into caller-allocated arrays.
+ *
+ * Every function returns a gmg_status; gmg_last_error() gives the text. There is no CPU fallback:
+ * without a usable CUDA device gmg_create fails with GMG_ERR_CUDA.
+ */
+#ifndef GRAVOMG_B200_H
+#define GRAVOMG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gmg_ctx gmg_ctx;
+typedef struct gmg_hierarchy gmg_hierarchy;
+
+typedef enum {
+    GMG_OK = 0,
+    GMG_ERR_CUDA = 1,            /* a CUDA runtime call or kernel failed */
+    GMG_ERR_INVALID = 2,         /* malformed input the reference would treat as undefined behaviour */
+    GMG_ERR_FALLBACK_RATIO = 3,  /* mirrors assert(fallbackCount / n < 0.5), src/multigrid.cpp:488 */
+    GMG_ERR_ZERO_LENGTH_EDGE = 4,/* an edge that does not increase the path length: Dijkstra tie order is dynamic */
+    GMG_ERR_ASYMMETRIC = 5,      /* the sparsity pattern is not symmetric; the parallel formulation needs it */
+    GMG_ERR_STATE = 6,           /* fetch without a matching compute call, or bad handle */
+    GMG_ERR_NCCL = 7
+} gmg_status;
+
+/* Weighting of include/gravomg/multigrid.h:12-16 */
+enum { GMG_BARYCENTRIC = 0, GMG_UNIFORM = 1, GMG_INVDIST = 2 };
+/* Sampler modes: EXACT reproduces src/sampling.cpp:22-50 (greedy in index order) bit-for-bit;
+ * PARALLEL is the same greedy rule run in a hashed priority order (cannot match the index-order set,
+ * validated statistically). */
+enum { GMG_SAMPLER_EXACT = 0, GMG_SAMPLER_PARALLEL = 1 };
+
+int gmg_create(int device, void* cuda_stream, gmg_ctx** out);
+void gmg_destroy(gmg_ctx* ctx);
+const char* gmg_last_error(const gmg_ctx* ctx);
+/* milliseconds spent in kernels of the most recent compute call, measured with CUDA events on the
+ * context's stream (excludes host<->device copies) */
+double gmg_last_kernel_ms(const gmg_ctx* ctx);
+/* number of kernel launches issued by this context since creation */
+int64_t gmg_launch_count(const gmg_ctx* ctx);
+
+int gmg_to_edge_distance_matrix(gmg_ctx* ctx, int64_t n, const int32_t* colptr, const int32_t* rowidx,
+                                const double* points, int64_t ld, double* out_val);
+
+/* out_edges: column-major nnz x 2 int32 (column 0 = col, column 1 = row), out_values: nnz */
+int gmg_extract_edges(gmg_ctx* ctx, int64_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                      int32_t* out_edges, double* out_values);
+
+/* sum of |p_j - p_i| over all rows of the edge list, divided by (n_edges - n). The summation order
+ * is a fixed pairwise tree (deterministic), not libstdc++'s transform_reduce order. */
+int gmg_average_edge_length(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int64_t n_edges,
+                            const int32_t* edges, double* out_mean);
+
+/* selection_out has room for n entries, ascending; *m_out receives the count */
+int gmg_fast_disc_sample(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                         const int32_t* rowidx, double radius, int mode, uint64_t seed, int64_t* selection_out,
+                         int64_t* m_out);
+
+int gmg_assign_parents(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                       const int32_t* rowidx, int64_t m, const int64_t* samples, int64_t* parents_out);
+
+/* out_colptr has m+1 entries; then gmg_fetch_sparse(ctx, rowidx[nnz], val[nnz]) */
+int gmg_extract_coarse_edges(gmg_ctx* ctx, int64_t n, const int32_t* colptr, const int32_t* rowidx,
+                             const double* val, int64_t m, const int64_t* parents, int32_t* out_colptr,
+                             int64_t* nnz_out);
+int gmg_fetch_sparse(gmg_ctx* ctx, int32_t* out_inner, double* out_val);
+
+int gmg_coarse_from_mean_of_fine_children(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld,
+                                          const int32_t* colptr, const int32_t* rowidx, const int64_t* parents,
+                                          int64_t m, double* out_points, int64_t out_ld);
+
+/* out_fan_ptr has m+1 entries; then gmg_fetch_triangles(ctx, tri[3T] row-major int64, normal[3T]
+ * row-major f64, fan[3T] int64) */
+int gmg_construct_voronoi_triangles(gmg_ctx* ctx, int64_t m, const double* points, int64_t ld,
+                                    const int32_t* colptr, const int32_t* rowidx, const double* val,
+                                    int64_t* T_out, int64_t* out_fan_ptr);
+int gmg_fetch_triangles(gmg_ctx* ctx, int64_t* out_tri, double* out_normal, int64_t* out_fan);
+
+/* counters the reference computes and drops (src/multigrid.cpp:281-283) */
+typedef struct {
+    int64_t no_triangle_found;   /* notrisfound */
+    int64_t edges_found;         /* edgesfound */
+    int64_t fallback_count;      /* fallbackCount */
+} gmg_prolongation_stats;
+
+/* out_rowptr has n+1 entries; then gmg_fetch_sparse(ctx, colidx[nnz], val[nnz]) */
+int gmg_construct_prolongation(gmg_ctx* ctx, int64_t n, const double* fine_points, int64_t fine_ld, int64_t m,
+                               const double* coarse_points, int64_t coarse_ld, const int32_t* c_colptr,
+                               const int32_t* c_rowidx, const double* c_val, const int64_t* parents, int weighting,
+                               int32_t* out_rowptr, int64_t* nnz_out, gmg_prolongation_stats* stats_out);
+
+int gmg_projected_points(gmg_ctx* ctx, int64_t n, int64_t m, const int32_t* rowptr, const int32_t* colidx,
+                         const double* val, const double* coarse_points, int64_t coarse_ld, double* out_points,
+                         int64_t out_ld);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAVOMG_B200_H */
