@@ -236,3 +236,133 @@ class Context:
                                                   _p(colidx, _i32p), _p(val, _f64p), _p(cp, _f64p),
                                                   C.c_int64(max(m, 1)), _p(out, _f64p), C.c_int64(max(n, 1))))
         return out
+
+
+# ---- resident hierarchy builder (gmg_hierarchy_*) ------------------------------------------------
+class HierarchyOptions(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("ratio", C.c_double), ("weighting", C.c_int32), ("sampler_mode", C.c_int32),
+                ("seed", C.c_uint64), ("radius_policy", C.c_int32), ("radius_override", _f64p),
+                ("build_galerkin", C.c_int32)]
+
+
+class LevelInfo(C.Structure):
+    _fields_ = [("n", C.c_int64), ("nnz", C.c_int64), ("m", C.c_int64), ("nnz_c", C.c_int64), ("T", C.c_int64),
+                ("nnz_p", C.c_int64), ("nnz_ac", C.c_int64), ("radius", C.c_double), ("sampler_rounds", C.c_int32),
+                ("parent_rounds", C.c_int32), ("stats", ProlongationStats), ("stage_ms", C.c_double * 9)]
+
+    def as_dict(self):
+        d = {k: getattr(self, k) for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_p", "nnz_ac", "radius",
+                                           "sampler_rounds", "parent_rounds")}
+        d["no_triangle_found"] = self.stats.no_triangle_found
+        d["edges_found"] = self.stats.edges_found
+        d["fallback_count"] = self.stats.fallback_count
+        d["stage_ms"] = list(self.stage_ms)
+        return d
+
+
+STAGE_NAMES = ["edge_lengths", "sampling", "parents", "cluster_csr", "coarse_edges", "coarse_points",
+               "triangle_fans", "prolongation_rows", "galerkin"]
+
+(H_SAMPLES, H_PARENTS, H_COARSE_COLPTR, H_COARSE_ROWIDX, H_COARSE_VAL, H_COARSE_POINTS, H_TRIANGLES, H_NORMALS,
+ H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL, H_AC_COLPTR, H_AC_ROWIDX, H_AC_VAL, H_FINE_VAL) = range(17)
+
+
+class Input:
+    """A level-0 problem resident in HBM (points + the pattern of A, optionally A's values)."""
+
+    def __init__(self, ctx, points, colptr, rowidx, a_val=None):
+        self.ctx = ctx
+        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
+        self.n, self.nnz = pts.shape[0], rowidx.shape[0]
+        a = None if a_val is None else _f64(a_val)
+        h = C.c_void_p()
+        ctx._check(ctx.lib.gmg_input_create(ctx.h, C.c_int64(self.n), _p(pts, _f64p), C.c_int64(self.n),
+                                            _p(colptr, _i32p), _p(rowidx, _i32p),
+                                            _p(a, _f64p) if a is not None else None, C.byref(h)))
+        self.h = h
+        self.h2d_bytes = pts.nbytes + colptr.nbytes + rowidx.nbytes + (a.nbytes if a is not None else 0)
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.lib.gmg_input_destroy.argtypes = [C.c_void_p]
+            self.ctx.lib.gmg_input_destroy(self.h)
+        self.h = None
+
+    __del__ = close
+
+
+class Hierarchy:
+    """levels-1 prolongations (and optionally Galerkin operators) built and kept on the device."""
+
+    def __init__(self, ctx, inp, levels, ratio=8.0, weighting=BARYCENTRIC, sampler_mode=SAMPLER_EXACT, seed=42,
+                 radius_policy=0, radius_override=None, build_galerkin=False):
+        self.ctx = ctx
+        ro = None
+        if radius_override is not None:
+            ro = np.zeros(max(levels - 1, 1), dtype=np.float64)
+            ro[:len(radius_override)] = radius_override
+        self._ro = ro
+        opt = HierarchyOptions(levels, ratio, weighting, sampler_mode, seed, radius_policy,
+                               _p(ro, _f64p) if ro is not None else None, 1 if build_galerkin else 0)
+        h = C.c_void_p()
+        ctx._check(ctx.lib.gmg_hierarchy_build(ctx.h, inp.h, C.byref(opt), C.byref(h)))
+        self.h = h
+        self.build_ms = ctx.last_kernel_ms
+        ctx.lib.gmg_hierarchy_num_levels.argtypes = [C.c_void_p]
+        self.num_levels = int(ctx.lib.gmg_hierarchy_num_levels(h))
+        self.info = []
+        for lvl in range(self.num_levels):
+            li = LevelInfo()
+            ctx.lib.gmg_hierarchy_level_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            ctx._check(ctx.lib.gmg_hierarchy_level_info(h, lvl, C.byref(li)))
+            self.info.append(li.as_dict())
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.lib.gmg_hierarchy_destroy.argtypes = [C.c_void_p]
+            self.ctx.lib.gmg_hierarchy_destroy(self.h)
+        self.h = None
+
+    __del__ = close
+
+    def fetch(self, level, which):
+        i = self.info[level]
+        n, m, T = i["n"], i["m"], i["T"]
+        shape_dtype = {
+            H_SAMPLES: (m, np.int64), H_PARENTS: (n, np.int64), H_COARSE_COLPTR: (m + 1, np.int32),
+            H_COARSE_ROWIDX: (i["nnz_c"], np.int32), H_COARSE_VAL: (i["nnz_c"], np.float64),
+            H_COARSE_POINTS: (3 * m, np.float64), H_TRIANGLES: (3 * T, np.int64), H_NORMALS: (3 * T, np.float64),
+            H_FAN_PTR: (m + 1, np.int64), H_FAN: (3 * T, np.int64), H_P_ROWPTR: (n + 1, np.int32),
+            H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64), H_AC_COLPTR: (m + 1, np.int32),
+            H_AC_ROWIDX: (i["nnz_ac"], np.int32), H_AC_VAL: (i["nnz_ac"], np.float64), H_FINE_VAL: (i["nnz"], np.float64),
+        }[which]
+        out = np.empty(max(shape_dtype[0], 1), dtype=shape_dtype[1])
+        self.ctx._check(self.ctx.lib.gmg_hierarchy_fetch(self.ctx.h, self.h, C.c_int(level), C.c_int(which),
+                                                         out.ctypes.data_as(C.c_void_p)))
+        out = out[:shape_dtype[0]]
+        if which == H_COARSE_POINTS:
+            return out.reshape((m, 3), order="F")
+        if which in (H_TRIANGLES, H_NORMALS):
+            return out.reshape(T, 3)
+        return out
+
+    def level_arrays(self, level):
+        """Everything the reference's per-level calls would have returned, keyed like tests/pipeline.py."""
+        f = self.fetch
+        return dict(radius=self.info[level]["radius"], sel=f(level, H_SAMPLES), par=f(level, H_PARENTS),
+                    ccp=f(level, H_COARSE_COLPTR), cri=f(level, H_COARSE_ROWIDX), cval=f(level, H_COARSE_VAL),
+                    cpts=f(level, H_COARSE_POINTS), tri=f(level, H_TRIANGLES), nrm=f(level, H_NORMALS),
+                    fptr=f(level, H_FAN_PTR), fan=f(level, H_FAN), prp=f(level, H_P_ROWPTR),
+                    pci=f(level, H_P_COLIDX), pva=f(level, H_P_VAL))
+
+    def prolongation(self, level):
+        import scipy.sparse as sp
+        i = self.info[level]
+        return sp.csr_matrix((self.fetch(level, H_P_VAL), self.fetch(level, H_P_COLIDX), self.fetch(level, H_P_ROWPTR)),
+                             shape=(i["n"], i["m"]))
+
+    def galerkin(self, level):
+        import scipy.sparse as sp
+        i = self.info[level]
+        return sp.csc_matrix((self.fetch(level, H_AC_VAL), self.fetch(level, H_AC_ROWIDX),
+                              self.fetch(level, H_AC_COLPTR)), shape=(i["m"], i["m"]))

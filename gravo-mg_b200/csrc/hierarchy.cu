@@ -1,0 +1,275 @@
+// Resident hierarchy builder [not in reference]: repeats the per-level call order of the
+// reference's demo (test/main.cpp:68-121) with every array kept in HBM between stages and levels.
+#include "stages.h"
+
+#include <cmath>
+#include <memory>
+#include <stdexcept>
+
+using namespace gmg;
+
+struct gmg_input {
+    gmg_ctx* ctx = nullptr;
+    int32_t n = 0;
+    int64_t nnz = 0;
+    DevBuf<double> pts;
+    DevBuf<int32_t> colptr, rowidx;
+    DevBuf<double> a_val;
+    bool has_a = false;
+};
+
+namespace {
+
+struct Level {
+    gmg_level_info info{};
+    DevBuf<int32_t> samples, parents;
+    DeviceCsc coarse;
+    DevBuf<double> coarse_pts;
+    Triangles tri;
+    DeviceCsr P;
+    DeviceCsc Ac;
+};
+
+struct StageClock {
+    gmg_ctx* c;
+    std::vector<cudaEvent_t> ev;
+    explicit StageClock(gmg_ctx* ctx) : c(ctx) {}
+    ~StageClock() { for (auto e : ev) cudaEventDestroy(e); }
+    void mark() {
+        cudaEvent_t e;
+        GMG_CUDA(cudaEventCreate(&e));
+        GMG_CUDA(cudaEventRecord(e, c->stream));
+        ev.push_back(e);
+    }
+    double ms(size_t i) const {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, ev[i], ev[i + 1]);
+        return t;
+    }
+};
+
+}  // namespace
+
+struct gmg_hierarchy {
+    gmg_ctx* ctx = nullptr;
+    DevBuf<double> fine_val;  // level-0 toEdgeDistanceMatrix values
+    int64_t fine_nnz = 0;
+    std::vector<std::unique_ptr<Level>> levels;
+};
+
+template <typename F> static int guarded_h(gmg_ctx* c, F&& body) {
+    if (!c) return GMG_ERR_STATE;
+    try {
+        GMG_CUDA(cudaSetDevice(c->device));
+        body();
+        c->last_error.clear();
+        return GMG_OK;
+    } catch (const Error& e) {
+        c->last_error = e.what;
+        cudaStreamSynchronize(c->stream);
+        return e.status;
+    } catch (const std::exception& e) {
+        c->last_error = e.what();
+        return GMG_ERR_INVALID;
+    }
+}
+
+extern "C" {
+
+int gmg_input_create(gmg_ctx* c, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                     const int32_t* rowidx, const double* A_val, gmg_input** out) {
+    if (!out) return GMG_ERR_INVALID;
+    *out = nullptr;
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(n >= 0 && n < (int64_t(1) << 31) / 3, GMG_ERR_INVALID, "vertex count too large for 32-bit indices");
+        GMG_REQUIRE(colptr && colptr[0] == 0 && colptr[n] >= 0, GMG_ERR_INVALID, "bad colptr");
+        std::unique_ptr<gmg_input> in(new gmg_input());
+        in->ctx = c; in->n = int32_t(n); in->nnz = colptr[n];
+        in->pts = points_to_device(c, points, n, ld);
+        in->colptr = to_device(c, colptr, n + 1);
+        in->rowidx = to_device(c, rowidx, in->nnz);
+        if (A_val) { in->a_val = to_device(c, A_val, in->nnz); in->has_a = true; }
+        check_pattern(c, in->n, in->colptr.p, in->rowidx.p, true);
+        sync(c);
+        *out = in.release();
+    });
+}
+
+void gmg_input_destroy(gmg_input* in) {
+    if (!in) return;
+    cudaSetDevice(in->ctx->device);
+    delete in;
+}
+
+int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_options* opt, gmg_hierarchy** out) {
+    if (!out) return GMG_ERR_INVALID;
+    *out = nullptr;
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(in && opt, GMG_ERR_INVALID, "null input or options");
+        GMG_REQUIRE(opt->levels >= 1, GMG_ERR_INVALID, "levels must be >= 1");
+        GMG_REQUIRE(!opt->build_galerkin || in->has_a, GMG_ERR_INVALID, "build_galerkin needs A values");
+        std::unique_ptr<gmg_hierarchy> h(new gmg_hierarchy());
+        h->ctx = c;
+        cudaEventRecord(c->ev0, c->stream);
+
+        // current fine level (views into the input or into the previous level)
+        int32_t n = in->n;
+        int64_t nnz = in->nnz;
+        const double* pts = in->pts.p;
+        const int32_t* colptr = in->colptr.p;
+        const int32_t* rowidx = in->rowidx.p;
+        const double* a_val = in->has_a ? in->a_val.p : nullptr;      // system matrix values of this level
+        const int32_t* a_colptr = colptr;
+        const int32_t* a_rowidx = rowidx;
+        int32_t a_n = n;
+
+        // level 0: fine_edge_matrix = toEdgeDistanceMatrix(L, points)  (test/main.cpp:69)
+        h->fine_val.alloc(c, nnz);
+        h->fine_nnz = nnz;
+        const double* val = h->fine_val.p;
+        DevBuf<double> len_buf;          // Euclidean lengths of the current level's entries (levels >= 1)
+        DevBuf<double> d_radius(c, 1);
+
+        for (int lvl = 0; lvl + 1 < opt->levels; ++lvl) {
+            if (n == 0) break;
+            std::unique_ptr<Level> L(new Level());
+            L->info.n = n; L->info.nnz = nnz;
+            StageClock clk(c);
+            clk.mark();
+            // stage 0: lengths (the sampler and the sweep use geometric lengths, never stored values)
+            const double* len;
+            if (lvl == 0) { edge_lengths(c, n, colptr, rowidx, pts, h->fine_val.p); len = h->fine_val.p; }
+            else { len_buf.alloc(c, nnz); edge_lengths(c, n, colptr, rowidx, pts, len_buf.p); len = len_buf.p; }
+            double radius = 0.0;
+            const bool overridden = opt->radius_override && opt->radius_override[lvl] > 0.0;
+            if (overridden) radius = opt->radius_override[lvl];
+            else {
+                // averageEdgeLength over extractEdges(matrix): every stored entry, divisor nnz - n
+                double denom = double(nnz - n);
+                if (opt->radius_policy == 1) denom = double(lvl == 0 ? nnz - n : nnz);
+                mean_length_dev(c, nnz, len, denom, d_radius.p);
+                double mean = 0.0;
+                d_radius.download(&mean, 1);
+                sync(c);
+                radius = std::cbrt(opt->ratio) * mean;
+            }
+            L->info.radius = radius;
+            clk.mark();
+            // stage 1: fastDiscSample
+            SamplerStats ss{};
+            const int32_t m = disc_sample(c, n, colptr, rowidx, len, radius, opt->sampler_mode, opt->seed + uint64_t(lvl),
+                                          L->samples, &ss);
+            L->info.m = m; L->info.sampler_rounds = ss.rounds;
+            clk.mark();
+            // stage 2: assignParents
+            L->parents.alloc(c, n);
+            ParentStats ps{};
+            assign_parents_dev(c, n, colptr, rowidx, len, m, L->samples.p, L->parents.p, &ps);
+            L->info.parent_rounds = ps.rounds;
+            clk.mark();
+            // stage 3: cluster CSR
+            Clusters cl;
+            build_clusters(c, n, m, L->parents.p, cl);
+            clk.mark();
+            // stage 4: extractCoarseEdges
+            coarse_edges(c, n, colptr, rowidx, val, m, L->parents.p, cl, L->coarse);
+            L->info.nnz_c = L->coarse.nnz;
+            clk.mark();
+            // stage 5: coarseFromMeanOfFineChildren
+            L->coarse_pts.alloc(c, 3 * int64_t(m));
+            coarse_points(c, n, pts, colptr, rowidx, m, cl, L->coarse_pts.p);
+            clk.mark();
+            // stage 6: constructVoronoiTriangles
+            voronoi_triangles(c, m, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->coarse.val.p, L->tri);
+            L->info.T = L->tri.T;
+            clk.mark();
+            // stage 7: constructProlongation
+            prolongation(c, n, pts, m, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->parents.p, L->tri,
+                         opt->weighting, L->P, &L->info.stats);
+            L->info.nnz_p = L->P.nnz;
+            clk.mark();
+            // stage 8: Galerkin coarse operator
+            if (opt->build_galerkin) {
+                galerkin(c, a_n, a_colptr, a_rowidx, a_val, L->P, L->Ac);
+                L->info.nnz_ac = L->Ac.nnz;
+            }
+            clk.mark();
+            sync(c);
+            for (int s = 0; s < 9; ++s) L->info.stage_ms[s] = clk.ms(size_t(s));
+
+            // next level's fine inputs
+            n = m; nnz = L->coarse.nnz;
+            pts = L->coarse_pts.p; colptr = L->coarse.colptr.p; rowidx = L->coarse.rowidx.p; val = L->coarse.val.p;
+            if (opt->build_galerkin) { a_n = m; a_colptr = L->Ac.colptr.p; a_rowidx = L->Ac.rowidx.p; a_val = L->Ac.val.p; }
+            h->levels.push_back(std::move(L));
+        }
+        cudaEventRecord(c->ev1, c->stream);
+        cudaEventSynchronize(c->ev1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        c->last_kernel_ms = ms;
+        *out = h.release();
+    });
+}
+
+void gmg_hierarchy_destroy(gmg_hierarchy* h) {
+    if (!h) return;
+    cudaSetDevice(h->ctx->device);
+    delete h;
+}
+
+int gmg_hierarchy_num_levels(const gmg_hierarchy* h) { return h ? int(h->levels.size()) : 0; }
+
+int gmg_hierarchy_level_info(const gmg_hierarchy* h, int level, gmg_level_info* out) {
+    if (!h || !out || level < 0 || level >= int(h->levels.size())) return GMG_ERR_STATE;
+    *out = h->levels[size_t(level)]->info;
+    return GMG_OK;
+}
+
+int gmg_hierarchy_fetch(gmg_ctx* c, const gmg_hierarchy* h, int level, int which, void* out) {
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(h && level >= 0 && level < int(h->levels.size()), GMG_ERR_STATE, "no such level");
+        const Level& L = *h->levels[size_t(level)];
+        const int64_t n = L.info.n, m = L.info.m, T = L.info.T;
+        auto copy = [&](const void* dev, size_t bytes) {
+            if (bytes) GMG_CUDA(cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+        };
+        auto copy_wide = [&](const int32_t* dev, int64_t count) {
+            DevBuf<int64_t> w(c, count);
+            widen_i32(c, dev, w.p, count);
+            copy(w.p, sizeof(int64_t) * size_t(count));
+            sync(c);
+        };
+        switch (which) {
+            case GMG_H_SAMPLES: copy_wide(L.samples.p, m); break;
+            case GMG_H_PARENTS: copy_wide(L.parents.p, n); break;
+            case GMG_H_COARSE_COLPTR: copy(L.coarse.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
+            case GMG_H_COARSE_ROWIDX: copy(L.coarse.rowidx.p, sizeof(int32_t) * size_t(L.coarse.nnz)); break;
+            case GMG_H_COARSE_VAL: copy(L.coarse.val.p, sizeof(double) * size_t(L.coarse.nnz)); break;
+            case GMG_H_COARSE_POINTS: copy(L.coarse_pts.p, sizeof(double) * size_t(3 * m)); break;
+            case GMG_H_TRIANGLES: copy_wide(L.tri.tri.p, 3 * T); break;
+            case GMG_H_NORMALS: copy(L.tri.normal.p, sizeof(double) * size_t(3 * T)); break;
+            case GMG_H_FAN_PTR: copy_wide(L.tri.fan_ptr.p, m + 1); break;
+            case GMG_H_FAN: copy_wide(L.tri.fan_tri.p, 3 * T); break;
+            case GMG_H_P_ROWPTR: copy(L.P.rowptr.p, sizeof(int32_t) * size_t(n + 1)); break;
+            case GMG_H_P_COLIDX: copy(L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz)); break;
+            case GMG_H_P_VAL: copy(L.P.val.p, sizeof(double) * size_t(L.P.nnz)); break;
+            case GMG_H_AC_COLPTR:
+                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+                copy(L.Ac.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
+            case GMG_H_AC_ROWIDX:
+                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+                copy(L.Ac.rowidx.p, sizeof(int32_t) * size_t(L.Ac.nnz)); break;
+            case GMG_H_AC_VAL:
+                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+                copy(L.Ac.val.p, sizeof(double) * size_t(L.Ac.nnz)); break;
+            case GMG_H_FINE_VAL:
+                GMG_REQUIRE(level == 0, GMG_ERR_STATE, "fine values exist on level 0 only");
+                copy(h->fine_val.p, sizeof(double) * size_t(h->fine_nnz)); break;
+            default: GMG_REQUIRE(false, GMG_ERR_INVALID, "unknown array id");
+        }
+        sync(c);
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,198 @@
+// Galerkin coarse operator A_c = P^T A P as a two-pass (symbolic, then numeric) SpGEMM.
+// [not in reference: README.md:6 says only the P/R builders were kept; BASELINE.json asks for it.
+//  Semantics are those of Eigen's un-pruned sparse product: structural pattern, sorted indices.]
+//
+// A and A_c are compressed by OUTER index (column-major, like Eigen::SparseMatrix<double>); the
+// row-wise Gustavson formulation below only ever walks outer vectors, so it computes
+//     out(inner j, outer i) = sum_k sum_l P(k,i) * A(l,k) * P(l,j)
+// which is exactly (P^T A P)(j,i) with A(l,k) read from outer vector k. No symmetry of A is assumed.
+//
+// One warp per coarse outer index i: R = P^T (CSR) lists the fine k with P(k,i) stored; lanes split
+// the entries of A's outer vector k; each (l, a_lk) contributes the <= 3 entries of P's row l into a
+// shared-memory hash keyed by j. Pass 1 (symbolic) counts distinct keys, a scan sizes the result,
+// pass 2 (numeric) accumulates values, sorts the keys and writes the outer vector.
+// Algorithmic bytes: symbolic 12n + 4nnzA + 8nnzP + 4m; numeric 12n + 12nnzA + 24nnzP + 4m + 12nnzAc.
+#include "stages.h"
+
+namespace gmg {
+
+// ---- R = P^T ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) count_columns_kernel(int64_t nnz, const int32_t* __restrict__ colidx,
+                                                               int32_t* __restrict__ count) {
+    const int64_t k = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (k < nnz) atomicAdd(count + __ldg(colidx + k), 1);
+}
+__global__ void __launch_bounds__(kBlock) transpose_fill_kernel(int32_t rows, const int32_t* __restrict__ rowptr,
+                                                                const int32_t* __restrict__ colidx,
+                                                                const double* __restrict__ val,
+                                                                const int32_t* __restrict__ tptr,
+                                                                int32_t* __restrict__ cursor, int32_t* __restrict__ tcol,
+                                                                double* __restrict__ tval) {
+    const int64_t r = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (r >= rows) return;
+    for (int32_t k = rowptr[r]; k < rowptr[r + 1]; ++k) {
+        const int32_t cidx = colidx[k];
+        const int32_t pos = tptr[cidx] + atomicAdd(cursor + cidx, 1);
+        tcol[pos] = int32_t(r);
+        tval[pos] = val[k];
+    }
+}
+__global__ void __launch_bounds__(kBlock) sort_rows_kernel(int32_t rows, const int32_t* __restrict__ ptr,
+                                                           int32_t* __restrict__ idx, double* __restrict__ val) {
+    const int64_t r = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (r >= rows) return;
+    const int32_t b = ptr[r], e = ptr[r + 1];
+    for (int32_t i = b + 1; i < e; ++i) {
+        const int32_t x = idx[i]; const double v = val[i];
+        int32_t j = i - 1;
+        while (j >= b && idx[j] > x) { idx[j + 1] = idx[j]; val[j + 1] = val[j]; --j; }
+        idx[j + 1] = x; val[j + 1] = v;
+    }
+}
+
+void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R) {
+    R.rows = P.cols; R.cols = P.rows; R.nnz = P.nnz;
+    R.rowptr.alloc(c, int64_t(R.rows) + 1);
+    R.colidx.alloc(c, R.nnz);
+    R.val.alloc(c, R.nnz);
+    DevBuf<int32_t> count(c, int64_t(R.rows) + 1);
+    count.zero();
+    if (P.nnz > 0) GMG_LAUNCH(c, count_columns_kernel, div_up(P.nnz, kBlock), kBlock, 0, P.nnz, P.colidx.p, count.p);
+    exclusive_scan_i32(c, count.p, R.rowptr.p, int64_t(R.rows) + 1, nullptr);
+    count.zero();
+    if (P.rows > 0) GMG_LAUNCH(c, transpose_fill_kernel, div_up(P.rows, kBlock), kBlock, 0, P.rows, P.rowptr.p, P.colidx.p,
+                               P.val.p, R.rowptr.p, count.p, R.colidx.p, R.val.p);
+    if (R.rows > 0) GMG_LAUNCH(c, sort_rows_kernel, div_up(R.rows, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
+}
+
+// ---- SpGEMM -------------------------------------------------------------------------------------
+struct GalerkinArgs {
+    int32_t m;
+    const int32_t* r_ptr; const int32_t* r_col; const double* r_val;      // R = P^T
+    const int32_t* a_ptr; const int32_t* a_idx; const double* a_val;      // A by outer vector
+    const int32_t* p_ptr; const int32_t* p_col; const double* p_val;      // P rows
+    int32_t* out_count;        // symbolic: distinct inner indices of outer vector i
+    const int32_t* out_ptr;    // numeric: scan of out_count
+    int32_t* out_idx; double* out_val;
+    int32_t* flags;            // [1] overflow list tail, [2] hard overflow
+    int32_t* overflow;
+};
+
+template <bool NUMERIC, int THREADS, int SLOTS>
+__device__ __forceinline__ bool galerkin_row(const GalerkinArgs& a, int32_t i, int tid, int32_t* keys, double* vals,
+                                             int32_t* scount) {
+    for (int s = tid; s < SLOTS; s += THREADS) { keys[s] = -1; if (NUMERIC) vals[s] = 0.0; }
+    if (tid == 0) *scount = 0;
+    if (THREADS == 32) __syncwarp(); else __syncthreads();
+    const int32_t rb = __ldg(a.r_ptr + i), re = __ldg(a.r_ptr + i + 1);
+    for (int32_t e = rb; e < re; ++e) {
+        const int32_t k = __ldg(a.r_col + e);
+        const double pki = NUMERIC ? __ldg(a.r_val + e) : 0.0;
+        const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
+        for (int32_t q = ab + tid; q < ae; q += THREADS) {
+            const int32_t l = __ldg(a.a_idx + q);
+            const double w = NUMERIC ? pki * __ldg(a.a_val + q) : 0.0;
+            const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
+            for (int32_t t = pb; t < pe; ++t) {
+                const int32_t j = __ldg(a.p_col + t);
+                uint32_t h = (uint32_t(j) * 0x9E3779B1u) >> 7;
+                for (int probe = 0; probe < SLOTS; ++probe, ++h) {
+                    const int s = int(h & (SLOTS - 1));
+                    const int32_t prev = atomicCAS(keys + s, -1, j);
+                    if (prev == -1) atomicAdd(scount, 1);
+                    if (prev == -1 || prev == j) {
+                        if (NUMERIC) atomicAdd(vals + s, w * __ldg(a.p_val + t));
+                        break;
+                    }
+                }
+            }
+        }
+    }
+    if (THREADS == 32) __syncwarp(); else __syncthreads();
+    const int32_t K = *scount;
+    if (K > SLOTS * 3 / 4) return false;
+    if (!NUMERIC) { if (tid == 0) a.out_count[i] = K; return true; }
+    const int32_t off = __ldg(a.out_ptr + i);
+    for (int s = tid; s < SLOTS; s += THREADS) {
+        const int32_t key = keys[s];
+        if (key < 0) continue;
+        int32_t rank = 0;
+        for (int s2 = 0; s2 < SLOTS; ++s2) { const int32_t k2 = keys[s2]; rank += (k2 >= 0 && k2 < key) ? 1 : 0; }
+        a.out_idx[off + rank] = key;
+        a.out_val[off + rank] = vals[s];
+    }
+    return true;
+}
+
+constexpr int kGWarpSlots = 128;
+constexpr int kGBlockSlots = 2048;
+
+template <bool NUMERIC>
+__global__ void __launch_bounds__(kBlock) galerkin_warp_kernel(GalerkinArgs a) {
+    __shared__ int32_t keys[kBlock / 32][kGWarpSlots];
+    __shared__ double vals[NUMERIC ? kBlock / 32 : 1][NUMERIC ? kGWarpSlots : 1];
+    __shared__ int32_t scount[kBlock / 32];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t i = int64_t(blockIdx.x) * (kBlock / 32) + w;
+    if (i >= a.m) return;
+    if (!galerkin_row<NUMERIC, 32, kGWarpSlots>(a, int32_t(i), lane, keys[w], NUMERIC ? vals[w] : nullptr, &scount[w])) {
+        // symbolic pass records the overflow; the numeric pass skips rows already on the list
+        if (!NUMERIC && lane == 0) { a.out_count[i] = 0; a.overflow[atomicAdd(a.flags + 1, 1)] = int32_t(i); }
+    }
+}
+
+template <bool NUMERIC>
+__global__ void __launch_bounds__(kBlock) galerkin_block_kernel(GalerkinArgs a, int32_t n_overflow) {
+    __shared__ int32_t keys[kGBlockSlots];
+    __shared__ double vals[NUMERIC ? kGBlockSlots : 1];
+    __shared__ int32_t scount;
+    for (int32_t o = blockIdx.x; o < n_overflow; o += gridDim.x) {
+        const int32_t i = a.overflow[o];
+        if (!galerkin_row<NUMERIC, kBlock, kGBlockSlots>(a, i, threadIdx.x, keys, vals, &scount)) {
+            if (threadIdx.x == 0) a.flags[2] = 1;
+        }
+        __syncthreads();
+    }
+}
+
+void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
+              const DeviceCsr& P, DeviceCsc& Ac) {
+    GMG_REQUIRE(P.rows == n, GMG_ERR_INVALID, "galerkin: P and A sizes disagree");
+    const int32_t m = P.cols;
+    Ac.n = m;
+    Ac.colptr.alloc(c, int64_t(m) + 1);
+    if (m == 0) { Ac.colptr.zero(); Ac.rowidx.alloc(c, 0); Ac.val.alloc(c, 0); Ac.nnz = 0; return; }
+    DeviceCsr R;
+    transpose_csr(c, P, R);
+    DevBuf<int32_t> count(c, int64_t(m) + 1), flags(c, 4), overflow(c, m);
+    DevBuf<int64_t> total(c, 1);
+    count.zero(); flags.zero();
+    GalerkinArgs a{m, R.rowptr.p, R.colidx.p, R.val.p, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p,
+                   count.p, nullptr, nullptr, nullptr, flags.p, overflow.p};
+    const int grid = div_up(m, kBlock / 32);
+    // pass 1: symbolic
+    GMG_LAUNCH(c, galerkin_warp_kernel<false>, grid, kBlock, 0, a);
+    int32_t hf[4];
+    flags.download(hf, 4);
+    sync(c);
+    const int32_t n_over = hf[1];
+    const int ogrid = n_over < 4 * c->sm_count ? n_over : 4 * c->sm_count;
+    if (n_over > 0) {
+        GMG_LAUNCH(c, galerkin_block_kernel<false>, ogrid, kBlock, 0, a, n_over);
+        flags.download(hf, 4);
+        sync(c);
+        GMG_REQUIRE(hf[2] == 0, GMG_ERR_INVALID, "galerkin: a coarse row has more than 1536 entries");
+    }
+    exclusive_scan_i32(c, count.p, Ac.colptr.p, int64_t(m) + 1, total.p);
+    total.download(&Ac.nnz, 1);
+    sync(c);
+    GMG_REQUIRE(Ac.nnz < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: A_c exceeds 32-bit indexing");
+    Ac.rowidx.alloc(c, Ac.nnz);
+    Ac.val.alloc(c, Ac.nnz);
+    // pass 2: numeric
+    a.out_ptr = Ac.colptr.p; a.out_idx = Ac.rowidx.p; a.out_val = Ac.val.p;
+    GMG_LAUNCH(c, galerkin_warp_kernel<true>, grid, kBlock, 0, a);
+    if (n_over > 0) GMG_LAUNCH(c, galerkin_block_kernel<true>, ogrid, kBlock, 0, a, n_over);
+}
+
+}  // namespace gmg

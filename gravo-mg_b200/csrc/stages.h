@@ -72,6 +72,14 @@ void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, cons
 void projected_points_dev(gmg_ctx* c, int32_t n, int32_t m, const int32_t* rowptr, const int32_t* colidx,
                           const double* val, const double* coarse_pts, double* out_pts);
 
+// ---- k_galerkin.cu ----------------------------------------------------------------------------
+// A_c = P^T A P as a two-pass (symbolic, numeric) SpGEMM. A and A_c are compressed column-major;
+// the structural pattern is kept (no numerical pruning), inner indices ascending.
+void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
+              const DeviceCsr& P, DeviceCsc& Ac);
+// R = P^T in CSR (rows = coarse), fine indices ascending per row
+void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R);
+
 // index conversions at the ABI boundary (std::vector<Eigen::Index> is int64, device indices int32)
 void narrow_i64(gmg_ctx* c, const int64_t* in, int32_t* out, int64_t n, int64_t upper, int32_t* d_flag);
 void widen_i32(gmg_ctx* c, const int32_t* in, int64_t* out, int64_t n);

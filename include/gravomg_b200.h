@@ -125,6 +125,75 @@ int gmg_projected_points(gmg_ctx* ctx, int64_t n, int64_t m, const int32_t* rowp
                          const double* val, const double* coarse_points, int64_t coarse_ld, double* out_points,
                          int64_t out_ld);
 
+/* ------------------------------------------------------------------------------------------------
+ * Resident hierarchy builder [not in reference]: the per-level call order of test/main.cpp:68-121
+ * (toEdgeDistanceMatrix once, then per level: averageEdgeLength -> fastDiscSample -> assignParents ->
+ * extractCoarseEdges -> coarseFromMeanOfFineChildren -> constructVoronoiTriangles ->
+ * constructProlongation), feeding (coarse_points, coarse_edge_matrix) back in as the next level's
+ * fine inputs. Everything stays in HBM between stages and levels.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct gmg_input gmg_input;
+
+/* Copy a level-0 problem to the device. A_val may be NULL when no Galerkin operator is wanted; the
+ * pattern of A (colptr/rowidx) IS the level-0 graph, as in test/main.cpp:68-69. */
+int gmg_input_create(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                     const int32_t* rowidx, const double* A_val, gmg_input** out);
+void gmg_input_destroy(gmg_input* in);
+
+typedef struct {
+    int32_t levels;          /* levels including the finest; levels-1 prolongations are built */
+    double ratio;            /* radius = cbrt(ratio) * averageEdgeLength  (test/main.cpp:74) */
+    int32_t weighting;       /* GMG_BARYCENTRIC / GMG_UNIFORM / GMG_INVDIST */
+    int32_t sampler_mode;    /* GMG_SAMPLER_EXACT / GMG_SAMPLER_PARALLEL */
+    uint64_t seed;           /* priority hash seed of the parallel sampler */
+    int32_t radius_policy;   /* 0: averageEdgeLength verbatim, divisor nnz - n on every level (src/multigrid.cpp:132);
+                                1: divisor = number of off-diagonal entries */
+    const double* radius_override; /* optional host array [levels-1]; entries > 0 replace the computed radius */
+    int32_t build_galerkin;  /* 1: also A_c = P^T A P on every level (needs A_val) */
+} gmg_hierarchy_options;
+
+typedef struct {
+    int64_t n, nnz;          /* fine side of this level */
+    int64_t m, nnz_c;        /* coarse side */
+    int64_t T;               /* Voronoi-neighbour triangles of the coarse graph */
+    int64_t nnz_p;           /* stored entries of P */
+    int64_t nnz_ac;          /* stored entries of A_c (0 unless build_galerkin) */
+    double radius;
+    int32_t sampler_rounds, parent_rounds;
+    gmg_prolongation_stats stats;
+    /* device milliseconds per stage (CUDA events on the context stream):
+       0 edge lengths+radius, 1 sampling, 2 parents, 3 cluster CSR, 4 coarse edges, 5 coarse points,
+       6 triangle fans, 7 prolongation rows, 8 Galerkin */
+    double stage_ms[9];
+} gmg_level_info;
+
+int gmg_hierarchy_build(gmg_ctx* ctx, const gmg_input* in, const gmg_hierarchy_options* opt, gmg_hierarchy** out);
+void gmg_hierarchy_destroy(gmg_hierarchy* h);
+int gmg_hierarchy_num_levels(const gmg_hierarchy* h);                 /* number of prolongations built */
+int gmg_hierarchy_level_info(const gmg_hierarchy* h, int level, gmg_level_info* out);
+
+/* Copy one array of level `level` to the host. Sizes follow gmg_level_info. */
+typedef enum {
+    GMG_H_SAMPLES = 0,        /* int64[m]      fastDiscSample result */
+    GMG_H_PARENTS = 1,        /* int64[n]      assignParents result */
+    GMG_H_COARSE_COLPTR = 2,  /* int32[m+1] */
+    GMG_H_COARSE_ROWIDX = 3,  /* int32[nnz_c] */
+    GMG_H_COARSE_VAL = 4,     /* f64[nnz_c] */
+    GMG_H_COARSE_POINTS = 5,  /* f64[3m], column-major, ld = m */
+    GMG_H_TRIANGLES = 6,      /* int64[3T] row-major */
+    GMG_H_NORMALS = 7,        /* f64[3T] row-major */
+    GMG_H_FAN_PTR = 8,        /* int64[m+1] */
+    GMG_H_FAN = 9,            /* int64[3T] */
+    GMG_H_P_ROWPTR = 10,      /* int32[n+1] */
+    GMG_H_P_COLIDX = 11,      /* int32[nnz_p] */
+    GMG_H_P_VAL = 12,         /* f64[nnz_p] */
+    GMG_H_AC_COLPTR = 13,     /* int32[m+1]   A_c = P^T A P, compressed column-major like A */
+    GMG_H_AC_ROWIDX = 14,     /* int32[nnz_ac] ascending per column, structural (un-pruned) pattern */
+    GMG_H_AC_VAL = 15,        /* f64[nnz_ac] */
+    GMG_H_FINE_VAL = 16       /* f64[nnz] level-0 only: the toEdgeDistanceMatrix values */
+} gmg_hierarchy_array;
+int gmg_hierarchy_fetch(gmg_ctx* ctx, const gmg_hierarchy* h, int level, int which, void* out);
+
 #ifdef __cplusplus
 }
 #endif
