@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py -- hierarchy-build throughput (Mverts/s) of the B200 path, with the HBM roofline of the
+dominant stage, the end-to-end number through the C ABI with host buffers, and the reference's CPU
+implementation timed beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C2|C3|C1] [--sampler exact|parallel]
+    python bench.py --impl reference ...        # the reference's CPU code (oracle/_ref, else the C port)
+
+A "step" is one full hierarchy build (all levels, all stages) over one synthetic mesh.
+N > 1: one process per GPU (torchrun); the path has no row-sharded build yet, so every rank builds an
+independent replica of the workload ("replicas only", weak scaling, no data-path collective).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "hierarchy-build Mverts/s"
+LEVELS = {"C1": 3, "C2": 4, "C3": 4, "C4": 4}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--sampler", default="exact", choices=["exact", "parallel"])
+    ap.add_argument("--galerkin", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    base = {"C1": "icosphere 6 subdivisions (40,962 verts), 3 levels",
+            "C2": "icosphere 9 subdivisions + vertex noise (2,621,442 verts), 4 levels, ratio 8",
+            "C3": "noisy torus 10000x1000 (10,000,000 verts), 4 levels, ratio 8",
+            "C4": "kNN k=8 sphere cloud 20M points, 4 levels"}[a.workload]
+    return base if a.scale == 1.0 else f"{base} [scaled x{a.scale}]"
+
+
+# ---- clocks sampler (B200_PROFILING.md recipe) ---------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- algorithmic bytes per stage (int32 indices, fp64 values, single touch) -------
+def stage_bytes(i):
+    n, nnz, m, nnz_c, T, nnzP, nnzAc = i["n"], i["nnz"], i["m"], i["nnz_c"], i["T"], i["nnz_p"], i["nnz_ac"]
+    return {
+        "edge_lengths": 28 * n + 12 * nnz,
+        "sampling": 32 * n + 4 * nnz + 4 * m,
+        "parents": 40 * n + 4 * nnz + 4 * m,
+        "cluster_csr": 8 * n + 4 * m,
+        "coarse_edges": 8 * n + 12 * nnz + 4 * m + 12 * nnz_c,
+        "coarse_points": 28 * n + 28 * m,
+        "triangle_fans": 32 * m + 12 * nnz_c + 48 * T,
+        "prolongation_rows": 32 * n + 12 * nnzP + 32 * m + 4 * nnz_c + 48 * T,
+        "galerkin": (12 * n + 4 * nnz + 8 * nnzP + 4 * m) + (12 * n + 12 * nnz + 24 * nnzP + 4 * m + 12 * nnzAc),
+    }
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---- CPU arm: the reference's own code on the host cores ---------------------------------------------
+def cpu_hierarchy_seconds(V, A, levels):
+    """One hierarchy build with the reference's CPU implementation (unmodified sources on the Eigen
+    shim when oracle/_ref exists, else the plain-C port). Single thread: the reference has no threading."""
+    from oracle.pyoracle import Oracle, available
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from pipeline import run_hierarchy
+    kind = "ref" if available("ref") else "orc"
+    be = Oracle(kind)
+    t0 = time.perf_counter()
+    run_hierarchy(be, V, A, levels)
+    return time.perf_counter() - t0, ("reference" if kind == "ref" else "port")
+
+
+def run_reference(a, rank, world):
+    if rank != 0:
+        return
+    from gravomg_b200 import meshgen
+    # bounded sample: keep (steps + warmup) * seconds-per-step within a few minutes (~0.25 Mverts/s on one core)
+    budget_s = 150.0
+    full_n = {"C1": 40962, "C2": 2621442, "C3": 10_000_000, "C4": 20_000_000}[a.workload] * a.scale
+    est = full_n / 0.25e6 * (a.steps + a.warmup)
+    scale = a.scale
+    while est > budget_s and scale > 1e-4:
+        scale /= 4.0
+        est /= 4.0
+    cfg = meshgen.make_config(a.workload, scale)
+    V, A = cfg["V"], cfg["A"]
+    n = V.shape[0]
+    times, kind = [], "port"
+    for s in range(a.warmup + a.steps):
+        dt, kind = cpu_hierarchy_seconds(V, A, LEVELS[a.workload])
+        if s >= a.warmup:
+            times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    value = n / (ms * 1e-3) / 1e6
+    sample = f"{a.workload} at scale {scale:g}: {n} verts, {LEVELS[a.workload]} levels, whole hierarchy per step"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mverts/s", "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "sampler": "exact (sequential greedy)", "cpu_sample_verts": n},
+            "cpu_baseline": {"value": value, "unit": "Mverts/s", "cores": 1, "kind": kind, "sample": sample,
+                             "host_cores": os.cpu_count()},
+            "e2e": {"value": value, "unit": "Mverts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---- B200 arm ------------------------------------------------------------------------------------------
+def run_b200(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from gravomg_b200 import meshgen
+    from gravomg_b200 import capi
+    from gravomg_b200.capi import Context, Input, Hierarchy
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    cfg = meshgen.make_config(a.workload, a.scale)
+    V, A = cfg["V"], cfg["A"]
+    levels = LEVELS[a.workload]
+    n = V.shape[0]
+    mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
+
+    stream = torch.cuda.current_stream()
+    ctx = Context(local_rank, stream.cuda_stream)
+
+    # pinned host copies of the inputs for the end-to-end arm
+    def pinned(arr):
+        t = torch.from_numpy(np.ascontiguousarray(arr)).pin_memory()
+        return t, t.numpy()
+    tV, hV = pinned(np.asfortranarray(V).T)             # (3, n) C-order == (n, 3) column-major
+    hV = hV.T
+    tcp, hcp = pinned(A.indptr.astype(np.int32))
+    tri, hri = pinned(A.indices.astype(np.int32))
+    tav, hav = pinned(A.data.astype(np.float64))
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    inp = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
+
+    def step_resident():
+        h = Hierarchy(ctx, inp, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin))
+        return h
+
+    def step_e2e():
+        i2 = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
+        h = Hierarchy(ctx, i2, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin))
+        d2h = 0
+        for lvl in range(h.num_levels):
+            for which in (capi.H_P_ROWPTR, capi.H_P_COLIDX, capi.H_P_VAL):
+                d2h += h.fetch(lvl, which).nbytes
+        nb = i2.h2d_bytes
+        h.close(); i2.close()
+        return nb, d2h
+
+    for _ in range(a.warmup):
+        step_resident().close()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    launches0 = ctx.launch_count
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    infos = None
+    stage_acc = None
+    barrier()
+    for s in range(a.steps):
+        flush.fill_(s & 0xFF)                        # flush L2 between timed iterations
+        torch.cuda.synchronize()
+        ev[s][0].record(stream)
+        h = step_resident()
+        ev[s][1].record(stream)
+        torch.cuda.synchronize()
+        infos = h.info
+        sm = np.array([i["stage_ms"] for i in h.info])
+        stage_acc = sm if stage_acc is None else stage_acc + sm
+        h.close()
+    barrier()
+    launches = ctx.launch_count - launches0
+    clk = clocks.stop()
+    ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in ev]))
+    stage_ms = stage_acc / a.steps                   # [level][stage]
+
+    # end-to-end through the C ABI with host buffers: H2D of the inputs + build + D2H of every P
+    e2e_ms, h2d, d2h = [], 0, 0
+    step_e2e()
+    barrier()
+    for s in range(max(1, min(a.steps, 3))):
+        flush.fill_(s)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        h2d, d2h = step_e2e()
+        torch.cuda.synchronize()
+        e2e_ms.append(1e3 * (time.perf_counter() - t0))
+    e2e = float(np.mean(e2e_ms))
+
+    if world > 1:
+        t = torch.tensor([ms, e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    # dominant stage at level 0 (the level that holds ~7/8 of the work)
+    names = capi.STAGE_NAMES
+    dom = int(np.argmax(stage_ms[0]))
+    bytes0 = stage_bytes(infos[0])[names[dom]]
+    achieved = bytes0 / (stage_ms[0][dom] * 1e-3) / 1e9
+    total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if (k != "galerkin" or a.galerkin)) for i in infos)
+    line = {"metric": METRIC, "value": world * n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": bool(a.galerkin),
+                       "l2": "256 MB flush write between timed steps; inputs (>200 MB) exceed the 126 MB L2",
+                       "multi_gpu": "replicas only (one independent build per rank)" if world > 1 else "single GPU",
+                       "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_p", "sampler_rounds",
+                                                      "parent_rounds")} for i in infos]},
+            "clocks": clk, "gpu_launches": int(launches),
+            "e2e": {"value": world * n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "roofline": {"bound": "hbm", "kernel": f"level-0 stage '{names[dom]}'", "achieved": achieved,
+                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "algorithmic_bytes": int(bytes0), "stage_ms": float(stage_ms[0][dom]),
+                         "whole_build": {"algorithmic_bytes": int(total_bytes),
+                                         "achieved": total_bytes / (ms * 1e-3) / 1e9,
+                                         "frac": total_bytes / (ms * 1e-3) / 1e9 / peak}},
+            "stage_ms": {f"L{l}": {names[s]: round(float(stage_ms[l][s]), 4) for s in range(9)}
+                         for l in range(len(infos))}}
+    if not a.no_cpu_baseline:
+        # bounded sample of the same workload on the host cores (about 10-30 s of CPU work)
+        scale = a.scale
+        while n * scale / a.scale / 0.25e6 > 30.0:
+            scale /= 4.0
+        c2 = cfg if scale == a.scale else meshgen.make_config(a.workload, scale)
+        dt, kind = cpu_hierarchy_seconds(c2["V"], c2["A"], levels)
+        nn = c2["V"].shape[0]
+        line["cpu_baseline"] = {"value": nn / dt / 1e6, "unit": "Mverts/s", "cores": 1, "kind": kind,
+                                "host_cores": os.cpu_count(), "seconds": dt,
+                                "sample": f"{a.workload} at scale {scale:g}: {nn} verts, whole {levels}-level hierarchy, "
+                                          f"one run, reference source on Eigen shim, -O2, 1 thread"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        run_reference(a, rank, world)
+    else:
+        run_b200(a, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

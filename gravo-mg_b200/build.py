@@ -67,3 +67,27 @@ def build(verbose=False, force=False):
 
 if __name__ == "__main__":
     print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+
+
+FACADE_DIR = os.path.join(HERE, "facade")
+FACADE_TEST = os.path.join(LIBDIR, "facade_test")
+
+
+def build_facade_test():
+    """Compile the C++ facade (namespace GravoMG, reference signatures) and its self-check program
+    against the Eigen shim. Skipped quietly if the facade sources are not there yet."""
+    src = os.path.join(FACADE_DIR, "facade_test.cpp")
+    if not os.path.exists(src):
+        return None
+    root = os.path.dirname(HERE)
+    deps = [src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), LIB]
+    if os.path.exists(FACADE_TEST) and os.path.getmtime(FACADE_TEST) > max(os.path.getmtime(d) for d in deps):
+        return FACADE_TEST
+    cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(FACADE_DIR, "include"),
+           "-I", os.path.join(root, "oracle", "eigen_shim"), "-I", os.path.join(root, "include"),
+           src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), "-L", LIBDIR, "-lgravomg_b200",
+           "-Wl,-rpath,$ORIGIN", "-o", FACADE_TEST]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"facade build failed:\n{r.stdout}\n{r.stderr}")
+    return FACADE_TEST

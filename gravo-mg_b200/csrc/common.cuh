@@ -149,6 +149,20 @@ __device__ __forceinline__ V3 normalized(V3 a) {
     return a;
 }
 
+// Warp-aggregated queue append: the converged lanes that reach this call together take consecutive
+// slots with ONE atomic on the shared counter (a single address serialises in the L2 atomic unit at
+// under 1 op/cycle, so per-lane atomics on one counter cap a whole level at ~2 G appends/s).
+__device__ __forceinline__ int32_t warp_append(int32_t* counter) {
+    const cg::coalesced_group g = cg::coalesced_threads();
+    int32_t base = 0;
+    if (g.thread_rank() == 0) base = atomicAdd(counter, int32_t(g.size()));
+    return g.shfl(base, 0) + int32_t(g.thread_rank());
+}
+__device__ __forceinline__ void warp_count(unsigned long long* counter) {
+    const cg::coalesced_group g = cg::coalesced_threads();
+    if (g.thread_rank() == 0) atomicAdd(counter, (unsigned long long)g.size());
+}
+
 // lower_bound of key in the ascending int32 range [lo, hi); returns hi when every entry is smaller
 __device__ __forceinline__ int32_t lower_bound_i32(const int32_t* __restrict__ a, int32_t lo, int32_t hi, int32_t key) {
     while (lo < hi) {

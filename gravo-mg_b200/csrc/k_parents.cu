@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(kBlock) parents_sweep_kernel(ParentArgs a) {
                 if (!(cand >= 0.0)) continue;                                   // NaN never wins a strict <
                 const unsigned long long old = atomicMin(a.dist + v, cb);
                 if (cb < old && atomicExch(a.stamp + v, round) != round)
-                    nxt[atomicAdd(a.counters + (cur_c ^ 1), 1)] = v;
+                    nxt[warp_append(a.counters + (cur_c ^ 1))] = v;
             }
         }
         grid.sync();

@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
         }
         if (i < 32) bits |= (unsigned long long)(b1 ? 1 : 0) << (2 * i) | (unsigned long long)(b2 ? 1 : 0) << (2 * i + 1);
     }
-    atomicAdd(a.stats + 0, 1ull);
+    warp_count(a.stats + 0);
     // First fallback (:407-448): smallest never-flagged key with a usable first-seen value.
     int32_t best = 0x7fffffff;
     for (int32_t i = 0; i < F; ++i) {
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
         }
     }
     if (best != 0x7fffffff) {                                                             // :422-448
-        atomicAdd(a.stats + 1, 1ull);
+        warp_count(a.stats + 1);
         const double w2 = edge_weight(p, pc, ld3(a.cp, a.m, best));
         ids[0] = c; ids[1] = best;
         if (a.weighting == GMG_BARYCENTRIC) { w[0] = 1. - w2; w[1] = w2; }
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
         return;
     }
     // Second fallback (:449-483): the two nearest coarse neighbours of c by (distance, index), plus c.
-    atomicAdd(a.stats + 2, 1ull);
+    warp_count(a.stats + 2);
     double d1 = 0, d2 = 0; int32_t i1 = -1, i2 = -1;
     for (int32_t k = cb; k < ce; ++k) {
         const int32_t nb = __ldg(a.c_rowidx + k);
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
         else if (i2 < 0 || d < d2 || (!(d2 < d) && nb < i2)) { d2 = d; i2 = nb; }
     }
     if (i2 < 0) {  // fewer than two non-self neighbours: out-of-range read in the reference (:472)
-        atomicAdd(a.stats + 3, 1ull);
+        warp_count(a.stats + 3);
         ids[0] = c; w[0] = 1.0; emit_row(a, f, ids, w, 1);
         return;
     }

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(kBlock) sampler_count_kernel(SamplerArgs a) {
         a.cnt[i] = c;
         if (c == 0) {
             a.state[i] = kIn;
-            a.inq[atomicAdd(a.counters + 0, 1)] = i;
+            a.inq[warp_append(a.counters + 0)] = i;
         } else {
             a.state[i] = kUndecided;
         }
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kBlock) sampler_sweep_kernel(SamplerArgs a) {
         for (int64_t q = in_head + group; q < in_tail; q += groups) {
             const int32_t j = a.inq[q];
             for_each_covered(a, j, sub, [&](int32_t t) {
-                if (atomicCAS(a.state + t, kUndecided, kOut) == kUndecided) a.outq[atomicAdd(a.counters + 1, 1)] = t;
+                if (atomicCAS(a.state + t, kUndecided, kOut) == kUndecided) a.outq[warp_append(a.counters + 1)] = t;
             });
         }
         in_head = in_tail;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kBlock) sampler_sweep_kernel(SamplerArgs a) {
             for_each_covered(a, j, sub, [&](int32_t t) {
                 if (precedes<MODE>(j, t, a.seed) && atomicSub(a.cnt + t, 1) == 1) {
                     a.state[t] = kIn;  // every preceding coverer is OUT, so nobody can mark t OUT
-                    a.inq[atomicAdd(a.counters + 0, 1)] = t;
+                    a.inq[warp_append(a.counters + 0)] = t;
                 }
             });
         }

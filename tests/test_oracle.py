@@ -1,0 +1,74 @@
+"""The oracle (plain-C restatement) is pinned two ways: against the committed golden fixtures, which
+are outputs of the reference itself (tests/golden/make_golden.py), and, where oracle/_ref has been
+built, against the unmodified reference sources directly on fresh inputs. CPU only."""
+import numpy as np
+import pytest
+
+from gravomg_b200 import meshgen
+from golden_util import GOLDEN, load_golden
+from pipeline import run_hierarchy, assert_level_equal, STAGE_KEYS
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_oracle_matches_golden(orc, name):
+    V, A, levels, weighting, fine_val, want = load_golden(name)
+    assert np.array_equal(orc.to_edge_distance_matrix(A.indptr, A.indices, V), fine_val)
+    got = run_hierarchy(orc, V, A, levels, weighting=weighting)
+    assert len(got) == len(want)
+    for lvl, (g, w) in enumerate(zip(got, want)):
+        assert g["radius"] == w["radius"], f"{name} level {lvl}: radius"
+        assert_level_equal(g, w, what=f"{name} level {lvl} ")
+
+
+@pytest.mark.parametrize("name,scale", [("C1", 1.0), ("C2", 1 / 256), ("C3", 0.002), ("C4", 0.0005)])
+def test_oracle_matches_reference_on_shim(orc, ref, name, scale):
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    got = run_hierarchy(orc, V, A, cfg["levels"])
+    want = run_hierarchy(ref, V, A, cfg["levels"])
+    for lvl, (g, w) in enumerate(zip(got, want)):
+        assert g["radius"] == w["radius"]
+        assert_level_equal(g, w, what=f"{name} level {lvl} ")
+
+
+def test_invariants(orc):
+    """Properties that follow from the reference code, no second implementation needed."""
+    cfg = meshgen.make_config("C4", 0.0005)
+    V, A = cfg["V"], cfg["A"]
+    res = run_hierarchy(orc, V, A, 3)
+    for r in res:
+        n, m = len(r["par"]), len(r["sel"])
+        assert np.all(np.diff(r["sel"]) > 0)                                   # ascending selection
+        assert np.array_equal(r["par"][r["sel"]], np.arange(m))                # parents[samples[c]] == c
+        rows = np.diff(r["prp"])
+        assert rows.min() >= 1 and rows.max() <= 3
+        sums = np.add.reduceat(r["pva"], r["prp"][:-1])
+        assert np.allclose(sums, 1.0, atol=1e-12)                              # rows of P sum to 1
+        import scipy.sparse as sp
+        C = sp.csc_matrix((r["cval"], r["cri"], r["ccp"]), shape=(m, m))
+        pat = C.copy(); pat.data[:] = 1
+        assert (pat != pat.T).nnz == 0 and C.diagonal().sum() == 0             # symmetric pattern, empty diagonal
+        assert np.all((r["tri"][:, 0] < r["tri"][:, 1]) & (r["tri"][:, 1] < r["tri"][:, 2]))
+        key = r["tri"][:, 0] * m * m + r["tri"][:, 1] * m + r["tri"][:, 2]
+        assert np.all(np.diff(key) > 0)                                        # lexicographic triangle ids
+        for v in range(0, m, max(1, m // 50)):
+            assert np.all(np.diff(r["fan"][r["fptr"][v]:r["fptr"][v + 1]]) > 0)
+
+
+def test_edge_cases(orc):
+    # empty graph, isolated vertices (degree-0 parents), a single edge (degree-1 parents)
+    V = np.asfortranarray(np.array([[0., 0, 0], [1, 0, 0], [5, 5, 5], [1.5, 0.2, 0]]))
+    import scipy.sparse as sp
+    A = sp.csc_matrix(np.array([[1., 1, 0, 0], [1, 1, 0, 1], [0, 0, 1, 0], [0, 1, 0, 1]]))
+    A.sort_indices()
+    val = orc.to_edge_distance_matrix(A.indptr, A.indices, V)
+    sel = orc.fast_disc_sample(V, A.indptr, A.indices, 0.6)
+    assert list(sel) == [0, 1, 2]
+    par = orc.assign_parents(V, A.indptr, A.indices, sel)
+    assert list(par) == [0, 1, 2, 1]
+    ccp, cri, cval = orc.extract_coarse_edges(A.indptr, A.indices, val, 3, par)
+    assert list(ccp) == [0, 1, 2, 2] and list(cri) == [1, 0]
+    cpts = orc.coarse_from_mean_of_fine_children(V, A.indptr, A.indices, par, 3)
+    prp, pci, pva, rc = orc.construct_prolongation(V, cpts, ccp, cri, cval, par, 0)
+    assert rc == 0 and list(np.diff(prp)) == [2, 2, 1, 2]
+    assert np.allclose(np.add.reduceat(pva, prp[:-1]), 1.0)
