@@ -80,12 +80,13 @@ def build_facade_test():
     if not os.path.exists(src):
         return None
     root = os.path.dirname(HERE)
-    deps = [src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), LIB]
+    srcs = [src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), os.path.join(FACADE_DIR, "facade_extras.cpp")]
+    deps = srcs + [LIB, os.path.join(FACADE_DIR, "include", "gravomg", "b200_facade.h")]
     if os.path.exists(FACADE_TEST) and os.path.getmtime(FACADE_TEST) > max(os.path.getmtime(d) for d in deps):
         return FACADE_TEST
     cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(FACADE_DIR, "include"),
            "-I", os.path.join(root, "oracle", "eigen_shim"), "-I", os.path.join(root, "include"),
-           src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), "-L", LIBDIR, "-lgravomg_b200",
+           *srcs, "-L", LIBDIR, "-lgravomg_b200",
            "-Wl,-rpath,$ORIGIN", "-o", FACADE_TEST]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

@@ -1,0 +1,5 @@
+// Drop-in for the reference header <gravomg/utility.h>: same include path, same namespace, same
+// signatures. All declarations live in b200_facade.h; the implementations call the CUDA library
+// through the C ABI (include/gravomg_b200.h).
+#pragma once
+#include "b200_facade.h"
