@@ -366,3 +366,53 @@ class Hierarchy:
         i = self.info[level]
         return sp.csc_matrix((self.fetch(level, H_AC_VAL), self.fetch(level, H_AC_ROWIDX),
                               self.fetch(level, H_AC_COLPTR)), shape=(i["m"], i["m"]))
+
+
+# ---- SpMV, multicolour Gauss-Seidel, V-cycle --------------------------------------------------------
+def spmv(ctx, outer, inner, val, x, n_inner=None):
+    """y[i] = sum_k val[k] * x[inner[k]] over outer vector i (A x for CSR arrays, A^T x for CSC arrays)."""
+    outer, inner, val, x = _i32(outer), _i32(inner), _f64(val), _f64(x)
+    n = outer.shape[0] - 1
+    y = np.empty(n, dtype=np.float64)
+    ctx._check(ctx.lib.gmg_spmv(ctx.h, C.c_int64(n), C.c_int64(x.shape[0] if n_inner is None else n_inner),
+                                _p(outer, _i32p), _p(inner, _i32p), _p(val, _f64p), _p(x, _f64p), _p(y, _f64p)))
+    return y
+
+
+def gauss_seidel(ctx, outer, inner, val, b, x, sweeps=1):
+    """Multicolour Gauss-Seidel sweeps; returns (x_new, colours, num_colours)."""
+    outer, inner, val, b = _i32(outer), _i32(inner), _f64(val), _f64(b)
+    x = np.array(x, dtype=np.float64)
+    n = outer.shape[0] - 1
+    colours = np.empty(n, dtype=np.int32)
+    nc = C.c_int32()
+    ctx._check(ctx.lib.gmg_gauss_seidel(ctx.h, C.c_int64(n), _p(outer, _i32p), _p(inner, _i32p), _p(val, _f64p),
+                                        _p(b, _f64p), _p(x, _f64p), C.c_int(sweeps), _p(colours, _i32p), C.byref(nc)))
+    return x, colours, nc.value
+
+
+class Solver:
+    """V-cycle on A x = b over a hierarchy built with build_galerkin=True."""
+
+    def __init__(self, ctx, inp, hierarchy):
+        self.ctx, self._inp, self._h = ctx, inp, hierarchy
+        h = C.c_void_p()
+        ctx._check(ctx.lib.gmg_solver_create(ctx.h, inp.h, hierarchy.h, C.byref(h)))
+        self.h = h
+
+    def vcycle(self, b, x0=None, cycles=1, pre=2, post=2, coarse_sweeps=50):
+        b = _f64(b)
+        x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=np.float64)
+        res = np.empty(cycles + 1, dtype=np.float64)
+        self.ctx._check(self.ctx.lib.gmg_solver_vcycle(self.ctx.h, self.h, _p(b, _f64p), _p(x, _f64p), C.c_int(cycles),
+                                                       C.c_int(pre), C.c_int(post), C.c_int(coarse_sweeps),
+                                                       _p(res, _f64p)))
+        return x, res
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.lib.gmg_solver_destroy.argtypes = [C.c_void_p]
+            self.ctx.lib.gmg_solver_destroy(self.h)
+        self.h = None
+
+    __del__ = close

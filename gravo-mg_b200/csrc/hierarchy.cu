@@ -1,6 +1,6 @@
 // Resident hierarchy builder [not in reference]: repeats the per-level call order of the
 // reference's demo (test/main.cpp:68-121) with every array kept in HBM between stages and levels.
-#include "stages.h"
+#include "hierarchy_types.h"
 
 #include <cmath>
 #include <memory>
@@ -8,27 +8,7 @@
 
 using namespace gmg;
 
-struct gmg_input {
-    gmg_ctx* ctx = nullptr;
-    int32_t n = 0;
-    int64_t nnz = 0;
-    DevBuf<double> pts;
-    DevBuf<int32_t> colptr, rowidx;
-    DevBuf<double> a_val;
-    bool has_a = false;
-};
-
 namespace {
-
-struct Level {
-    gmg_level_info info{};
-    DevBuf<int32_t> samples, parents;
-    DeviceCsc coarse;
-    DevBuf<double> coarse_pts;
-    Triangles tri;
-    DeviceCsr P;
-    DeviceCsc Ac;
-};
 
 struct StageClock {
     gmg_ctx* c;
@@ -49,13 +29,6 @@ struct StageClock {
 };
 
 }  // namespace
-
-struct gmg_hierarchy {
-    gmg_ctx* ctx = nullptr;
-    DevBuf<double> fine_val;  // level-0 toEdgeDistanceMatrix values
-    int64_t fine_nnz = 0;
-    std::vector<std::unique_ptr<Level>> levels;
-};
 
 template <typename F> static int guarded_h(gmg_ctx* c, F&& body) {
     if (!c) return GMG_ERR_STATE;

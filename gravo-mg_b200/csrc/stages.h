@@ -80,6 +80,22 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
 // R = P^T in CSR (rows = coarse), fine indices ascending per row
 void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R);
 
+// ---- k_solver.cu ------------------------------------------------------------------------------
+struct Colouring {
+    int num_colours = 0;
+    DevBuf<int32_t> colour;        // n
+    DevBuf<int32_t> rows;          // n, rows bucketed by colour, ascending inside a bucket
+    std::vector<int32_t> offsets;  // num_colours + 1 (host)
+};
+// y = alpha * (M x) + b over outer vectors (b may be null)
+void spmv(gmg_ctx* c, int32_t n, const int32_t* outer, const int32_t* inner, const double* val, const double* x,
+          double* y, double alpha, const double* b);
+void axpy(gmg_ctx* c, int32_t n, double a, const double* x, double* y);
+void colour_graph(gmg_ctx* c, int32_t n, const int32_t* outer, const int32_t* inner, Colouring& out);
+void gauss_seidel(gmg_ctx* c, const Colouring& col, const int32_t* outer, const int32_t* inner, const double* val,
+                  const double* b, double* x, int sweeps, bool reverse);
+double norm2(gmg_ctx* c, int32_t n, const double* x);
+
 // index conversions at the ABI boundary (std::vector<Eigen::Index> is int64, device indices int32)
 void narrow_i64(gmg_ctx* c, const int64_t* in, int32_t* out, int64_t n, int64_t upper, int32_t* d_flag);
 void widen_i32(gmg_ctx* c, const int32_t* in, int64_t* out, int64_t n);

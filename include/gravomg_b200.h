@@ -194,6 +194,32 @@ typedef enum {
 } gmg_hierarchy_array;
 int gmg_hierarchy_fetch(gmg_ctx* ctx, const gmg_hierarchy* h, int level, int which, void* out);
 
+/* ------------------------------------------------------------------------------------------------
+ * SpMV, multicolour Gauss-Seidel and the V-cycle that validates a hierarchy [not in reference;
+ * BASELINE.json north star]. Matrices are compressed by outer index; gmg_spmv computes
+ * y[i] = sum_k val[k] * x[inner[k]] over outer vector i (A x for row-major storage, A^T x for
+ * column-major storage -- the same thing for the symmetric operators used here).
+ * ------------------------------------------------------------------------------------------------ */
+int gmg_spmv(gmg_ctx* ctx, int64_t n, int64_t n_inner, const int32_t* outer, const int32_t* inner, const double* val,
+             const double* x, double* y);
+/* `sweeps` multicolour Gauss-Seidel sweeps on A x = b, x updated in place. colours_out (optional,
+ * int32[n]) receives the Jones-Plassmann colouring used; the sweep equals sequential Gauss-Seidel in
+ * (colour, row) order. */
+int gmg_gauss_seidel(gmg_ctx* ctx, int64_t n, const int32_t* outer, const int32_t* inner, const double* val,
+                     const double* b, double* x, int sweeps, int32_t* colours_out, int32_t* num_colours_out);
+
+typedef struct gmg_solver gmg_solver;
+/* Needs a hierarchy built with build_galerkin = 1; `in` and `h` must outlive the solver. */
+int gmg_solver_create(gmg_ctx* ctx, const gmg_input* in, const gmg_hierarchy* h, gmg_solver** out);
+void gmg_solver_destroy(gmg_solver* s);
+/* `cycles` V-cycles on A x = b from the x passed in: pre/post multicolour Gauss-Seidel sweeps per
+ * level (post in reverse colour order), restriction r_c = P^T r, prolongation x += P e,
+ * coarse_sweeps sweeps on the coarsest operator. residual_out (optional) has cycles+1 entries:
+ * ||b - A x||_2 before the first and after every cycle. */
+int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, int cycles, int pre, int post,
+                      int coarse_sweeps, double* residual_out);
+/* device milliseconds of the last gmg_spmv / gmg_solver_vcycle are available through gmg_last_kernel_ms */
+
 #ifdef __cplusplus
 }
 #endif

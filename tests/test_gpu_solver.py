@@ -1,0 +1,63 @@
+"""SpMV, multicolour Gauss-Seidel and the V-cycle [not in reference; BASELINE.json north star].
+Checker: scipy for A x, a numpy restatement of Gauss-Seidel in (colour, row) order, tolerance 1e-12."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from gravomg_b200 import meshgen
+
+pytestmark = pytest.mark.gpu
+
+
+def numpy_colour_gs(A, b, x, colours, nc, sweeps):
+    A = sp.csr_matrix(A)
+    d = A.diagonal()
+    x = x.copy()
+    for _ in range(sweeps):
+        for c in range(nc):
+            rows = np.nonzero(colours == c)[0]
+            Ax = A[rows] @ x
+            x[rows] = (b[rows] - (Ax - d[rows] * x[rows])) / d[rows]
+    return x
+
+
+@pytest.mark.parametrize("name,scale", [("C1", 1.0), ("C3", 0.004)])
+def test_spmv_and_gauss_seidel(ctx, name, scale):
+    from gravomg_b200 import capi
+    cfg = meshgen.make_config(name, scale)
+    A = cfg["A"]
+    n = A.shape[0]
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(n)
+    y = capi.spmv(ctx, A.indptr, A.indices, A.data, x)
+    want = A.T @ x
+    assert np.abs(y - want).max() <= 1e-12 * np.abs(want).max()
+    As = (A + 1e-3 * sp.identity(n)).tocsc(); As.sort_indices()
+    b = rng.standard_normal(n)
+    x1, colours, nc = capi.gauss_seidel(ctx, As.indptr, As.indices, As.data, b, np.zeros(n), sweeps=3)
+    # proper colouring
+    coo = As.tocoo(); off = coo.row != coo.col
+    assert np.all(colours[coo.row[off]] != colours[coo.col[off]]) and colours.min() >= 0 and nc <= 16
+    want = numpy_colour_gs(As, b, np.zeros(n), colours, nc, 3)
+    assert np.abs(x1 - want).max() <= 1e-12 * np.abs(want).max()
+
+
+def test_vcycle_poisson(ctx):
+    """One V-cycle (2 pre + 2 post sweeps) on the SPD torus operator of config C3 (scaled): the
+    residual must drop, and repeated cycles must converge."""
+    from gravomg_b200.capi import Input, Hierarchy, Solver
+    cfg = meshgen.make_config("C3", 0.01)
+    V, A = cfg["V"], cfg["A"]
+    n = V.shape[0]
+    xstar = np.sin(3 * V[:, 0]) * np.cos(2 * V[:, 1]) + V[:, 2]
+    b = A @ xstar
+    inp = Input(ctx, V, A.indptr, A.indices, A.data)
+    h = Hierarchy(ctx, inp, cfg["levels"], build_galerkin=True)
+    s = Solver(ctx, inp, h)
+    x, res = s.vcycle(b, cycles=8, pre=2, post=2, coarse_sweeps=50)
+    assert res[1] < 0.5 * res[0]
+    assert res[-1] < 1e-3 * res[0], res
+    assert np.abs(A @ x - b).max() <= 1.01 * res[-1]
+    factors = res[1:] / res[:-1]
+    assert factors.max() < 0.9
+    s.close(); h.close(); inp.close()
