@@ -148,8 +148,32 @@ __device__ __forceinline__ bool coarse_row(const CoarseArgs& a, int32_t P, int t
     const int32_t K = *scount;
     if (nonpos) a.flags[0] = 1;
     if (K > SLOTS * 3 / 4) return false;   // too full to trust probing: let the caller escalate
-    // rank sort of the occupied slots by key into the scratch row
     const int32_t off = __ldg(a.boff + P);
+    if constexpr (THREADS == 32) {
+        // compact the occupied slots to the front (in place: a slot only ever moves down, and every
+        // chunk is read before it is written), then rank-sort the K survivors: K*K/32 steps per lane
+        // instead of SLOTS*SLOTS/32
+        int32_t base = 0;
+        for (int s0 = 0; s0 < SLOTS; s0 += 32) {
+            const int32_t q = keys[s0 + tid];
+            const unsigned long long v = vals[s0 + tid];
+            const unsigned occ = __ballot_sync(0xffffffffu, q >= 0);
+            __syncwarp();
+            if (q >= 0) { const int pos = base + __popc(occ & ((1u << tid) - 1u)); keys[pos] = q; vals[pos] = v; }
+            base += __popc(occ);
+            __syncwarp();
+        }
+        for (int s = tid; s < K; s += 32) {
+            const int32_t q = keys[s];
+            int32_t rank = 0;
+            for (int s2 = 0; s2 < K; ++s2) rank += keys[s2] < q ? 1 : 0;
+            a.sQ[off + rank] = q;
+            a.st[off + rank] = from_ordered_bits(vals[s]);
+        }
+        if (tid == 0) a.cnt[P] = K;
+        return true;
+    }
+    // rank sort of the occupied slots by key into the scratch row
     for (int s = tid; s < SLOTS; s += THREADS) {
         const int32_t q = keys[s];
         if (q < 0) continue;

@@ -29,66 +29,75 @@ struct ParentArgs {
     const int32_t* rowidx;
     const double* len;
     unsigned long long* dist;  // bit patterns of non-negative doubles
-    int32_t* stamp;            // round in which a vertex was last queued
-    int32_t* q0;
-    int32_t* q1;
-    int32_t* counters;         // [0],[1] tails of q0,q1; [2] rounds
+    int32_t* stamp;            // round in which a vertex's distance last improved (-1: never, 0: source)
+    int32_t* counters;         // [0..2] rotating "something improved" flags; [3] rounds
 };
 
 __global__ void __launch_bounds__(kBlock) parents_init_kernel(int32_t n, unsigned long long* __restrict__ dist,
                                                               int32_t* __restrict__ stamp, int32_t* __restrict__ srcid) {
     const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (i < n) { dist[i] = kInfBits; stamp[i] = 0; srcid[i] = -1; }
+    if (i < n) { dist[i] = kInfBits; stamp[i] = -1; srcid[i] = -1; }
 }
 
 // Later sources overwrite earlier ones exactly like the loop at :89-93 (duplicates: last wins).
 __global__ void __launch_bounds__(kBlock) parents_seed_kernel(int32_t m, const int32_t* __restrict__ samples,
                                                               unsigned long long* __restrict__ dist,
-                                                              int32_t* __restrict__ srcid, int32_t* __restrict__ q0,
-                                                              int32_t* __restrict__ counters) {
+                                                              int32_t* __restrict__ srcid, int32_t* __restrict__ stamp) {
     const int64_t cidx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (cidx >= m) return;
     const int32_t v = samples[cidx];
     dist[v] = 0ull;
+    stamp[v] = 0;
     atomicMax(srcid + v, int32_t(cidx));
-    q0[cidx] = v;
-    if (cidx == 0) counters[0] = m;
 }
 
+// Round r relaxes out of every vertex whose distance improved in round r-1. The frontier is not a
+// queue: every warp reads 32 stamps (coalesced), ballots the active ones and hands them to its four
+// 8-lane groups. A queue would put one atomic per improved vertex on a single tail word, which
+// serialises in the L2 atomic unit; the stamp scan costs 4 bytes per vertex and round instead.
 __global__ void __launch_bounds__(kBlock) parents_sweep_kernel(ParentArgs a) {
     cg::grid_group grid = cg::this_grid();
-    const int64_t groups = int64_t(gridDim.x) * (kBlock / kPLanes);
-    const int64_t group = (int64_t(blockIdx.x) * kBlock + threadIdx.x) / kPLanes;
-    const int sub = threadIdx.x % kPLanes;
-    int32_t* cur = a.q0;
-    int32_t* nxt = a.q1;
-    int cur_c = 0;
+    const int lane = threadIdx.x & 31;
+    const int grp = lane / kPLanes;
+    const int sub = lane % kPLanes;
+    const int64_t warps = (int64_t(gridDim.x) * kBlock) >> 5;
+    const int64_t warp = (int64_t(blockIdx.x) * kBlock + threadIdx.x) >> 5;
     int round = 1;
-    for (;;) {
-        const int32_t count = *(volatile int32_t*)(a.counters + cur_c);
-        if (count == 0) break;
-        for (int64_t q = group; q < count; q += groups) {
-            const int32_t u = cur[q];
-            const double du = __longlong_as_double((long long)*(volatile unsigned long long*)(a.dist + u));
-            const int32_t b = __ldg(a.colptr + u), e = __ldg(a.colptr + u + 1);
-            for (int32_t k = b + sub; k < e; k += kPLanes) {
-                const int32_t v = __ldg(a.rowidx + k);
-                const double cand = __ldg(a.len + k) + du;                      // edge + path, :108
-                const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
-                if (!(cand >= 0.0)) continue;                                   // NaN never wins a strict <
-                const unsigned long long old = atomicMin(a.dist + v, cb);
-                if (cb < old && atomicExch(a.stamp + v, round) != round)
-                    nxt[warp_append(a.counters + (cur_c ^ 1))] = v;
+    for (;; ++round) {
+        bool improved = false;
+        for (int64_t base = warp * 32; base < a.n; base += warps * 32) {
+            const int64_t mine = base + lane;
+            const bool active = mine < a.n && *(volatile int32_t*)(a.stamp + mine) == round - 1;
+            unsigned mask = __ballot_sync(0xffffffffu, active);
+            while (mask) {
+                unsigned m = mask;
+                for (int i = 0; i < grp; ++i) m &= m - 1;               // the grp-th set bit is ours
+                if (m) {
+                    const int32_t u = int32_t(base) + (__ffs(m) - 1);
+                    const double du = __longlong_as_double((long long)*(volatile unsigned long long*)(a.dist + u));
+                    const int32_t b = __ldg(a.colptr + u), e = __ldg(a.colptr + u + 1);
+                    for (int32_t k = b + sub; k < e; k += kPLanes) {
+                        const int32_t v = __ldg(a.rowidx + k);
+                        const double cand = __ldg(a.len + k) + du;                  // edge + path, :108
+                        if (!(cand >= 0.0)) continue;                               // NaN never wins a strict <
+                        const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
+                        if (cb < *(volatile unsigned long long*)(a.dist + v) && cb < atomicMin(a.dist + v, cb)) {
+                            *(volatile int32_t*)(a.stamp + v) = round;              // every writer stores the same value
+                            improved = true;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 32 / kPLanes; ++i) mask &= mask - 1;
             }
         }
+        if (improved) *(volatile int32_t*)(a.counters + round % 3) = 1;
         grid.sync();
-        if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[cur_c] = 0;
-        int32_t* t = cur; cur = nxt; nxt = t;
-        cur_c ^= 1;
-        ++round;
-        grid.sync();
+        const bool more = *(volatile int32_t*)(a.counters + round % 3) != 0;
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[(round + 2) % 3] = 0;   // flag of round+2; round+1's is live
+        if (!more) break;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[2] = round - 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[3] = round;
 }
 
 // pred[v] by the (dist, index) rule; also detects edges that do not increase the path length.
@@ -152,18 +161,18 @@ void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int3
     if (stats) stats->rounds = 0;
     if (n == 0) return;
     DevBuf<unsigned long long> dist(c, n);
-    DevBuf<int32_t> stamp(c, n), srcid(c, n), q0(c, n), q1(c, n), counters(c, 4), pred(c, n), flags(c, 2);
+    DevBuf<int32_t> stamp(c, n), srcid(c, n), counters(c, 4), pred(c, n), flags(c, 2);
     counters.zero();
     flags.zero();
     GMG_LAUNCH(c, parents_init_kernel, div_up(n, kBlock), kBlock, 0, n, dist.p, stamp.p, srcid.p);
     if (m > 0) {
-        GMG_LAUNCH(c, parents_seed_kernel, div_up(m, kBlock), kBlock, 0, m, samples, dist.p, srcid.p, q0.p, counters.p);
-        ParentArgs a{n, colptr, rowidx, len, dist.p, stamp.p, q0.p, q1.p, counters.p};
+        GMG_LAUNCH(c, parents_seed_kernel, div_up(m, kBlock), kBlock, 0, m, samples, dist.p, srcid.p, stamp.p);
+        ParentArgs a{n, colptr, rowidx, len, dist.p, stamp.p, counters.p};
         int per_sm = 0;
         GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parents_sweep_kernel, kBlock, 0));
         GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "parent sweep kernel does not fit on an SM");
         int grid = per_sm * c->sm_count;
-        const int needed = div_up(int64_t(n) * kPLanes, kBlock);
+        const int needed = div_up(n, kBlock);
         if (grid > needed) grid = needed;
         void* args[] = {&a};
         GMG_CUDA(cudaLaunchCooperativeKernel((void*)parents_sweep_kernel, dim3(grid), dim3(kBlock), args, 0, c->stream));
@@ -176,7 +185,7 @@ void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int3
     flags.download(hf, 2);
     counters.download(hc, 4);
     sync(c);
-    if (stats) stats->rounds = hc[2];
+    if (stats) stats->rounds = hc[3];
     GMG_REQUIRE(hf[0] == 0, GMG_ERR_ZERO_LENGTH_EDGE,
                 "assignParents: an edge does not increase the path length (duplicate points?); "
                 "the reference's heap order is then dynamic and is not reproduced");
