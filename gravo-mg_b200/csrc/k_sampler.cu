@@ -229,6 +229,17 @@ __global__ void __launch_bounds__(kBlock) sampler_flow_kernel(SamplerArgs a) {
     }
 }
 
+__global__ void __launch_bounds__(kBlock) flag_in_kernel(int32_t n, const int32_t* __restrict__ state,
+                                                         int32_t* __restrict__ flag) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n) flag[i] = state[i] == kIn ? 1 : 0;
+}
+__global__ void __launch_bounds__(kBlock) compact_kernel(int32_t n, const int32_t* __restrict__ state,
+                                                         const int32_t* __restrict__ pos, int32_t* __restrict__ out) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n && state[i] == kIn) out[pos[i]] = int32_t(i);
+}
+
 // sum over columns of deg^2: with nnz it bounds the number of covering paths
 __global__ void __launch_bounds__(kBlock) degree_square_kernel(int32_t n, const int32_t* __restrict__ colptr,
                                                                unsigned long long* __restrict__ out) {
