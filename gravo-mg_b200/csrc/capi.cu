@@ -238,7 +238,7 @@ int gmg_extract_coarse_edges(gmg_ctx* c, int64_t n, const int32_t* colptr, const
         Clusters cl;
         build_clusters(c, int32_t(n), int32_t(m), d_par.p, cl);
         DeviceCsc out;
-        coarse_edges(c, int32_t(n), d_cp.p, d_ri.p, d_va.p, int32_t(m), d_par.p, cl, out);
+        coarse_edges(c, int32_t(n), nnz, d_cp.p, d_ri.p, d_va.p, int32_t(m), d_par.p, cl, out);
         t.stop();
         out.colptr.download(out_colptr, m + 1);
         sync(c);
@@ -293,7 +293,7 @@ int gmg_construct_voronoi_triangles(gmg_ctx* c, int64_t m, const double* points,
         check_pattern(c, int32_t(m), d_cp.p, d_ri.p, false);
         KernelTimer t(c);
         Triangles tr;
-        voronoi_triangles(c, int32_t(m), d_pts.p, d_cp.p, d_ri.p, d_va.p, tr);
+        voronoi_triangles(c, int32_t(m), nnz, d_pts.p, d_cp.p, d_ri.p, d_va.p, tr);
         DevBuf<int64_t> tri64(c, 3 * tr.T), fan64(c, 3 * tr.T), ptr64(c, m + 1);
         widen_i32(c, tr.tri.p, tri64.p, 3 * tr.T);
         widen_i32(c, tr.fan_tri.p, fan64.p, 3 * tr.T);
@@ -337,7 +337,7 @@ int gmg_construct_prolongation(gmg_ctx* c, int64_t n, const double* fine_points,
         check_pattern(c, int32_t(m), d_cp.p, d_ri.p, false);
         KernelTimer t(c);
         Triangles tr;
-        voronoi_triangles(c, int32_t(m), d_cpts.p, d_cp.p, d_ri.p, d_va.p, tr);
+        voronoi_triangles(c, int32_t(m), cnnz, d_cpts.p, d_cp.p, d_ri.p, d_va.p, tr);
         DeviceCsr P;
         gmg_prolongation_stats st{};
         Error pending{GMG_OK, ""};

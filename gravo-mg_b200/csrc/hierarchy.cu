@@ -102,12 +102,15 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
         const double* val = h->fine_val.p;
         DevBuf<double> len_buf;          // Euclidean lengths of the current level's entries (levels >= 1)
         DevBuf<double> d_radius(c, 1);
+        DevBuf<unsigned long long> d_degsq(c, 1);
+        StageStatus status;              // device-side flags and counters, fetched once per level
 
         for (int lvl = 0; lvl + 1 < opt->levels; ++lvl) {
             if (n == 0) break;
             std::unique_ptr<Level> L(new Level());
             L->info.n = n; L->info.nnz = nnz;
             StageClock clk(c);
+            status.begin(c);
             clk.mark();
             // stage 0: lengths (the sampler and the sweep use geometric lengths, never stored values)
             const double* len;
@@ -115,37 +118,39 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             else { len_buf.alloc(c, nnz); edge_lengths(c, n, colptr, rowidx, pts, len_buf.p); len = len_buf.p; }
             double radius = 0.0;
             const bool overridden = opt->radius_override && opt->radius_override[lvl] > 0.0;
-            if (overridden) radius = opt->radius_override[lvl];
-            else {
+            // one host round trip for the radius and the sampler's list bound
+            d_degsq.zero();
+            degree_square_sum(c, n, colptr, d_degsq.p);
+            unsigned long long degsq = 0;
+            double mean = 0.0;
+            if (!overridden) {
                 // averageEdgeLength over extractEdges(matrix): every stored entry, divisor nnz - n
                 double denom = double(nnz - n);
                 if (opt->radius_policy == 1) denom = double(lvl == 0 ? nnz - n : nnz);
                 mean_length_dev(c, nnz, len, denom, d_radius.p);
-                double mean = 0.0;
                 d_radius.download(&mean, 1);
-                sync(c);
-                radius = std::cbrt(opt->ratio) * mean;
             }
+            d_degsq.download(&degsq, 1);
+            sync(c);
+            radius = overridden ? opt->radius_override[lvl] : std::cbrt(opt->ratio) * mean;
             L->info.radius = radius;
             clk.mark();
             // stage 1: fastDiscSample
             SamplerStats ss{};
             const int32_t m = disc_sample(c, n, colptr, rowidx, len, radius, opt->sampler_mode, opt->seed + uint64_t(lvl),
-                                          L->samples, &ss);
+                                          L->samples, &ss, int64_t(degsq) + nnz);
             L->info.m = m; L->info.sampler_rounds = ss.rounds;
             clk.mark();
             // stage 2: assignParents
             L->parents.alloc(c, n);
-            ParentStats ps{};
-            assign_parents_dev(c, n, colptr, rowidx, len, m, L->samples.p, L->parents.p, &ps);
-            L->info.parent_rounds = ps.rounds;
+            assign_parents_dev(c, n, colptr, rowidx, len, m, L->samples.p, L->parents.p, nullptr, &status);
             clk.mark();
             // stage 3: cluster CSR
             Clusters cl;
             build_clusters(c, n, m, L->parents.p, cl);
             clk.mark();
             // stage 4: extractCoarseEdges
-            coarse_edges(c, n, colptr, rowidx, val, m, L->parents.p, cl, L->coarse);
+            coarse_edges(c, n, nnz, colptr, rowidx, val, m, L->parents.p, cl, L->coarse, &status);
             L->info.nnz_c = L->coarse.nnz;
             clk.mark();
             // stage 5: coarseFromMeanOfFineChildren
@@ -153,14 +158,22 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             coarse_points(c, n, pts, colptr, rowidx, m, cl, L->coarse_pts.p);
             clk.mark();
             // stage 6: constructVoronoiTriangles
-            voronoi_triangles(c, m, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->coarse.val.p, L->tri);
+            voronoi_triangles(c, m, L->coarse.nnz, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->coarse.val.p,
+                              L->tri);
             L->info.T = L->tri.T;
             clk.mark();
             // stage 7: constructProlongation
             prolongation(c, n, pts, m, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->parents.p, L->tri,
-                         opt->weighting, L->P, &L->info.stats);
-            L->info.nnz_p = L->P.nnz;
+                         opt->weighting, L->P, nullptr, &status);
             clk.mark();
+            // the level's deferred checks and counters: one round trip
+            status.fetch(c);
+            L->info.parent_rounds = status.host[StageStatus::kParentRounds];
+            finish_prolongation(status, L->P, &L->info.stats);
+            L->info.nnz_p = L->P.nnz;
+            status.raise_parents();
+            status.raise_coarse();
+            status.raise_prolong(n);
             // stage 8: Galerkin coarse operator
             if (opt->build_galerkin) {
                 galerkin(c, a_n, a_colptr, a_rowidx, a_val, L->P, L->Ac);

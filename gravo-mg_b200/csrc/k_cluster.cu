@@ -126,11 +126,13 @@ __device__ __forceinline__ bool coarse_row(const CoarseArgs& a, int32_t P, int t
     if (THREADS == 32) __syncwarp(); else __syncthreads();
     bool nonpos = false;
     const int32_t cb = __ldg(a.cptr + P), ce = __ldg(a.cptr + P + 1);
-    for (int32_t ci = cb; ci < ce; ++ci) {
+    // 8 lanes per child (mesh columns hold ~7 entries), THREADS/8 children in flight
+    constexpr int kSub = 8;
+    for (int32_t ci = cb + tid / kSub; ci < ce; ci += THREADS / kSub) {
         const int32_t f = __ldg(a.child + ci);
         const double base = __ldg(a.q0 + f);
         const int32_t b = __ldg(a.colptr + f), e = __ldg(a.colptr + f + 1);
-        for (int32_t k = b + tid; k < e; k += THREADS) {
+        for (int32_t k = b + tid % kSub; k < e; k += kSub) {
             const int32_t Q = __ldg(a.parents + __ldg(a.rowidx + k));
             if (Q == P) continue;                                                 // :148
             const double t = base + __ldg(a.val + k);                            // :150-151
@@ -201,14 +203,15 @@ __global__ void __launch_bounds__(kBlock) coarse_rows_warp_kernel(CoarseArgs a) 
     }
 }
 
-__global__ void __launch_bounds__(kBlock) coarse_rows_block_kernel(CoarseArgs a, int32_t n_overflow) {
+__global__ void __launch_bounds__(kBlock) coarse_rows_block_kernel(CoarseArgs a, int32_t* __restrict__ hard_overflow) {
     __shared__ int32_t keys[kBlockSlots];
     __shared__ unsigned long long vals[kBlockSlots];
     __shared__ int32_t scount;
+    const int32_t n_overflow = a.flags[1];
     for (int32_t o = blockIdx.x; o < n_overflow; o += gridDim.x) {
         const int32_t P = a.overflow[o];
         if (!coarse_row<kBlock, kBlockSlots>(a, P, threadIdx.x, keys, vals, &scount)) {
-            if (threadIdx.x == 0) a.flags[2] = 1;
+            if (threadIdx.x == 0) *hard_overflow = 1;
         }
         __syncthreads();
     }
@@ -217,7 +220,7 @@ __global__ void __launch_bounds__(kBlock) coarse_rows_block_kernel(CoarseArgs a,
 // Exact in-order fold of the reference (:156-164) into the already-known pattern of row P.
 __global__ void __launch_bounds__(kBlock) coarse_rows_strict_kernel(CoarseArgs a) {
     const int64_t P = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (P >= a.m) return;
+    if (P >= a.m || a.flags[0] == 0) return;                      // only when some candidate was not > 0
     const int32_t off = a.boff[P], K = a.cnt[P];
     for (int32_t i = 0; i < K; ++i) a.st[off + i] = 0.0;          // absent == reads as 0
     for (int32_t ci = a.cptr[P]; ci < a.cptr[P + 1]; ++ci) {      // children ascending = fine ascending
@@ -243,7 +246,7 @@ __global__ void __launch_bounds__(kBlock) coarse_gather_kernel(int32_t m, const 
                                                                const int32_t* __restrict__ colptr_out,
                                                                int32_t* __restrict__ rowidx_out,
                                                                double* __restrict__ val_out,
-                                                               int32_t* __restrict__ flags) {
+                                                               int32_t* __restrict__ asym_flag) {
     constexpr int G = 8;
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t P = int32_t(gid / G);
@@ -256,12 +259,12 @@ __global__ void __launch_bounds__(kBlock) coarse_gather_kernel(int32_t m, const 
         const int32_t pos = lower_bound_i32(sQ, qoff, qoff + qK, P);
         rowidx_out[dst + e] = Q;
         if (pos < qoff + qK && sQ[pos] == P) val_out[dst + e] = st[pos];
-        else { val_out[dst + e] = 0.0; flags[3] = 1; }
+        else { val_out[dst + e] = 0.0; *asym_flag = 1; }
     }
 }
 
-void coarse_edges(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val, int32_t m,
-                  const int32_t* parents, const Clusters& cl, DeviceCsc& out) {
+void coarse_edges(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                  int32_t m, const int32_t* parents, const Clusters& cl, DeviceCsc& out, StageStatus* status) {
     out.n = m;
     out.colptr.alloc(c, int64_t(m) + 1);
     if (m == 0 || n == 0) {
@@ -269,6 +272,9 @@ void coarse_edges(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* r
         return;
     }
     GMG_REQUIRE(m <= n, GMG_ERR_INVALID, "extractCoarseEdges: more coarse points than fine points");
+    StageStatus local;
+    StageStatus* st = status ? status : &local;
+    if (!status) local.begin(c);
     DevBuf<double> q0(c, n);
     GMG_LAUNCH(c, quirk_term_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, rowidx, val, parents, q0.p);
     DevBuf<int32_t> degsum(c, int64_t(m) + 1), boff(c, int64_t(m) + 1), cnt(c, int64_t(m) + 1), flags(c, 4),
@@ -276,34 +282,33 @@ void coarse_edges(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* r
     degsum.zero(); cnt.zero(); flags.zero();
     GMG_LAUNCH(c, cluster_degree_kernel, div_up(m, kBlock), kBlock, 0, m, cl.ptr.p, cl.child.p, colptr, degsum.p);
     DevBuf<int64_t> total(c, 1);
-    exclusive_scan_i32(c, degsum.p, boff.p, int64_t(m) + 1, total.p);
-    int64_t bound = 0;
-    total.download(&bound, 1);
-    sync(c);
-    DevBuf<int32_t> sQ(c, bound);
-    DevBuf<double> st(c, bound);
-    CoarseArgs a{m, cl.ptr.p, cl.child.p, colptr, rowidx, val, parents, q0.p, boff.p, sQ.p, st.p, cnt.p, flags.p, overflow.p};
+    exclusive_scan_i32(c, degsum.p, boff.p, int64_t(m) + 1, nullptr);
+    // every fine vertex belongs to exactly one cluster, so the scratch rows hold exactly nnz candidates
+    DevBuf<int32_t> sQ(c, nnz);
+    DevBuf<double> st_val(c, nnz);
+    CoarseArgs a{m, cl.ptr.p, cl.child.p, colptr, rowidx, val, parents, q0.p, boff.p, sQ.p, st_val.p, cnt.p, flags.p, overflow.p};
     GMG_LAUNCH(c, coarse_rows_warp_kernel, div_up(m, kBlock / 32), kBlock, 0, a);
-    int32_t hf[4];
-    flags.download(hf, 4);
-    sync(c);
-    if (hf[1] > 0) {
-        GMG_LAUNCH(c, coarse_rows_block_kernel, hf[1] < 4 * c->sm_count ? hf[1] : 4 * c->sm_count, kBlock, 0, a, hf[1]);
-        flags.download(hf, 4);
-        sync(c);
-        GMG_REQUIRE(hf[2] == 0, GMG_ERR_INVALID, "extractCoarseEdges: a cluster has more than 1536 distinct coarse neighbours");
-    }
-    if (hf[0]) GMG_LAUNCH(c, coarse_rows_strict_kernel, div_up(m, kBlock), kBlock, 0, a);
+    // The two repair passes read their trigger on the device and return at once when it is clear, so the
+    // host never waits for the flags: oversized neighbourhoods (flags[1] clusters), and the in-order fold
+    // for a candidate that is not > 0 (flags[0]).
+    GMG_LAUNCH(c, coarse_rows_block_kernel, 2 * c->sm_count, kBlock, 0, a, st->dev.p + StageStatus::kCoarseHardOverflow);
+    GMG_LAUNCH(c, coarse_rows_strict_kernel, div_up(m, kBlock), kBlock, 0, a);
     exclusive_scan_i32(c, cnt.p, out.colptr.p, int64_t(m) + 1, total.p);
     total.download(&out.nnz, 1);
     sync(c);
     out.rowidx.alloc(c, out.nnz);
     out.val.alloc(c, out.nnz);
-    GMG_LAUNCH(c, coarse_gather_kernel, div_up(int64_t(m) * 8, kBlock), kBlock, 0, m, boff.p, cnt.p, sQ.p, st.p,
-               out.colptr.p, out.rowidx.p, out.val.p, flags.p);
-    flags.download(hf, 4);
-    sync(c);
-    GMG_REQUIRE(hf[3] == 0, GMG_ERR_ASYMMETRIC, "extractCoarseEdges: the fine pattern is not symmetric");
+    GMG_LAUNCH(c, coarse_gather_kernel, div_up(int64_t(m) * 8, kBlock), kBlock, 0, m, boff.p, cnt.p, sQ.p, st_val.p,
+               out.colptr.p, out.rowidx.p, out.val.p, st->dev.p + StageStatus::kCoarseAsym);
+    if (status) return;
+    local.fetch(c);
+    local.raise_coarse();
+}
+
+void StageStatus::raise_coarse() const {
+    GMG_REQUIRE(host[kCoarseHardOverflow] == 0, GMG_ERR_INVALID,
+                "extractCoarseEdges: a cluster has more than 1536 distinct coarse neighbours");
+    GMG_REQUIRE(host[kCoarseAsym] == 0, GMG_ERR_ASYMMETRIC, "extractCoarseEdges: the fine pattern is not symmetric");
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -147,7 +147,9 @@ __global__ void __launch_bounds__(kBlock) parents_resolve_kernel(int32_t n, cons
     const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (i >= n) return;
     int32_t u = int32_t(i);
-    for (;;) {                       // dist strictly decreases along pred, so this walk ends at a root
+    // dist strictly decreases along pred, so this walk ends at a root; the step cap only matters when a
+    // zero-length edge (reported separately) has closed a cycle
+    for (int32_t steps = 0; steps < n; ++steps) {
         const int32_t p = pred[u];
         if (p == u) break;
         u = p;
@@ -157,13 +159,17 @@ __global__ void __launch_bounds__(kBlock) parents_resolve_kernel(int32_t n, cons
 }
 
 void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
-                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats) {
+                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats,
+                        StageStatus* status) {
     if (stats) stats->rounds = 0;
     if (n == 0) return;
+    StageStatus local;
+    StageStatus* st = status ? status : &local;
+    if (!status) local.begin(c);
+    int32_t* flags = st->dev.p + StageStatus::kZeroEdge;     // [0] zero-length edge, [1] no offerer
     DevBuf<unsigned long long> dist(c, n);
-    DevBuf<int32_t> stamp(c, n), srcid(c, n), counters(c, 4), pred(c, n), flags(c, 2);
+    DevBuf<int32_t> stamp(c, n), srcid(c, n), counters(c, 4), pred(c, n);
     counters.zero();
-    flags.zero();
     GMG_LAUNCH(c, parents_init_kernel, div_up(n, kBlock), kBlock, 0, n, dist.p, stamp.p, srcid.p);
     if (m > 0) {
         GMG_LAUNCH(c, parents_seed_kernel, div_up(m, kBlock), kBlock, 0, m, samples, dist.p, srcid.p, stamp.p);
@@ -179,17 +185,21 @@ void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int3
         ++c->launches;
     }
     GMG_LAUNCH(c, parents_pred_kernel, div_up(int64_t(n) * kPLanes, kBlock), kBlock, 0, n, colptr, rowidx, len, dist.p,
-               srcid.p, pred.p, flags.p);
+               srcid.p, pred.p, flags);
     GMG_LAUNCH(c, parents_resolve_kernel, div_up(n, kBlock), kBlock, 0, n, pred.p, srcid.p, parents);
-    int32_t hf[2], hc[4];
-    flags.download(hf, 2);
-    counters.download(hc, 4);
-    sync(c);
-    if (stats) stats->rounds = hc[3];
-    GMG_REQUIRE(hf[0] == 0, GMG_ERR_ZERO_LENGTH_EDGE,
+    GMG_CUDA(cudaMemcpyAsync(st->dev.p + StageStatus::kParentRounds, counters.p + 3, sizeof(int32_t),
+                             cudaMemcpyDeviceToDevice, c->stream));
+    if (status) return;                       // the caller fetches and checks once per level
+    local.fetch(c);
+    if (stats) stats->rounds = local.host[StageStatus::kParentRounds];
+    local.raise_parents();
+}
+
+void StageStatus::raise_parents() const {
+    GMG_REQUIRE(host[kZeroEdge] == 0, GMG_ERR_ZERO_LENGTH_EDGE,
                 "assignParents: an edge does not increase the path length (duplicate points?); "
                 "the reference's heap order is then dynamic and is not reproduced");
-    GMG_REQUIRE(hf[1] == 0, GMG_ERR_ASYMMETRIC, "assignParents: a reached vertex has no offering neighbour (asymmetric pattern)");
+    GMG_REQUIRE(host[kNoOffer] == 0, GMG_ERR_ASYMMETRIC, "assignParents: a reached vertex has no offering neighbour (asymmetric pattern)");
 }
 
 }  // namespace gmg

@@ -208,36 +208,46 @@ __global__ void __launch_bounds__(kBlock) prolong_compact_kernel(int32_t n, cons
 
 void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, const double* coarse_pts,
                   const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
-                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats) {
+                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status) {
     GMG_REQUIRE(weighting >= 0 && weighting <= 2, GMG_ERR_INVALID, "unknown weighting scheme");
+    StageStatus local;
+    StageStatus* st = status ? status : &local;
+    if (!status) local.begin(c);
     P.rows = n; P.cols = m;
     P.rowptr.alloc(c, int64_t(n) + 1);
     DevBuf<int32_t> row_col(c, 3 * int64_t(n));
     DevBuf<double> row_val(c, 3 * int64_t(n));
-    DevBuf<unsigned long long> dstats(c, 4);
-    DevBuf<int64_t> total(c, 1);
-    dstats.zero();
+    unsigned long long* dstats = reinterpret_cast<unsigned long long*>(st->dev.p + StageStatus::kProlongStats);
+    int64_t* total = reinterpret_cast<int64_t*>(st->dev.p + StageStatus::kProlongNnz);
     P.rowptr.zero();
     ProlongArgs a{n, m, fine_pts, coarse_pts, c_colptr, c_rowidx, parents, tr.fan_ptr.p, tr.fan_tri.p, tr.fan_o1.p,
-                  tr.fan_o2.p, tr.normal.p, weighting, P.rowptr.p, row_col.p, row_val.p, dstats.p};
+                  tr.fan_o2.p, tr.normal.p, weighting, P.rowptr.p, row_col.p, row_val.p, dstats};
     if (n > 0) GMG_LAUNCH(c, prolong_rows_kernel, div_up(n, kBlock), kBlock, 0, a);
-    exclusive_scan_i32(c, P.rowptr.p, P.rowptr.p, int64_t(n) + 1, total.p);
-    unsigned long long hs[4];
-    total.download(&P.nnz, 1);
-    dstats.download(hs, 4);
-    sync(c);
-    P.colidx.alloc(c, P.nnz);
-    P.val.alloc(c, P.nnz);
+    exclusive_scan_i32(c, P.rowptr.p, P.rowptr.p, int64_t(n) + 1, total);
+    // rows hold at most three entries: the arrays are sized 3n, so the host need not know nnz yet
+    P.colidx.alloc(c, 3 * int64_t(n));
+    P.val.alloc(c, 3 * int64_t(n));
     if (n > 0) GMG_LAUNCH(c, prolong_compact_kernel, div_up(n, kBlock), kBlock, 0, n, P.rowptr.p, row_col.p, row_val.p,
                           P.colidx.p, P.val.p);
+    if (status) return;
+    local.fetch(c);
+    finish_prolongation(local, P, stats);
+    local.raise_prolong(n);
+}
+
+void finish_prolongation(const StageStatus& status, DeviceCsr& P, gmg_prolongation_stats* stats) {
+    P.nnz = status.host_i64(StageStatus::kProlongNnz);
     if (stats) {
-        stats->no_triangle_found = int64_t(hs[0]);
-        stats->edges_found = int64_t(hs[1]);
-        stats->fallback_count = int64_t(hs[2]);
+        stats->no_triangle_found = status.host_i64(StageStatus::kProlongStats);
+        stats->edges_found = status.host_i64(StageStatus::kProlongStats + 2);
+        stats->fallback_count = status.host_i64(StageStatus::kProlongStats + 4);
     }
-    GMG_REQUIRE(hs[3] == 0, GMG_ERR_INVALID,
+}
+
+void StageStatus::raise_prolong(int64_t n) const {
+    GMG_REQUIRE(host_i64(kProlongStats + 6) == 0, GMG_ERR_INVALID,
                 "constructProlongation: a coarse point with degree >= 2 has fewer than two non-self neighbours");
-    GMG_REQUIRE(n == 0 || float(hs[2]) / float(n) < 0.5f, GMG_ERR_FALLBACK_RATIO,
+    GMG_REQUIRE(n == 0 || float(host_i64(kProlongStats + 4)) / float(n) < 0.5f, GMG_ERR_FALLBACK_RATIO,
                 "constructProlongation: more than half of the fine points fell back to three-nearest weights");
 }
 

@@ -251,6 +251,10 @@ __global__ void __launch_bounds__(kBlock) degree_square_kernel(int32_t n, const 
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
 }
 
+void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned long long* d_out) {
+    if (n > 0) GMG_LAUNCH(c, degree_square_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, d_out);
+}
+
 template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a) {
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
     int per_sm = 0;
@@ -263,20 +267,24 @@ template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a) {
 }
 
 int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
-                    double radius, int mode, uint64_t seed, DevBuf<int32_t>& selection, SamplerStats* stats) {
+                    double radius, int mode, uint64_t seed, DevBuf<int32_t>& selection, SamplerStats* stats,
+                    int64_t path_bound) {
     if (stats) stats->rounds = 0;
     if (n == 0) { selection.alloc(c, 0); return 0; }
     GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL, GMG_ERR_INVALID, "unknown sampler mode");
     // bound on the later-path lists: every path has a mirror image, exactly one of the two is "later"
     DevBuf<unsigned long long> cursor(c, 3);          // [0] list cursor, [1] sum deg^2, [2] ticket counter
     cursor.zero();
-    GMG_LAUNCH(c, degree_square_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, cursor.p + 1);
-    unsigned long long hsq[2];
-    int32_t nnz = 0;
-    cursor.download(hsq, 2);
-    GMG_CUDA(cudaMemcpyAsync(&nnz, colptr + n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-    sync(c);
-    const int64_t list_cap = int64_t((hsq[1] + (unsigned long long)nnz) / 2 + 1);
+    if (path_bound < 0) {
+        degree_square_sum(c, n, colptr, cursor.p + 1);
+        unsigned long long hsq[2];
+        int32_t nnz = 0;
+        cursor.download(hsq, 2);
+        GMG_CUDA(cudaMemcpyAsync(&nnz, colptr + n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        sync(c);
+        path_bound = int64_t(hsq[1]) + nnz;
+    }
+    const int64_t list_cap = path_bound / 2 + 1;
     DevBuf<int32_t> state(c, n), cnt(c, n), lcnt(c, n), lst(c, list_cap);
     DevBuf<long long> lptr(c, n);
     const Order order = make_order(n, seed);

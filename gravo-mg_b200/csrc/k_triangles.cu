@@ -98,12 +98,10 @@ __global__ void __launch_bounds__(kBlock) fan_finish_kernel(int32_t m, const int
     }
 }
 
-void voronoi_triangles(gmg_ctx* c, int32_t m, const double* pts, const int32_t* colptr, const int32_t* rowidx,
-                       const double* val, Triangles& out) {
+void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, const int32_t* colptr,
+                       const int32_t* rowidx, const double* val, Triangles& out) {
     out.fan_ptr.alloc(c, int64_t(m) + 1);
     out.T = 0;
-    int32_t nnz = 0;
-    if (m > 0) { GMG_CUDA(cudaMemcpyAsync(&nnz, colptr + m, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream)); sync(c); }
     if (m == 0 || nnz == 0) {
         out.fan_ptr.zero();
         out.tri.alloc(c, 0); out.normal.alloc(c, 0); out.fan_tri.alloc(c, 0); out.fan_o1.alloc(c, 0); out.fan_o2.alloc(c, 0);

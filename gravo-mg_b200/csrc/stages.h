@@ -2,6 +2,8 @@
 // hierarchy builder (hierarchy.cu) are both thin sequences of these calls.
 #pragma once
 
+#include <cstring>
+
 #include "common.cuh"
 
 namespace gmg {
@@ -16,17 +18,39 @@ void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n
 void mean_length_dev(gmg_ctx* c, int64_t nnz, const double* len, double denom, double* d_out);
 void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric);
 
+// Device status block that a stage writes INSTEAD of synchronising with the host; the hierarchy builder
+// fetches it once per level. A stage called without one (the per-function C ABI) uses a private block
+// and checks it before returning, which is the old behaviour.
+struct StageStatus {
+    enum : int { kZeroEdge = 0, kNoOffer = 1, kParentRounds = 2, kCoarseHardOverflow = 3, kCoarseAsym = 4,
+                 kProlongStats = 8 /* 4 x uint64 */, kProlongNnz = 16 /* int64 */, kWords = 32 };
+    DevBuf<int32_t> dev;
+    int32_t host[kWords] = {0};
+    void begin(gmg_ctx* c) { if (!dev.p) dev.alloc(c, kWords); dev.zero(); }
+    void fetch(gmg_ctx* c) { dev.download(host, kWords); sync(c); }
+    int64_t host_i64(int word) const { int64_t v; memcpy(&v, host + word, sizeof v); return v; }
+    void raise_parents() const;
+    void raise_coarse() const;
+    void raise_prolong(int64_t n) const;
+};
+
 // ---- k_sampler.cu -----------------------------------------------------------------------------
 // Greedy disc sampling in priority order (index order = the reference's set). `len` holds the
 // Euclidean length of every stored entry. Returns m; selection receives ascending fine indices.
 struct SamplerStats { int rounds; };
+// `path_bound` = nnz + sum over columns of deg^2 when the caller already knows it (saves a host round
+// trip), or < 0 to have it computed here.
 int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
-                    double radius, int mode, uint64_t seed, DevBuf<int32_t>& selection, SamplerStats* stats);
+                    double radius, int mode, uint64_t seed, DevBuf<int32_t>& selection, SamplerStats* stats,
+                    int64_t path_bound = -1);
+// *d_out (device) += sum over columns of deg^2
+void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned long long* d_out);
 
 // ---- k_parents.cu -----------------------------------------------------------------------------
 struct ParentStats { int rounds; };
 void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
-                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats);
+                        int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats,
+                        StageStatus* status = nullptr);
 
 // ---- k_cluster.cu -----------------------------------------------------------------------------
 struct Clusters {
@@ -41,8 +65,8 @@ struct DeviceCsc {
     DevBuf<int32_t> colptr, rowidx;
     DevBuf<double> val;
 };
-void coarse_edges(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val, int32_t m,
-                  const int32_t* parents, const Clusters& cl, DeviceCsc& out);
+void coarse_edges(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                  int32_t m, const int32_t* parents, const Clusters& cl, DeviceCsc& out, StageStatus* status = nullptr);
 void coarse_points(gmg_ctx* c, int32_t n, const double* pts, const int32_t* colptr, const int32_t* rowidx, int32_t m,
                    const Clusters& cl, double* out_pts);
 
@@ -56,8 +80,8 @@ struct Triangles {
     DevBuf<int32_t> fan_o1;   // 3T: second vertex after rotating the owner to the front
     DevBuf<int32_t> fan_o2;   // 3T: third vertex after rotation
 };
-void voronoi_triangles(gmg_ctx* c, int32_t m, const double* pts, const int32_t* colptr, const int32_t* rowidx,
-                       const double* val, Triangles& out);
+void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, const int32_t* colptr,
+                       const int32_t* rowidx, const double* val, Triangles& out);
 
 // ---- k_prolong.cu -----------------------------------------------------------------------------
 struct DeviceCsr {
@@ -68,7 +92,9 @@ struct DeviceCsr {
 };
 void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, const double* coarse_pts,
                   const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
-                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats);
+                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status = nullptr);
+// With a StageStatus, P.nnz and the counters are only known after status->fetch(): this fills them in.
+void finish_prolongation(const StageStatus& status, DeviceCsr& P, gmg_prolongation_stats* stats);
 void projected_points_dev(gmg_ctx* c, int32_t n, int32_t m, const int32_t* rowptr, const int32_t* colidx,
                           const double* val, const double* coarse_pts, double* out_pts);
 
