@@ -89,19 +89,20 @@ __global__ void __launch_bounds__(kBlock) quirk_term_kernel(int32_t n, const int
     q0[f] = (pos < e && __ldg(rowidx + pos) == int32_t(f)) ? __ldg(val + pos) : 0.0;
 }
 
-__global__ void __launch_bounds__(kBlock) cluster_degree_kernel(int32_t m, const int32_t* __restrict__ cptr,
+// degsum[P - p_lo] for the clusters [p_lo, p_hi)
+__global__ void __launch_bounds__(kBlock) cluster_degree_kernel(int32_t p_lo, int32_t p_hi, const int32_t* __restrict__ cptr,
                                                                 const int32_t* __restrict__ child,
                                                                 const int32_t* __restrict__ colptr,
                                                                 int32_t* __restrict__ degsum) {
-    const int64_t P = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (P >= m) return;
+    const int64_t P = int64_t(p_lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (P >= p_hi) return;
     int32_t s = 0;
     for (int32_t i = cptr[P]; i < cptr[P + 1]; ++i) { const int32_t f = child[i]; s += colptr[f + 1] - colptr[f]; }
-    degsum[P] = s;
+    degsum[P - p_lo] = s;
 }
 
 struct CoarseArgs {
-    int32_t m;
+    int32_t p_lo, p_hi;       // clusters handled by this call (all of them, or the rank's share)
     const int32_t* cptr;
     const int32_t* child;
     const int32_t* colptr;
@@ -109,7 +110,7 @@ struct CoarseArgs {
     const double* val;
     const int32_t* parents;
     const double* q0;
-    const int32_t* boff;      // scratch offset of row P
+    const int32_t* boff;      // scratch offset of row P (pointer pre-shifted so that boff[P] is valid on [p_lo, p_hi])
     int32_t* sQ;              // scratch: sorted neighbour clusters of row P
     double* st;               // scratch: min t per neighbour
     int32_t* cnt;             // distinct neighbours of row P
@@ -196,8 +197,8 @@ __global__ void __launch_bounds__(kBlock) coarse_rows_warp_kernel(CoarseArgs a) 
     __shared__ unsigned long long vals[kBlock / 32][kWarpSlots];
     __shared__ int32_t scount[kBlock / 32];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t P = int64_t(blockIdx.x) * (kBlock / 32) + w;
-    if (P >= a.m) return;
+    const int64_t P = int64_t(a.p_lo) + int64_t(blockIdx.x) * (kBlock / 32) + w;
+    if (P >= a.p_hi) return;
     if (!coarse_row<32, kWarpSlots>(a, int32_t(P), lane, keys[w], vals[w], &scount[w])) {
         if (lane == 0) { a.cnt[P] = 0; a.overflow[atomicAdd(a.flags + 1, 1)] = int32_t(P); }
     }
@@ -219,8 +220,8 @@ __global__ void __launch_bounds__(kBlock) coarse_rows_block_kernel(CoarseArgs a,
 
 // Exact in-order fold of the reference (:156-164) into the already-known pattern of row P.
 __global__ void __launch_bounds__(kBlock) coarse_rows_strict_kernel(CoarseArgs a) {
-    const int64_t P = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (P >= a.m || a.flags[0] == 0) return;                      // only when some candidate was not > 0
+    const int64_t P = int64_t(a.p_lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (P >= a.p_hi || a.flags[0] == 0) return;                   // only when some candidate was not > 0
     const int32_t off = a.boff[P], K = a.cnt[P];
     for (int32_t i = 0; i < K; ++i) a.st[off + i] = 0.0;          // absent == reads as 0
     for (int32_t ci = a.cptr[P]; ci < a.cptr[P + 1]; ++ci) {      // children ascending = fine ascending
@@ -263,11 +264,59 @@ __global__ void __launch_bounds__(kBlock) coarse_gather_kernel(int32_t m, const 
     }
 }
 
+// Rows [p_lo, p_hi) of the coarse matrix into degree-bounded scratch segments: out.cnt[P] entries at
+// out.boff[P - p_lo], sorted by neighbour cluster.
+void coarse_rows_range(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                       int32_t p_lo, int32_t p_hi, const int32_t* parents, const Clusters& cl, int32_t* cnt,
+                       CoarseRows& out, int32_t* d_hard_overflow) {
+    const int32_t own = p_hi - p_lo;
+    out.p_lo = p_lo; out.p_hi = p_hi;
+    out.boff.alloc(c, int64_t(own) + 1);
+    if (own <= 0) { out.sQ.alloc(c, 0); out.st.alloc(c, 0); out.bound = 0; return; }
+    DevBuf<double> q0(c, n);
+    GMG_LAUNCH(c, quirk_term_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, rowidx, val, parents, q0.p);
+    DevBuf<int32_t> degsum(c, int64_t(own) + 1), flags(c, 4), overflow(c, own);
+    degsum.zero(); flags.zero();
+    GMG_CUDA(cudaMemsetAsync(cnt + p_lo, 0, sizeof(int32_t) * size_t(own), c->stream));
+    GMG_LAUNCH(c, cluster_degree_kernel, div_up(own, kBlock), kBlock, 0, p_lo, p_hi, cl.ptr.p, cl.child.p, colptr, degsum.p);
+    DevBuf<int64_t> total(c, 1);
+    exclusive_scan_i32(c, degsum.p, out.boff.p, int64_t(own) + 1, total.p);
+    if (out.bound < 0) {                      // caller does not know the number of candidates
+        total.download(&out.bound, 1);
+        sync(c);
+    }
+    out.sQ.alloc(c, out.bound);
+    out.st.alloc(c, out.bound);
+    CoarseArgs a{p_lo, p_hi, cl.ptr.p, cl.child.p, colptr, rowidx, val, parents, q0.p, out.boff.p - p_lo, out.sQ.p, out.st.p,
+                 cnt, flags.p, overflow.p};
+    GMG_LAUNCH(c, coarse_rows_warp_kernel, div_up(own, kBlock / 32), kBlock, 0, a);
+    // The two repair passes read their trigger on the device and return at once when it is clear, so the
+    // host never waits for the flags: oversized neighbourhoods (flags[1] clusters), and the in-order fold
+    // for a candidate that is not > 0 (flags[0]).
+    GMG_LAUNCH(c, coarse_rows_block_kernel, 2 * c->sm_count, kBlock, 0, a, d_hard_overflow);
+    GMG_LAUNCH(c, coarse_rows_strict_kernel, div_up(own, kBlock), kBlock, 0, a);
+}
+
+// Column-major coarse matrix from ALL rows: rows of P at boff[P] with cnt[P] entries each.
+void coarse_assemble(gmg_ctx* c, int32_t m, const int32_t* boff, const int32_t* cnt, const int32_t* sQ, const double* st,
+                     DeviceCsc& out, int32_t* d_asym) {
+    out.n = m;
+    out.colptr.alloc(c, int64_t(m) + 1);
+    DevBuf<int64_t> total(c, 1);
+    exclusive_scan_i32(c, cnt, out.colptr.p, int64_t(m) + 1, total.p);
+    total.download(&out.nnz, 1);
+    sync(c);
+    out.rowidx.alloc(c, out.nnz);
+    out.val.alloc(c, out.nnz);
+    GMG_LAUNCH(c, coarse_gather_kernel, div_up(int64_t(m) * 8, kBlock), kBlock, 0, m, boff, cnt, sQ, st, out.colptr.p,
+               out.rowidx.p, out.val.p, d_asym);
+}
+
 void coarse_edges(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const int32_t* rowidx, const double* val,
                   int32_t m, const int32_t* parents, const Clusters& cl, DeviceCsc& out, StageStatus* status) {
     out.n = m;
-    out.colptr.alloc(c, int64_t(m) + 1);
     if (m == 0 || n == 0) {
+        out.colptr.alloc(c, int64_t(m) + 1);
         out.colptr.zero(); out.rowidx.alloc(c, 0); out.val.alloc(c, 0); out.nnz = 0;
         return;
     }
@@ -275,31 +324,12 @@ void coarse_edges(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, con
     StageStatus local;
     StageStatus* st = status ? status : &local;
     if (!status) local.begin(c);
-    DevBuf<double> q0(c, n);
-    GMG_LAUNCH(c, quirk_term_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, rowidx, val, parents, q0.p);
-    DevBuf<int32_t> degsum(c, int64_t(m) + 1), boff(c, int64_t(m) + 1), cnt(c, int64_t(m) + 1), flags(c, 4),
-        overflow(c, m);
-    degsum.zero(); cnt.zero(); flags.zero();
-    GMG_LAUNCH(c, cluster_degree_kernel, div_up(m, kBlock), kBlock, 0, m, cl.ptr.p, cl.child.p, colptr, degsum.p);
-    DevBuf<int64_t> total(c, 1);
-    exclusive_scan_i32(c, degsum.p, boff.p, int64_t(m) + 1, nullptr);
-    // every fine vertex belongs to exactly one cluster, so the scratch rows hold exactly nnz candidates
-    DevBuf<int32_t> sQ(c, nnz);
-    DevBuf<double> st_val(c, nnz);
-    CoarseArgs a{m, cl.ptr.p, cl.child.p, colptr, rowidx, val, parents, q0.p, boff.p, sQ.p, st_val.p, cnt.p, flags.p, overflow.p};
-    GMG_LAUNCH(c, coarse_rows_warp_kernel, div_up(m, kBlock / 32), kBlock, 0, a);
-    // The two repair passes read their trigger on the device and return at once when it is clear, so the
-    // host never waits for the flags: oversized neighbourhoods (flags[1] clusters), and the in-order fold
-    // for a candidate that is not > 0 (flags[0]).
-    GMG_LAUNCH(c, coarse_rows_block_kernel, 2 * c->sm_count, kBlock, 0, a, st->dev.p + StageStatus::kCoarseHardOverflow);
-    GMG_LAUNCH(c, coarse_rows_strict_kernel, div_up(m, kBlock), kBlock, 0, a);
-    exclusive_scan_i32(c, cnt.p, out.colptr.p, int64_t(m) + 1, total.p);
-    total.download(&out.nnz, 1);
-    sync(c);
-    out.rowidx.alloc(c, out.nnz);
-    out.val.alloc(c, out.nnz);
-    GMG_LAUNCH(c, coarse_gather_kernel, div_up(int64_t(m) * 8, kBlock), kBlock, 0, m, boff.p, cnt.p, sQ.p, st_val.p,
-               out.colptr.p, out.rowidx.p, out.val.p, st->dev.p + StageStatus::kCoarseAsym);
+    DevBuf<int32_t> cnt(c, int64_t(m) + 1);
+    cnt.zero();
+    CoarseRows rows;
+    rows.bound = nnz;   // every fine vertex belongs to exactly one cluster: the scratch rows hold exactly nnz candidates
+    coarse_rows_range(c, n, colptr, rowidx, val, 0, m, parents, cl, cnt.p, rows, st->dev.p + StageStatus::kCoarseHardOverflow);
+    coarse_assemble(c, m, rows.boff.p, cnt.p, rows.sQ.p, rows.st.p, out, st->dev.p + StageStatus::kCoarseAsym);
     if (status) return;
     local.fetch(c);
     local.raise_coarse();

@@ -101,14 +101,14 @@ __global__ void __launch_bounds__(kBlock) parents_sweep_kernel(ParentArgs a) {
 }
 
 // pred[v] by the (dist, index) rule; also detects edges that do not increase the path length.
-__global__ void __launch_bounds__(kBlock) parents_pred_kernel(int32_t n, const int32_t* __restrict__ colptr,
+__global__ void __launch_bounds__(kBlock) parents_pred_kernel(int32_t lo, int32_t n, const int32_t* __restrict__ colptr,
                                                               const int32_t* __restrict__ rowidx,
                                                               const double* __restrict__ len,
                                                               const unsigned long long* __restrict__ dist,
                                                               const int32_t* __restrict__ srcid,
                                                               int32_t* __restrict__ pred, int32_t* __restrict__ flags) {
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    const int32_t v = int32_t(gid / kPLanes);
+    const int32_t v = lo + int32_t(gid / kPLanes);                  // vertices [lo, n)
     const int sub = int(gid % kPLanes);
     if (v >= n) return;
     const unsigned long long dvb = dist[v];
@@ -141,15 +141,15 @@ __global__ void __launch_bounds__(kBlock) parents_pred_kernel(int32_t n, const i
     }
 }
 
-__global__ void __launch_bounds__(kBlock) parents_resolve_kernel(int32_t n, const int32_t* __restrict__ pred,
+__global__ void __launch_bounds__(kBlock) parents_resolve_kernel(int32_t lo, int32_t n, int32_t cap, const int32_t* __restrict__ pred,
                                                                  const int32_t* __restrict__ srcid,
                                                                  int32_t* __restrict__ parents) {
-    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int64_t i = int64_t(lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;   // vertices [lo, n)
     if (i >= n) return;
     int32_t u = int32_t(i);
     // dist strictly decreases along pred, so this walk ends at a root; the step cap only matters when a
     // zero-length edge (reported separately) has closed a cycle
-    for (int32_t steps = 0; steps < n; ++steps) {
+    for (int32_t steps = 0; steps < cap; ++steps) {
         const int32_t p = pred[u];
         if (p == u) break;
         u = p;
@@ -184,9 +184,9 @@ void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int3
         GMG_CUDA(cudaLaunchCooperativeKernel((void*)parents_sweep_kernel, dim3(grid), dim3(kBlock), args, 0, c->stream));
         ++c->launches;
     }
-    GMG_LAUNCH(c, parents_pred_kernel, div_up(int64_t(n) * kPLanes, kBlock), kBlock, 0, n, colptr, rowidx, len, dist.p,
+    GMG_LAUNCH(c, parents_pred_kernel, div_up(int64_t(n) * kPLanes, kBlock), kBlock, 0, 0, n, colptr, rowidx, len, dist.p,
                srcid.p, pred.p, flags);
-    GMG_LAUNCH(c, parents_resolve_kernel, div_up(n, kBlock), kBlock, 0, n, pred.p, srcid.p, parents);
+    GMG_LAUNCH(c, parents_resolve_kernel, div_up(n, kBlock), kBlock, 0, 0, n, n, pred.p, srcid.p, parents);
     GMG_CUDA(cudaMemcpyAsync(st->dev.p + StageStatus::kParentRounds, counters.p + 3, sizeof(int32_t),
                              cudaMemcpyDeviceToDevice, c->stream));
     if (status) return;                       // the caller fetches and checks once per level
@@ -200,6 +200,82 @@ void StageStatus::raise_parents() const {
                 "assignParents: an edge does not increase the path length (duplicate points?); "
                 "the reference's heap order is then dynamic and is not reproduced");
     GMG_REQUIRE(host[kNoOffer] == 0, GMG_ERR_ASYMMETRIC, "assignParents: a reached vertex has no offering neighbour (asymmetric pattern)");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row-sharded variant. A rank may only write the vertices it owns, so the relaxation is a PULL:
+// an owned vertex whose neighbour improved in the previous round recomputes
+// min(dist[v], min_u fl(len_uv + dist[u])) over the improved neighbours -- the same rounded sums,
+// hence the same fixed point, as the push sweep above. dist (uint64 bit patterns) and the
+// "improved" bytes are replicated; the caller all-gathers the owned slices after every round.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) shard_parents_init_kernel(int32_t n, unsigned long long* __restrict__ dist,
+                                                                    uint8_t* __restrict__ changed, int32_t* __restrict__ srcid) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n) { dist[i] = kInfBits; changed[i] = 0; srcid[i] = -1; }
+}
+__global__ void __launch_bounds__(kBlock) shard_parents_seed_kernel(int32_t m, const int32_t* __restrict__ samples,
+                                                                    unsigned long long* __restrict__ dist,
+                                                                    uint8_t* __restrict__ changed, int32_t* __restrict__ srcid) {
+    const int64_t cidx = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (cidx >= m) return;
+    const int32_t v = samples[cidx];
+    dist[v] = 0ull;
+    changed[v] = 1;
+    atomicMax(srcid + v, int32_t(cidx));
+}
+__global__ void __launch_bounds__(kBlock) shard_parents_pull_kernel(int32_t lo, int32_t hi, const int32_t* __restrict__ colptr,
+                                                                    const int32_t* __restrict__ rowidx,
+                                                                    const double* __restrict__ len,
+                                                                    unsigned long long* dist,
+                                                                    const uint8_t* __restrict__ changed_in,
+                                                                    uint8_t* __restrict__ changed_out) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t v = lo + int32_t(gid / kPLanes);
+    const int sub = int(gid % kPLanes);
+    if (v >= hi) return;
+    const unsigned long long dv = *(volatile unsigned long long*)(dist + v);
+    unsigned long long best = dv;
+    const int32_t b = __ldg(colptr + v), e = __ldg(colptr + v + 1);
+    for (int32_t k = b + sub; k < e; k += kPLanes) {
+        const int32_t u = __ldg(rowidx + k);
+        if (!changed_in[u]) continue;                               // only an improved neighbour can offer less
+        const double cand = __ldg(len + k) + __longlong_as_double((long long)*(volatile unsigned long long*)(dist + u));
+        if (!(cand >= 0.0)) continue;
+        const unsigned long long cb = (unsigned long long)__double_as_longlong(cand);
+        best = cb < best ? cb : best;
+    }
+#pragma unroll
+    for (int d = kPLanes / 2; d > 0; d >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, d, kPLanes);
+        best = o < best ? o : best;
+    }
+    if (sub == 0) {
+        if (best < dv) { *(volatile unsigned long long*)(dist + v) = best; changed_out[v] = 1; }
+        else changed_out[v] = 0;
+    }
+}
+
+void shard_parents_init(gmg_ctx* c, int32_t n, int32_t m, const int32_t* samples, unsigned long long* dist,
+                        uint8_t* changed, int32_t* srcid) {
+    if (n > 0) GMG_LAUNCH(c, shard_parents_init_kernel, div_up(n, kBlock), kBlock, 0, n, dist, changed, srcid);
+    if (m > 0) GMG_LAUNCH(c, shard_parents_seed_kernel, div_up(m, kBlock), kBlock, 0, m, samples, dist, changed, srcid);
+}
+void shard_parents_pull(gmg_ctx* c, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                        const double* len, unsigned long long* dist, const uint8_t* changed_in, uint8_t* changed_out) {
+    if (hi > lo) GMG_LAUNCH(c, shard_parents_pull_kernel, div_up(int64_t(hi - lo) * kPLanes, kBlock), kBlock, 0, lo, hi,
+                            colptr, rowidx, len, dist, changed_in, changed_out);
+}
+void shard_parents_pred(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                        const double* len, const unsigned long long* dist, const int32_t* srcid, int32_t* pred,
+                        int32_t* d_flags) {
+    (void)n;
+    if (hi > lo) GMG_LAUNCH(c, parents_pred_kernel, div_up(int64_t(hi - lo) * kPLanes, kBlock), kBlock, 0, lo, hi, colptr,
+                            rowidx, len, dist, srcid, pred, d_flags);
+}
+void shard_parents_resolve(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* pred, const int32_t* srcid,
+                           int32_t* parents) {
+    if (hi > lo) GMG_LAUNCH(c, parents_resolve_kernel, div_up(hi - lo, kBlock), kBlock, 0, lo, hi, n, pred, srcid, parents);
 }
 
 }  // namespace gmg

@@ -21,6 +21,7 @@
 namespace gmg {
 
 struct ProlongArgs {
+    int32_t f_lo, f_hi;    // fine rows built by this call; row_cnt/row_col/row_val are indexed by f - f_lo
     int32_t n, m;
     const double* fp;
     const double* cp;
@@ -96,13 +97,14 @@ __device__ __forceinline__ void emit_row(const ProlongArgs& a, int32_t f, const 
         if (c[2] < c[1]) { int32_t tc = c[1]; c[1] = c[2]; c[2] = tc; double tv = v[1]; v[1] = v[2]; v[2] = tv; }
         if (c[1] < c[0]) { int32_t tc = c[0]; c[0] = c[1]; c[1] = tc; double tv = v[0]; v[0] = v[1]; v[1] = tv; }
     }
-    a.row_cnt[f] = k;
-    for (int i = 0; i < k; ++i) { a.row_col[3 * int64_t(f) + i] = c[i]; a.row_val[3 * int64_t(f) + i] = v[i]; }
+    const int64_t r = f - a.f_lo;
+    a.row_cnt[r] = k;
+    for (int i = 0; i < k; ++i) { a.row_col[3 * r + i] = c[i]; a.row_val[3 * r + i] = v[i]; }
 }
 
 __global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
-    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (gid >= a.n) return;
+    const int64_t gid = int64_t(a.f_lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (gid >= a.f_hi) return;
     const int32_t f = int32_t(gid);
     const int32_t c = __ldg(a.parents + f);
     const V3 p = ld3(a.fp, a.n, f), pc = ld3(a.cp, a.m, c);
@@ -208,8 +210,12 @@ __global__ void __launch_bounds__(kBlock) prolong_compact_kernel(int32_t n, cons
 
 void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, const double* coarse_pts,
                   const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
-                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status) {
+                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status, int32_t f_lo,
+                  int32_t f_hi) {
     GMG_REQUIRE(weighting >= 0 && weighting <= 2, GMG_ERR_INVALID, "unknown weighting scheme");
+    if (f_hi < 0) { f_lo = 0; f_hi = n; }
+    const int32_t n_all = n;                       // fine vertices of the level (stride of the point arrays)
+    n = f_hi - f_lo;                               // rows built here
     StageStatus local;
     StageStatus* st = status ? status : &local;
     if (!status) local.begin(c);
@@ -220,7 +226,7 @@ void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, cons
     unsigned long long* dstats = reinterpret_cast<unsigned long long*>(st->dev.p + StageStatus::kProlongStats);
     int64_t* total = reinterpret_cast<int64_t*>(st->dev.p + StageStatus::kProlongNnz);
     P.rowptr.zero();
-    ProlongArgs a{n, m, fine_pts, coarse_pts, c_colptr, c_rowidx, parents, tr.fan_ptr.p, tr.fan_tri.p, tr.fan_o1.p,
+    ProlongArgs a{f_lo, f_hi, n_all, m, fine_pts, coarse_pts, c_colptr, c_rowidx, parents, tr.fan_ptr.p, tr.fan_tri.p, tr.fan_o1.p,
                   tr.fan_o2.p, tr.normal.p, weighting, P.rowptr.p, row_col.p, row_val.p, dstats};
     if (n > 0) GMG_LAUNCH(c, prolong_rows_kernel, div_up(n, kBlock), kBlock, 0, a);
     exclusive_scan_i32(c, P.rowptr.p, P.rowptr.p, int64_t(n) + 1, total);

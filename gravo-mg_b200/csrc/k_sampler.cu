@@ -305,4 +305,163 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     return int32_t(m);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row-sharded variant (one rank owns the vertices [lo, hi); the state array is replicated and
+// all-gathered between rounds by the caller). The same greedy set is computed -- the
+// lexicographically-first maximal independent set under the chosen order is unique -- but by
+// PULL rounds, because a rank can only write the vertices it owns: an undecided owned vertex looks
+// at the states of its PRECEDING coverers; one IN makes it OUT, all OUT makes it IN. Rounds needed
+// = dependency depth (O(log n) in the hashed order, ~10 for an index-ordered subdivision mesh).
+// ---------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) shard_path_bound_kernel(SamplerArgs a, int32_t lo, int32_t hi,
+                                                                  unsigned long long* __restrict__ out) {
+    const int64_t i = int64_t(lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    unsigned long long v = 0;
+    if (i < hi) {
+        for (int32_t k = a.colptr[i]; k < a.colptr[i + 1]; ++k) {
+            const int32_t j = a.rowidx[k];
+            v += 1ull + (unsigned long long)(a.colptr[j + 1] - a.colptr[j]);
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, v);
+}
+
+// Lists of PRECEDING coverers of the owned vertices; owned vertices without any are IN at once.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) shard_build_kernel(SamplerArgs a, int32_t lo, int32_t hi,
+                                                             uint8_t* __restrict__ state8) {
+    __shared__ int32_t s_group[kBlock / kLanes];
+    __shared__ unsigned long long s_base;
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t i = lo + int32_t(gid / kLanes);
+    const int sub = threadIdx.x % kLanes;
+    const int g = threadIdx.x / kLanes;
+    const bool active = i < hi;
+    int32_t prev = 0;
+    uint32_t ri = 0;
+    if (active) {
+        ri = rank_of<MODE>(a, i);
+        for_each_covered(a, i, sub, [&](int32_t t) { if (rank_of<MODE>(a, t) < ri) ++prev; });
+    }
+    int32_t incl = prev;
+#pragma unroll
+    for (int d = 1; d < kLanes; d <<= 1) {
+        const int32_t t = __shfl_up_sync(0xffffffffu, incl, d, kLanes);
+        if (sub >= d) incl += t;
+    }
+    const int32_t group_total = __shfl_sync(0xffffffffu, incl, kLanes - 1, kLanes);
+    if (sub == 0) s_group[g] = group_total;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int32_t v = s_group[threadIdx.x];
+        int32_t s = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int32_t t = __shfl_up_sync(0xffffffffu, s, d);
+            if (int(threadIdx.x) >= d) s += t;
+        }
+        s_group[threadIdx.x] = s - v;
+        if (threadIdx.x == 31) s_base = atomicAdd(a.cursor, (unsigned long long)s);
+    }
+    __syncthreads();
+    if (!active) return;
+    const long long start = (long long)s_base + s_group[g];
+    int32_t* dst = a.lst + start + (incl - prev);
+    int32_t w = 0;
+    for_each_covered(a, i, sub, [&](int32_t t) { if (rank_of<MODE>(a, t) < ri) dst[w++] = t; });
+    if (sub == 0) {
+        a.lptr[i - lo] = start;
+        a.lcnt[i - lo] = group_total;
+        state8[i] = group_total == 0 ? uint8_t(kIn) : uint8_t(kUndecided);
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) shard_pull_kernel(int32_t lo, int32_t hi, const long long* __restrict__ lptr,
+                                                            const int32_t* __restrict__ lcnt,
+                                                            const int32_t* __restrict__ lst, uint8_t* state8) {
+    const int64_t v = int64_t(lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (v >= hi || state8[v] != kUndecided) return;
+    const long long p = lptr[v - lo];
+    const int32_t c = lcnt[v - lo];
+    bool all_out = true;
+    for (int32_t k = 0; k < c; ++k) {
+        const uint8_t st = *(volatile uint8_t*)(state8 + lst[p + k]);
+        if (st == kIn) { state8[v] = uint8_t(kOut); return; }          // a preceding coverer is selected (:38,45)
+        all_out = all_out && st == kOut;
+    }
+    if (all_out) state8[v] = uint8_t(kIn);                               // nobody before it covers it (:25-28)
+}
+
+__global__ void __launch_bounds__(kBlock) count_state_kernel(int64_t n, const uint8_t* __restrict__ state8, uint8_t what,
+                                                             unsigned long long* __restrict__ out) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const unsigned m = __ballot_sync(0xffffffffu, i < n && state8[i] == what);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, (unsigned long long)__popc(m));
+}
+__global__ void __launch_bounds__(kBlock) flag_in8_kernel(int32_t n, const uint8_t* __restrict__ state8,
+                                                          int32_t* __restrict__ flag) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n) flag[i] = state8[i] == kIn ? 1 : 0;
+}
+__global__ void __launch_bounds__(kBlock) compact8_kernel(int32_t n, const uint8_t* __restrict__ state8,
+                                                          const int32_t* __restrict__ pos, int32_t* __restrict__ out) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n && state8[i] == kIn) out[pos[i]] = int32_t(i);
+}
+
+void shard_sampler_build(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                         const double* len, double radius, int mode, uint64_t seed, uint8_t* state8, ShardSampler& out) {
+    GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL, GMG_ERR_INVALID, "unknown sampler mode");
+    out.lo = lo; out.hi = hi;
+    const int32_t own = hi - lo;
+    out.lptr.alloc(c, own); out.lcnt.alloc(c, own);
+    if (own <= 0) { out.lst.alloc(c, 0); return; }
+    DevBuf<unsigned long long> cursor(c, 2);
+    cursor.zero();
+    SamplerArgs a{n, colptr, rowidx, len, radius, make_order(n, seed), nullptr, nullptr, out.lptr.p, out.lcnt.p, nullptr,
+                  cursor.p, nullptr, 0};
+    if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_EXACT>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
+    else GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_PARALLEL>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
+    unsigned long long hb[2];
+    cursor.download(hb, 2);
+    sync(c);
+    out.lst.alloc(c, int64_t(hb[1]) + 1);
+    a.lst = out.lst.p;
+    const int grid = div_up(int64_t(own) * kLanes, kBlock);
+    if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_build_kernel<GMG_SAMPLER_EXACT>, grid, kBlock, 0, a, lo, hi, state8);
+    else GMG_LAUNCH(c, shard_build_kernel<GMG_SAMPLER_PARALLEL>, grid, kBlock, 0, a, lo, hi, state8);
+}
+
+void shard_sampler_round(gmg_ctx* c, const ShardSampler& s, uint8_t* state8) {
+    const int32_t own = s.hi - s.lo;
+    if (own > 0) GMG_LAUNCH(c, shard_pull_kernel, div_up(own, kBlock), kBlock, 0, s.lo, s.hi, s.lptr.p, s.lcnt.p, s.lst.p, state8);
+}
+
+int64_t count_state(gmg_ctx* c, int64_t n, const uint8_t* state8, int what) {
+    DevBuf<unsigned long long> out(c, 1);
+    out.zero();
+    if (n > 0) GMG_LAUNCH(c, count_state_kernel, div_up(n, kBlock), kBlock, 0, n, state8, uint8_t(what), out.p);
+    unsigned long long h = 0;
+    out.download(&h, 1);
+    sync(c);
+    return int64_t(h);
+}
+
+int32_t compact_selected(gmg_ctx* c, int32_t n, const uint8_t* state8, DevBuf<int32_t>& selection) {
+    if (n == 0) { selection.alloc(c, 0); return 0; }
+    DevBuf<int32_t> pos(c, n);
+    DevBuf<int64_t> total(c, 1);
+    GMG_LAUNCH(c, flag_in8_kernel, div_up(n, kBlock), kBlock, 0, n, state8, pos.p);
+    exclusive_scan_i32(c, pos.p, pos.p, n, total.p);
+    int64_t m = 0;
+    total.download(&m, 1);
+    sync(c);
+    selection.alloc(c, m);
+    GMG_LAUNCH(c, compact8_kernel, div_up(n, kBlock), kBlock, 0, n, state8, pos.p, selection.p);
+    return int32_t(m);
+}
+
 }  // namespace gmg

@@ -1,0 +1,399 @@
+// Row-sharded hierarchy build [not in reference; SURVEY.md 8(e)]: one process per GPU, fine vertices
+// split into contiguous ranges, one per rank. Design of this first version:
+//
+//   * every rank holds the whole level graph (colptr, rowidx, lengths, points): 112 B per vertex of a
+//     triangle mesh, so a 100 M-vertex level is 11 GB of 180 GB. What is SHARDED is the work and the
+//     large per-level products: the sampler's coverer lists, the relaxation, the coarse rows and the
+//     rows of P are computed for the owned range only;
+//   * a rank only ever writes the entries it owns of a replicated per-vertex array (state, distance,
+//     predecessor, parent, coarse row counts); the caller all-gathers the owned slices after each
+//     phase (NCCL all-gather over NVLink through torch.distributed, or an in-process loop-back when
+//     several virtual ranks share one GPU in the tests). There is no reduction and no all-to-all;
+//   * the sampler and the relaxation are therefore PULL formulations (k_sampler.cu, k_parents.cu):
+//     same greedy set, same distances, same parents as the single-GPU kernels, bit for bit;
+//   * cheap stages (cluster CSR, coarse positions, triangle fans, compaction scans) are computed
+//     redundantly by every rank from replicated inputs, so they need no exchange;
+//   * P stays sharded by rows ("P rows shard trivially"). Galerkin products on the sharded P are the
+//     next step and are not built here.
+//
+// The object below is driven phase by phase from the host (gravo-mg_b200/sharded.py): run a phase on
+// every rank, all-gather the buffers that phase names, go on.
+#include "hierarchy_types.h"
+
+#include <cmath>
+
+using namespace gmg;
+
+struct gmg_shard {
+    gmg_ctx* ctx = nullptr;
+    int rank = 0, world = 1;
+    gmg_hierarchy_options opt{};
+    std::vector<double> radius_override;
+    // current level (replicated)
+    int level = 0;
+    int32_t n = 0;
+    int64_t nnz = 0;
+    int32_t lo = 0, hi = 0;          // owned fine vertices
+    int32_t chunk = 0;               // slice length of the per-vertex exchange buffers (n_pad = chunk * world)
+    DevBuf<double> pts_own, val_own; // level-0 copies (later levels view the previous level's coarse data)
+    DevBuf<int32_t> colptr_own, rowidx_own;
+    const double* pts = nullptr;
+    const int32_t* colptr = nullptr;
+    const int32_t* rowidx = nullptr;
+    const double* val = nullptr;     // stored values of the level's edge matrix
+    DevBuf<double> len;              // Euclidean lengths (level 0: also the stored values)
+    double radius = 0.0;
+    // exchange buffers (per-vertex, chunk * world entries; a rank writes [lo, hi) only)
+    DevBuf<uint8_t> state, changed[2];
+    DevBuf<unsigned long long> dist;
+    DevBuf<int32_t> srcid, pred, parents;
+    int parity = 0;
+    ShardSampler sampler;
+    // coarse side
+    int32_t m = 0, clo = 0, chi = 0, cchunk = 0;
+    DevBuf<int32_t> samples;
+    Clusters clusters;
+    DevBuf<int32_t> ccnt;            // exchange: distinct neighbours per coarse row, cchunk * world (+1)
+    CoarseRows rows;
+    DevBuf<int32_t> rowoff;          // exclusive scan of ccnt over ALL rows (m + 1) = global row-major offsets
+    int64_t rows_max = 0;            // largest per-rank row volume: slice length of the two buffers below
+    DevBuf<int32_t> xQ;              // exchange: packed rows (neighbour ids), rows_max * world
+    DevBuf<double> xt;               // exchange: packed rows (values)
+    std::vector<int64_t> rank_rows;  // entries per rank
+    StageStatus status;
+    // finished levels: replicated coarse data + the owned rows of P
+    struct Done {
+        gmg_level_info info{};
+        int32_t lo = 0, hi = 0;
+        DevBuf<int32_t> samples, parents;
+        DeviceCsc coarse;
+        DevBuf<double> coarse_pts;
+        Triangles tri;
+        DeviceCsr P;                 // rows [lo, hi)
+    };
+    std::vector<std::unique_ptr<Done>> done;
+    std::unique_ptr<Done> cur;
+};
+
+namespace {
+
+template <typename F> int guarded_s(gmg_ctx* c, F&& body) {
+    if (!c) return GMG_ERR_STATE;
+    try {
+        GMG_CUDA(cudaSetDevice(c->device));
+        body();
+        c->last_error.clear();
+        return GMG_OK;
+    } catch (const Error& e) {
+        c->last_error = e.what;
+        cudaStreamSynchronize(c->stream);
+        return e.status;
+    } catch (const std::exception& e) {
+        c->last_error = e.what();
+        return GMG_ERR_INVALID;
+    }
+}
+
+int32_t round_up(int64_t a, int64_t b) { return int32_t((a + b - 1) / b * b); }
+
+// contiguous split of [0, count) into `world` slices of `chunk` (a multiple of 32) entries
+void split(int64_t count, int world, int rank, int32_t& chunk, int32_t& lo, int32_t& hi) {
+    chunk = round_up((count + world - 1) / world, 32);
+    if (chunk == 0) chunk = 32;
+    lo = int32_t(std::min<int64_t>(count, int64_t(rank) * chunk));
+    hi = int32_t(std::min<int64_t>(count, int64_t(rank + 1) * chunk));
+}
+
+__global__ void __launch_bounds__(kBlock) pack_rows_kernel(int32_t p_lo, int32_t p_hi, const int32_t* __restrict__ boff,
+                                                           const int32_t* __restrict__ cnt,
+                                                           const int32_t* __restrict__ rowoff, int32_t base,
+                                                           const int32_t* __restrict__ sQ, const double* __restrict__ st,
+                                                           int32_t* __restrict__ outQ, double* __restrict__ outt) {
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t P = p_lo + int32_t(gid / 8);
+    const int sub = int(gid % 8);
+    if (P >= p_hi) return;
+    const int32_t src = boff[P - p_lo], dst = rowoff[P] - base, k = cnt[P];
+    for (int32_t i = sub; i < k; i += 8) { outQ[dst + i] = sQ[src + i]; outt[dst + i] = st[src + i]; }
+}
+
+void begin_level(gmg_shard* s) {
+    gmg_ctx* c = s->ctx;
+    split(s->n, s->world, s->rank, s->chunk, s->lo, s->hi);
+    const int64_t n_pad = int64_t(s->chunk) * s->world;
+    s->state.alloc(c, n_pad); s->changed[0].alloc(c, n_pad); s->changed[1].alloc(c, n_pad);
+    s->dist.alloc(c, n_pad); s->srcid.alloc(c, n_pad); s->pred.alloc(c, n_pad); s->parents.alloc(c, n_pad);
+    s->state.zero(); s->pred.zero(); s->parents.zero();
+    s->cur.reset(new gmg_shard::Done());
+    s->cur->info.n = s->n; s->cur->info.nnz = s->nnz;
+    s->cur->lo = s->lo; s->cur->hi = s->hi;
+    s->status.begin(c);
+    // lengths and radius: replicated (every rank needs the lengths of the columns its walks touch)
+    if (s->level == 0) {
+        s->len.alloc(c, s->nnz);
+        edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p);
+        s->val = s->len.p;                                   // toEdgeDistanceMatrix (test/main.cpp:69)
+    } else {
+        s->len.alloc(c, s->nnz);
+        edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p);
+    }
+    const bool overridden = !s->radius_override.empty() && s->radius_override[size_t(s->level)] > 0.0;
+    if (overridden) s->radius = s->radius_override[size_t(s->level)];
+    else {
+        double denom = double(s->nnz - s->n);
+        if (s->opt.radius_policy == 1) denom = double(s->level == 0 ? s->nnz - s->n : s->nnz);
+        DevBuf<double> d_mean(c, 1);
+        mean_length_dev(c, s->nnz, s->len.p, denom, d_mean.p);
+        double mean = 0.0;
+        d_mean.download(&mean, 1);
+        sync(c);
+        s->radius = std::cbrt(s->opt.ratio) * mean;
+    }
+    s->cur->info.radius = s->radius;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gmg_shard_create(gmg_ctx* c, int rank, int world, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                     const int32_t* rowidx, const gmg_hierarchy_options* opt, gmg_shard** out) {
+    if (!out) return GMG_ERR_INVALID;
+    *out = nullptr;
+    return guarded_s(c, [&] {
+        GMG_REQUIRE(opt && opt->levels >= 1, GMG_ERR_INVALID, "levels must be >= 1");
+        GMG_REQUIRE(world >= 1 && rank >= 0 && rank < world, GMG_ERR_INVALID, "bad rank/world");
+        GMG_REQUIRE(n >= 0 && n < (int64_t(1) << 31) / 3, GMG_ERR_INVALID, "vertex count too large for 32-bit indices");
+        GMG_REQUIRE(!opt->build_galerkin, GMG_ERR_INVALID, "the row-sharded build does not form Galerkin operators yet");
+        std::unique_ptr<gmg_shard> s(new gmg_shard());
+        s->ctx = c; s->rank = rank; s->world = world; s->opt = *opt;
+        if (opt->radius_override) s->radius_override.assign(opt->radius_override, opt->radius_override + (opt->levels - 1));
+        s->opt.radius_override = nullptr;
+        s->n = int32_t(n); s->nnz = colptr[n];
+        s->pts_own = points_to_device(c, points, n, ld);
+        s->colptr_own = to_device(c, colptr, n + 1);
+        s->rowidx_own = to_device(c, rowidx, s->nnz);
+        s->pts = s->pts_own.p; s->colptr = s->colptr_own.p; s->rowidx = s->rowidx_own.p;
+        check_pattern(c, s->n, s->colptr, s->rowidx, true);
+        sync(c);
+        *out = s.release();
+    });
+}
+
+void gmg_shard_destroy(gmg_shard* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    delete s;
+}
+
+/* io: small host array, meaning per phase (see include/gravomg_b200.h) */
+int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
+    return guarded_s(c, [&] {
+        GMG_REQUIRE(s && io, GMG_ERR_STATE, "null shard");
+        switch (phase) {
+            case GMG_PH_LEVEL_BEGIN: {
+                io[0] = (s->level + 1 < s->opt.levels && s->n > 0) ? 1 : 0;
+                if (!io[0]) break;
+                begin_level(s);
+                io[1] = s->n; io[2] = s->lo; io[3] = s->hi; io[4] = s->chunk;
+                break;
+            }
+            case GMG_PH_SAMPLER_BUILD:
+                shard_sampler_build(c, s->n, s->lo, s->hi, s->colptr, s->rowidx, s->len.p, s->radius, s->opt.sampler_mode,
+                                    s->opt.seed + uint64_t(s->level), s->state.p, s->sampler);
+                break;
+            case GMG_PH_SAMPLER_ROUND:
+                shard_sampler_round(c, s->sampler, s->state.p);
+                break;
+            case GMG_PH_SAMPLER_CHECK:      // on the gathered state: identical on every rank
+                io[0] = count_state(c, s->n, s->state.p, 0);
+                ++s->cur->info.sampler_rounds;
+                break;
+            case GMG_PH_SAMPLES: {
+                s->sampler = ShardSampler();
+                s->m = compact_selected(c, s->n, s->state.p, s->samples);
+                split(s->m, s->world, s->rank, s->cchunk, s->clo, s->chi);
+                s->cur->info.m = s->m;
+                shard_parents_init(c, s->n, s->m, s->samples.p, s->dist.p, s->changed[0].p, s->srcid.p);
+                s->parity = 0;
+                io[0] = s->m;
+                break;
+            }
+            case GMG_PH_PARENTS_PULL:       // reads changed[parity], writes changed[parity ^ 1] and dist on [lo, hi)
+                shard_parents_pull(c, s->lo, s->hi, s->colptr, s->rowidx, s->len.p, s->dist.p, s->changed[s->parity].p,
+                                   s->changed[s->parity ^ 1].p);
+                s->parity ^= 1;
+                break;
+            case GMG_PH_PARENTS_CHECK:      // on the gathered bytes: identical on every rank
+                io[0] = count_state(c, s->n, s->changed[s->parity].p, 1);
+                ++s->cur->info.parent_rounds;
+                break;
+            case GMG_PH_PARENTS_PRED:
+                shard_parents_pred(c, s->n, s->lo, s->hi, s->colptr, s->rowidx, s->len.p, s->dist.p, s->srcid.p, s->pred.p,
+                                   s->status.dev.p + StageStatus::kZeroEdge);
+                break;
+            case GMG_PH_PARENTS_RESOLVE:
+                shard_parents_resolve(c, s->n, s->lo, s->hi, s->pred.p, s->srcid.p, s->parents.p);
+                break;
+            case GMG_PH_COARSE_ROWS: {
+                build_clusters(c, s->n, s->m, s->parents.p, s->clusters);           // replicated
+                s->ccnt.alloc(c, int64_t(s->cchunk) * s->world + 1);
+                s->ccnt.zero();
+                s->rows = CoarseRows();
+                coarse_rows_range(c, s->n, s->colptr, s->rowidx, s->val, s->clo, s->chi, s->parents.p, s->clusters,
+                                  s->ccnt.p, s->rows, s->status.dev.p + StageStatus::kCoarseHardOverflow);
+                break;
+            }
+            case GMG_PH_COARSE_PACK: {      // after the row counts have been gathered
+                s->rowoff.alloc(c, int64_t(s->m) + 1);
+                DevBuf<int64_t> total(c, 1);
+                GMG_CUDA(cudaMemsetAsync(s->ccnt.p + s->m, 0, sizeof(int32_t), c->stream));   // scan sentinel
+                exclusive_scan_i32(c, s->ccnt.p, s->rowoff.p, int64_t(s->m) + 1, total.p);
+                // volume of every rank's rows = rowoff at the rank boundaries
+                std::vector<int32_t> bounds(size_t(s->world) + 1, 0);
+                for (int r = 0; r <= s->world; ++r) {
+                    const int64_t at = std::min<int64_t>(s->m, int64_t(r) * s->cchunk);
+                    GMG_CUDA(cudaMemcpyAsync(&bounds[size_t(r)], s->rowoff.p + at, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+                }
+                sync(c);
+                s->rank_rows.assign(size_t(s->world), 0);
+                s->rows_max = 1;
+                for (int r = 0; r < s->world; ++r) {
+                    s->rank_rows[size_t(r)] = bounds[size_t(r) + 1] - bounds[size_t(r)];
+                    s->rows_max = std::max<int64_t>(s->rows_max, s->rank_rows[size_t(r)]);
+                }
+                s->rows_max = round_up(s->rows_max, 32);
+                s->xQ.alloc(c, s->rows_max * s->world);
+                s->xt.alloc(c, s->rows_max * s->world);
+                const int32_t own = s->chi - s->clo;
+                if (own > 0)
+                    GMG_LAUNCH(c, pack_rows_kernel, div_up(int64_t(own) * 8, kBlock), kBlock, 0, s->clo, s->chi, s->rows.boff.p,
+                               s->ccnt.p, s->rowoff.p, bounds[size_t(s->rank)], s->rows.sQ.p, s->rows.st.p,
+                               s->xQ.p + s->rows_max * s->rank, s->xt.p + s->rows_max * s->rank);
+                s->rows = CoarseRows();
+                io[0] = s->rows_max;
+                break;
+            }
+            case GMG_PH_COARSE_ASSEMBLE: {  // after the packed rows have been gathered
+                // concatenate the rank slices into the global row-major arrays (rowoff addresses them)
+                const int64_t total = [&] { int64_t t = 0; for (auto v : s->rank_rows) t += v; return t; }();
+                DevBuf<int32_t> allQ(c, total);
+                DevBuf<double> allt(c, total);
+                int64_t at = 0;
+                for (int r = 0; r < s->world; ++r) {
+                    const int64_t k = s->rank_rows[size_t(r)];
+                    if (k > 0) {
+                        GMG_CUDA(cudaMemcpyAsync(allQ.p + at, s->xQ.p + s->rows_max * r, sizeof(int32_t) * size_t(k), cudaMemcpyDeviceToDevice, c->stream));
+                        GMG_CUDA(cudaMemcpyAsync(allt.p + at, s->xt.p + s->rows_max * r, sizeof(double) * size_t(k), cudaMemcpyDeviceToDevice, c->stream));
+                    }
+                    at += k;
+                }
+                gmg_shard::Done& L = *s->cur;
+                coarse_assemble(c, s->m, s->rowoff.p, s->ccnt.p, allQ.p, allt.p, L.coarse, s->status.dev.p + StageStatus::kCoarseAsym);
+                L.info.nnz_c = L.coarse.nnz;
+                s->xQ = DevBuf<int32_t>(); s->xt = DevBuf<double>();
+                // replicated cheap stages
+                L.coarse_pts.alloc(c, 3 * int64_t(s->m));
+                coarse_points(c, s->n, s->pts, s->colptr, s->rowidx, s->m, s->clusters, L.coarse_pts.p);
+                voronoi_triangles(c, s->m, L.coarse.nnz, L.coarse_pts.p, L.coarse.colptr.p, L.coarse.rowidx.p, L.coarse.val.p, L.tri);
+                L.info.T = L.tri.T;
+                break;
+            }
+            case GMG_PH_PROLONG: {          // owned rows of P
+                gmg_shard::Done& L = *s->cur;
+                prolongation(c, s->n, s->pts, s->m, L.coarse_pts.p, L.coarse.colptr.p, L.coarse.rowidx.p, s->parents.p, L.tri,
+                             s->opt.weighting, L.P, nullptr, &s->status, s->lo, s->hi);
+                break;
+            }
+            case GMG_PH_LEVEL_END: {
+                gmg_shard::Done& L = *s->cur;
+                s->status.fetch(c);
+                finish_prolongation(s->status, L.P, &L.info.stats);
+                L.info.nnz_p = L.P.nnz;
+                s->status.raise_parents();
+                s->status.raise_coarse();
+                s->status.raise_prolong(s->hi - s->lo);
+                // keep what a consumer of the level needs; the rest goes back to the pool
+                L.samples = std::move(s->samples);
+                L.parents.alloc(c, s->n);
+                GMG_CUDA(cudaMemcpyAsync(L.parents.p, s->parents.p, sizeof(int32_t) * size_t(s->n), cudaMemcpyDeviceToDevice, c->stream));
+                s->clusters = Clusters();
+                // next level's fine inputs
+                s->n = s->m; s->nnz = L.coarse.nnz;
+                s->pts = L.coarse_pts.p; s->colptr = L.coarse.colptr.p; s->rowidx = L.coarse.rowidx.p; s->val = L.coarse.val.p;
+                io[0] = L.info.m; io[1] = L.info.nnz_c; io[2] = L.info.T; io[3] = L.info.nnz_p;
+                s->done.push_back(std::move(s->cur));
+                ++s->level;
+                sync(c);
+                break;
+            }
+            default: GMG_REQUIRE(false, GMG_ERR_INVALID, "unknown phase");
+        }
+    });
+}
+
+/* Exchange buffer `which` of the current level: device pointer, element size in bytes, and the slice
+ * length in elements (the buffer holds slice * world elements; rank r owns [r*slice, (r+1)*slice)). */
+int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* slice) {
+    if (!s || !ptr || !elem_bytes || !slice) return GMG_ERR_STATE;
+    switch (which) {
+        case GMG_XB_STATE: *ptr = s->state.p; *elem_bytes = 1; *slice = s->chunk; break;
+        case GMG_XB_CHANGED: *ptr = s->changed[s->parity].p; *elem_bytes = 1; *slice = s->chunk; break;
+        case GMG_XB_DIST: *ptr = s->dist.p; *elem_bytes = 8; *slice = s->chunk; break;
+        case GMG_XB_PRED: *ptr = s->pred.p; *elem_bytes = 4; *slice = s->chunk; break;
+        case GMG_XB_PARENTS: *ptr = s->parents.p; *elem_bytes = 4; *slice = s->chunk; break;
+        case GMG_XB_COARSE_COUNT: *ptr = s->ccnt.p; *elem_bytes = 4; *slice = s->cchunk; break;
+        case GMG_XB_ROWS_ID: *ptr = s->xQ.p; *elem_bytes = 4; *slice = s->rows_max; break;
+        case GMG_XB_ROWS_VAL: *ptr = s->xt.p; *elem_bytes = 8; *slice = s->rows_max; break;
+        default: return GMG_ERR_INVALID;
+    }
+    return GMG_OK;
+}
+
+int gmg_shard_num_levels(const gmg_shard* s) { return s ? int(s->done.size()) : 0; }
+
+int gmg_shard_level_info(const gmg_shard* s, int level, gmg_level_info* out, int64_t* row_lo, int64_t* row_hi) {
+    if (!s || !out || level < 0 || level >= int(s->done.size())) return GMG_ERR_STATE;
+    *out = s->done[size_t(level)]->info;
+    if (row_lo) *row_lo = s->done[size_t(level)]->lo;
+    if (row_hi) *row_hi = s->done[size_t(level)]->hi;
+    return GMG_OK;
+}
+
+/* Same array ids as gmg_hierarchy_fetch. Replicated arrays are complete on every rank; the three P
+ * arrays hold the owned rows [row_lo, row_hi) only (rowptr has row_hi - row_lo + 1 entries, from 0). */
+int gmg_shard_fetch(gmg_ctx* c, const gmg_shard* s, int level, int which, void* out) {
+    return guarded_s(c, [&] {
+        GMG_REQUIRE(s && level >= 0 && level < int(s->done.size()), GMG_ERR_STATE, "no such level");
+        const gmg_shard::Done& L = *s->done[size_t(level)];
+        const int64_t n = L.info.n, m = L.info.m, T = L.info.T, own = L.hi - L.lo;
+        auto copy = [&](const void* dev, size_t bytes) {
+            if (bytes) GMG_CUDA(cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+        };
+        auto copy_wide = [&](const int32_t* dev, int64_t count) {
+            DevBuf<int64_t> w(c, count);
+            widen_i32(c, dev, w.p, count);
+            copy(w.p, sizeof(int64_t) * size_t(count));
+            sync(c);
+        };
+        switch (which) {
+            case GMG_H_SAMPLES: copy_wide(L.samples.p, m); break;
+            case GMG_H_PARENTS: copy_wide(L.parents.p, n); break;
+            case GMG_H_COARSE_COLPTR: copy(L.coarse.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
+            case GMG_H_COARSE_ROWIDX: copy(L.coarse.rowidx.p, sizeof(int32_t) * size_t(L.coarse.nnz)); break;
+            case GMG_H_COARSE_VAL: copy(L.coarse.val.p, sizeof(double) * size_t(L.coarse.nnz)); break;
+            case GMG_H_COARSE_POINTS: copy(L.coarse_pts.p, sizeof(double) * size_t(3 * m)); break;
+            case GMG_H_TRIANGLES: copy_wide(L.tri.tri.p, 3 * T); break;
+            case GMG_H_NORMALS: copy(L.tri.normal.p, sizeof(double) * size_t(3 * T)); break;
+            case GMG_H_FAN_PTR: copy_wide(L.tri.fan_ptr.p, m + 1); break;
+            case GMG_H_FAN: copy_wide(L.tri.fan_tri.p, 3 * T); break;
+            case GMG_H_P_ROWPTR: copy(L.P.rowptr.p, sizeof(int32_t) * size_t(own + 1)); break;
+            case GMG_H_P_COLIDX: copy(L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz)); break;
+            case GMG_H_P_VAL: copy(L.P.val.p, sizeof(double) * size_t(L.P.nnz)); break;
+            default: GMG_REQUIRE(false, GMG_ERR_INVALID, "array not available from a sharded build");
+        }
+        sync(c);
+    });
+}
+
+}  // extern "C"

@@ -46,11 +46,36 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
 // *d_out (device) += sum over columns of deg^2
 void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned long long* d_out);
 
+// Row-sharded variant: rank-local lists of preceding coverers for the owned vertices [lo, hi); the
+// uint8 state array (0 undecided, 1 in, 2 out) is replicated and all-gathered by the caller between rounds.
+struct ShardSampler {
+    int32_t lo = 0, hi = 0;
+    DevBuf<long long> lptr;
+    DevBuf<int32_t> lcnt, lst;
+};
+void shard_sampler_build(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                         const double* len, double radius, int mode, uint64_t seed, uint8_t* state8, ShardSampler& out);
+void shard_sampler_round(gmg_ctx* c, const ShardSampler& s, uint8_t* state8);
+int64_t count_state(gmg_ctx* c, int64_t n, const uint8_t* state8, int what);
+int32_t compact_selected(gmg_ctx* c, int32_t n, const uint8_t* state8, DevBuf<int32_t>& selection);
+
 // ---- k_parents.cu -----------------------------------------------------------------------------
 struct ParentStats { int rounds; };
 void assign_parents_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
                         int32_t m, const int32_t* samples, int32_t* parents, ParentStats* stats,
                         StageStatus* status = nullptr);
+
+// Row-sharded variant: pull relaxation over the owned vertices [lo, hi); dist (uint64 bit patterns of
+// non-negative doubles), the "improved last round" bytes and srcid are replicated arrays.
+void shard_parents_init(gmg_ctx* c, int32_t n, int32_t m, const int32_t* samples, unsigned long long* dist,
+                        uint8_t* changed, int32_t* srcid);
+void shard_parents_pull(gmg_ctx* c, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                        const double* len, unsigned long long* dist, const uint8_t* changed_in, uint8_t* changed_out);
+void shard_parents_pred(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
+                        const double* len, const unsigned long long* dist, const int32_t* srcid, int32_t* pred,
+                        int32_t* d_flags);
+void shard_parents_resolve(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* pred, const int32_t* srcid,
+                           int32_t* parents);
 
 // ---- k_cluster.cu -----------------------------------------------------------------------------
 struct Clusters {
@@ -67,6 +92,20 @@ struct DeviceCsc {
 };
 void coarse_edges(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const int32_t* rowidx, const double* val,
                   int32_t m, const int32_t* parents, const Clusters& cl, DeviceCsc& out, StageStatus* status = nullptr);
+// The two halves of coarse_edges, used separately by the row-sharded build: rows of the owned clusters
+// [p_lo, p_hi), then (after the ranks have exchanged their rows) the column-major matrix.
+struct CoarseRows {
+    int32_t p_lo = 0, p_hi = 0;
+    int64_t bound = -1;          // candidates in the owned rows; < 0: compute (one host round trip)
+    DevBuf<int32_t> boff;        // p_hi - p_lo + 1 scratch offsets
+    DevBuf<int32_t> sQ;          // neighbour clusters, ascending per row
+    DevBuf<double> st;           // min-reduced value per neighbour
+};
+void coarse_rows_range(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
+                       int32_t p_lo, int32_t p_hi, const int32_t* parents, const Clusters& cl, int32_t* cnt,
+                       CoarseRows& out, int32_t* d_hard_overflow);
+void coarse_assemble(gmg_ctx* c, int32_t m, const int32_t* boff, const int32_t* cnt, const int32_t* sQ, const double* st,
+                     DeviceCsc& out, int32_t* d_asym);
 void coarse_points(gmg_ctx* c, int32_t n, const double* pts, const int32_t* colptr, const int32_t* rowidx, int32_t m,
                    const Clusters& cl, double* out_pts);
 
@@ -92,7 +131,8 @@ struct DeviceCsr {
 };
 void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, const double* coarse_pts,
                   const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
-                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status = nullptr);
+                  int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status = nullptr,
+                  int32_t f_lo = 0, int32_t f_hi = -1);   // rows [f_lo, f_hi) only (default: all); P.rows = f_hi - f_lo
 // With a StageStatus, P.nnz and the counters are only known after status->fetch(): this fills them in.
 void finish_prolongation(const StageStatus& status, DeviceCsr& P, gmg_prolongation_stats* stats);
 void projected_points_dev(gmg_ctx* c, int32_t n, int32_t m, const int32_t* rowptr, const int32_t* colidx,

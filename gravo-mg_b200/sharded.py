@@ -1,0 +1,264 @@
+"""Row-sharded hierarchy build: the host-side driver of gmg_shard_* (include/gravomg_b200.h) [not in
+reference; SURVEY.md 8(e)].
+
+One process per GPU. The C library runs the PHASES of a level on the rank's own range of fine
+vertices and exposes the replicated per-vertex buffers it writes; this module runs the phases in
+order and all-gathers those buffers between them:
+
+    TorchComm      torch.distributed (backend "nccl" over NVLink / NVSwitch on the GPU box, "gloo" for the
+                   CPU tests of the exchange logic) -- in-place all_gather_into_tensor of the owned slices;
+    LoopbackComm   several VIRTUAL ranks in one process on one GPU: the same phases run for every
+                   virtual rank in lock-step and the gather is a set of device-to-device copies. This is
+                   how the sharded path is parity-tested against the single-GPU build on one B200.
+
+The data path has no reduction and no all-to-all: every exchange is an all-gather of contiguous owned
+slices. Results equal the single-GPU build bit for bit; P comes back sharded by rows.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, _i32p, _p, _pts,
+                   H_SAMPLES, H_PARENTS, H_COARSE_COLPTR, H_COARSE_ROWIDX, H_COARSE_VAL, H_COARSE_POINTS, H_TRIANGLES,
+                   H_NORMALS, H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL)
+
+(PH_LEVEL_BEGIN, PH_SAMPLER_BUILD, PH_SAMPLER_ROUND, PH_SAMPLER_CHECK, PH_SAMPLES, PH_PARENTS_PULL, PH_PARENTS_CHECK,
+ PH_PARENTS_PRED, PH_PARENTS_RESOLVE, PH_COARSE_ROWS, PH_COARSE_PACK, PH_COARSE_ASSEMBLE, PH_PROLONG,
+ PH_LEVEL_END) = range(14)
+(XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL) = range(8)
+
+
+def partition(count, world, rank):
+    """Contiguous split used by the C library (shard.cu split()): slices of a multiple of 32 entries.
+    Returns (slice_length, lo, hi)."""
+    chunk = ((count + world - 1) // world + 31) // 32 * 32
+    if chunk == 0:
+        chunk = 32
+    return chunk, min(count, rank * chunk), min(count, (rank + 1) * chunk)
+
+
+class _DeviceBytes:
+    """A raw device range as a __cuda_array_interface__ object, so torch can wrap it without copying."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def device_bytes_as_tensor(ptr, nbytes, device):
+    import torch
+    return torch.as_tensor(_DeviceBytes(ptr, nbytes), device=device)
+
+
+class TorchComm:
+    """All-gather through torch.distributed. `buffers` are byte tensors that alias the library's
+    exchange buffers (CUDA for nccl). One rank per process."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.bytes_gathered = 0
+
+    def all_gather_inplace(self, full, slice_bytes):
+        """full: uint8 tensor of world * slice_bytes; rank r's slice is [r*slice_bytes, (r+1)*slice_bytes)."""
+        mine = full[self.rank * slice_bytes:(self.rank + 1) * slice_bytes]
+        self.dist.all_gather_into_tensor(full, mine, group=self.group)
+        self.bytes_gathered += int(full.numel())
+
+
+class ShardRank:
+    """One rank's gmg_shard handle."""
+
+    def __init__(self, ctx, rank, world, points, colptr, rowidx, opt):
+        self.ctx, self.rank, self.world = ctx, rank, world
+        lib = ctx.lib
+        lib.gmg_shard_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
+        lib.gmg_shard_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int32),
+                                         C.POINTER(C.c_int64)]
+        lib.gmg_shard_destroy.argtypes = [C.c_void_p]
+        lib.gmg_shard_destroy.restype = None
+        lib.gmg_shard_num_levels.argtypes = [C.c_void_p]
+        lib.gmg_shard_level_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        lib.gmg_shard_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
+        n = pts.shape[0]
+        h = C.c_void_p()
+        ctx._check(lib.gmg_shard_create(ctx.h, C.c_int(rank), C.c_int(world), C.c_int64(n), _p(pts, _f64p), C.c_int64(n),
+                                        _p(colptr, _i32p), _p(rowidx, _i32p), C.byref(opt), C.byref(h)))
+        self.h = h
+        self.io = (C.c_int64 * 8)()
+
+    def phase(self, ph):
+        self.ctx._check(self.ctx.lib.gmg_shard_phase(self.ctx.h, self.h, C.c_int(ph), self.io))
+        return self.io
+
+    def buffer(self, which):
+        """(device pointer, bytes per slice) of an exchange buffer."""
+        ptr, eb, sl = C.c_void_p(), C.c_int32(), C.c_int64()
+        rc = self.ctx.lib.gmg_shard_buffer(self.h, C.c_int(which), C.byref(ptr), C.byref(eb), C.byref(sl))
+        if rc != 0:
+            raise GmgError(rc, "gmg_shard_buffer")
+        return ptr.value, int(eb.value) * int(sl.value)
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.lib.gmg_shard_destroy(self.h)
+        self.h = None
+
+    __del__ = close
+
+
+class ShardedHierarchy:
+    """Row-sharded build. `ranks` is the list of ranks THIS process runs: one (its torch.distributed rank)
+    in production, all of them as virtual ranks with comm=None (loop-back on one GPU) in the tests."""
+
+    def __init__(self, ctx, points, colptr, rowidx, levels, world, ranks, comm=None, ratio=8.0,
+                 weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_PARALLEL, seed=0, radius_policy=0,
+                 radius_override=None, device=None, same_stream=False):
+        import torch
+        self.torch = torch
+        self.ctx, self.world, self.comm = ctx, world, comm
+        # The exchange runs on torch's current stream. If `ctx` was created on that very stream
+        # (Context(device, torch.cuda.current_stream().cuda_stream)) the phases and the exchanges are
+        # ordered by the stream itself; otherwise every exchange is fenced by a device synchronise.
+        self.same_stream = same_stream
+        if comm is not None and len(ranks) != 1:
+            raise ValueError("with a communicator every process runs exactly one rank")
+        if comm is None and sorted(ranks) != list(range(world)):
+            raise ValueError("the loop-back exchange needs every virtual rank in this process")
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        ro = None
+        if radius_override is not None:
+            ro = np.zeros(max(levels - 1, 1), dtype=np.float64)
+            ro[:len(radius_override)] = radius_override
+        self._ro = ro
+        opt = HierarchyOptions(levels, ratio, weighting, sampler_mode, seed, radius_policy,
+                               _p(ro, _f64p) if ro is not None else None, 0)
+        self.shards = [ShardRank(ctx, r, world, points, colptr, rowidx, opt) for r in ranks]
+        self.exchanges = 0
+        self.exchange_bytes = 0
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        self._build()
+        ev1.record()
+        torch.cuda.synchronize()
+        self.build_ms = ev0.elapsed_time(ev1)
+        self.num_levels = int(ctx.lib.gmg_shard_num_levels(self.shards[0].h))
+
+    # ---- exchange ------------------------------------------------------------------------------------
+    def _gather(self, which):
+        t = self.torch
+        bufs = [s.buffer(which) for s in self.shards]
+        slice_bytes = bufs[0][1]
+        total = slice_bytes * self.world
+        self.exchanges += 1
+        self.exchange_bytes += total
+        if not self.same_stream:
+            t.cuda.synchronize()
+        if self.comm is not None:
+            full = device_bytes_as_tensor(bufs[0][0], total, self.device)
+            self.comm.all_gather_inplace(full, slice_bytes)
+            if not self.same_stream:
+                t.cuda.synchronize()
+            return
+        # loop-back: copy every virtual rank's owned slice into all the other replicas
+        views = [device_bytes_as_tensor(p, total, self.device) for p, _ in bufs]
+        for src, shard in enumerate(self.shards):
+            r = shard.rank
+            piece = views[src][r * slice_bytes:(r + 1) * slice_bytes]
+            for dst in range(len(views)):
+                if dst != src:
+                    views[dst][r * slice_bytes:(r + 1) * slice_bytes].copy_(piece)
+        if not self.same_stream:
+            t.cuda.synchronize()
+
+    def _phase(self, ph):
+        ios = [s.phase(ph) for s in self.shards]
+        return ios[0]
+
+    def _build(self):
+        while True:
+            if not self._phase(PH_LEVEL_BEGIN)[0]:
+                break
+            self._phase(PH_SAMPLER_BUILD)
+            self._gather(XB_STATE)
+            while self._phase(PH_SAMPLER_CHECK)[0] > 0:
+                self._phase(PH_SAMPLER_ROUND)
+                self._gather(XB_STATE)
+            self._phase(PH_SAMPLES)
+            while True:
+                self._phase(PH_PARENTS_PULL)
+                self._gather(XB_DIST)
+                self._gather(XB_CHANGED)
+                if self._phase(PH_PARENTS_CHECK)[0] == 0:
+                    break
+            self._phase(PH_PARENTS_PRED)
+            self._gather(XB_PRED)
+            self._phase(PH_PARENTS_RESOLVE)
+            self._gather(XB_PARENTS)
+            self._phase(PH_COARSE_ROWS)
+            self._gather(XB_COARSE_COUNT)
+            self._phase(PH_COARSE_PACK)
+            self._gather(XB_ROWS_ID)
+            self._gather(XB_ROWS_VAL)
+            self._phase(PH_COARSE_ASSEMBLE)
+            self._phase(PH_PROLONG)
+            self._phase(PH_LEVEL_END)
+
+    # ---- results -------------------------------------------------------------------------------------
+    def info(self, level, shard=0):
+        li = LevelInfo()
+        lo, hi = C.c_int64(), C.c_int64()
+        s = self.shards[shard]
+        self.ctx._check(self.ctx.lib.gmg_shard_level_info(s.h, C.c_int(level), C.byref(li), C.byref(lo), C.byref(hi)))
+        d = li.as_dict()
+        d["row_lo"], d["row_hi"] = int(lo.value), int(hi.value)
+        return d
+
+    def fetch(self, level, which, shard=0):
+        i = self.info(level, shard)
+        n, m, T, own = i["n"], i["m"], i["T"], i["row_hi"] - i["row_lo"]
+        count, dtype = {
+            H_SAMPLES: (m, np.int64), H_PARENTS: (n, np.int64), H_COARSE_COLPTR: (m + 1, np.int32),
+            H_COARSE_ROWIDX: (i["nnz_c"], np.int32), H_COARSE_VAL: (i["nnz_c"], np.float64),
+            H_COARSE_POINTS: (3 * m, np.float64), H_TRIANGLES: (3 * T, np.int64), H_NORMALS: (3 * T, np.float64),
+            H_FAN_PTR: (m + 1, np.int64), H_FAN: (3 * T, np.int64), H_P_ROWPTR: (own + 1, np.int32),
+            H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64)}[which]
+        out = np.empty(max(count, 1), dtype=dtype)
+        s = self.shards[shard]
+        self.ctx._check(self.ctx.lib.gmg_shard_fetch(self.ctx.h, s.h, C.c_int(level), C.c_int(which),
+                                                     out.ctypes.data_as(C.c_void_p)))
+        out = out[:count]
+        if which == H_COARSE_POINTS:
+            return out.reshape((m, 3), order="F")
+        if which in (H_TRIANGLES, H_NORMALS):
+            return out.reshape(T, 3)
+        return out
+
+    def level_arrays(self, level):
+        """Like Hierarchy.level_arrays; the rows of P are concatenated over the ranks this process runs
+        (all of them under the loop-back exchange, so the result is the whole of P)."""
+        f = self.fetch
+        out = dict(radius=self.info(level)["radius"], sel=f(level, H_SAMPLES), par=f(level, H_PARENTS),
+                   ccp=f(level, H_COARSE_COLPTR), cri=f(level, H_COARSE_ROWIDX), cval=f(level, H_COARSE_VAL),
+                   cpts=f(level, H_COARSE_POINTS), tri=f(level, H_TRIANGLES), nrm=f(level, H_NORMALS),
+                   fptr=f(level, H_FAN_PTR), fan=f(level, H_FAN))
+        rowptr, cols, vals, base = [np.zeros(1, dtype=np.int32)], [], [], 0
+        for k in range(len(self.shards)):
+            rp = f(level, H_P_ROWPTR, k)
+            rowptr.append(rp[1:] + base)
+            cols.append(f(level, H_P_COLIDX, k))
+            vals.append(f(level, H_P_VAL, k))
+            base += int(rp[-1])
+        out["prp"] = np.concatenate(rowptr).astype(np.int32)
+        out["pci"] = np.concatenate(cols)
+        out["pva"] = np.concatenate(vals)
+        return out
+
+    def close(self):
+        for s in getattr(self, "shards", []):
+            s.close()
+        self.shards = []

@@ -220,6 +220,44 @@ int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, i
                       int coarse_sweeps, double* residual_out);
 /* device milliseconds of the last gmg_spmv / gmg_solver_vcycle are available through gmg_last_kernel_ms */
 
+/* ------------------------------------------------------------------------------------------------
+ * Row-sharded hierarchy build [not in reference; one process per GPU]. Fine vertices are split into
+ * contiguous ranges, one per rank. Every rank holds the whole level graph; the work and the large
+ * products (coverer lists, relaxation, coarse rows, rows of P) are computed for the owned range only.
+ * A rank writes only the entries it owns of a replicated per-vertex buffer, and the HOST all-gathers
+ * the owned slices after the phases named below (NCCL through torch.distributed in
+ * gravo-mg_b200/sharded.py; an in-process loop-back in the single-GPU tests). Results equal the
+ * single-GPU build bit for bit; P comes back sharded by rows.
+ *
+ * Driver loop per level (G = all-gather of that buffer over the ranks):
+ *   LEVEL_BEGIN (io[0] = 0: no level left) ; SAMPLER_BUILD ; G(STATE) ;
+ *   repeat { SAMPLER_CHECK -> io[0] = undecided vertices; stop at 0 ; SAMPLER_ROUND ; G(STATE) } ;
+ *   SAMPLES -> io[0] = m ; repeat { PARENTS_PULL ; G(DIST) ; G(CHANGED) ; PARENTS_CHECK -> io[0] =
+ *   improved vertices; stop at 0 } ; PARENTS_PRED ; G(PRED) ; PARENTS_RESOLVE ; G(PARENTS) ;
+ *   COARSE_ROWS ; G(COARSE_COUNT) ; COARSE_PACK ; G(ROWS_ID) ; G(ROWS_VAL) ; COARSE_ASSEMBLE ;
+ *   PROLONG ; LEVEL_END -> io = {m, nnz_c, T, nnz_p of the owned rows}.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct gmg_shard gmg_shard;
+enum { GMG_PH_LEVEL_BEGIN = 0, GMG_PH_SAMPLER_BUILD, GMG_PH_SAMPLER_ROUND, GMG_PH_SAMPLER_CHECK, GMG_PH_SAMPLES,
+       GMG_PH_PARENTS_PULL, GMG_PH_PARENTS_CHECK, GMG_PH_PARENTS_PRED, GMG_PH_PARENTS_RESOLVE, GMG_PH_COARSE_ROWS,
+       GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END };
+enum { GMG_XB_STATE = 0, GMG_XB_CHANGED, GMG_XB_DIST, GMG_XB_PRED, GMG_XB_PARENTS, GMG_XB_COARSE_COUNT, GMG_XB_ROWS_ID,
+       GMG_XB_ROWS_VAL };
+/* points/colptr/rowidx are HOST pointers to the whole level-0 problem (the same on every rank) */
+int gmg_shard_create(gmg_ctx* ctx, int rank, int world, int64_t n, const double* points, int64_t ld,
+                     const int32_t* colptr, const int32_t* rowidx, const gmg_hierarchy_options* opt, gmg_shard** out);
+void gmg_shard_destroy(gmg_shard* s);
+/* io: host array of at least 8 int64 */
+int gmg_shard_phase(gmg_ctx* ctx, gmg_shard* s, int phase, int64_t* io);
+/* exchange buffer: device pointer, element size, slice length in elements; the buffer holds
+ * slice * world elements and rank r owns [r * slice, (r + 1) * slice) */
+int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* slice);
+int gmg_shard_num_levels(const gmg_shard* s);
+int gmg_shard_level_info(const gmg_shard* s, int level, gmg_level_info* out, int64_t* row_lo, int64_t* row_hi);
+/* array ids of gmg_hierarchy_array; replicated arrays are complete on every rank, the P arrays hold
+ * the owned rows [row_lo, row_hi) (rowptr: row_hi - row_lo + 1 entries starting at 0) */
+int gmg_shard_fetch(gmg_ctx* ctx, const gmg_shard* s, int level, int which, void* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,64 @@
+"""Row-sharded build (gmg_shard_*, gravo-mg_b200/sharded.py) against the single-GPU build.
+
+Several VIRTUAL ranks run in lock-step on the one GPU with the loop-back exchange; the phases, the
+owned ranges and the buffers are exactly those of the multi-process NCCL run. The sharded build must
+reproduce the single-GPU hierarchy bit for bit (indices AND values), for every world size, because
+the greedy sample set, the shortest-path distances and the tie rules are order-independent facts.
+"""
+import numpy as np
+import pytest
+
+from gravomg_b200 import capi, meshgen
+from pipeline import assert_level_equal, run_hierarchy
+
+pytestmark = pytest.mark.gpu
+KEYS = "sel par ccp cri cval cpts tri nrm fptr fan prp pci pva".split()
+
+
+def _single(ctx, V, A, levels, mode, radii=None):
+    inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+    h = capi.Hierarchy(ctx, inp, levels, sampler_mode=mode, seed=7, radius_override=radii)
+    out = [h.level_arrays(l) for l in range(h.num_levels)]
+    h.close(); inp.close()
+    return out
+
+
+@pytest.mark.parametrize("name,scale,world,mode", [
+    ("C1", 1.0, 2, capi.SAMPLER_EXACT), ("C1", 1.0, 3, capi.SAMPLER_PARALLEL), ("C3", 0.004, 4, capi.SAMPLER_PARALLEL),
+    ("C4", 0.002, 2, capi.SAMPLER_PARALLEL), ("C3", 0.004, 8, capi.SAMPLER_EXACT)])
+def test_sharded_equals_single_gpu(ctx, name, scale, world, mode):
+    from gravomg_b200.sharded import ShardedHierarchy
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    want = _single(ctx, V, A, cfg["levels"], mode)
+    sh = ShardedHierarchy(ctx, V, A.indptr, A.indices, cfg["levels"], world, list(range(world)), comm=None,
+                          sampler_mode=mode, seed=7)
+    assert sh.num_levels == len(want)
+    for lvl, w in enumerate(want):
+        g = sh.level_arrays(lvl)
+        assert g["radius"] == w["radius"]
+        assert_level_equal(g, w, keys=KEYS, what=f"{name} world {world} level {lvl} ")
+        # every rank holds the same replicated coarse data
+        for k in range(1, world):
+            assert np.array_equal(sh.fetch(lvl, capi.H_PARENTS, k), w["par"])
+            assert np.array_equal(sh.fetch(lvl, capi.H_COARSE_ROWIDX, k), w["cri"])
+        # the owned row ranges tile [0, n)
+        los = [sh.info(lvl, k)["row_lo"] for k in range(world)]
+        his = [sh.info(lvl, k)["row_hi"] for k in range(world)]
+        assert los[0] == 0 and his[-1] == sh.info(lvl)["n"] and all(a == b for a, b in zip(his[:-1], los[1:]))
+    assert sh.exchanges > 0
+    sh.close()
+
+
+def test_sharded_exact_matches_oracle(ctx, orc):
+    """The sharded build in exact-sampler mode is the reference's hierarchy: checked against the oracle."""
+    from gravomg_b200.sharded import ShardedHierarchy
+    cfg = meshgen.make_config("C1")
+    V, A = cfg["V"], cfg["A"]
+    sh = ShardedHierarchy(ctx, V, A.indptr, A.indices, cfg["levels"], 4, [0, 1, 2, 3], comm=None,
+                          sampler_mode=capi.SAMPLER_EXACT)
+    radii = [sh.info(l)["radius"] for l in range(sh.num_levels)]
+    want = run_hierarchy(orc, V, A, cfg["levels"], radii=radii)
+    for lvl, w in enumerate(want):
+        assert_level_equal(sh.level_arrays(lvl), w, keys=KEYS, what=f"sharded C1 level {lvl} ")
+    sh.close()
