@@ -7,8 +7,11 @@ implementation timed beside it.
     python bench.py --impl reference ...        # the reference's CPU code (oracle/_ref, else the C port)
 
 A "step" is one full hierarchy build (all levels, all stages) over one synthetic mesh.
-N > 1: one process per GPU (torchrun); the path has no row-sharded build yet, so every rank builds an
-independent replica of the workload ("replicas only", weak scaling, no data-path collective).
+N = 1: config C2 (the configuration the metric is quoted on), single-GPU resident builder.
+N > 1: one process per GPU (torchrun), ROW-SHARDED build (gravo-mg_b200/sharded.py) of ONE noisy torus
+with 12.5 M vertices per GPU (N = 8 is the 100 M-vertex mesh of config C5), generated on the device;
+exchanges are NCCL all-gathers over NVLink; weak scaling. `--workload T<millions>` builds a torus of that
+many vertices at any N (e.g. T25 at N=1 and N=2 gives the strong-scaling pair).
 """
 import argparse
 import json
@@ -33,15 +36,29 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--workload", default=None, help="C1|C2|C3|C4 (single GPU) or T<millions> (torus; sharded when N>1)")
+    ap.add_argument("--per-gpu-mverts", type=float, default=12.5, help="default N>1 workload: torus vertices per GPU (millions)")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--sampler", default="exact", choices=["exact", "parallel"])
     ap.add_argument("--galerkin", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.workload is None:
+        a.workload = "C2" if a.gpus == 1 else f"T{a.per_gpu_mverts * a.gpus:g}"
+    return a
+
+
+def torus_dims(workload):
+    """T<millions> -> (nu, nv) of a square noisy torus grid with about that many vertices."""
+    total = float(workload[1:]) * 1e6
+    side = max(8, int(round(np.sqrt(total))))
+    return side, side
 
 
 def workload_name(a):
+    if a.workload.startswith("T"):
+        nu, nv = torus_dims(a.workload)
+        return f"noisy torus {nu}x{nv} ({nu * nv:,} verts, C5 family), 4 levels, ratio 8, generated on the device"
     base = {"C1": "icosphere 6 subdivisions (40,962 verts), 3 levels",
             "C2": "icosphere 9 subdivisions + vertex noise (2,621,442 verts), 4 levels, ratio 8",
             "C3": "noisy torus 10000x1000 (10,000,000 verts), 4 levels, ratio 8",
@@ -56,9 +73,21 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.nvml = index, [], None, None
 
     def start(self):
+        # NVML in a thread when the binding is importable (no process spawn, no driver-wide stall while the
+        # timed region runs); otherwise the nvidia-smi loop of the profiling recipe.
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.stop_flag = False
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
@@ -66,14 +95,36 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll_nvml(self):
+        n = self.nvml
+        bits = {"hw_slowdown": n.nvmlClocksEventReasonHwSlowdown if hasattr(n, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self.stop_flag:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+                try:
+                    reasons = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                except Exception:
+                    reasons = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.rows.append(["", str(sm), str(mx), "", ""] + ["Active" if reasons & b else "Not Active"
+                                                                       for b in bits.values()])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
-        if self.proc is None:
+        if getattr(self, "nvml", None) is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
+        else:
+            self.proc.terminate()
         sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         reasons = set()
@@ -129,14 +180,18 @@ def run_reference(a, rank, world):
     if rank != 0:
         return
     from gravomg_b200 import meshgen
-    # bounded sample: keep (steps + warmup) * seconds-per-step within a few minutes (~0.25 Mverts/s on one core)
-    budget_s = 150.0
+    name = workload_name(a)
+    if a.workload.startswith("T"):      # the torus family: the CPU sample is the C3 generator at a bounded size
+        nu, nv = torus_dims(a.workload)
+        a.scale = nu * nv / 10_000_000.0
+        a.workload = "C3"
+    # bounded sample: every step about 10-25 s of CPU work and the whole run within a few minutes
+    # (the reference builds ~0.13-0.4 Mverts/s on one core, depending on the mesh)
+    per_step_s = min(25.0, 150.0 / max(1, a.steps + a.warmup))
     full_n = {"C1": 40962, "C2": 2621442, "C3": 10_000_000, "C4": 20_000_000}[a.workload] * a.scale
-    est = full_n / 0.25e6 * (a.steps + a.warmup)
     scale = a.scale
-    while est > budget_s and scale > 1e-4:
+    while full_n * (scale / a.scale) / 0.13e6 > per_step_s and scale > 1e-5:
         scale /= 4.0
-        est /= 4.0
     cfg = meshgen.make_config(a.workload, scale)
     V, A = cfg["V"], cfg["A"]
     n = V.shape[0]
@@ -151,7 +206,7 @@ def run_reference(a, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mverts/s", "n_gpus": a.gpus,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sampler": "exact (sequential greedy)", "cpu_sample_verts": n},
+            "config": {"workload": name, "sampler": "exact (sequential greedy)", "cpu_sample_verts": n},
             "cpu_baseline": {"value": value, "unit": "Mverts/s", "cores": 1, "kind": kind, "sample": sample,
                              "host_cores": os.cpu_count()},
             "e2e": {"value": value, "unit": "Mverts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -177,7 +232,8 @@ def run_b200(a, rank, world, local_rank):
     n = V.shape[0]
     mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)         # a real stream shared by the library and the timing events
     ctx = Context(local_rank, stream.cuda_stream)
 
     # pinned host copies of the inputs for the end-to-end arm
@@ -306,6 +362,128 @@ def run_b200(a, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+# ---- B200 arm, N > 1 (and any torus workload): row-sharded build --------------------------------------
+def run_b200_sharded(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from gravomg_b200 import capi
+    from gravomg_b200.capi import Context, Input
+    from gravomg_b200.sharded import ShardedHierarchy, TorchComm
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)         # a real stream shared by the library, the NCCL exchanges and the timing events
+    ctx = Context(local_rank, stream.cuda_stream)
+    comm = TorchComm() if world > 1 else None
+    nu, nv = torus_dims(a.workload)
+    n = nu * nv
+    levels = 4
+    mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
+    inp = Input.torus(ctx, nu, nv)                       # the whole mesh, resident on every rank
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def build(which):
+        return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode)
+
+    for _ in range(a.warmup):
+        build(inp).close()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    launches0 = ctx.launch_count
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    infos, exchanges, xbytes = None, 0, 0
+    barrier()
+    t_all0 = time.perf_counter()
+    for s in range(a.steps):
+        flush.fill_(s & 0xFF)
+        barrier()
+        ev[s][0].record(stream)
+        h = build(inp)
+        ev[s][1].record(stream)
+        torch.cuda.synchronize()
+        infos = [h.info(l) for l in range(h.num_levels)]
+        exchanges, xbytes = h.exchanges, h.exchange_bytes
+        h.close()
+    barrier()
+    launches = ctx.launch_count - launches0
+    clk = clocks.stop()
+    ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in ev]))
+
+    # end to end: host buffers -> device (every rank uploads the whole mesh), build, owned rows of P -> host
+    hV, hcp, hri = inp.fetch_arrays()
+    tV = torch.from_numpy(hV.T).pin_memory(); hV = tV.numpy().T
+    tcp = torch.from_numpy(hcp).pin_memory(); hcp = tcp.numpy()
+    tri = torch.from_numpy(hri).pin_memory(); hri = tri.numpy()
+
+    def step_e2e():
+        i2 = Input(ctx, hV, hcp, hri, None)
+        h2 = build(i2)
+        d2h = 0
+        for lvl in range(h2.num_levels):
+            for which in (capi.H_P_ROWPTR, capi.H_P_COLIDX, capi.H_P_VAL):
+                d2h += h2.fetch(lvl, which).nbytes
+        nb = i2.h2d_bytes
+        h2.close(); i2.close()
+        return nb, d2h
+
+    step_e2e()
+    e2e_ms, h2d, d2h = [], 0, 0
+    for s in range(max(1, min(a.steps, 2))):
+        barrier()
+        t0 = time.perf_counter()
+        h2d, d2h = step_e2e()
+        barrier()
+        e2e_ms.append(1e3 * (time.perf_counter() - t0))
+    e2e = float(np.mean(e2e_ms))
+
+    if world > 1:
+        t = torch.tensor([ms, e2e], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e = float(t[0]), float(t[1])
+        b = torch.tensor([float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(b, op=dist.ReduceOp.SUM)
+        h2d, d2h = int(b[0]), int(b[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = measured_peak()
+    for i in infos:
+        i.setdefault("nnz_ac", 0)
+    total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if k != "galerkin") for i in infos)
+    achieved = total_bytes / (ms * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": False,
+                       "l2": "256 MB flush write between timed steps; inputs exceed the 126 MB L2",
+                       "multi_gpu": (f"row-sharded over {world} ranks: owned ranges of fine vertices, replicated level "
+                                     f"graph, {exchanges} NCCL all-gathers ({xbytes / 1e6:.1f} MB gathered per rank) per build")
+                       if world > 1 else "single GPU through the sharded driver (world 1)",
+                       "verts_per_gpu": n // world,
+                       "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "sampler_rounds", "parent_rounds")}
+                                  for i in infos]},
+            "clocks": clk, "gpu_launches": int(launches),
+            "e2e": {"value": n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "roofline": {"bound": "hbm", "kernel": "whole sharded build (all stages, all levels, exchanges included)",
+                         "achieved": achieved / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s per GPU",
+                         "frac": achieved / world / peak, "traffic": None, "algorithmic_bytes": int(total_bytes)}}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -313,6 +491,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
         run_reference(a, rank, world)
+    elif world > 1 or a.workload.startswith("T"):
+        run_b200_sharded(a, rank, world, local_rank)
     else:
         run_b200(a, rank, world, local_rank)
 

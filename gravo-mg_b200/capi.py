@@ -92,6 +92,9 @@ class Context:
 
     def __init__(self, device=0, stream=None):
         self.lib = load_library()
+        # stream: a cudaStream_t handle to run on (e.g. torch.cuda.Stream().cuda_stream); None or 0 makes
+        # the library create its own stream (0 is the legacy default stream, which it never uses)
+        self.stream_handle = int(stream or 0)
         h = C.c_void_p()
         rc = self.lib.gmg_create(C.c_int(device), C.c_void_p(stream or 0), C.byref(h))
         if rc != 0:
@@ -281,6 +284,31 @@ class Input:
                                             _p(a, _f64p) if a is not None else None, C.byref(h)))
         self.h = h
         self.h2d_bytes = pts.nbytes + colptr.nbytes + rowidx.nbytes + (a.nbytes if a is not None else 0)
+
+    @classmethod
+    def torus(cls, ctx, nu, nv, R=1.0, r=0.3, amplitude=0.2, seed=42):
+        """The noisy torus grid of configs C3/C5 generated on the device (gmg_generate_torus)."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx.lib.gmg_generate_torus.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
+                                               C.c_uint64, C.POINTER(C.c_void_p)]
+        ctx._check(ctx.lib.gmg_generate_torus(ctx.h, nu, nv, R, r, amplitude, seed, C.byref(h)))
+        self.h = h
+        self.n, self.nnz = nu * nv, 7 * nu * nv
+        self.h2d_bytes = 0
+        return self
+
+    def fetch_arrays(self):
+        """(points (n,3) F-order, colptr, rowidx) copied back to the host."""
+        lib = self.ctx.lib
+        lib.gmg_input_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        pts = np.empty((self.n, 3), dtype=np.float64, order="F")
+        cp = np.empty(self.n + 1, dtype=np.int32)
+        ri = np.empty(self.nnz, dtype=np.int32)
+        for which, arr in ((0, pts), (1, cp), (2, ri)):
+            self.ctx._check(lib.gmg_input_fetch(self.ctx.h, self.h, which, arr.ctypes.data_as(C.c_void_p)))
+        return pts, cp, ri
 
     def close(self):
         if getattr(self, "h", None) and getattr(self.ctx, "h", None):

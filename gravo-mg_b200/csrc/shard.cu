@@ -35,8 +35,6 @@ struct gmg_shard {
     int64_t nnz = 0;
     int32_t lo = 0, hi = 0;          // owned fine vertices
     int32_t chunk = 0;               // slice length of the per-vertex exchange buffers (n_pad = chunk * world)
-    DevBuf<double> pts_own, val_own; // level-0 copies (later levels view the previous level's coarse data)
-    DevBuf<int32_t> colptr_own, rowidx_own;
     const double* pts = nullptr;
     const int32_t* colptr = nullptr;
     const int32_t* rowidx = nullptr;
@@ -156,26 +154,22 @@ void begin_level(gmg_shard* s) {
 
 extern "C" {
 
-int gmg_shard_create(gmg_ctx* c, int rank, int world, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
-                     const int32_t* rowidx, const gmg_hierarchy_options* opt, gmg_shard** out) {
+int gmg_shard_create(gmg_ctx* c, int rank, int world, const gmg_input* in, const gmg_hierarchy_options* opt,
+                     gmg_shard** out) {
     if (!out) return GMG_ERR_INVALID;
     *out = nullptr;
     return guarded_s(c, [&] {
+        GMG_REQUIRE(in, GMG_ERR_INVALID, "null input");
         GMG_REQUIRE(opt && opt->levels >= 1, GMG_ERR_INVALID, "levels must be >= 1");
         GMG_REQUIRE(world >= 1 && rank >= 0 && rank < world, GMG_ERR_INVALID, "bad rank/world");
-        GMG_REQUIRE(n >= 0 && n < (int64_t(1) << 31) / 3, GMG_ERR_INVALID, "vertex count too large for 32-bit indices");
         GMG_REQUIRE(!opt->build_galerkin, GMG_ERR_INVALID, "the row-sharded build does not form Galerkin operators yet");
         std::unique_ptr<gmg_shard> s(new gmg_shard());
         s->ctx = c; s->rank = rank; s->world = world; s->opt = *opt;
         if (opt->radius_override) s->radius_override.assign(opt->radius_override, opt->radius_override + (opt->levels - 1));
         s->opt.radius_override = nullptr;
-        s->n = int32_t(n); s->nnz = colptr[n];
-        s->pts_own = points_to_device(c, points, n, ld);
-        s->colptr_own = to_device(c, colptr, n + 1);
-        s->rowidx_own = to_device(c, rowidx, s->nnz);
-        s->pts = s->pts_own.p; s->colptr = s->colptr_own.p; s->rowidx = s->rowidx_own.p;
-        check_pattern(c, s->n, s->colptr, s->rowidx, true);
-        sync(c);
+        // level 0 is a VIEW of the input (which must outlive the shard): the whole graph, on every rank
+        s->n = in->n; s->nnz = in->nnz;
+        s->pts = in->pts.p; s->colptr = in->colptr.p; s->rowidx = in->rowidx.p;
         *out = s.release();
     });
 }

@@ -72,8 +72,8 @@ class TorchComm:
 class ShardRank:
     """One rank's gmg_shard handle."""
 
-    def __init__(self, ctx, rank, world, points, colptr, rowidx, opt):
-        self.ctx, self.rank, self.world = ctx, rank, world
+    def __init__(self, ctx, rank, world, inp, opt):
+        self.ctx, self.rank, self.world, self._inp = ctx, rank, world, inp
         lib = ctx.lib
         lib.gmg_shard_phase.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
         lib.gmg_shard_buffer.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int32),
@@ -83,11 +83,9 @@ class ShardRank:
         lib.gmg_shard_num_levels.argtypes = [C.c_void_p]
         lib.gmg_shard_level_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
         lib.gmg_shard_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
-        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
-        n = pts.shape[0]
+        lib.gmg_shard_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
         h = C.c_void_p()
-        ctx._check(lib.gmg_shard_create(ctx.h, C.c_int(rank), C.c_int(world), C.c_int64(n), _p(pts, _f64p), C.c_int64(n),
-                                        _p(colptr, _i32p), _p(rowidx, _i32p), C.byref(opt), C.byref(h)))
+        ctx._check(lib.gmg_shard_create(ctx.h, C.c_int(rank), C.c_int(world), inp.h, C.byref(opt), C.byref(h)))
         self.h = h
         self.io = (C.c_int64 * 8)()
 
@@ -115,16 +113,18 @@ class ShardedHierarchy:
     """Row-sharded build. `ranks` is the list of ranks THIS process runs: one (its torch.distributed rank)
     in production, all of them as virtual ranks with comm=None (loop-back on one GPU) in the tests."""
 
-    def __init__(self, ctx, points, colptr, rowidx, levels, world, ranks, comm=None, ratio=8.0,
+    def __init__(self, ctx, inp, levels, world, ranks, comm=None, ratio=8.0,
                  weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_PARALLEL, seed=0, radius_policy=0,
-                 radius_override=None, device=None, same_stream=False):
+                 radius_override=None, device=None):
         import torch
         self.torch = torch
         self.ctx, self.world, self.comm = ctx, world, comm
         # The exchange runs on torch's current stream. If `ctx` was created on that very stream
-        # (Context(device, torch.cuda.current_stream().cuda_stream)) the phases and the exchanges are
-        # ordered by the stream itself; otherwise every exchange is fenced by a device synchronise.
-        self.same_stream = same_stream
+        # (s = torch.cuda.Stream(); torch.cuda.set_stream(s); Context(device, s.cuda_stream)) the phases and
+        # the exchanges are ordered by the stream itself; otherwise (the library's own stream, or torch's
+        # legacy default stream 0, which the library never runs on) every exchange is fenced by a device
+        # synchronise on both sides.
+        self.same_stream = ctx.stream_handle != 0 and ctx.stream_handle == torch.cuda.current_stream().cuda_stream
         if comm is not None and len(ranks) != 1:
             raise ValueError("with a communicator every process runs exactly one rank")
         if comm is None and sorted(ranks) != list(range(world)):
@@ -137,7 +137,8 @@ class ShardedHierarchy:
         self._ro = ro
         opt = HierarchyOptions(levels, ratio, weighting, sampler_mode, seed, radius_policy,
                                _p(ro, _f64p) if ro is not None else None, 0)
-        self.shards = [ShardRank(ctx, r, world, points, colptr, rowidx, opt) for r in ranks]
+        # `inp` (capi.Input): the whole level-0 problem resident on this device; virtual ranks share it
+        self.shards = [ShardRank(ctx, r, world, inp, opt) for r in ranks]
         self.exchanges = 0
         self.exchange_bytes = 0
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

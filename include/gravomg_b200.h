@@ -140,6 +140,16 @@ int gmg_input_create(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, 
                      const int32_t* rowidx, const double* A_val, gmg_input** out);
 void gmg_input_destroy(gmg_input* in);
 
+/* Level-0 problems generated on the device [not in reference; the step before the hot path]: the noisy
+ * torus grid of configs C3/C5 (nu x nv vertices, vertex (i,j) = i*nv + j, quads split on the same
+ * diagonal, positions displaced by amplitude * h * splitmix64 noise; pattern = adjacency + diagonal).
+ * gmg_input_fetch copies an array back to the host: 0 points (f64[3n], column-major n x 3),
+ * 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]). */
+int gmg_generate_torus(gmg_ctx* ctx, int32_t nu, int32_t nv, double R, double r, double amplitude, uint64_t seed,
+                       gmg_input** out);
+int gmg_input_fetch(gmg_ctx* ctx, const gmg_input* in, int which, void* host_out);
+int gmg_input_size(const gmg_input* in, int64_t* n, int64_t* nnz);
+
 typedef struct {
     int32_t levels;          /* levels including the finest; levels-1 prolongations are built */
     double ratio;            /* radius = cbrt(ratio) * averageEdgeLength  (test/main.cpp:74) */
@@ -243,9 +253,10 @@ enum { GMG_PH_LEVEL_BEGIN = 0, GMG_PH_SAMPLER_BUILD, GMG_PH_SAMPLER_ROUND, GMG_P
        GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END };
 enum { GMG_XB_STATE = 0, GMG_XB_CHANGED, GMG_XB_DIST, GMG_XB_PRED, GMG_XB_PARENTS, GMG_XB_COARSE_COUNT, GMG_XB_ROWS_ID,
        GMG_XB_ROWS_VAL };
-/* points/colptr/rowidx are HOST pointers to the whole level-0 problem (the same on every rank) */
-int gmg_shard_create(gmg_ctx* ctx, int rank, int world, int64_t n, const double* points, int64_t ld,
-                     const int32_t* colptr, const int32_t* rowidx, const gmg_hierarchy_options* opt, gmg_shard** out);
+/* `in` is the WHOLE level-0 problem, resident on this rank's device (the same on every rank); it must
+ * outlive the shard */
+int gmg_shard_create(gmg_ctx* ctx, int rank, int world, const gmg_input* in, const gmg_hierarchy_options* opt,
+                     gmg_shard** out);
 void gmg_shard_destroy(gmg_shard* s);
 /* io: host array of at least 8 int64 */
 int gmg_shard_phase(gmg_ctx* ctx, gmg_shard* s, int phase, int64_t* io);

@@ -31,8 +31,8 @@ def test_sharded_equals_single_gpu(ctx, name, scale, world, mode):
     cfg = meshgen.make_config(name, scale)
     V, A = cfg["V"], cfg["A"]
     want = _single(ctx, V, A, cfg["levels"], mode)
-    sh = ShardedHierarchy(ctx, V, A.indptr, A.indices, cfg["levels"], world, list(range(world)), comm=None,
-                          sampler_mode=mode, seed=7)
+    inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=mode, seed=7)
     assert sh.num_levels == len(want)
     for lvl, w in enumerate(want):
         g = sh.level_arrays(lvl)
@@ -47,7 +47,7 @@ def test_sharded_equals_single_gpu(ctx, name, scale, world, mode):
         his = [sh.info(lvl, k)["row_hi"] for k in range(world)]
         assert los[0] == 0 and his[-1] == sh.info(lvl)["n"] and all(a == b for a, b in zip(his[:-1], los[1:]))
     assert sh.exchanges > 0
-    sh.close()
+    sh.close(); inp.close()
 
 
 def test_sharded_exact_matches_oracle(ctx, orc):
@@ -55,10 +55,27 @@ def test_sharded_exact_matches_oracle(ctx, orc):
     from gravomg_b200.sharded import ShardedHierarchy
     cfg = meshgen.make_config("C1")
     V, A = cfg["V"], cfg["A"]
-    sh = ShardedHierarchy(ctx, V, A.indptr, A.indices, cfg["levels"], 4, [0, 1, 2, 3], comm=None,
-                          sampler_mode=capi.SAMPLER_EXACT)
+    inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], 4, [0, 1, 2, 3], comm=None, sampler_mode=capi.SAMPLER_EXACT)
     radii = [sh.info(l)["radius"] for l in range(sh.num_levels)]
     want = run_hierarchy(orc, V, A, cfg["levels"], radii=radii)
     for lvl, w in enumerate(want):
         assert_level_equal(sh.level_arrays(lvl), w, keys=KEYS, what=f"sharded C1 level {lvl} ")
-    sh.close()
+    sh.close(); inp.close()
+
+
+def test_device_torus_generator(ctx):
+    """gmg_generate_torus against the host generator: identical pattern; positions equal up to the last
+    ulp of sin/cos (the noise is bit-identical by construction)."""
+    nu, nv = 50, 20
+    V, F = meshgen.torus_grid(nu, nv)
+    V = meshgen.add_noise(V, min(2 * np.pi * 1.3 / nu, 2 * np.pi * 0.3 / nv))
+    A = meshgen.cotangent_laplacian(V, F)
+    inp = capi.Input.torus(ctx, nu, nv)
+    pts, cp, ri = inp.fetch_arrays()
+    assert np.array_equal(cp, A.indptr) and np.array_equal(ri, A.indices)
+    assert np.abs(pts - V).max() < 1e-15
+    # and it feeds the build
+    h = capi.Hierarchy(ctx, inp, 3, sampler_mode=capi.SAMPLER_PARALLEL)
+    assert h.num_levels == 2 and h.info[0]["m"] > 0
+    h.close(); inp.close()

@@ -1,0 +1,62 @@
+#!/usr/bin/env python
+"""Multi-process check of the row-sharded build over NCCL (run under torchrun on a multi-GPU box):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        tools/dist_parity_check.py [C3 0.05]
+
+Every rank builds the sharded hierarchy (its own range, NCCL all-gathers) AND the single-GPU hierarchy of
+the same mesh, and compares: replicated arrays whole, P on its owned rows. Bit-exact or it fails."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+from gravomg_b200 import capi, meshgen
+from gravomg_b200.sharded import ShardedHierarchy, TorchComm
+
+name = sys.argv[1] if len(sys.argv) > 1 else "C3"
+scale = float(sys.argv[2]) if len(sys.argv) > 2 else 0.05
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+stream = torch.cuda.Stream()
+torch.cuda.set_stream(stream)                 # a real stream: the library never runs on the legacy stream 0
+ctx = capi.Context(local, stream.cuda_stream)
+cfg = meshgen.make_config(name, scale)
+V, A = cfg["V"], cfg["A"]
+inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+bad = 0
+for mode in (capi.SAMPLER_PARALLEL, capi.SAMPLER_EXACT) if name != "C3" else (capi.SAMPLER_PARALLEL,):
+    single = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=mode, seed=3)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=mode, seed=3)
+    assert sh.same_stream
+    assert sh.num_levels == single.num_levels
+    for lvl in range(single.num_levels):
+        w = single.level_arrays(lvl)
+        for key, which in (("sel", capi.H_SAMPLES), ("par", capi.H_PARENTS), ("ccp", capi.H_COARSE_COLPTR),
+                           ("cri", capi.H_COARSE_ROWIDX), ("cval", capi.H_COARSE_VAL), ("cpts", capi.H_COARSE_POINTS),
+                           ("tri", capi.H_TRIANGLES), ("nrm", capi.H_NORMALS), ("fan", capi.H_FAN)):
+            if not np.array_equal(sh.fetch(lvl, which), w[key]):
+                bad += 1
+                print(f"rank {rank} mode {mode} level {lvl}: {key} differs", flush=True)
+        i = sh.info(lvl)
+        lo, hi = i["row_lo"], i["row_hi"]
+        rp = sh.fetch(lvl, capi.H_P_ROWPTR)
+        b, e = w["prp"][lo], w["prp"][hi]
+        if not (np.array_equal(rp, w["prp"][lo:hi + 1] - b) and np.array_equal(sh.fetch(lvl, capi.H_P_COLIDX), w["pci"][b:e])
+                and np.array_equal(sh.fetch(lvl, capi.H_P_VAL), w["pva"][b:e])):
+            bad += 1
+            print(f"rank {rank} mode {mode} level {lvl}: P rows [{lo},{hi}) differ", flush=True)
+    print(f"rank {rank}/{world} mode {mode}: {single.num_levels} levels, n={V.shape[0]}, exchanges {sh.exchanges}, "
+          f"sharded {sh.build_ms:.2f} ms vs single {single.build_ms:.2f} ms, mismatches so far {bad}", flush=True)
+    sh.close(); single.close()
+t = torch.tensor([bad], device="cuda")
+dist.all_reduce(t)
+if rank == 0:
+    print("DIST PARITY OK" if int(t[0]) == 0 else f"DIST PARITY FAILED ({int(t[0])} mismatches)", flush=True)
+dist.destroy_process_group()
+sys.exit(0 if int(t[0]) == 0 else 1)
