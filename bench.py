@@ -162,6 +162,24 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+# kernels of each stage (for roofline.traffic: DRAM bytes per launch from the committed ncu --set full capture)
+STAGE_KERNELS = {"edge_lengths": ["edge_length_kernel"], "sampling": ["sampler_build_kernel<0>", "sampler_flow_kernel<0>"],
+                 "parents": ["parents_sweep_kernel", "parents_pred_kernel"], "coarse_edges": ["coarse_rows_warp_kernel"],
+                 "prolongation_rows": ["prolong_rows_kernel"]}
+
+
+def ncu_traffic(workload, stage):
+    """DRAM read+write bytes of the stage's main kernels at level 0, from profiles/traffic_<workload>_level0.json
+    (written by tools/ncu_summary.py from an `ncu --set full` capture of this same command); None if absent."""
+    p = os.path.join(ROOT, "profiles", f"traffic_{workload.lower()}_level0.json")
+    if not os.path.exists(p) or stage not in STAGE_KERNELS:
+        return None, None
+    with open(p) as f:
+        js = json.load(f)
+    got = [js["kernels"][k]["dram_bytes"] for k in STAGE_KERNELS[stage] if k in js["kernels"]]
+    return (int(sum(got)), js["capture"]) if got else (None, None)
+
+
 # ---- CPU arm: the reference's own code on the host cores ---------------------------------------------
 def cpu_hierarchy_seconds(V, A, levels):
     """One hierarchy build with the reference's CPU implementation (unmodified sources on the Eigen
@@ -325,6 +343,7 @@ def run_b200(a, rank, world, local_rank):
     dom = int(np.argmax(stage_ms[0]))
     bytes0 = stage_bytes(infos[0])[names[dom]]
     achieved = bytes0 / (stage_ms[0][dom] * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(a.workload, names[dom]) if a.scale == 1.0 and a.sampler == "exact" else (None, None)
     total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if (k != "galerkin" or a.galerkin)) for i in infos)
     line = {"metric": METRIC, "value": world * n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -337,9 +356,11 @@ def run_b200(a, rank, world, local_rank):
             "clocks": clk, "gpu_launches": int(launches),
             "e2e": {"value": world * n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
-            "roofline": {"bound": "hbm", "kernel": f"level-0 stage '{names[dom]}'", "achieved": achieved,
-                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "algorithmic_bytes": int(bytes0), "stage_ms": float(stage_ms[0][dom]),
+            "roofline": {"bound": "hbm",
+                         "kernel": f"level-0 stage '{names[dom]}' ({' + '.join(STAGE_KERNELS.get(names[dom], [names[dom]]))})",
+                         "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "algorithmic_bytes": int(bytes0), "stage_ms": float(stage_ms[0][dom]),
                          "whole_build": {"algorithmic_bytes": int(total_bytes),
                                          "achieved": total_bytes / (ms * 1e-3) / 1e9,
                                          "frac": total_bytes / (ms * 1e-3) / 1e9 / peak}},
@@ -391,8 +412,8 @@ def run_b200_sharded(a, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def build(which):
-        return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode)
+    def build(which, profile=False):
+        return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode, profile=profile)
 
     for _ in range(a.warmup):
         build(inp).close()
@@ -418,6 +439,10 @@ def run_b200_sharded(a, rank, world, local_rank):
     launches = ctx.launch_count - launches0
     clk = clocks.stop()
     ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in ev]))
+    # one extra, untimed build with per-phase events: where the step goes (rank 0's view)
+    hp = build(inp, profile=True)
+    phase_ms = {k: round(v, 3) for k, v in sorted(hp.phase_ms().items(), key=lambda kv: -kv[1])}
+    hp.close()
 
     # end to end: host buffers -> device (every rank uploads the whole mesh), build, owned rows of P -> host
     hV, hcp, hri = inp.fetch_arrays()
@@ -473,7 +498,7 @@ def run_b200_sharded(a, rank, world, local_rank):
                        "verts_per_gpu": n // world,
                        "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "sampler_rounds", "parent_rounds")}
                                   for i in infos]},
-            "clocks": clk, "gpu_launches": int(launches),
+            "clocks": clk, "gpu_launches": int(launches), "phase_ms": phase_ms,
             "e2e": {"value": n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "roofline": {"bound": "hbm", "kernel": "whole sharded build (all stages, all levels, exchanges included)",

@@ -27,6 +27,9 @@ from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, 
  PH_PARENTS_PRED, PH_PARENTS_RESOLVE, PH_COARSE_ROWS, PH_COARSE_PACK, PH_COARSE_ASSEMBLE, PH_PROLONG,
  PH_LEVEL_END) = range(14)
 (XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL) = range(8)
+PHASE_NAMES = ["level_begin", "sampler_build", "sampler_round", "sampler_check", "samples", "parents_pull", "parents_check",
+               "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end"]
+BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val"]
 
 
 def partition(count, world, rank):
@@ -115,7 +118,7 @@ class ShardedHierarchy:
 
     def __init__(self, ctx, inp, levels, world, ranks, comm=None, ratio=8.0,
                  weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_PARALLEL, seed=0, radius_policy=0,
-                 radius_override=None, device=None):
+                 radius_override=None, device=None, profile=False):
         import torch
         self.torch = torch
         self.ctx, self.world, self.comm = ctx, world, comm
@@ -141,6 +144,7 @@ class ShardedHierarchy:
         self.shards = [ShardRank(ctx, r, world, inp, opt) for r in ranks]
         self.exchanges = 0
         self.exchange_bytes = 0
+        self.profile = {} if profile else None          # name -> [event pairs]; see phase_ms()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         self._build()
@@ -151,6 +155,9 @@ class ShardedHierarchy:
 
     # ---- exchange ------------------------------------------------------------------------------------
     def _gather(self, which):
+        return self._timed("gather_" + BUFFER_NAMES[which], lambda: self._gather_now(which))
+
+    def _gather_now(self, which):
         t = self.torch
         bufs = [s.buffer(which) for s in self.shards]
         slice_bytes = bufs[0][1]
@@ -176,9 +183,26 @@ class ShardedHierarchy:
         if not self.same_stream:
             t.cuda.synchronize()
 
+    def _timed(self, name, fn):
+        if self.profile is None:
+            return fn()
+        t = self.torch
+        e0, e1 = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        self.profile.setdefault(name, []).append((e0, e1))
+        return out
+
+    def phase_ms(self):
+        """Device milliseconds per phase / exchange name, summed over levels (profile=True builds only)."""
+        self.torch.cuda.synchronize()
+        return {k: float(sum(a.elapsed_time(b) for a, b in v)) for k, v in (self.profile or {}).items()}
+
     def _phase(self, ph):
-        ios = [s.phase(ph) for s in self.shards]
-        return ios[0]
+        def run():
+            return [s.phase(ph) for s in self.shards][0]
+        return self._timed(PHASE_NAMES[ph], run)
 
     def _build(self):
         while True:

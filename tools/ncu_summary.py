@@ -58,6 +58,17 @@ def main():
         lines.append(f"| `{name}` | " + " | ".join(cells) + f" | {(rd + wr) / 1e6:.1f} | {(rd + wr) / t_us / 1e3:.0f} |")
     with open(out, "w") as f:
         f.write("\n".join(lines) + "\n")
+    if len(sys.argv) > 4:      # also a machine-readable copy: kernel -> dram bytes per launch (bench.py's roofline.traffic)
+        import json
+        js = {}
+        for r in data:
+            name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("gmg::", "")
+            rd = to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]])
+            wr = to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]])
+            js[name] = {"dram_bytes": int(rd + wr),
+                        "time_us": to_us(r[idx["gpu__time_duration.sum"]], units[idx["gpu__time_duration.sum"]])}
+        with open(sys.argv[4], "w") as f:
+            json.dump({"capture": title, "kernels": js}, f, indent=1)
     print("\n".join(lines))
 
 
