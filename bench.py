@@ -40,7 +40,8 @@ def parse():
     ap.add_argument("--per-gpu-mverts", type=float, default=12.5, help="default N>1 workload: torus vertices per GPU (millions)")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--sampler", default="exact", choices=["exact", "parallel"])
-    ap.add_argument("--galerkin", type=int, default=0)
+    ap.add_argument("--galerkin", type=int, default=0, help="1: also A_c = P^T A P on every level (config C3)")
+    ap.add_argument("--vcycle", type=int, default=0, help="1 (with --galerkin 1): one V-cycle Poisson solve and an SpMV, timed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
     if a.workload is None:
@@ -366,6 +367,37 @@ def run_b200(a, rank, world, local_rank):
                                          "frac": total_bytes / (ms * 1e-3) / 1e9 / peak}},
             "stage_ms": {f"L{l}": {names[s]: round(float(stage_ms[l][s]), 4) for s in range(9)}
                          for l in range(len(infos))}}
+    if a.galerkin:
+        # SpGEMM (P^T A P) of level 0 against the HBM roofline, from the build's own stage events
+        gi = names.index("galerkin")
+        gb = stage_bytes(infos[0])["galerkin"]
+        gms = float(stage_ms[0][gi])
+        line["spgemm"] = {"ms": gms, "algorithmic_bytes": int(gb), "achieved": gb / (gms * 1e-3) / 1e9, "unit": "GB/s",
+                          "frac": gb / (gms * 1e-3) / 1e9 / peak, "nnz_ac": int(infos[0]["nnz_ac"]),
+                          "what": "level-0 transpose + symbolic + numeric passes of A_c = P^T A P"}
+    if a.galerkin and a.vcycle:
+        from gravomg_b200.capi import Solver, spmv
+        h = Hierarchy(ctx, inp, levels, sampler_mode=mode, build_galerkin=True)
+        xs = np.sin(3.0 * V[:, 0]) * np.cos(2.0 * V[:, 1]) + V[:, 2]          # smooth function of position
+        Acsr = A.tocsr()
+        bvec = Acsr @ xs
+        for _ in range(3):
+            spmv(ctx, A.indptr, A.indices, A.data, xs)
+        sp_ms = []
+        for _ in range(5):
+            spmv(ctx, A.indptr, A.indices, A.data, xs)
+            sp_ms.append(ctx.last_kernel_ms)
+        sb = 20 * n + 12 * A.nnz
+        sms = float(np.median(sp_ms))
+        line["spmv"] = {"ms": sms, "algorithmic_bytes": int(sb), "achieved": sb / (sms * 1e-3) / 1e9, "unit": "GB/s",
+                        "frac": sb / (sms * 1e-3) / 1e9 / peak, "what": "y = A x on the level-0 operator, device time"}
+        sol = Solver(ctx, inp, h)
+        sol.vcycle(bvec, cycles=1)                                             # warm-up (colourings are built here)
+        x1, res = sol.vcycle(bvec, cycles=1, pre=2, post=2)
+        line["vcycle"] = {"ms": ctx.last_kernel_ms, "residual_before": float(res[0]), "residual_after": float(res[1]),
+                          "reduction": float(res[1] / res[0]), "what": "one V(2,2) cycle on A x = b, multicolour Gauss-Seidel, "
+                          "b = A x*, x* smooth; device time of the cycle"}
+        sol.close(); h.close()
     if not a.no_cpu_baseline:
         # bounded sample of the same workload on the host cores (about 10-30 s of CPU work)
         scale = a.scale

@@ -105,7 +105,7 @@ void exclusive_scan_i32(gmg_ctx* c, const int32_t* in, int32_t* out, int64_t n, 
 // ---------------------------------------------------------------------------------------------
 constexpr int kGroup = 8;
 
-__global__ void __launch_bounds__(kBlock) edge_length_kernel(int32_t n, const int32_t* __restrict__ colptr,
+__global__ void __launch_bounds__(kBlock, 8) edge_length_kernel(int32_t n, const int32_t* __restrict__ colptr,
                                                              const int32_t* __restrict__ rowidx,
                                                              const double* __restrict__ pts,
                                                              double* __restrict__ out_len) {

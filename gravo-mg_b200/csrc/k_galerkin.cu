@@ -85,11 +85,13 @@ __device__ __forceinline__ bool galerkin_row(const GalerkinArgs& a, int32_t i, i
     if (tid == 0) *scount = 0;
     if (THREADS == 32) __syncwarp(); else __syncthreads();
     const int32_t rb = __ldg(a.r_ptr + i), re = __ldg(a.r_ptr + i + 1);
-    for (int32_t e = rb; e < re; ++e) {
+    // 8 lanes per fine row k (outer vectors of A hold ~7 entries), THREADS/8 rows in flight
+    constexpr int kSub = 8;
+    for (int32_t e = rb + tid / kSub; e < re; e += THREADS / kSub) {
         const int32_t k = __ldg(a.r_col + e);
         const double pki = NUMERIC ? __ldg(a.r_val + e) : 0.0;
         const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
-        for (int32_t q = ab + tid; q < ae; q += THREADS) {
+        for (int32_t q = ab + tid % kSub; q < ae; q += kSub) {
             const int32_t l = __ldg(a.a_idx + q);
             const double w = NUMERIC ? pki * __ldg(a.a_val + q) : 0.0;
             const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
@@ -113,6 +115,28 @@ __device__ __forceinline__ bool galerkin_row(const GalerkinArgs& a, int32_t i, i
     if (K > SLOTS * 3 / 4) return false;
     if (!NUMERIC) { if (tid == 0) a.out_count[i] = K; return true; }
     const int32_t off = __ldg(a.out_ptr + i);
+    if constexpr (THREADS == 32) {
+        // compact the occupied slots to the front (in place: a slot only moves down and every chunk is
+        // read before it is written), then rank-sort the K survivors
+        int32_t base = 0;
+        for (int s0 = 0; s0 < SLOTS; s0 += 32) {
+            const int32_t key = keys[s0 + tid];
+            const double v = vals[s0 + tid];
+            const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
+            __syncwarp();
+            if (key >= 0) { const int pos = base + __popc(occ & ((1u << tid) - 1u)); keys[pos] = key; vals[pos] = v; }
+            base += __popc(occ);
+            __syncwarp();
+        }
+        for (int s = tid; s < K; s += 32) {
+            const int32_t key = keys[s];
+            int32_t rank = 0;
+            for (int s2 = 0; s2 < K; ++s2) rank += keys[s2] < key ? 1 : 0;
+            a.out_idx[off + rank] = key;
+            a.out_val[off + rank] = vals[s];
+        }
+        return true;
+    }
     for (int s = tid; s < SLOTS; s += THREADS) {
         const int32_t key = keys[s];
         if (key < 0) continue;

@@ -102,7 +102,7 @@ __device__ __forceinline__ void emit_row(const ProlongArgs& a, int32_t f, const 
     for (int i = 0; i < k; ++i) { a.row_col[3 * r + i] = c[i]; a.row_val[3 * r + i] = v[i]; }
 }
 
-__global__ void __launch_bounds__(kBlock) prolong_rows_kernel(ProlongArgs a) {
+__global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a) {
     const int64_t gid = int64_t(a.f_lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (gid >= a.f_hi) return;
     const int32_t f = int32_t(gid);
