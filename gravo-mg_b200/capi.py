@@ -353,7 +353,10 @@ class Hierarchy:
 
     __del__ = close
 
-    def fetch(self, level, which):
+    def fetch(self, level, which, out=None):
+        """Copy one array of a level to the host. `out`: optional preallocated (e.g. pinned) 1-D numpy array of
+        the right dtype and at least the right length -- device-to-pinned copies run at PCIe speed, copies
+        into fresh pageable memory are staged and several times slower."""
         i = self.info[level]
         n, m, T = i["n"], i["m"], i["T"]
         shape_dtype = {
@@ -364,7 +367,10 @@ class Hierarchy:
             H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64), H_AC_COLPTR: (m + 1, np.int32),
             H_AC_ROWIDX: (i["nnz_ac"], np.int32), H_AC_VAL: (i["nnz_ac"], np.float64), H_FINE_VAL: (i["nnz"], np.float64),
         }[which]
-        out = np.empty(max(shape_dtype[0], 1), dtype=shape_dtype[1])
+        if out is None:
+            out = np.empty(max(shape_dtype[0], 1), dtype=shape_dtype[1])
+        elif out.dtype != shape_dtype[1] or out.ndim != 1 or out.shape[0] < shape_dtype[0] or not out.flags.c_contiguous:
+            raise ValueError("fetch: `out` must be a contiguous 1-D array of the array's dtype and length")
         self.ctx._check(self.ctx.lib.gmg_hierarchy_fetch(self.ctx.h, self.h, C.c_int(level), C.c_int(which),
                                                          out.ctypes.data_as(C.c_void_p)))
         out = out[:shape_dtype[0]]

@@ -395,11 +395,30 @@ __global__ void __launch_bounds__(kBlock) shard_pull_kernel(int32_t lo, int32_t 
     if (all_out) state8[v] = uint8_t(kIn);                               // nobody before it covers it (:25-28)
 }
 
+// how many of the n bytes equal `what`: 16 bytes per thread and load, one atomic per block
 __global__ void __launch_bounds__(kBlock) count_state_kernel(int64_t n, const uint8_t* __restrict__ state8, uint8_t what,
                                                              unsigned long long* __restrict__ out) {
-    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    const unsigned m = __ballot_sync(0xffffffffu, i < n && state8[i] == what);
-    if ((threadIdx.x & 31) == 0 && m) atomicAdd(out, (unsigned long long)__popc(m));
+    __shared__ unsigned int s_warp[kBlock / 32];
+    const int64_t chunks = n / 16;
+    unsigned int c = 0;
+    for (int64_t q = int64_t(blockIdx.x) * kBlock + threadIdx.x; q < chunks; q += int64_t(gridDim.x) * kBlock) {
+        const uint4 w = __ldg(reinterpret_cast<const uint4*>(state8) + q);
+        const unsigned int words[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) c += ((words[k] >> (8 * b)) & 0xFFu) == what ? 1u : 0u;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < n - chunks * 16) c += state8[chunks * 16 + threadIdx.x] == what ? 1u : 0u;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) c += __shfl_down_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned int t = 0;
+        for (int w = 0; w < kBlock / 32; ++w) t += s_warp[w];
+        if (t) atomicAdd(out, (unsigned long long)t);
+    }
 }
 __global__ void __launch_bounds__(kBlock) flag_in8_kernel(int32_t n, const uint8_t* __restrict__ state8,
                                                           int32_t* __restrict__ flag) {
@@ -443,7 +462,11 @@ void shard_sampler_round(gmg_ctx* c, const ShardSampler& s, uint8_t* state8) {
 int64_t count_state(gmg_ctx* c, int64_t n, const uint8_t* state8, int what) {
     DevBuf<unsigned long long> out(c, 1);
     out.zero();
-    if (n > 0) GMG_LAUNCH(c, count_state_kernel, div_up(n, kBlock), kBlock, 0, n, state8, uint8_t(what), out.p);
+    if (n > 0) {
+        const int64_t want = div_up(n / 16 + 1, kBlock);
+        const int grid = int(want < 4 * int64_t(c->sm_count) ? want : 4 * int64_t(c->sm_count));
+        GMG_LAUNCH(c, count_state_kernel, grid, kBlock, 0, n, state8, uint8_t(what), out.p);
+    }
     unsigned long long h = 0;
     out.download(&h, 1);
     sync(c);

@@ -243,7 +243,7 @@ class ShardedHierarchy:
         d["row_lo"], d["row_hi"] = int(lo.value), int(hi.value)
         return d
 
-    def fetch(self, level, which, shard=0):
+    def fetch(self, level, which, shard=0, out=None):
         i = self.info(level, shard)
         n, m, T, own = i["n"], i["m"], i["T"], i["row_hi"] - i["row_lo"]
         count, dtype = {
@@ -252,7 +252,10 @@ class ShardedHierarchy:
             H_COARSE_POINTS: (3 * m, np.float64), H_TRIANGLES: (3 * T, np.int64), H_NORMALS: (3 * T, np.float64),
             H_FAN_PTR: (m + 1, np.int64), H_FAN: (3 * T, np.int64), H_P_ROWPTR: (own + 1, np.int32),
             H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64)}[which]
-        out = np.empty(max(count, 1), dtype=dtype)
+        if out is None:
+            out = np.empty(max(count, 1), dtype=dtype)
+        elif out.dtype != dtype or out.ndim != 1 or out.shape[0] < count:
+            raise ValueError("fetch: `out` must be a 1-D array of the array's dtype and length")
         s = self.shards[shard]
         self.ctx._check(self.ctx.lib.gmg_shard_fetch(self.ctx.h, s.h, C.c_int(level), C.c_int(which),
                                                      out.ctypes.data_as(C.c_void_p)))
