@@ -109,9 +109,21 @@ __device__ __forceinline__ void for_each_covered(const SamplerArgs& a, int32_t s
         if (d < a.radius) {                                            // src/sampling.cpp:35
             if (j != self) f(j);
             const int32_t b2 = __ldg(a.colptr + j), e2 = __ldg(a.colptr + j + 1);
-            for (int32_t k2 = b2; k2 < e2; ++k2) {                     // :43
-                const int32_t t = __ldg(a.rowidx + k2);
-                if (d + __ldg(a.len + k2) < a.radius && t != self) f(t);  // :44
+            // four entries per step, loads issued before any is consumed: the kernel waits on memory
+            // latency (long-scoreboard stalls), so what counts is how many loads a lane has in flight
+            constexpr int kUnroll = 4;
+            for (int32_t k2 = b2; k2 < e2; k2 += kUnroll) {            // :43
+                int32_t t[kUnroll];
+                double l[kUnroll];
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    const bool in = k2 + u < e2;
+                    t[u] = in ? __ldg(a.rowidx + k2 + u) : self;
+                    l[u] = in ? __ldg(a.len + k2 + u) : 0.0;
+                }
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u)
+                    if (d + l[u] < a.radius && t[u] != self) f(t[u]);  // :44
             }
         }
     }
@@ -207,7 +219,13 @@ __global__ void __launch_bounds__(kBlock) sampler_flow_kernel(SamplerArgs a) {
                 if (st == kIn) {
                     // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); later
                     // coverees of an IN vertex are undecided or already OUT, never IN
-                    for (int32_t k = 0; k < c; ++k) *(volatile int32_t*)(a.state + a.lst[p + k]) = kOut;
+                    for (int32_t k = 0; k < c; k += 4) {
+                        int32_t t[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) t[u] = k + u < c ? a.lst[p + k + u] : -1;
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) if (t[u] >= 0) *(volatile int32_t*)(a.state + t[u]) = kOut;
+                    }
                 } else {
                     for (int32_t k = 0; k < c; k += 4) {
                         int32_t t[4], old[4];
