@@ -127,7 +127,7 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
                 // averageEdgeLength over extractEdges(matrix): every stored entry, divisor nnz - n
                 double denom = double(nnz - n);
                 if (opt->radius_policy == 1) denom = double(lvl == 0 ? nnz - n : nnz);
-                mean_length_dev(c, nnz, len, denom, d_radius.p);
+                mean_length_dev(c, n, nnz, colptr, len, denom, d_radius.p);
                 d_radius.download(&mean, 1);
             }
             d_degsq.download(&degsq, 1);

@@ -108,11 +108,13 @@ constexpr int kGroup = 8;
 __global__ void __launch_bounds__(kBlock, 8) edge_length_kernel(int32_t n, const int32_t* __restrict__ colptr,
                                                              const int32_t* __restrict__ rowidx,
                                                              const double* __restrict__ pts,
-                                                             double* __restrict__ out_len) {
+                                                             double* __restrict__ out_len,
+                                                             const uint8_t* __restrict__ col_mask) {
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t col = int32_t(gid / kGroup);
     const int sub = int(gid % kGroup);
     if (col >= n) return;
+    if (col_mask && !col_mask[col]) return;        // row-sharded build: a column this rank never reads
     const int32_t b = __ldg(colptr + col), e = __ldg(colptr + col + 1);
     const V3 pc = ld3(pts, n, col);
     for (int32_t k = b + sub; k < e; k += kGroup) {
@@ -122,9 +124,10 @@ __global__ void __launch_bounds__(kBlock, 8) edge_length_kernel(int32_t n, const
 }
 
 void edge_lengths(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* pts,
-                  double* out_len) {
+                  double* out_len, const uint8_t* col_mask) {
     if (n == 0) return;
-    GMG_LAUNCH(c, edge_length_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, pts, out_len);
+    GMG_LAUNCH(c, edge_length_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, pts, out_len,
+               col_mask);
 }
 
 // extractEdges: edge e of column c, row r -> edges(e,0) = c, edges(e,1) = r; values copied.
@@ -195,20 +198,6 @@ __global__ void __launch_bounds__(kBlock) sum_partials(const double* __restrict_
     if (threadIdx.x == 0) *out = s / denom;
 }
 
-// Same reduction straight from the CSC arrays (used inside the hierarchy: no edge list is built).
-__global__ void __launch_bounds__(kBlock) length_partial(int64_t nnz, const double* __restrict__ len,
-                                                         double* __restrict__ partial) {
-    const int64_t base = int64_t(blockIdx.x) * kBlock * kSumPerThread;
-    double s = 0.0;
-#pragma unroll
-    for (int k = 0; k < kSumPerThread; ++k) {
-        const int64_t e = base + int64_t(k) * kBlock + threadIdx.x;
-        if (e < nnz) s += __ldg(len + e);
-    }
-    s = block_sum(s);
-    if (threadIdx.x == 0) partial[blockIdx.x] = s;
-}
-
 void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n_edges, const int32_t* edges,
                              double* d_out) {
     const int blocks = n_edges > 0 ? div_up(n_edges, int64_t(kBlock) * kSumPerThread) : 1;
@@ -218,12 +207,66 @@ void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n
     GMG_LAUNCH(c, sum_partials, 1, kBlock, 0, partial.p, int64_t(blocks), double(n_edges - n), d_out);
 }
 
-void mean_length_dev(gmg_ctx* c, int64_t nnz, const double* len, double denom, double* d_out) {
-    const int blocks = nnz > 0 ? div_up(nnz, int64_t(kBlock) * kSumPerThread) : 1;
-    DevBuf<double> partial(c, blocks);
-    if (nnz > 0) GMG_LAUNCH(c, length_partial, blocks, kBlock, 0, nnz, len, partial.p);
-    else partial.zero();
-    GMG_LAUNCH(c, sum_partials, 1, kBlock, 0, partial.p, int64_t(blocks), denom, d_out);
+// Mean stored length inside the hierarchy builders. The summation tree is defined on COLUMN GROUPS so that
+// a row-sharded build reproduces it bit for bit: partial[g] = sum of the entries of columns [32g, 32g+32)
+// (one warp, lane-strided, fixed shuffle tree); the partials are then folded 2048 at a time by fixed block
+// trees until one value is left. Rank boundaries are multiples of 32 columns, so every group has one owner.
+__global__ void __launch_bounds__(kBlock) length_group_partial(int32_t n, int32_t g_lo, int32_t g_hi,
+                                                               const int32_t* __restrict__ colptr,
+                                                               const double* __restrict__ len, double* __restrict__ partial) {
+    const int lane = threadIdx.x & 31;
+    const int64_t g = int64_t(g_lo) + ((int64_t(blockIdx.x) * kBlock + threadIdx.x) >> 5);
+    if (g >= g_hi) return;
+    const int64_t c0 = g * 32, c1 = c0 + 32 < n ? c0 + 32 : n;
+    const int32_t b = colptr[c0], e = colptr[c1];
+    double s = 0.0;
+    for (int32_t k = b + lane; k < e; k += 32) s += __ldg(len + k);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+    if (lane == 0) partial[g] = s;
+}
+
+__global__ void __launch_bounds__(kBlock) fold_partials(const double* __restrict__ in, int64_t count, double* __restrict__ out) {
+    const int64_t base = int64_t(blockIdx.x) * kBlock * kSumPerThread;
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < kSumPerThread; ++k) {
+        const int64_t e = base + int64_t(k) * kBlock + threadIdx.x;
+        if (e < count) s += in[e];
+    }
+    s = block_sum(s);
+    if (threadIdx.x == 0) out[blockIdx.x] = s;
+}
+
+void length_group_partials(gmg_ctx* c, int32_t n, int32_t g_lo, int32_t g_hi, const int32_t* colptr, const double* len,
+                           double* partial) {
+    if (g_hi > g_lo) GMG_LAUNCH(c, length_group_partial, div_up(int64_t(g_hi - g_lo) * 32, kBlock), kBlock, 0, n, g_lo, g_hi,
+                                colptr, len, partial);
+}
+
+void mean_from_group_partials(gmg_ctx* c, int64_t groups, const double* partial, double denom, double* d_out) {
+    const int64_t tile = int64_t(kBlock) * kSumPerThread;
+    DevBuf<double> a, b;
+    const double* cur = partial;
+    int64_t count = groups;
+    bool use_a = true;
+    while (count > tile) {
+        const int64_t blocks = (count + tile - 1) / tile;
+        DevBuf<double>& dst = use_a ? a : b;
+        dst.alloc(c, blocks);
+        GMG_LAUNCH(c, fold_partials, int(blocks), kBlock, 0, cur, count, dst.p);
+        cur = dst.p; count = blocks; use_a = !use_a;
+    }
+    GMG_LAUNCH(c, sum_partials, 1, kBlock, 0, cur, count, denom, d_out);
+}
+
+void mean_length_dev(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const double* len, double denom,
+                     double* d_out) {
+    (void)nnz;
+    const int32_t groups = (n + 31) / 32;
+    DevBuf<double> partial(c, groups > 0 ? groups : 1);
+    length_group_partials(c, n, 0, groups, colptr, len, partial.p);
+    mean_from_group_partials(c, groups, partial.p, denom, d_out);
 }
 
 // Pattern checks: row indices strictly ascending and in range; (r,c) stored => (c,r) stored.

@@ -75,8 +75,9 @@ __device__ __forceinline__ double from_ordered_bits(unsigned long long o) {
     return __longlong_as_double((long long)b);
 }
 
-// q0[fine] = fine_edge_matrix.coeff(fine, parent[fine])
-__global__ void __launch_bounds__(kBlock) quirk_term_kernel(int32_t n, const int32_t* __restrict__ colptr,
+// q0[fine] = fine_edge_matrix.coeff(fine, parent[fine]), for the children of the clusters [p_lo, p_hi)
+__global__ void __launch_bounds__(kBlock) quirk_term_kernel(int32_t n, int32_t p_lo, int32_t p_hi,
+                                                            const int32_t* __restrict__ colptr,
                                                             const int32_t* __restrict__ rowidx,
                                                             const double* __restrict__ val,
                                                             const int32_t* __restrict__ parents,
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(kBlock) quirk_term_kernel(int32_t n, const int
     const int64_t f = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (f >= n) return;
     const int32_t P = __ldg(parents + f);
+    if (P < p_lo || P >= p_hi) { q0[f] = 0.0; return; }
     const int32_t b = __ldg(colptr + P), e = __ldg(colptr + P + 1);
     const int32_t pos = lower_bound_i32(rowidx, b, e, int32_t(f));
     q0[f] = (pos < e && __ldg(rowidx + pos) == int32_t(f)) ? __ldg(val + pos) : 0.0;
@@ -274,7 +276,7 @@ void coarse_rows_range(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32
     out.boff.alloc(c, int64_t(own) + 1);
     if (own <= 0) { out.sQ.alloc(c, 0); out.st.alloc(c, 0); out.bound = 0; return; }
     DevBuf<double> q0(c, n);
-    GMG_LAUNCH(c, quirk_term_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, rowidx, val, parents, q0.p);
+    GMG_LAUNCH(c, quirk_term_kernel, div_up(n, kBlock), kBlock, 0, n, p_lo, p_hi, colptr, rowidx, val, parents, q0.p);
     DevBuf<int32_t> degsum(c, int64_t(own) + 1), flags(c, 4), overflow(c, own);
     degsum.zero(); flags.zero();
     GMG_CUDA(cudaMemsetAsync(cnt + p_lo, 0, sizeof(int32_t) * size_t(own), c->stream));

@@ -31,12 +31,17 @@ __global__ void __launch_bounds__(kBlock) triangle_kernel(int32_t m, const doubl
                                                           int32_t* __restrict__ entry_count,   // !WRITE: out
                                                           const int32_t* __restrict__ entry_off,  // WRITE: in
                                                           int32_t* __restrict__ tri, double* __restrict__ normal,
-                                                          int32_t* __restrict__ fan_count) {
+                                                          int32_t* __restrict__ fan_count,
+                                                          const uint8_t* __restrict__ v0_mask) {
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t v0 = int32_t(gid / kTLanes);
     const int sub = int(gid % kTLanes);
     if (v0 >= m) return;
     const int32_t b = __ldg(colptr + v0), e = __ldg(colptr + v0 + 1);
+    if (v0_mask && !v0_mask[v0]) {                 // row-sharded build: this rank does not need v0's triangles
+        if (!WRITE) for (int32_t a = b + sub; a < e; a += kTLanes) entry_count[a] = 0;
+        return;
+    }
     for (int32_t a = b + sub; a < e; a += kTLanes) {
         const int32_t v1 = __ldg(rowidx + a);
         int32_t count = 0;
@@ -99,7 +104,7 @@ __global__ void __launch_bounds__(kBlock) fan_finish_kernel(int32_t m, const int
 }
 
 void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, const int32_t* colptr,
-                       const int32_t* rowidx, const double* val, Triangles& out) {
+                       const int32_t* rowidx, const double* val, Triangles& out, const uint8_t* v0_mask) {
     out.fan_ptr.alloc(c, int64_t(m) + 1);
     out.T = 0;
     if (m == 0 || nnz == 0) {
@@ -111,7 +116,7 @@ void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, co
     DevBuf<int32_t> entry(c, nnz), fan_count(c, int64_t(m) + 1);
     DevBuf<int64_t> total(c, 1);
     GMG_LAUNCH(c, triangle_kernel<false>, grid, kBlock, 0, m, pts, colptr, rowidx, val, entry.p, nullptr, nullptr,
-               nullptr, nullptr);
+               nullptr, nullptr, v0_mask);
     exclusive_scan_i32(c, entry.p, entry.p, nnz, total.p);
     total.download(&out.T, 1);
     sync(c);
@@ -120,7 +125,7 @@ void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, co
     out.fan_tri.alloc(c, 3 * out.T); out.fan_o1.alloc(c, 3 * out.T); out.fan_o2.alloc(c, 3 * out.T);
     fan_count.zero();
     GMG_LAUNCH(c, triangle_kernel<true>, grid, kBlock, 0, m, pts, colptr, rowidx, val, nullptr, entry.p, out.tri.p,
-               out.normal.p, fan_count.p);
+               out.normal.p, fan_count.p, v0_mask);
     exclusive_scan_i32(c, fan_count.p, out.fan_ptr.p, int64_t(m) + 1, nullptr);
     fan_count.zero();
     if (out.T > 0) GMG_LAUNCH(c, fan_fill_kernel, div_up(out.T, kBlock), kBlock, 0, out.T, out.tri.p, out.fan_ptr.p, fan_count.p, out.fan_tri.p);

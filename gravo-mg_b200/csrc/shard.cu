@@ -11,8 +11,14 @@
 //     several virtual ranks share one GPU in the tests). There is no reduction and no all-to-all;
 //   * the sampler and the relaxation are therefore PULL formulations (k_sampler.cu, k_parents.cu):
 //     same greedy set, same distances, same parents as the single-GPU kernels, bit for bit;
-//   * cheap stages (cluster CSR, coarse positions, triangle fans, compaction scans) are computed
-//     redundantly by every rank from replicated inputs, so they need no exchange;
+//   * triangle fans are enumerated only where the owned rows of P read them (a byte mask over the
+//     smallest vertex of a triangle), so that stage is sharded without any exchange; the triangle
+//     list of a sharded build is therefore rank-local;
+//   * edge lengths are computed only for the columns a rank reads (owned + one hop, plus at level 0 the
+//     children of its clusters); the mean length keeps the single-GPU summation tree because that
+//     tree is defined on groups of 32 columns, whose partial sums are all-gathered;
+//   * cheap stages (cluster CSR, coarse positions, compaction scans) are computed redundantly by
+//     every rank from replicated inputs, so they need no exchange;
 //   * P stays sharded by rows ("P rows shard trivially"). Galerkin products on the sharded P are the
 //     next step and are not built here.
 //
@@ -40,6 +46,10 @@ struct gmg_shard {
     const int32_t* rowidx = nullptr;
     const double* val = nullptr;     // stored values of the level's edge matrix
     DevBuf<double> len;              // Euclidean lengths (level 0: also the stored values)
+    DevBuf<uint8_t> need;            // world > 1: columns whose lengths this rank computes
+    bool val_is_len = false;
+    int32_t gchunk = 0;              // column groups (32 columns) per rank
+    DevBuf<double> len_partial;      // exchange: sum of the lengths of every column group
     double radius = 0.0;
     // exchange buffers (per-vertex, chunk * world entries; a rank writes [lo, hi) only)
     DevBuf<uint8_t> state, changed[2];
@@ -115,6 +125,39 @@ __global__ void __launch_bounds__(kBlock) pack_rows_kernel(int32_t p_lo, int32_t
     for (int32_t i = sub; i < k; i += 8) { outQ[dst + i] = sQ[src + i]; outt[dst + i] = st[src + i]; }
 }
 
+// coarse vertices whose fans the owned rows of P read, and the smallest-vertex set that yields those fans
+__global__ void __launch_bounds__(kBlock) mark_parents_kernel(int32_t lo, int32_t hi, const int32_t* __restrict__ parents,
+                                                              uint8_t* __restrict__ need_c) {
+    const int64_t f = int64_t(lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (f < hi) need_c[parents[f]] = 1;
+}
+__global__ void __launch_bounds__(kBlock) mark_closure_kernel(int32_t m, const int32_t* __restrict__ colptr,
+                                                              const int32_t* __restrict__ rowidx,
+                                                              const uint8_t* __restrict__ need_c, uint8_t* __restrict__ need_v0) {
+    const int64_t v = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (v >= m || !need_c[v]) return;
+    need_v0[v] = 1;
+    for (int32_t k = colptr[v]; k < colptr[v + 1]; ++k) need_v0[rowidx[k]] = 1;
+}
+
+// columns whose lengths this rank reads: its own (relaxation, first hop) and their neighbours (second hop)
+__global__ void __launch_bounds__(kBlock) mark_columns_kernel(int32_t lo, int32_t hi, const int32_t* __restrict__ colptr,
+                                                              const int32_t* __restrict__ rowidx, uint8_t* __restrict__ need) {
+    const int64_t i = int64_t(lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i >= hi) return;
+    need[i] = 1;
+    for (int32_t k = colptr[i]; k < colptr[i + 1]; ++k) need[rowidx[k]] = 1;
+}
+// level 0 only (the stored values ARE the lengths): columns the owned coarse rows read -- the children of
+// the owned clusters, and fine column number P for every owned cluster P (the index-space quirk, :151)
+__global__ void __launch_bounds__(kBlock) mark_children_kernel(int32_t n, int32_t p_lo, int32_t p_hi,
+                                                               const int32_t* __restrict__ parents, uint8_t* __restrict__ need) {
+    const int64_t f = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (f >= n) return;
+    const int32_t P = parents[f];
+    if (P >= p_lo && P < p_hi) { need[f] = 1; need[P] = 1; }
+}
+
 void begin_level(gmg_shard* s) {
     gmg_ctx* c = s->ctx;
     split(s->n, s->world, s->rank, s->chunk, s->lo, s->hi);
@@ -126,28 +169,23 @@ void begin_level(gmg_shard* s) {
     s->cur->info.n = s->n; s->cur->info.nnz = s->nnz;
     s->cur->lo = s->lo; s->cur->hi = s->hi;
     s->status.begin(c);
-    // lengths and radius: replicated (every rank needs the lengths of the columns its walks touch)
-    if (s->level == 0) {
-        s->len.alloc(c, s->nnz);
-        edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p);
-        s->val = s->len.p;                                   // toEdgeDistanceMatrix (test/main.cpp:69)
-    } else {
-        s->len.alloc(c, s->nnz);
-        edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p);
+    // lengths: only the columns this rank reads (all of them when it is alone)
+    const uint8_t* mask = nullptr;
+    if (s->world > 1) {
+        s->need.alloc(c, int64_t(s->n) + 1);
+        s->need.zero();
+        if (s->hi > s->lo) GMG_LAUNCH(c, mark_columns_kernel, div_up(s->hi - s->lo, kBlock), kBlock, 0, s->lo, s->hi, s->colptr, s->rowidx, s->need.p);
+        mask = s->need.p;
     }
-    const bool overridden = !s->radius_override.empty() && s->radius_override[size_t(s->level)] > 0.0;
-    if (overridden) s->radius = s->radius_override[size_t(s->level)];
-    else {
-        double denom = double(s->nnz - s->n);
-        if (s->opt.radius_policy == 1) denom = double(s->level == 0 ? s->nnz - s->n : s->nnz);
-        DevBuf<double> d_mean(c, 1);
-        mean_length_dev(c, s->nnz, s->len.p, denom, d_mean.p);
-        double mean = 0.0;
-        d_mean.download(&mean, 1);
-        sync(c);
-        s->radius = std::cbrt(s->opt.ratio) * mean;
-    }
-    s->cur->info.radius = s->radius;
+    s->len.alloc(c, s->nnz);
+    edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p, mask);
+    if (s->level == 0) s->val = s->len.p;                    // toEdgeDistanceMatrix (test/main.cpp:69)
+    s->val_is_len = s->level == 0;
+    // mean length: the owned column groups' partial sums; the host gathers them, PH_RADIUS folds them
+    s->gchunk = s->chunk / 32;
+    s->len_partial.alloc(c, int64_t(s->gchunk) * s->world);
+    s->len_partial.zero();
+    if (s->hi > s->lo) length_group_partials(c, s->n, s->lo / 32, (s->hi + 31) / 32, s->colptr, s->len.p, s->len_partial.p);
 }
 
 }  // namespace
@@ -192,6 +230,22 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 io[1] = s->n; io[2] = s->lo; io[3] = s->hi; io[4] = s->chunk;
                 break;
             }
+            case GMG_PH_RADIUS: {           // after the column-group partials have been gathered
+                const bool overridden = !s->radius_override.empty() && s->radius_override[size_t(s->level)] > 0.0;
+                if (overridden) s->radius = s->radius_override[size_t(s->level)];
+                else {
+                    double denom = double(s->nnz - s->n);
+                    if (s->opt.radius_policy == 1) denom = double(s->level == 0 ? s->nnz - s->n : s->nnz);
+                    DevBuf<double> d_mean(c, 1);
+                    mean_from_group_partials(c, (int64_t(s->n) + 31) / 32, s->len_partial.p, denom, d_mean.p);
+                    double mean = 0.0;
+                    d_mean.download(&mean, 1);
+                    sync(c);
+                    s->radius = std::cbrt(s->opt.ratio) * mean;
+                }
+                s->cur->info.radius = s->radius;
+                break;
+            }
             case GMG_PH_SAMPLER_BUILD:
                 shard_sampler_build(c, s->n, s->lo, s->hi, s->colptr, s->rowidx, s->len.p, s->radius, s->opt.sampler_mode,
                                     s->opt.seed + uint64_t(s->level), s->state.p, s->sampler);
@@ -231,6 +285,12 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 break;
             case GMG_PH_COARSE_ROWS: {
                 build_clusters(c, s->n, s->m, s->parents.p, s->clusters);           // replicated
+                if (s->world > 1 && s->val_is_len) {
+                    // level 0: the owned coarse rows read the stored values (= lengths) of more columns
+                    s->need.zero();
+                    GMG_LAUNCH(c, mark_children_kernel, div_up(s->n, kBlock), kBlock, 0, s->n, s->clo, s->chi, s->parents.p, s->need.p);
+                    edge_lengths(c, s->n, s->colptr, s->rowidx, s->pts, s->len.p, s->need.p);
+                }
                 s->ccnt.alloc(c, int64_t(s->cchunk) * s->world + 1);
                 s->ccnt.zero();
                 s->rows = CoarseRows();
@@ -289,8 +349,15 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 // replicated cheap stages
                 L.coarse_pts.alloc(c, 3 * int64_t(s->m));
                 coarse_points(c, s->n, s->pts, s->colptr, s->rowidx, s->m, s->clusters, L.coarse_pts.p);
-                voronoi_triangles(c, s->m, L.coarse.nnz, L.coarse_pts.p, L.coarse.colptr.p, L.coarse.rowidx.p, L.coarse.val.p, L.tri);
-                L.info.T = L.tri.T;
+                // Triangle fans: only what the owned rows of P read. A fan of c lists every triangle that contains c,
+                // and a triangle is enumerated at its smallest vertex, which is c or a neighbour of c.
+                DevBuf<uint8_t> need_c(c, int64_t(s->m) + 1), need_v0(c, int64_t(s->m) + 1);
+                need_c.zero(); need_v0.zero();
+                if (s->hi > s->lo) GMG_LAUNCH(c, mark_parents_kernel, div_up(s->hi - s->lo, kBlock), kBlock, 0, s->lo, s->hi, s->parents.p, need_c.p);
+                if (s->m > 0) GMG_LAUNCH(c, mark_closure_kernel, div_up(s->m, kBlock), kBlock, 0, s->m, L.coarse.colptr.p, L.coarse.rowidx.p, need_c.p, need_v0.p);
+                voronoi_triangles(c, s->m, L.coarse.nnz, L.coarse_pts.p, L.coarse.colptr.p, L.coarse.rowidx.p, L.coarse.val.p, L.tri,
+                                  s->world > 1 ? need_v0.p : nullptr);
+                L.info.T = L.tri.T;       // with more than one rank: the triangles THIS rank enumerated
                 break;
             }
             case GMG_PH_PROLONG: {          // owned rows of P
@@ -339,6 +406,7 @@ int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, i
         case GMG_XB_COARSE_COUNT: *ptr = s->ccnt.p; *elem_bytes = 4; *slice = s->cchunk; break;
         case GMG_XB_ROWS_ID: *ptr = s->xQ.p; *elem_bytes = 4; *slice = s->rows_max; break;
         case GMG_XB_ROWS_VAL: *ptr = s->xt.p; *elem_bytes = 8; *slice = s->rows_max; break;
+        case GMG_XB_LEN_PARTIAL: *ptr = s->len_partial.p; *elem_bytes = 8; *slice = s->gchunk; break;
         default: return GMG_ERR_INVALID;
     }
     return GMG_OK;

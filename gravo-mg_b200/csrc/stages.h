@@ -9,13 +9,20 @@
 namespace gmg {
 
 // ---- k_basic.cu -------------------------------------------------------------------------------
+// col_mask (optional, n bytes): compute only the flagged columns (row-sharded build)
 void edge_lengths(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* pts,
-                  double* out_len);
+                  double* out_len, const uint8_t* col_mask = nullptr);
 void extract_edges_dev(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* val,
                        int64_t nnz, int32_t* out_edges, double* out_values);
 void average_edge_length_dev(gmg_ctx* c, int32_t n, const double* pts, int64_t n_edges, const int32_t* edges,
                              double* d_out);
-void mean_length_dev(gmg_ctx* c, int64_t nnz, const double* len, double denom, double* d_out);
+// mean stored length = (sum of all entries) / denom, with a summation tree defined on groups of 32 columns
+// so that the row-sharded build (owned groups per rank, partials all-gathered) reproduces it bit for bit
+void mean_length_dev(gmg_ctx* c, int32_t n, int64_t nnz, const int32_t* colptr, const double* len, double denom,
+                     double* d_out);
+void length_group_partials(gmg_ctx* c, int32_t n, int32_t g_lo, int32_t g_hi, const int32_t* colptr, const double* len,
+                           double* partial);
+void mean_from_group_partials(gmg_ctx* c, int64_t groups, const double* partial, double denom, double* d_out);
 void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric);
 
 // Device status block that a stage writes INSTEAD of synchronising with the host; the hierarchy builder
@@ -119,8 +126,11 @@ struct Triangles {
     DevBuf<int32_t> fan_o1;   // 3T: second vertex after rotating the owner to the front
     DevBuf<int32_t> fan_o2;   // 3T: third vertex after rotation
 };
+// v0_mask (optional, m bytes): enumerate only the triangles whose smallest vertex is flagged. Ids then
+// number the enumerated subset in the same lexicographic order, and only vertices whose whole closed
+// neighbourhood is flagged have complete fans (the row-sharded build flags what its own rows of P need).
 void voronoi_triangles(gmg_ctx* c, int32_t m, int64_t nnz, const double* pts, const int32_t* colptr,
-                       const int32_t* rowidx, const double* val, Triangles& out);
+                       const int32_t* rowidx, const double* val, Triangles& out, const uint8_t* v0_mask = nullptr);
 
 // ---- k_prolong.cu -----------------------------------------------------------------------------
 struct DeviceCsr {

@@ -25,11 +25,12 @@ from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, 
 
 (PH_LEVEL_BEGIN, PH_SAMPLER_BUILD, PH_SAMPLER_ROUND, PH_SAMPLER_CHECK, PH_SAMPLES, PH_PARENTS_PULL, PH_PARENTS_CHECK,
  PH_PARENTS_PRED, PH_PARENTS_RESOLVE, PH_COARSE_ROWS, PH_COARSE_PACK, PH_COARSE_ASSEMBLE, PH_PROLONG,
- PH_LEVEL_END) = range(14)
-(XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL) = range(8)
+ PH_LEVEL_END, PH_RADIUS) = range(15)
+(XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL, XB_LEN_PARTIAL) = range(9)
 PHASE_NAMES = ["level_begin", "sampler_build", "sampler_round", "sampler_check", "samples", "parents_pull", "parents_check",
-               "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end"]
-BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val"]
+               "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end",
+               "radius"]
+BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val", "len_partial"]
 
 
 def partition(count, world, rank):
@@ -208,6 +209,8 @@ class ShardedHierarchy:
         while True:
             if not self._phase(PH_LEVEL_BEGIN)[0]:
                 break
+            self._gather(XB_LEN_PARTIAL)
+            self._phase(PH_RADIUS)
             self._phase(PH_SAMPLER_BUILD)
             self._gather(XB_STATE)
             while self._phase(PH_SAMPLER_CHECK)[0] > 0:

@@ -240,7 +240,7 @@ int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, i
  * single-GPU build bit for bit; P comes back sharded by rows.
  *
  * Driver loop per level (G = all-gather of that buffer over the ranks):
- *   LEVEL_BEGIN (io[0] = 0: no level left) ; SAMPLER_BUILD ; G(STATE) ;
+ *   LEVEL_BEGIN (io[0] = 0: no level left) ; G(LEN_PARTIAL) ; RADIUS ; SAMPLER_BUILD ; G(STATE) ;
  *   repeat { SAMPLER_CHECK -> io[0] = undecided vertices; stop at 0 ; SAMPLER_ROUND ; G(STATE) } ;
  *   SAMPLES -> io[0] = m ; repeat { PARENTS_PULL ; G(DIST) ; G(CHANGED) ; PARENTS_CHECK -> io[0] =
  *   improved vertices; stop at 0 } ; PARENTS_PRED ; G(PRED) ; PARENTS_RESOLVE ; G(PARENTS) ;
@@ -250,9 +250,9 @@ int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, i
 typedef struct gmg_shard gmg_shard;
 enum { GMG_PH_LEVEL_BEGIN = 0, GMG_PH_SAMPLER_BUILD, GMG_PH_SAMPLER_ROUND, GMG_PH_SAMPLER_CHECK, GMG_PH_SAMPLES,
        GMG_PH_PARENTS_PULL, GMG_PH_PARENTS_CHECK, GMG_PH_PARENTS_PRED, GMG_PH_PARENTS_RESOLVE, GMG_PH_COARSE_ROWS,
-       GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END };
+       GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END, GMG_PH_RADIUS };
 enum { GMG_XB_STATE = 0, GMG_XB_CHANGED, GMG_XB_DIST, GMG_XB_PRED, GMG_XB_PARENTS, GMG_XB_COARSE_COUNT, GMG_XB_ROWS_ID,
-       GMG_XB_ROWS_VAL };
+       GMG_XB_ROWS_VAL, GMG_XB_LEN_PARTIAL };
 /* `in` is the WHOLE level-0 problem, resident on this rank's device (the same on every rank); it must
  * outlive the shard */
 int gmg_shard_create(gmg_ctx* ctx, int rank, int world, const gmg_input* in, const gmg_hierarchy_options* opt,

@@ -12,7 +12,9 @@ from gravomg_b200 import capi, meshgen
 from pipeline import assert_level_equal, run_hierarchy
 
 pytestmark = pytest.mark.gpu
-KEYS = "sel par ccp cri cval cpts tri nrm fptr fan prp pci pva".split()
+# triangles and fans are rank-local in a sharded build (each rank enumerates what its rows of P read);
+# the rows of P, which are computed FROM those fans, are compared instead
+KEYS = "sel par ccp cri cval cpts prp pci pva".split()
 
 
 def _single(ctx, V, A, levels, mode, radii=None):

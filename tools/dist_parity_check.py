@@ -38,8 +38,7 @@ for mode in (capi.SAMPLER_PARALLEL, capi.SAMPLER_EXACT) if name != "C3" else (ca
     for lvl in range(single.num_levels):
         w = single.level_arrays(lvl)
         for key, which in (("sel", capi.H_SAMPLES), ("par", capi.H_PARENTS), ("ccp", capi.H_COARSE_COLPTR),
-                           ("cri", capi.H_COARSE_ROWIDX), ("cval", capi.H_COARSE_VAL), ("cpts", capi.H_COARSE_POINTS),
-                           ("tri", capi.H_TRIANGLES), ("nrm", capi.H_NORMALS), ("fan", capi.H_FAN)):
+                           ("cri", capi.H_COARSE_ROWIDX), ("cval", capi.H_COARSE_VAL), ("cpts", capi.H_COARSE_POINTS)):
             if not np.array_equal(sh.fetch(lvl, which), w[key]):
                 bad += 1
                 print(f"rank {rank} mode {mode} level {lvl}: {key} differs", flush=True)
