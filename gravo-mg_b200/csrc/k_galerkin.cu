@@ -23,14 +23,17 @@
 namespace gmg {
 
 // ---- R = P^T ------------------------------------------------------------------------------------
+// Only the columns [c_lo, c_hi) of P become rows of R (the row-sharded build transposes the coarse rows it owns).
 __global__ void __launch_bounds__(kBlock) count_columns_kernel(int64_t nnz, const int32_t* __restrict__ colidx,
-                                                               int32_t* __restrict__ count) {
+                                                               int32_t c_lo, int32_t c_hi, int32_t* __restrict__ count) {
     const int64_t k = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (k < nnz) atomicAdd(count + __ldg(colidx + k), 1);
+    if (k >= nnz) return;
+    const int32_t cidx = __ldg(colidx + k);
+    if (cidx >= c_lo && cidx < c_hi) atomicAdd(count + (cidx - c_lo), 1);
 }
 __global__ void __launch_bounds__(kBlock) transpose_fill_kernel(int32_t rows, const int32_t* __restrict__ rowptr,
                                                                 const int32_t* __restrict__ colidx,
-                                                                const double* __restrict__ val,
+                                                                const double* __restrict__ val, int32_t c_lo, int32_t c_hi,
                                                                 const int32_t* __restrict__ tptr,
                                                                 int32_t* __restrict__ cursor, int32_t* __restrict__ tcol,
                                                                 double* __restrict__ tval) {
@@ -38,7 +41,8 @@ __global__ void __launch_bounds__(kBlock) transpose_fill_kernel(int32_t rows, co
     if (r >= rows) return;
     for (int32_t k = rowptr[r]; k < rowptr[r + 1]; ++k) {
         const int32_t cidx = colidx[k];
-        const int32_t pos = tptr[cidx] + atomicAdd(cursor + cidx, 1);
+        if (cidx < c_lo || cidx >= c_hi) continue;
+        const int32_t pos = tptr[cidx - c_lo] + atomicAdd(cursor + (cidx - c_lo), 1);
         tcol[pos] = int32_t(r);
         tval[pos] = val[k];
     }
@@ -56,18 +60,23 @@ __global__ void __launch_bounds__(kBlock) sort_rows_kernel(int32_t rows, const i
     }
 }
 
-void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R) {
-    R.rows = P.cols; R.cols = P.rows; R.nnz = P.nnz;
+void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, int32_t c_hi) {
+    if (c_hi < 0) c_hi = P.cols;
+    const bool all = c_lo == 0 && c_hi == P.cols;
+    R.rows = c_hi - c_lo; R.cols = P.rows;
     R.rowptr.alloc(c, int64_t(R.rows) + 1);
+    DevBuf<int32_t> count(c, int64_t(R.rows) + 1);
+    DevBuf<int64_t> total(c, 1);
+    count.zero();
+    if (P.nnz > 0) GMG_LAUNCH(c, count_columns_kernel, div_up(P.nnz, kBlock), kBlock, 0, P.nnz, P.colidx.p, c_lo, c_hi, count.p);
+    exclusive_scan_i32(c, count.p, R.rowptr.p, int64_t(R.rows) + 1, all ? nullptr : total.p);
+    R.nnz = P.nnz;
+    if (!all) { total.download(&R.nnz, 1); sync(c); }
     R.colidx.alloc(c, R.nnz);
     R.val.alloc(c, R.nnz);
-    DevBuf<int32_t> count(c, int64_t(R.rows) + 1);
-    count.zero();
-    if (P.nnz > 0) GMG_LAUNCH(c, count_columns_kernel, div_up(P.nnz, kBlock), kBlock, 0, P.nnz, P.colidx.p, count.p);
-    exclusive_scan_i32(c, count.p, R.rowptr.p, int64_t(R.rows) + 1, nullptr);
     count.zero();
     if (P.rows > 0) GMG_LAUNCH(c, transpose_fill_kernel, div_up(P.rows, kBlock), kBlock, 0, P.rows, P.rowptr.p, P.colidx.p,
-                               P.val.p, R.rowptr.p, count.p, R.colidx.p, R.val.p);
+                               P.val.p, c_lo, c_hi, R.rowptr.p, count.p, R.colidx.p, R.val.p);
     if (R.rows > 0) GMG_LAUNCH(c, sort_rows_kernel, div_up(R.rows, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
 }
 
@@ -274,14 +283,16 @@ __global__ void __launch_bounds__(kBlock) galerkin_block_kernel(GalerkinArgs a, 
 }
 
 void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
-              const DeviceCsr& P, DeviceCsc& Ac) {
+              const DeviceCsr& P, DeviceCsc& Ac, int32_t c_lo, int32_t c_hi, DeviceCsr* keep_R) {
     GMG_REQUIRE(P.rows == n, GMG_ERR_INVALID, "galerkin: P and A sizes disagree");
-    const int32_t m = P.cols;
+    if (c_hi < 0) c_hi = P.cols;
+    const int32_t m = c_hi - c_lo;     // outer vectors computed here; Ac is indexed from c_lo
     Ac.n = m;
     Ac.colptr.alloc(c, int64_t(m) + 1);
     if (m == 0) { Ac.colptr.zero(); Ac.rowidx.alloc(c, 0); Ac.val.alloc(c, 0); Ac.nnz = 0; return; }
-    DeviceCsr R;
-    transpose_csr(c, P, R);
+    DeviceCsr R_local;
+    DeviceCsr& R = keep_R ? *keep_R : R_local;
+    transpose_csr(c, P, R, c_lo, c_hi);
     DevBuf<int32_t> count(c, int64_t(m) + 1), flags(c, 4), overflow(c, m);
     DevBuf<int64_t> total(c, 1);
     count.zero(); flags.zero();

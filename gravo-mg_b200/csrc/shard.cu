@@ -19,8 +19,11 @@
 //     tree is defined on groups of 32 columns, whose partial sums are all-gathered;
 //   * cheap stages (cluster CSR, coarse positions, compaction scans) are computed redundantly by
 //     every rank from replicated inputs, so they need no exchange;
-//   * P stays sharded by rows ("P rows shard trivially"). Galerkin products on the sharded P are the
-//     next step and are not built here.
+//   * P stays sharded by rows ("P rows shard trivially");
+//   * Galerkin operators (build_galerkin): the ranks all-gather their rows of P (variable-size slices,
+//     like the coarse rows), every rank transposes the coarse columns it OWNS and runs the single-GPU
+//     two-pass SpGEMM on exactly those outer vectors of A_c; the owned outer vectors are all-gathered and
+//     A_c is replicated, because it is the next level's A.
 //
 // The object below is driven phase by phase from the host (gravo-mg_b200/sharded.py): run a phase on
 // every rank, all-gather the buffers that phase names, go on.
@@ -69,6 +72,20 @@ struct gmg_shard {
     DevBuf<double> xt;               // exchange: packed rows (values)
     std::vector<int64_t> rank_rows;  // entries per rank
     StageStatus status;
+    // Galerkin side (build_galerkin): the level's system matrix (replicated, pattern = any) and the exchange
+    int32_t a_n = 0;
+    const int32_t* a_colptr = nullptr;
+    const int32_t* a_rowidx = nullptr;
+    const double* a_val = nullptr;
+    DevBuf<int32_t> pcnt;            // exchange: entries per row of P, chunk * world (+1)
+    DeviceCsr Pfull;                 // all rows of P (transient)
+    int64_t p_max = 0;               // largest per-rank P volume: slice length of xPc / xPv
+    DevBuf<int32_t> xPc;             // exchange: the ranks' colidx arrays
+    DevBuf<double> xPv;              // exchange: the ranks' value arrays
+    std::vector<int64_t> rank_p;
+    DeviceCsc ac_own;                // the owned outer vectors of A_c, indexed from clo
+    int64_t ac_max = 0;
+    std::vector<int64_t> rank_ac;
     // finished levels: replicated coarse data + the owned rows of P
     struct Done {
         gmg_level_info info{};
@@ -78,6 +95,9 @@ struct gmg_shard {
         DevBuf<double> coarse_pts;
         Triangles tri;
         DeviceCsr P;                 // rows [lo, hi)
+        int32_t clo = 0, chi = 0;    // owned coarse vertices
+        DeviceCsr R;                 // build_galerkin: rows [clo, chi) of P^T (restriction of the owned coarse rows)
+        DeviceCsc Ac;                // build_galerkin: A_c, replicated
     };
     std::vector<std::unique_ptr<Done>> done;
     std::unique_ptr<Done> cur;
@@ -158,6 +178,43 @@ __global__ void __launch_bounds__(kBlock) mark_children_kernel(int32_t n, int32_
     if (P >= p_lo && P < p_hi) { need[f] = 1; need[P] = 1; }
 }
 
+// Volumes of the ranks' slices of a row-major packed array: offsets (device, exclusive scan over `count`
+// items, count + 1 entries) read at the rank boundaries (multiples of `chunk`). Returns the largest, rounded
+// up to 32 elements; bounds[r] is where rank r's slice starts. One host round trip.
+int64_t rank_volumes(gmg_shard* s, const int32_t* offsets, int64_t count, int32_t chunk, std::vector<int64_t>& vol,
+                     std::vector<int32_t>& bounds) {
+    gmg_ctx* c = s->ctx;
+    bounds.assign(size_t(s->world) + 1, 0);
+    for (int r = 0; r <= s->world; ++r) {
+        const int64_t at = std::min<int64_t>(count, int64_t(r) * chunk);
+        GMG_CUDA(cudaMemcpyAsync(&bounds[size_t(r)], offsets + at, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    }
+    sync(c);
+    vol.assign(size_t(s->world), 0);
+    int64_t most = 1;
+    for (int r = 0; r < s->world; ++r) {
+        vol[size_t(r)] = bounds[size_t(r) + 1] - bounds[size_t(r)];
+        most = std::max<int64_t>(most, vol[size_t(r)]);
+    }
+    return round_up(most, 32);
+}
+
+// the ranks' slices of an exchange buffer, concatenated
+template <typename T>
+void concat_slices(gmg_shard* s, const T* xbuf, int64_t slice, const std::vector<int64_t>& vol, T* out) {
+    int64_t at = 0;
+    for (int r = 0; r < s->world; ++r) {
+        const int64_t k = vol[size_t(r)];
+        if (k > 0) GMG_CUDA(cudaMemcpyAsync(out + at, xbuf + slice * r, sizeof(T) * size_t(k), cudaMemcpyDeviceToDevice, s->ctx->stream));
+        at += k;
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) row_counts_kernel(int32_t rows, const int32_t* __restrict__ ptr, int32_t* __restrict__ cnt) {
+    const int64_t r = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (r < rows) cnt[r] = ptr[r + 1] - ptr[r];
+}
+
 void begin_level(gmg_shard* s) {
     gmg_ctx* c = s->ctx;
     split(s->n, s->world, s->rank, s->chunk, s->lo, s->hi);
@@ -200,7 +257,7 @@ int gmg_shard_create(gmg_ctx* c, int rank, int world, const gmg_input* in, const
         GMG_REQUIRE(in, GMG_ERR_INVALID, "null input");
         GMG_REQUIRE(opt && opt->levels >= 1, GMG_ERR_INVALID, "levels must be >= 1");
         GMG_REQUIRE(world >= 1 && rank >= 0 && rank < world, GMG_ERR_INVALID, "bad rank/world");
-        GMG_REQUIRE(!opt->build_galerkin, GMG_ERR_INVALID, "the row-sharded build does not form Galerkin operators yet");
+        GMG_REQUIRE(!opt->build_galerkin || in->has_a, GMG_ERR_INVALID, "build_galerkin needs A values");
         std::unique_ptr<gmg_shard> s(new gmg_shard());
         s->ctx = c; s->rank = rank; s->world = world; s->opt = *opt;
         if (opt->radius_override) s->radius_override.assign(opt->radius_override, opt->radius_override + (opt->levels - 1));
@@ -208,6 +265,7 @@ int gmg_shard_create(gmg_ctx* c, int rank, int world, const gmg_input* in, const
         // level 0 is a VIEW of the input (which must outlive the shard): the whole graph, on every rank
         s->n = in->n; s->nnz = in->nnz;
         s->pts = in->pts.p; s->colptr = in->colptr.p; s->rowidx = in->rowidx.p;
+        s->a_n = in->n; s->a_colptr = in->colptr.p; s->a_rowidx = in->rowidx.p; s->a_val = in->has_a ? in->a_val.p : nullptr;
         *out = s.release();
     });
 }
@@ -303,20 +361,8 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 DevBuf<int64_t> total(c, 1);
                 GMG_CUDA(cudaMemsetAsync(s->ccnt.p + s->m, 0, sizeof(int32_t), c->stream));   // scan sentinel
                 exclusive_scan_i32(c, s->ccnt.p, s->rowoff.p, int64_t(s->m) + 1, total.p);
-                // volume of every rank's rows = rowoff at the rank boundaries
-                std::vector<int32_t> bounds(size_t(s->world) + 1, 0);
-                for (int r = 0; r <= s->world; ++r) {
-                    const int64_t at = std::min<int64_t>(s->m, int64_t(r) * s->cchunk);
-                    GMG_CUDA(cudaMemcpyAsync(&bounds[size_t(r)], s->rowoff.p + at, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
-                }
-                sync(c);
-                s->rank_rows.assign(size_t(s->world), 0);
-                s->rows_max = 1;
-                for (int r = 0; r < s->world; ++r) {
-                    s->rank_rows[size_t(r)] = bounds[size_t(r) + 1] - bounds[size_t(r)];
-                    s->rows_max = std::max<int64_t>(s->rows_max, s->rank_rows[size_t(r)]);
-                }
-                s->rows_max = round_up(s->rows_max, 32);
+                std::vector<int32_t> bounds;
+                s->rows_max = rank_volumes(s, s->rowoff.p, s->m, s->cchunk, s->rank_rows, bounds);
                 s->xQ.alloc(c, s->rows_max * s->world);
                 s->xt.alloc(c, s->rows_max * s->world);
                 const int32_t own = s->chi - s->clo;
@@ -333,15 +379,8 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 const int64_t total = [&] { int64_t t = 0; for (auto v : s->rank_rows) t += v; return t; }();
                 DevBuf<int32_t> allQ(c, total);
                 DevBuf<double> allt(c, total);
-                int64_t at = 0;
-                for (int r = 0; r < s->world; ++r) {
-                    const int64_t k = s->rank_rows[size_t(r)];
-                    if (k > 0) {
-                        GMG_CUDA(cudaMemcpyAsync(allQ.p + at, s->xQ.p + s->rows_max * r, sizeof(int32_t) * size_t(k), cudaMemcpyDeviceToDevice, c->stream));
-                        GMG_CUDA(cudaMemcpyAsync(allt.p + at, s->xt.p + s->rows_max * r, sizeof(double) * size_t(k), cudaMemcpyDeviceToDevice, c->stream));
-                    }
-                    at += k;
-                }
+                concat_slices(s, s->xQ.p, s->rows_max, s->rank_rows, allQ.p);
+                concat_slices(s, s->xt.p, s->rows_max, s->rank_rows, allt.p);
                 gmg_shard::Done& L = *s->cur;
                 coarse_assemble(c, s->m, s->rowoff.p, s->ccnt.p, allQ.p, allt.p, L.coarse, s->status.dev.p + StageStatus::kCoarseAsym);
                 L.info.nnz_c = L.coarse.nnz;
@@ -366,6 +405,89 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                              s->opt.weighting, L.P, nullptr, &s->status, s->lo, s->hi);
                 break;
             }
+            case GMG_PH_P_COUNT: {          // build_galerkin: entries per owned row of P
+                GMG_REQUIRE(s->opt.build_galerkin, GMG_ERR_STATE, "shard was created without build_galerkin");
+                gmg_shard::Done& L = *s->cur;
+                s->status.fetch(c);
+                finish_prolongation(s->status, L.P, &L.info.stats);
+                s->pcnt.alloc(c, int64_t(s->chunk) * s->world + 1);
+                s->pcnt.zero();
+                if (s->hi > s->lo) GMG_LAUNCH(c, row_counts_kernel, div_up(s->hi - s->lo, kBlock), kBlock, 0, s->hi - s->lo, L.P.rowptr.p, s->pcnt.p + s->lo);
+                break;
+            }
+            case GMG_PH_P_PACK: {           // after the row counts have been gathered
+                gmg_shard::Done& L = *s->cur;
+                s->Pfull = DeviceCsr();
+                s->Pfull.rows = s->n; s->Pfull.cols = s->m;
+                s->Pfull.rowptr.alloc(c, int64_t(s->n) + 1);
+                DevBuf<int64_t> total(c, 1);
+                GMG_CUDA(cudaMemsetAsync(s->pcnt.p + s->n, 0, sizeof(int32_t), c->stream));     // scan sentinel
+                exclusive_scan_i32(c, s->pcnt.p, s->Pfull.rowptr.p, int64_t(s->n) + 1, total.p);
+                std::vector<int32_t> bounds;
+                s->p_max = rank_volumes(s, s->Pfull.rowptr.p, s->n, s->chunk, s->rank_p, bounds);
+                GMG_REQUIRE(s->rank_p[size_t(s->rank)] == L.P.nnz, GMG_ERR_STATE, "gathered row counts disagree with the owned rows of P");
+                s->xPc.alloc(c, s->p_max * s->world);
+                s->xPv.alloc(c, s->p_max * s->world);
+                if (L.P.nnz > 0) {
+                    GMG_CUDA(cudaMemcpyAsync(s->xPc.p + s->p_max * s->rank, L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(s->xPv.p + s->p_max * s->rank, L.P.val.p, sizeof(double) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                }
+                io[0] = s->p_max;
+                break;
+            }
+            case GMG_PH_GALERKIN_ROWS: {    // after the rows of P have been gathered: the owned outer vectors of A_c
+                gmg_shard::Done& L = *s->cur;
+                int64_t nnz_p = 0;
+                for (auto v : s->rank_p) nnz_p += v;
+                s->Pfull.nnz = nnz_p;
+                s->Pfull.colidx.alloc(c, nnz_p);
+                s->Pfull.val.alloc(c, nnz_p);
+                concat_slices(s, s->xPc.p, s->p_max, s->rank_p, s->Pfull.colidx.p);
+                concat_slices(s, s->xPv.p, s->p_max, s->rank_p, s->Pfull.val.p);
+                s->xPc = DevBuf<int32_t>(); s->xPv = DevBuf<double>();
+                L.clo = s->clo; L.chi = s->chi;
+                galerkin(c, s->a_n, s->a_colptr, s->a_rowidx, s->a_val, s->Pfull, s->ac_own, s->clo, s->chi, &L.R);
+                s->Pfull = DeviceCsr();
+                // entries per owned outer vector -> the count exchange buffer (the coarse-graph counts are done with)
+                s->ccnt.zero();
+                if (s->chi > s->clo) GMG_LAUNCH(c, row_counts_kernel, div_up(s->chi - s->clo, kBlock), kBlock, 0, s->chi - s->clo, s->ac_own.colptr.p, s->ccnt.p + s->clo);
+                break;
+            }
+            case GMG_PH_GALERKIN_PACK: {    // after the counts have been gathered
+                gmg_shard::Done& L = *s->cur;
+                L.Ac.n = s->m;
+                L.Ac.colptr.alloc(c, int64_t(s->m) + 1);
+                DevBuf<int64_t> total(c, 1);
+                GMG_CUDA(cudaMemsetAsync(s->ccnt.p + s->m, 0, sizeof(int32_t), c->stream));
+                exclusive_scan_i32(c, s->ccnt.p, L.Ac.colptr.p, int64_t(s->m) + 1, total.p);
+                std::vector<int32_t> bounds;
+                s->ac_max = rank_volumes(s, L.Ac.colptr.p, s->m, s->cchunk, s->rank_ac, bounds);
+                GMG_REQUIRE(s->rank_ac[size_t(s->rank)] == s->ac_own.nnz, GMG_ERR_STATE, "gathered counts disagree with the owned part of A_c");
+                s->xQ.alloc(c, s->ac_max * s->world);
+                s->xt.alloc(c, s->ac_max * s->world);
+                if (s->ac_own.nnz > 0) {
+                    GMG_CUDA(cudaMemcpyAsync(s->xQ.p + s->ac_max * s->rank, s->ac_own.rowidx.p, sizeof(int32_t) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(s->xt.p + s->ac_max * s->rank, s->ac_own.val.p, sizeof(double) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                }
+                s->ac_own = DeviceCsc();
+                s->rows_max = s->ac_max;        // slice length reported for ROWS_ID / ROWS_VAL
+                io[0] = s->ac_max;
+                break;
+            }
+            case GMG_PH_GALERKIN_ASSEMBLE: {    // after the owned outer vectors have been gathered
+                gmg_shard::Done& L = *s->cur;
+                int64_t nnz = 0;
+                for (auto v : s->rank_ac) nnz += v;
+                L.Ac.nnz = nnz;
+                L.Ac.rowidx.alloc(c, nnz);
+                L.Ac.val.alloc(c, nnz);
+                concat_slices(s, s->xQ.p, s->ac_max, s->rank_ac, L.Ac.rowidx.p);
+                concat_slices(s, s->xt.p, s->ac_max, s->rank_ac, L.Ac.val.p);
+                s->xQ = DevBuf<int32_t>(); s->xt = DevBuf<double>();
+                L.info.nnz_ac = nnz;
+                s->a_n = s->m; s->a_colptr = L.Ac.colptr.p; s->a_rowidx = L.Ac.rowidx.p; s->a_val = L.Ac.val.p;
+                break;
+            }
             case GMG_PH_LEVEL_END: {
                 gmg_shard::Done& L = *s->cur;
                 s->status.fetch(c);
@@ -382,7 +504,7 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 // next level's fine inputs
                 s->n = s->m; s->nnz = L.coarse.nnz;
                 s->pts = L.coarse_pts.p; s->colptr = L.coarse.colptr.p; s->rowidx = L.coarse.rowidx.p; s->val = L.coarse.val.p;
-                io[0] = L.info.m; io[1] = L.info.nnz_c; io[2] = L.info.T; io[3] = L.info.nnz_p;
+                io[0] = L.info.m; io[1] = L.info.nnz_c; io[2] = L.info.T; io[3] = L.info.nnz_p; io[4] = L.info.nnz_ac;
                 s->done.push_back(std::move(s->cur));
                 ++s->level;
                 sync(c);
@@ -407,6 +529,9 @@ int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, i
         case GMG_XB_ROWS_ID: *ptr = s->xQ.p; *elem_bytes = 4; *slice = s->rows_max; break;
         case GMG_XB_ROWS_VAL: *ptr = s->xt.p; *elem_bytes = 8; *slice = s->rows_max; break;
         case GMG_XB_LEN_PARTIAL: *ptr = s->len_partial.p; *elem_bytes = 8; *slice = s->gchunk; break;
+        case GMG_XB_P_COUNT: *ptr = s->pcnt.p; *elem_bytes = 4; *slice = s->chunk; break;
+        case GMG_XB_P_COL: *ptr = s->xPc.p; *elem_bytes = 4; *slice = s->p_max; break;
+        case GMG_XB_P_VAL: *ptr = s->xPv.p; *elem_bytes = 8; *slice = s->p_max; break;
         default: return GMG_ERR_INVALID;
     }
     return GMG_OK;
@@ -452,6 +577,12 @@ int gmg_shard_fetch(gmg_ctx* c, const gmg_shard* s, int level, int which, void* 
             case GMG_H_P_ROWPTR: copy(L.P.rowptr.p, sizeof(int32_t) * size_t(own + 1)); break;
             case GMG_H_P_COLIDX: copy(L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz)); break;
             case GMG_H_P_VAL: copy(L.P.val.p, sizeof(double) * size_t(L.P.nnz)); break;
+            case GMG_H_AC_COLPTR: case GMG_H_AC_ROWIDX: case GMG_H_AC_VAL:
+                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "shard was built without the Galerkin operator");
+                if (which == GMG_H_AC_COLPTR) copy(L.Ac.colptr.p, sizeof(int32_t) * size_t(m + 1));
+                else if (which == GMG_H_AC_ROWIDX) copy(L.Ac.rowidx.p, sizeof(int32_t) * size_t(L.Ac.nnz));
+                else copy(L.Ac.val.p, sizeof(double) * size_t(L.Ac.nnz));
+                break;
             default: GMG_REQUIRE(false, GMG_ERR_INVALID, "array not available from a sharded build");
         }
         sync(c);

@@ -12,7 +12,9 @@ order and all-gathers those buffers between them:
                    how the sharded path is parity-tested against the single-GPU build on one B200.
 
 The data path has no reduction and no all-to-all: every exchange is an all-gather of contiguous owned
-slices. Results equal the single-GPU build bit for bit; P comes back sharded by rows.
+slices. Results equal the single-GPU build bit for bit; P comes back sharded by rows. With
+build_galerkin the rows of P are gathered, every rank forms the outer vectors of A_c = P^T A P that it
+owns, and A_c is gathered (replicated: it is the next level's A).
 """
 import ctypes as C
 
@@ -21,16 +23,18 @@ import numpy as np
 from . import capi
 from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, _i32p, _p, _pts,
                    H_SAMPLES, H_PARENTS, H_COARSE_COLPTR, H_COARSE_ROWIDX, H_COARSE_VAL, H_COARSE_POINTS, H_TRIANGLES,
-                   H_NORMALS, H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL)
+                   H_NORMALS, H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL, H_AC_COLPTR, H_AC_ROWIDX, H_AC_VAL)
 
 (PH_LEVEL_BEGIN, PH_SAMPLER_BUILD, PH_SAMPLER_ROUND, PH_SAMPLER_CHECK, PH_SAMPLES, PH_PARENTS_PULL, PH_PARENTS_CHECK,
  PH_PARENTS_PRED, PH_PARENTS_RESOLVE, PH_COARSE_ROWS, PH_COARSE_PACK, PH_COARSE_ASSEMBLE, PH_PROLONG,
- PH_LEVEL_END, PH_RADIUS) = range(15)
-(XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL, XB_LEN_PARTIAL) = range(9)
+ PH_LEVEL_END, PH_RADIUS, PH_P_COUNT, PH_P_PACK, PH_GALERKIN_ROWS, PH_GALERKIN_PACK, PH_GALERKIN_ASSEMBLE) = range(20)
+(XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL, XB_LEN_PARTIAL,
+ XB_P_COUNT, XB_P_COL, XB_P_VAL) = range(12)
 PHASE_NAMES = ["level_begin", "sampler_build", "sampler_round", "sampler_check", "samples", "parents_pull", "parents_check",
                "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end",
-               "radius"]
-BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val", "len_partial"]
+               "radius", "p_count", "p_pack", "galerkin_rows", "galerkin_pack", "galerkin_assemble"]
+BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val", "len_partial",
+                "p_count", "p_col", "p_val"]
 
 
 def partition(count, world, rank):
@@ -119,7 +123,7 @@ class ShardedHierarchy:
 
     def __init__(self, ctx, inp, levels, world, ranks, comm=None, ratio=8.0,
                  weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_PARALLEL, seed=0, radius_policy=0,
-                 radius_override=None, device=None, profile=False):
+                 radius_override=None, device=None, profile=False, build_galerkin=False):
         import torch
         self.torch = torch
         self.ctx, self.world, self.comm = ctx, world, comm
@@ -140,7 +144,8 @@ class ShardedHierarchy:
             ro[:len(radius_override)] = radius_override
         self._ro = ro
         opt = HierarchyOptions(levels, ratio, weighting, sampler_mode, seed, radius_policy,
-                               _p(ro, _f64p) if ro is not None else None, 0)
+                               _p(ro, _f64p) if ro is not None else None, 1 if build_galerkin else 0)
+        self.build_galerkin = bool(build_galerkin)
         # `inp` (capi.Input): the whole level-0 problem resident on this device; virtual ranks share it
         self.shards = [ShardRank(ctx, r, world, inp, opt) for r in ranks]
         self.exchanges = 0
@@ -234,6 +239,18 @@ class ShardedHierarchy:
             self._gather(XB_ROWS_VAL)
             self._phase(PH_COARSE_ASSEMBLE)
             self._phase(PH_PROLONG)
+            if self.build_galerkin:
+                self._phase(PH_P_COUNT)
+                self._gather(XB_P_COUNT)
+                self._phase(PH_P_PACK)
+                self._gather(XB_P_COL)
+                self._gather(XB_P_VAL)
+                self._phase(PH_GALERKIN_ROWS)
+                self._gather(XB_COARSE_COUNT)
+                self._phase(PH_GALERKIN_PACK)
+                self._gather(XB_ROWS_ID)
+                self._gather(XB_ROWS_VAL)
+                self._phase(PH_GALERKIN_ASSEMBLE)
             self._phase(PH_LEVEL_END)
 
     # ---- results -------------------------------------------------------------------------------------
@@ -254,7 +271,8 @@ class ShardedHierarchy:
             H_COARSE_ROWIDX: (i["nnz_c"], np.int32), H_COARSE_VAL: (i["nnz_c"], np.float64),
             H_COARSE_POINTS: (3 * m, np.float64), H_TRIANGLES: (3 * T, np.int64), H_NORMALS: (3 * T, np.float64),
             H_FAN_PTR: (m + 1, np.int64), H_FAN: (3 * T, np.int64), H_P_ROWPTR: (own + 1, np.int32),
-            H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64)}[which]
+            H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64), H_AC_COLPTR: (m + 1, np.int32),
+            H_AC_ROWIDX: (i["nnz_ac"], np.int32), H_AC_VAL: (i["nnz_ac"], np.float64)}[which]
         if out is None:
             out = np.empty(max(count, 1), dtype=dtype)
         elif out.dtype != dtype or out.ndim != 1 or out.shape[0] < count:
@@ -288,6 +306,13 @@ class ShardedHierarchy:
         out["pci"] = np.concatenate(cols)
         out["pva"] = np.concatenate(vals)
         return out
+
+    def galerkin(self, level, shard=0):
+        """A_c of a level (replicated) as scipy CSC."""
+        import scipy.sparse as sp
+        m = self.info(level, shard)["m"]
+        return sp.csc_matrix((self.fetch(level, H_AC_VAL, shard), self.fetch(level, H_AC_ROWIDX, shard),
+                              self.fetch(level, H_AC_COLPTR, shard)), shape=(m, m))
 
     def close(self):
         for s in getattr(self, "shards", []):

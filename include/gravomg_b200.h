@@ -245,14 +245,19 @@ int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, i
  *   SAMPLES -> io[0] = m ; repeat { PARENTS_PULL ; G(DIST) ; G(CHANGED) ; PARENTS_CHECK -> io[0] =
  *   improved vertices; stop at 0 } ; PARENTS_PRED ; G(PRED) ; PARENTS_RESOLVE ; G(PARENTS) ;
  *   COARSE_ROWS ; G(COARSE_COUNT) ; COARSE_PACK ; G(ROWS_ID) ; G(ROWS_VAL) ; COARSE_ASSEMBLE ;
- *   PROLONG ; LEVEL_END -> io = {m, nnz_c, T, nnz_p of the owned rows}.
+ *   PROLONG ; [Galerkin, below] ; LEVEL_END -> io = {m, nnz_c, T, nnz_p of the owned rows, nnz_ac}.
+ * With build_galerkin (A_c = P^T A P on every level, replicated because it is the next level's A):
+ *   P_COUNT ; G(P_COUNT) ; P_PACK ; G(P_COL) ; G(P_VAL) ; GALERKIN_ROWS (transpose the owned coarse
+ *   columns of P, two-pass SpGEMM on the owned outer vectors) ; G(COARSE_COUNT) ; GALERKIN_PACK ;
+ *   G(ROWS_ID) ; G(ROWS_VAL) ; GALERKIN_ASSEMBLE.
  * ------------------------------------------------------------------------------------------------ */
 typedef struct gmg_shard gmg_shard;
 enum { GMG_PH_LEVEL_BEGIN = 0, GMG_PH_SAMPLER_BUILD, GMG_PH_SAMPLER_ROUND, GMG_PH_SAMPLER_CHECK, GMG_PH_SAMPLES,
        GMG_PH_PARENTS_PULL, GMG_PH_PARENTS_CHECK, GMG_PH_PARENTS_PRED, GMG_PH_PARENTS_RESOLVE, GMG_PH_COARSE_ROWS,
-       GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END, GMG_PH_RADIUS };
+       GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END, GMG_PH_RADIUS,
+       GMG_PH_P_COUNT, GMG_PH_P_PACK, GMG_PH_GALERKIN_ROWS, GMG_PH_GALERKIN_PACK, GMG_PH_GALERKIN_ASSEMBLE };
 enum { GMG_XB_STATE = 0, GMG_XB_CHANGED, GMG_XB_DIST, GMG_XB_PRED, GMG_XB_PARENTS, GMG_XB_COARSE_COUNT, GMG_XB_ROWS_ID,
-       GMG_XB_ROWS_VAL, GMG_XB_LEN_PARTIAL };
+       GMG_XB_ROWS_VAL, GMG_XB_LEN_PARTIAL, GMG_XB_P_COUNT, GMG_XB_P_COL, GMG_XB_P_VAL };
 /* `in` is the WHOLE level-0 problem, resident on this rank's device (the same on every rank); it must
  * outlive the shard */
 int gmg_shard_create(gmg_ctx* ctx, int rank, int world, const gmg_input* in, const gmg_hierarchy_options* opt,

@@ -52,6 +52,37 @@ def test_sharded_equals_single_gpu(ctx, name, scale, world, mode):
     sh.close(); inp.close()
 
 
+@pytest.mark.parametrize("name,scale,world", [("C1", 1.0, 2), ("C3", 0.004, 4), ("C3", 0.004, 7)])
+def test_sharded_galerkin_equals_single_gpu(ctx, name, scale, world):
+    """A_c = P^T A P on every level of the sharded build (rows of P gathered, owned outer vectors formed per
+    rank, A_c gathered): same pattern as the single-GPU product, values to 1e-12 (the accumulation order inside
+    a row's hash table is not fixed), and equal to scipy's P^T A P."""
+    from gravomg_b200.sharded import ShardedHierarchy
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    inp = capi.Input(ctx, V, A.indptr, A.indices, A.data)
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=3, build_galerkin=True)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_PARALLEL,
+                          seed=3, build_galerkin=True)
+    assert sh.num_levels == h.num_levels
+    Acur = A.tocsc()
+    for lvl in range(h.num_levels):
+        want = h.galerkin(lvl)
+        assert sh.info(lvl)["nnz_ac"] == want.nnz
+        for k in (0, world - 1):
+            got = sh.galerkin(lvl, k)
+            assert np.array_equal(got.indptr, want.indptr) and np.array_equal(got.indices, want.indices)
+            assert np.abs(got.data - want.data).max() <= 1e-12 * np.abs(want.data).max()
+        P = h.prolongation(lvl)
+        ref = (P.T @ Acur @ P).tocsc()
+        D = (got - ref).tocoo()
+        assert np.abs(D.data).max(initial=0.0) <= 1e-12 * np.abs(ref.data).max()
+        # P itself is still the single-GPU P
+        assert_level_equal(sh.level_arrays(lvl), h.level_arrays(lvl), keys=KEYS, what=f"{name} galerkin level {lvl} ")
+        Acur = want
+    sh.close(); h.close(); inp.close()
+
+
 def test_sharded_exact_matches_oracle(ctx, orc):
     """The sharded build in exact-sampler mode is the reference's hierarchy: checked against the oracle."""
     from gravomg_b200.sharded import ShardedHierarchy
