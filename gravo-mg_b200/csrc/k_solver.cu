@@ -165,6 +165,11 @@ __global__ void __launch_bounds__(kBlock) gs_colour_kernel(int32_t count, const 
     if (sub == 0) x[i] = (b[i] - s) / d;
 }
 
+void gauss_seidel_rows(gmg_ctx* c, const int32_t* rows, int32_t count, const int32_t* outer, const int32_t* inner,
+                       const double* val, const double* b, double* x) {
+    if (count > 0) GMG_LAUNCH(c, gs_colour_kernel, div_up(int64_t(count) * kSLanes, kBlock), kBlock, 0, count, rows, outer, inner, val, b, x);
+}
+
 void gauss_seidel(gmg_ctx* c, const Colouring& col, const int32_t* outer, const int32_t* inner, const double* val,
                   const double* b, double* x, int sweeps, bool reverse) {
     for (int s = 0; s < sweeps; ++s)

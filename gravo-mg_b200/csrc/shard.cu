@@ -27,81 +27,9 @@
 //
 // The object below is driven phase by phase from the host (gravo-mg_b200/sharded.py): run a phase on
 // every rank, all-gather the buffers that phase names, go on.
-#include "hierarchy_types.h"
+#include "shard_types.h"
 
 #include <cmath>
-
-using namespace gmg;
-
-struct gmg_shard {
-    gmg_ctx* ctx = nullptr;
-    int rank = 0, world = 1;
-    gmg_hierarchy_options opt{};
-    std::vector<double> radius_override;
-    // current level (replicated)
-    int level = 0;
-    int32_t n = 0;
-    int64_t nnz = 0;
-    int32_t lo = 0, hi = 0;          // owned fine vertices
-    int32_t chunk = 0;               // slice length of the per-vertex exchange buffers (n_pad = chunk * world)
-    const double* pts = nullptr;
-    const int32_t* colptr = nullptr;
-    const int32_t* rowidx = nullptr;
-    const double* val = nullptr;     // stored values of the level's edge matrix
-    DevBuf<double> len;              // Euclidean lengths (level 0: also the stored values)
-    DevBuf<uint8_t> need;            // world > 1: columns whose lengths this rank computes
-    bool val_is_len = false;
-    int32_t gchunk = 0;              // column groups (32 columns) per rank
-    DevBuf<double> len_partial;      // exchange: sum of the lengths of every column group
-    double radius = 0.0;
-    // exchange buffers (per-vertex, chunk * world entries; a rank writes [lo, hi) only)
-    DevBuf<uint8_t> state, changed[2];
-    DevBuf<unsigned long long> dist;
-    DevBuf<int32_t> srcid, pred, parents;
-    int parity = 0;
-    ShardSampler sampler;
-    // coarse side
-    int32_t m = 0, clo = 0, chi = 0, cchunk = 0;
-    DevBuf<int32_t> samples;
-    Clusters clusters;
-    DevBuf<int32_t> ccnt;            // exchange: distinct neighbours per coarse row, cchunk * world (+1)
-    CoarseRows rows;
-    DevBuf<int32_t> rowoff;          // exclusive scan of ccnt over ALL rows (m + 1) = global row-major offsets
-    int64_t rows_max = 0;            // largest per-rank row volume: slice length of the two buffers below
-    DevBuf<int32_t> xQ;              // exchange: packed rows (neighbour ids), rows_max * world
-    DevBuf<double> xt;               // exchange: packed rows (values)
-    std::vector<int64_t> rank_rows;  // entries per rank
-    StageStatus status;
-    // Galerkin side (build_galerkin): the level's system matrix (replicated, pattern = any) and the exchange
-    int32_t a_n = 0;
-    const int32_t* a_colptr = nullptr;
-    const int32_t* a_rowidx = nullptr;
-    const double* a_val = nullptr;
-    DevBuf<int32_t> pcnt;            // exchange: entries per row of P, chunk * world (+1)
-    DeviceCsr Pfull;                 // all rows of P (transient)
-    int64_t p_max = 0;               // largest per-rank P volume: slice length of xPc / xPv
-    DevBuf<int32_t> xPc;             // exchange: the ranks' colidx arrays
-    DevBuf<double> xPv;              // exchange: the ranks' value arrays
-    std::vector<int64_t> rank_p;
-    DeviceCsc ac_own;                // the owned outer vectors of A_c, indexed from clo
-    int64_t ac_max = 0;
-    std::vector<int64_t> rank_ac;
-    // finished levels: replicated coarse data + the owned rows of P
-    struct Done {
-        gmg_level_info info{};
-        int32_t lo = 0, hi = 0;
-        DevBuf<int32_t> samples, parents;
-        DeviceCsc coarse;
-        DevBuf<double> coarse_pts;
-        Triangles tri;
-        DeviceCsr P;                 // rows [lo, hi)
-        int32_t clo = 0, chi = 0;    // owned coarse vertices
-        DeviceCsr R;                 // build_galerkin: rows [clo, chi) of P^T (restriction of the owned coarse rows)
-        DeviceCsc Ac;                // build_galerkin: A_c, replicated
-    };
-    std::vector<std::unique_ptr<Done>> done;
-    std::unique_ptr<Done> cur;
-};
 
 namespace {
 
@@ -496,6 +424,7 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 s->status.raise_parents();
                 s->status.raise_coarse();
                 s->status.raise_prolong(s->hi - s->lo);
+                L.clo = s->clo; L.chi = s->chi; L.chunk = s->chunk; L.cchunk = s->cchunk;
                 // keep what a consumer of the level needs; the rest goes back to the pool
                 L.samples = std::move(s->samples);
                 L.parents.alloc(c, s->n);

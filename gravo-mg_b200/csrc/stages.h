@@ -172,6 +172,9 @@ void axpy(gmg_ctx* c, int32_t n, double a, const double* x, double* y);
 void colour_graph(gmg_ctx* c, int32_t n, const int32_t* outer, const int32_t* inner, Colouring& out);
 void gauss_seidel(gmg_ctx* c, const Colouring& col, const int32_t* outer, const int32_t* inner, const double* val,
                   const double* b, double* x, int sweeps, bool reverse);
+// one colour's worth: x[i] = (b[i] - sum_{j != i} a_ij x[j]) / a_ii for the listed (mutually independent) rows
+void gauss_seidel_rows(gmg_ctx* c, const int32_t* rows, int32_t count, const int32_t* outer, const int32_t* inner,
+                       const double* val, const double* b, double* x);
 double norm2(gmg_ctx* c, int32_t n, const double* x);
 
 // index conversions at the ABI boundary (std::vector<Eigen::Index> is int64, device indices int32)

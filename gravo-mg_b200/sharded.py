@@ -318,3 +318,242 @@ class ShardedHierarchy:
         for s in getattr(self, "shards", []):
             s.close()
         self.shards = []
+
+
+# ---- row-sharded smoothing / V-cycle -----------------------------------------------------------------
+(SV_X, SV_B, SV_R, SV_COLOUR, SV_MASK) = range(5)
+(HP_A, HP_R, HP_P) = range(3)
+(SO_GS_COLOUR, SO_RESIDUAL, SO_RESTRICT, SO_PROLONG, SO_ZERO_X, SO_SUMSQ_R) = range(6)
+
+
+def halo_counts(ghost, chunk, world):
+    """Entries of an ascending ghost list per owning rank (owner of vertex j = j // chunk)."""
+    import torch
+    if ghost.numel() == 0:
+        return [0] * world
+    return torch.bincount(torch.div(ghost, chunk, rounding_mode="floor"), minlength=world).tolist()
+
+
+class HaloPlan:
+    """Who sends what for one halo pattern. Per local rank: `ghost` (ascending global indices this rank
+    reads but does not own, hence grouped by owner), `recv_counts` per owner, `send_idx` (the owned
+    indices the other ranks read, grouped by reader, ascending per reader) and `send_counts`."""
+
+    def __init__(self, ghost, recv_counts, send_idx, send_counts):
+        self.ghost, self.recv_counts, self.send_idx, self.send_counts = ghost, recv_counts, send_idx, send_counts
+        self.volume = sum(sum(c) for c in send_counts)
+
+    def select(self, keep_ghost, keep_send):
+        """Sub-plan over the entries flagged by the boolean tensors (same rule on both sides of a pair)."""
+        import torch
+        ghost, rc, sidx, sc = [], [], [], []
+        for g, r_counts, kg in zip(self.ghost, self.recv_counts, keep_ghost):
+            ghost.append(g[kg])
+            rc.append([int(p.sum()) for p in torch.split(kg, r_counts)])
+        for si, s_counts, ks in zip(self.send_idx, self.send_counts, keep_send):
+            sidx.append(si[ks])
+            sc.append([int(p.sum()) for p in torch.split(ks, s_counts)])
+        return HaloPlan(ghost, rc, sidx, sc)
+
+
+class ShardedSolver:
+    """V-cycle on A x = b over a ShardedHierarchy built with build_galerkin=True. Operators run on the
+    owned rows (gmg_shard_solver_op); ghost entries move between ranks as packed all-to-all exchanges
+    (torch.distributed all_to_all_single over NCCL, or the loop-back between virtual ranks)."""
+
+    def __init__(self, sh, inp):
+        import torch
+        self.torch, self.sh, self.ctx, self._inp = torch, sh, sh.ctx, inp
+        self.comm, self.world, self.device = sh.comm, sh.world, sh.device
+        self.same_stream = sh.same_stream
+        lib = self.ctx.lib
+        lib.gmg_shard_solver_create.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+        lib.gmg_shard_solver_destroy.argtypes = [C.c_void_p]
+        lib.gmg_shard_solver_destroy.restype = None
+        lib.gmg_shard_solver_num_levels.argtypes = [C.c_void_p]
+        lib.gmg_shard_solver_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
+        lib.gmg_shard_solver_vector.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        lib.gmg_shard_solver_halo_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64)]
+        lib.gmg_shard_solver_op.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        self.ranks = [s.rank for s in sh.shards]
+        self.h = []
+        for s in sh.shards:
+            h = C.c_void_p()
+            self.ctx._check(lib.gmg_shard_solver_create(self.ctx.h, s.h, inp.h, C.byref(h)))
+            self.h.append(h)
+        self.num_levels = int(lib.gmg_shard_solver_num_levels(self.h[0]))
+        self.exchanges = 0
+        self.exchange_bytes = 0
+        self.geom = []        # per level: list over local ranks of dict(n, lo, hi, chunk, colours)
+        io = (C.c_int64 * 8)()
+        for l in range(self.num_levels):
+            g = []
+            for h in self.h:
+                self.ctx._check(lib.gmg_shard_solver_level(h, C.c_int(l), io))
+                g.append(dict(n=int(io[0]), lo=int(io[1]), hi=int(io[2]), chunk=int(io[3]), colours=int(io[4])))
+            self.geom.append(g)
+        self._fence()
+        # halo plans: per level the operator's ghosts split by colour, the restriction's and the prolongation's
+        self.plan_a, self.plan_colour, self.plan_r, self.plan_p = [], [], [], []
+        for l in range(self.num_levels):
+            pa = self._plan(l, HP_A)
+            self.plan_a.append(pa)
+            colour = [self._vec(k, l, SV_COLOUR) for k in range(len(self.h))]
+            per_colour = []
+            for col in range(self.geom[l][0]["colours"]):
+                per_colour.append(pa.select([colour[k][pa.ghost[k]] == col for k in range(len(self.h))],
+                                            [colour[k][pa.send_idx[k]] == col for k in range(len(self.h))]))
+            self.plan_colour.append(per_colour)
+            if l + 1 < self.num_levels:
+                self.plan_r.append(self._plan(l, HP_R))
+                self.plan_p.append(self._plan(l, HP_P))
+        self.last_ms = 0.0
+
+    # ---- plumbing --------------------------------------------------------------------------------------
+    def _fence(self):
+        if not self.same_stream:
+            self.torch.cuda.synchronize()
+
+    def _vec(self, k, level, which):
+        t = self.torch
+        ptr = C.c_void_p()
+        rc = self.ctx.lib.gmg_shard_solver_vector(self.h[k], C.c_int(level), C.c_int(which), C.byref(ptr))
+        if rc != 0:
+            raise GmgError(rc, "gmg_shard_solver_vector")
+        g = self.geom[level][k]
+        n_pad = max(g["n"], g["chunk"] * self.world)
+        if which == SV_COLOUR:
+            return device_bytes_as_tensor(ptr.value, 4 * g["n"], self.device).view(t.int32)
+        if which == SV_MASK:
+            return device_bytes_as_tensor(ptr.value, n_pad, self.device)
+        return device_bytes_as_tensor(ptr.value, 8 * n_pad, self.device).view(t.float64)
+
+    def _op(self, level, op, arg=0):
+        out = C.c_double(0.0)
+        vals = []
+        for h in self.h:
+            self.ctx._check(self.ctx.lib.gmg_shard_solver_op(self.ctx.h, h, C.c_int(level), C.c_int(op), C.c_int(arg), C.byref(out)))
+            vals.append(out.value)
+        return vals
+
+    def _plan(self, level, pattern):
+        """Ghost lists from the library's halo mask, then the matching send lists from the other ranks."""
+        t = self.torch
+        space = C.c_int64()
+        target = level + 1 if pattern == HP_P else level
+        chunk = self.geom[target][0]["chunk"]
+        ghosts = []
+        for k, h in enumerate(self.h):
+            self.ctx._check(self.ctx.lib.gmg_shard_solver_halo_mask(self.ctx.h, h, C.c_int(level), C.c_int(pattern), C.byref(space)))
+            self._fence()
+            mask = self._vec(k, target, SV_MASK)[:int(space.value)]
+            ghosts.append(t.nonzero(mask).flatten())
+        recv_counts = [halo_counts(g, chunk, self.world) for g in ghosts]
+        if self.comm is None:
+            send_idx, send_counts = [], []
+            for r in self.ranks:
+                parts = [g[t.div(g, chunk, rounding_mode="floor") == r] for g in ghosts]
+                send_idx.append(t.cat(parts))
+                send_counts.append([int(p.numel()) for p in parts])
+        else:
+            d = self.comm.dist
+            rc = t.tensor(recv_counts[0], dtype=t.int64, device=self.device)
+            sc = t.empty_like(rc)
+            d.all_to_all_single(sc, rc, group=self.comm.group)
+            send_counts = [sc.tolist()]
+            sidx = t.empty(sum(send_counts[0]), dtype=t.int64, device=self.device)
+            d.all_to_all_single(sidx, ghosts[0], output_split_sizes=send_counts[0], input_split_sizes=recv_counts[0],
+                                group=self.comm.group)
+            send_idx = [sidx]
+        return HaloPlan(ghosts, recv_counts, send_idx, send_counts)
+
+    def _exchange(self, plan, level, which):
+        """Owner values -> ghost slots of vector `which` of `level`, for the entries of `plan`."""
+        t = self.torch
+        vecs = [self._vec(k, level, which) for k in range(len(self.h))]
+        self._fence()
+        packed = [v[idx] for v, idx in zip(vecs, plan.send_idx)]
+        self.exchanges += 1
+        self.exchange_bytes += 8 * plan.volume
+        if self.comm is None:
+            offs = [np.concatenate([[0], np.cumsum(c)]) for c in plan.send_counts]
+            for q in range(len(self.h)):               # reader q receives, from every owner r, what r packed for q
+                parts = [packed[r][int(offs[r][q]):int(offs[r][q + 1])] for r in range(len(self.h))]
+                if plan.ghost[q].numel():
+                    vecs[q][plan.ghost[q]] = t.cat(parts)
+        else:
+            recv = t.empty(sum(plan.recv_counts[0]), dtype=t.float64, device=self.device)
+            self.comm.dist.all_to_all_single(recv, packed[0], output_split_sizes=plan.recv_counts[0],
+                                             input_split_sizes=plan.send_counts[0], group=self.comm.group)
+            if recv.numel():
+                vecs[0][plan.ghost[0]] = recv
+        self._fence()
+
+    # ---- the cycle -------------------------------------------------------------------------------------
+    def _smooth(self, level, sweeps, reverse):
+        nc = self.geom[level][0]["colours"]
+        for _ in range(sweeps):
+            for kk in range(nc):
+                col = nc - 1 - kk if reverse else kk
+                self._op(level, SO_GS_COLOUR, col)
+                self._exchange(self.plan_colour[level][col], level, SV_X)
+
+    def _vcycle(self, level, pre, post, coarse_sweeps):
+        if level + 1 == self.num_levels:
+            self._smooth(level, coarse_sweeps, False)
+            return
+        self._smooth(level, pre, False)
+        self._op(level, SO_RESIDUAL)
+        self._exchange(self.plan_r[level], level, SV_R)
+        self._op(level, SO_RESTRICT)
+        self._op(level + 1, SO_ZERO_X)
+        self._vcycle(level + 1, pre, post, coarse_sweeps)
+        self._exchange(self.plan_p[level], level + 1, SV_X)
+        self._op(level, SO_PROLONG)
+        self._exchange(self.plan_a[level], level, SV_X)
+        self._smooth(level, post, True)
+
+    def _residual_norm(self):
+        t = self.torch
+        self._op(0, SO_RESIDUAL)
+        total = float(sum(self._op(0, SO_SUMSQ_R)))
+        if self.comm is not None:
+            v = t.tensor([total], dtype=t.float64, device=self.device)
+            self.comm.dist.all_reduce(v, group=self.comm.group)
+            total = float(v.item())
+        return float(np.sqrt(total))
+
+    def vcycle(self, b, x0=None, cycles=1, pre=2, post=2, coarse_sweeps=50):
+        """b, x0: the WHOLE right-hand side / start vector (every rank passes the same). Returns (x, residuals):
+        x holds the owned entries of the ranks this process runs (everything under the loop-back), NaN elsewhere."""
+        t = self.torch
+        n = self.geom[0][0]["n"]
+        hb = t.from_numpy(np.ascontiguousarray(b, dtype=np.float64))
+        hx = t.zeros(n, dtype=t.float64) if x0 is None else t.from_numpy(np.ascontiguousarray(x0, dtype=np.float64))
+        self._fence()
+        for k in range(len(self.h)):
+            self._vec(k, 0, SV_B)[:n].copy_(hb)
+            self._vec(k, 0, SV_X)[:n].copy_(hx)
+        self._fence()
+        res = [self._residual_norm()]
+        e0, e1 = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
+        self.last_ms = 0.0
+        for _ in range(cycles):
+            self._fence()
+            e0.record()
+            self._vcycle(0, pre, post, coarse_sweeps)
+            e1.record()
+            t.cuda.synchronize()
+            self.last_ms += e0.elapsed_time(e1)
+            res.append(self._residual_norm())
+        x = np.full(n, np.nan)
+        for k in range(len(self.h)):
+            g = self.geom[0][k]
+            x[g["lo"]:g["hi"]] = self._vec(k, 0, SV_X)[g["lo"]:g["hi"]].cpu().numpy()
+        return x, np.array(res)
+
+    def close(self):
+        for h in getattr(self, "h", []):
+            if getattr(self.ctx, "h", None):
+                self.ctx.lib.gmg_shard_solver_destroy(h)
+        self.h = []

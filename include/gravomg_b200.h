@@ -274,6 +274,36 @@ int gmg_shard_level_info(const gmg_shard* s, int level, gmg_level_info* out, int
  * the owned rows [row_lo, row_hi) (rowptr: row_hi - row_lo + 1 entries starting at 0) */
 int gmg_shard_fetch(gmg_ctx* ctx, const gmg_shard* s, int level, int which, void* out);
 
+/* ------------------------------------------------------------------------------------------------
+ * Row-sharded smoothing and V-cycle on a shard built with build_galerkin [not in reference]. Every rank
+ * keeps full-length vectors per level (levels = prolongations + 1); only the owned entries [lo, hi) and the
+ * ghost entries its rows read are valid. An op acts on the owned rows; between ops the HOST exchanges
+ * ghost entries (packed all-to-all over NCCL in gravo-mg_b200/sharded.py), guided by the halo masks.
+ *   V-cycle on level l:  for each colour k { GS_COLOUR(k) ; exchange x over the ghosts of colour k } (pre
+ *   sweeps) ; RESIDUAL ; exchange r over pattern R ; RESTRICT ; ZERO_X(l+1) ; recurse ; exchange x(l+1) over
+ *   pattern P ; PROLONG ; exchange x over pattern A ; post sweeps in reverse colour order.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct gmg_shard_solver gmg_shard_solver;
+enum { GMG_SV_X = 0, GMG_SV_B, GMG_SV_R, GMG_SV_COLOUR, GMG_SV_MASK };
+enum { GMG_HP_A = 0, GMG_HP_R, GMG_HP_P };
+enum { GMG_SO_GS_COLOUR = 0, GMG_SO_RESIDUAL, GMG_SO_RESTRICT, GMG_SO_PROLONG, GMG_SO_ZERO_X, GMG_SO_SUMSQ_R };
+/* `shard` and `in` must outlive the solver */
+int gmg_shard_solver_create(gmg_ctx* ctx, const gmg_shard* shard, const gmg_input* in, gmg_shard_solver** out);
+void gmg_shard_solver_destroy(gmg_shard_solver* s);
+int gmg_shard_solver_num_levels(const gmg_shard_solver* s);
+/* io (>= 8 int64) = {n, lo, hi, slice length of the level's split (owner of vertex j = j / slice), colours} */
+int gmg_shard_solver_level(const gmg_shard_solver* s, int level, int64_t* io);
+/* device pointer of a level's vector: X, B, R f64[max(n, slice * world)]; COLOUR int32[n]; MASK uint8[same as X] */
+int gmg_shard_solver_vector(gmg_shard_solver* s, int level, int which, void** ptr);
+/* Fill the MASK vector with a halo pattern: 1 for every entry outside the owned range that the owned rows of
+ * the operator read. GMG_HP_A: x of `level` read by A; GMG_HP_R: r of `level` read by the restriction to
+ * level + 1; GMG_HP_P: x of level + 1 read by the prolongation (written to the mask OF level + 1).
+ * *space = number of entries of that mask. */
+int gmg_shard_solver_halo_mask(gmg_ctx* ctx, gmg_shard_solver* s, int level, int pattern, int64_t* space);
+/* One operator on the owned rows. GS_COLOUR: arg = colour. RESIDUAL: r = b - A x. RESTRICT: b(level+1) = R r.
+ * PROLONG: x += P x(level+1). ZERO_X: x = 0 (all entries). SUMSQ_R: *out = sum over owned rows of r^2. */
+int gmg_shard_solver_op(gmg_ctx* ctx, gmg_shard_solver* s, int level, int op, int arg, double* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,6 +83,36 @@ def test_sharded_galerkin_equals_single_gpu(ctx, name, scale, world):
     sh.close(); h.close(); inp.close()
 
 
+@pytest.mark.parametrize("world", [2, 5])
+def test_sharded_vcycle_equals_single_gpu(ctx, world):
+    """Row-sharded multicolour Gauss-Seidel / V-cycle with halo exchanges of ghost entries (packed all-to-all;
+    loop-back here) against the single-GPU V-cycle on the same hierarchy: same colouring, same (colour, row)
+    sweep order, so the iterates agree to rounding (A_c's accumulation order is the only difference)."""
+    from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver
+    cfg = meshgen.make_config("C3", 0.01)
+    V, A = cfg["V"], cfg["A"]
+    n = V.shape[0]
+    b = A @ (np.sin(3 * V[:, 0]) * np.cos(2 * V[:, 1]) + V[:, 2])
+    inp = capi.Input(ctx, V, A.indptr, A.indices, A.data)
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=5, build_galerkin=True)
+    ref = capi.Solver(ctx, inp, h)
+    x_ref, res_ref = ref.vcycle(b, cycles=3, pre=2, post=2, coarse_sweeps=20)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_PARALLEL,
+                          seed=5, build_galerkin=True)
+    sv = ShardedSolver(sh, inp)
+    assert sv.num_levels == h.num_levels + 1
+    x, res = sv.vcycle(b, cycles=3, pre=2, post=2, coarse_sweeps=20)
+    assert not np.isnan(x).any()
+    assert np.abs(res - res_ref).max() <= 1e-9 * res_ref[0], (res, res_ref)
+    assert np.abs(x - x_ref).max() <= 1e-9 * np.abs(x_ref).max()
+    assert res[-1] < 0.05 * res[0]
+    assert sv.exchanges > 0 and sv.exchange_bytes > 0
+    # the halo is a boundary layer, not the vector: far fewer ghosts than vertices
+    ghosts = sum(int(g.numel()) for g in sv.plan_a[0].ghost)
+    assert 0 < ghosts < 0.5 * n * world
+    sv.close(); sh.close(); ref.close(); h.close(); inp.close()
+
+
 def test_sharded_exact_matches_oracle(ctx, orc):
     """The sharded build in exact-sampler mode is the reference's hierarchy: checked against the oracle."""
     from gravomg_b200.sharded import ShardedHierarchy
