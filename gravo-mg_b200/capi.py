@@ -311,6 +311,8 @@ class Input:
         return pts, cp, ri
 
     def close(self):
+        if C is None:       # interpreter shutdown: module globals are already gone
+            return
         if getattr(self, "h", None) and getattr(self.ctx, "h", None):
             self.ctx.lib.gmg_input_destroy.argtypes = [C.c_void_p]
             self.ctx.lib.gmg_input_destroy(self.h)
@@ -346,6 +348,8 @@ class Hierarchy:
             self.info.append(li.as_dict())
 
     def close(self):
+        if C is None:
+            return
         if getattr(self, "h", None) and getattr(self.ctx, "h", None):
             self.ctx.lib.gmg_hierarchy_destroy.argtypes = [C.c_void_p]
             self.ctx.lib.gmg_hierarchy_destroy(self.h)
@@ -444,6 +448,8 @@ class Solver:
         return x, res
 
     def close(self):
+        if C is None:
+            return
         if getattr(self, "h", None) and getattr(self.ctx, "h", None):
             self.ctx.lib.gmg_solver_destroy.argtypes = [C.c_void_p]
             self.ctx.lib.gmg_solver_destroy(self.h)

@@ -356,6 +356,31 @@ class HaloPlan:
         return HaloPlan(ghost, rc, sidx, sc)
 
 
+def plan_over_dist(dist, group, ghost, chunk, world):
+    """HaloPlan of ONE rank per process: the ghost list goes to the owners (all_to_all_single of the counts,
+    then of the indices), which answer nothing -- what they receive IS their send list."""
+    import torch
+    recv_counts = halo_counts(ghost, chunk, world)
+    rc = torch.tensor(recv_counts, dtype=torch.int64, device=ghost.device)
+    sc = torch.empty_like(rc)
+    dist.all_to_all_single(sc, rc, group=group)
+    send_counts = sc.tolist()
+    send_idx = torch.empty(sum(send_counts), dtype=torch.int64, device=ghost.device)
+    dist.all_to_all_single(send_idx, ghost, output_split_sizes=send_counts, input_split_sizes=recv_counts, group=group)
+    return HaloPlan([ghost], [recv_counts], [send_idx], [send_counts])
+
+
+def exchange_over_dist(dist, group, plan, vec):
+    """Owner values -> ghost slots of `vec` (one rank per process)."""
+    import torch
+    packed = vec[plan.send_idx[0]]
+    recv = torch.empty(sum(plan.recv_counts[0]), dtype=vec.dtype, device=vec.device)
+    dist.all_to_all_single(recv, packed, output_split_sizes=plan.recv_counts[0], input_split_sizes=plan.send_counts[0],
+                           group=group)
+    if recv.numel():
+        vec[plan.ghost[0]] = recv
+
+
 class ShardedSolver:
     """V-cycle on A x = b over a ShardedHierarchy built with build_galerkin=True. Operators run on the
     owned rows (gmg_shard_solver_op); ghost entries move between ranks as packed all-to-all exchanges
@@ -448,23 +473,14 @@ class ShardedSolver:
             self._fence()
             mask = self._vec(k, target, SV_MASK)[:int(space.value)]
             ghosts.append(t.nonzero(mask).flatten())
+        if self.comm is not None:
+            return plan_over_dist(self.comm.dist, self.comm.group, ghosts[0], chunk, self.world)
         recv_counts = [halo_counts(g, chunk, self.world) for g in ghosts]
-        if self.comm is None:
-            send_idx, send_counts = [], []
-            for r in self.ranks:
-                parts = [g[t.div(g, chunk, rounding_mode="floor") == r] for g in ghosts]
-                send_idx.append(t.cat(parts))
-                send_counts.append([int(p.numel()) for p in parts])
-        else:
-            d = self.comm.dist
-            rc = t.tensor(recv_counts[0], dtype=t.int64, device=self.device)
-            sc = t.empty_like(rc)
-            d.all_to_all_single(sc, rc, group=self.comm.group)
-            send_counts = [sc.tolist()]
-            sidx = t.empty(sum(send_counts[0]), dtype=t.int64, device=self.device)
-            d.all_to_all_single(sidx, ghosts[0], output_split_sizes=send_counts[0], input_split_sizes=recv_counts[0],
-                                group=self.comm.group)
-            send_idx = [sidx]
+        send_idx, send_counts = [], []
+        for r in self.ranks:
+            parts = [g[t.div(g, chunk, rounding_mode="floor") == r] for g in ghosts]
+            send_idx.append(t.cat(parts))
+            send_counts.append([int(p.numel()) for p in parts])
         return HaloPlan(ghosts, recv_counts, send_idx, send_counts)
 
     def _exchange(self, plan, level, which):
@@ -472,21 +488,17 @@ class ShardedSolver:
         t = self.torch
         vecs = [self._vec(k, level, which) for k in range(len(self.h))]
         self._fence()
-        packed = [v[idx] for v, idx in zip(vecs, plan.send_idx)]
         self.exchanges += 1
         self.exchange_bytes += 8 * plan.volume
-        if self.comm is None:
+        if self.comm is not None:
+            exchange_over_dist(self.comm.dist, self.comm.group, plan, vecs[0])
+        else:
+            packed = [v[idx] for v, idx in zip(vecs, plan.send_idx)]
             offs = [np.concatenate([[0], np.cumsum(c)]) for c in plan.send_counts]
             for q in range(len(self.h)):               # reader q receives, from every owner r, what r packed for q
                 parts = [packed[r][int(offs[r][q]):int(offs[r][q + 1])] for r in range(len(self.h))]
                 if plan.ghost[q].numel():
                     vecs[q][plan.ghost[q]] = t.cat(parts)
-        else:
-            recv = t.empty(sum(plan.recv_counts[0]), dtype=t.float64, device=self.device)
-            self.comm.dist.all_to_all_single(recv, packed[0], output_split_sizes=plan.recv_counts[0],
-                                             input_split_sizes=plan.send_counts[0], group=self.comm.group)
-            if recv.numel():
-                vecs[0][plan.ghost[0]] = recv
         self._fence()
 
     # ---- the cycle -------------------------------------------------------------------------------------

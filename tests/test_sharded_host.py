@@ -70,3 +70,63 @@ def test_all_gather_exchange_gloo(world):
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(r, True) for r in range(world)]
+
+
+def _halo_worker(rank, world, port, n, q):
+    """A 1-D periodic stencil (i-2 .. i+2) row-sharded over `world` ranks: every rank lists the ghost entries its
+    rows read, the plan is exchanged with all_to_all_single, and one halo exchange must fill exactly those ghosts
+    with the owners' values -- for the whole pattern and for a "colour" sub-plan (i % 3)."""
+    import torch
+    import torch.distributed as dist
+    from gravomg_b200.sharded import partition, plan_over_dist, exchange_over_dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        chunk, lo, hi = partition(n, world, rank)
+        own = np.arange(lo, hi)
+        reads = np.unique(np.concatenate([(own + d) % n for d in (-2, -1, 1, 2)])) if hi > lo else np.zeros(0, dtype=np.int64)
+        ghost_np = reads[(reads < lo) | (reads >= hi)]
+        ghost = torch.from_numpy(ghost_np.astype(np.int64))
+        plan = plan_over_dist(dist, None, ghost, chunk, world)
+        ok = sum(plan.recv_counts[0]) == len(ghost_np)
+        # what the others read from me must be mine
+        sidx = plan.send_idx[0].numpy()
+        ok = ok and bool(np.all((sidx >= lo) & (sidx < hi)))
+        truth = np.arange(n, dtype=np.float64) * 1.5 + 3.0
+        vec = torch.full((chunk * world,), -1.0, dtype=torch.float64)
+        vec[lo:hi] = torch.from_numpy(truth[lo:hi])
+        exchange_over_dist(dist, None, plan, vec)
+        got = vec.numpy()
+        ok = ok and np.array_equal(got[ghost_np], truth[ghost_np])
+        untouched = np.ones(chunk * world, dtype=bool)
+        untouched[lo:hi] = False
+        untouched[ghost_np] = False
+        ok = ok and bool(np.all(got[untouched] == -1.0))
+        # colour sub-plan: both sides filter with the same rule
+        colour = torch.arange(chunk * world) % 3
+        sub = plan.select([colour[plan.ghost[0]] == 1], [colour[plan.send_idx[0]] == 1])
+        vec2 = torch.full((chunk * world,), -1.0, dtype=torch.float64)
+        vec2[lo:hi] = torch.from_numpy(truth[lo:hi])
+        exchange_over_dist(dist, None, sub, vec2)
+        g1 = ghost_np[ghost_np % 3 == 1]
+        g0 = ghost_np[ghost_np % 3 != 1]
+        ok = ok and np.array_equal(vec2.numpy()[g1], truth[g1]) and bool(np.all(vec2.numpy()[g0] == -1.0))
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 200), (3, 1000), (4, 97)])
+def test_halo_exchange_gloo(world, n):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_halo_worker, args=(r, world, port, n, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(r, True) for r in range(world)]
