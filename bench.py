@@ -14,6 +14,7 @@ exchanges are NCCL all-gathers over NVLink; weak scaling. `--workload T<millions
 many vertices at any N (e.g. T25 at N=1 and N=2 gives the strong-scaling pair).
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -432,7 +433,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     import torch.distributed as dist
     from gravomg_b200 import capi
     from gravomg_b200.capi import Context, Input
-    from gravomg_b200.sharded import ShardedHierarchy, TorchComm
+    from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
@@ -447,7 +448,9 @@ def run_b200_sharded(a, rank, world, local_rank):
     n = nu * nv
     levels = 4
     mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
-    inp = Input.torus(ctx, nu, nv)                       # the whole mesh, resident on every rank
+    galerkin = bool(a.galerkin or a.vcycle)
+    # the whole mesh, resident on every rank (with its system matrix when A_c is asked for)
+    inp = Input.torus(ctx, nu, nv, mass_shift=1e-3 if galerkin else None)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -455,8 +458,16 @@ def run_b200_sharded(a, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def device_points(which):
+        """x, y, z of an Input as device tensors (via pinned host memory: the C ABI hands out host copies)."""
+        ctx.lib.gmg_input_fetch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        host = torch.empty(3 * which.n, dtype=torch.float64).pin_memory()
+        ctx._check(ctx.lib.gmg_input_fetch(ctx.h, which.h, 0, ctypes.c_void_p(host.data_ptr())))
+        return host.cuda().view(3, which.n)
+
     def build(which, profile=False):
-        return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode, profile=profile)
+        return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode, profile=profile,
+                                build_galerkin=galerkin)
 
     for _ in range(a.warmup):
         build(inp).close()
@@ -485,6 +496,26 @@ def run_b200_sharded(a, rank, world, local_rank):
     # one extra, untimed build with per-phase events: where the step goes (rank 0's view)
     hp = build(inp, profile=True)
     phase_ms = {k: round(v, 3) for k, v in sorted(hp.phase_ms().items(), key=lambda kv: -kv[1])}
+    vc = None
+    if a.vcycle:
+        # one V(2,2) cycle on A x = b with b = A x*, x* smooth: row-sharded smoothing with halo exchanges
+        sv = ShardedSolver(hp, inp)
+        px = device_points(inp)                                               # x* from the device-resident positions
+        sv.rhs_from_solution(torch.sin(3 * px[0]) * torch.cos(2 * px[1]) + px[2])
+        del px
+        sv.vcycle(None, cycles=1, pre=2, post=2, coarse_sweeps=20, fetch=False)   # warm-up (allocator, NCCL channels)
+        ex0, xb0 = sv.exchanges, sv.exchange_bytes
+        _, res = sv.vcycle(None, cycles=1, pre=2, post=2, coarse_sweeps=20, fetch=False)
+        vms = torch.tensor([sv.last_ms], device="cuda", dtype=torch.float64)
+        xb = torch.tensor([float(sv.exchange_bytes - xb0)], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(vms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(xb, op=dist.ReduceOp.SUM)
+        vc = {"ms": float(vms[0]), "residual_before": float(res[0]), "residual_after": float(res[1]),
+              "sweeps": "2 pre + 2 post multicolour Gauss-Seidel per level, 20 on the coarsest",
+              "halo_exchanges": int(sv.exchanges - ex0), "halo_bytes_all_ranks": int(xb[0]),
+              "colours": [g[0]["colours"] for g in sv.geom]}
+        sv.close()
     hp.close()
 
     # end to end: host buffers -> device (every rank uploads the whole mesh), build, owned rows of P -> host
@@ -492,6 +523,9 @@ def run_b200_sharded(a, rank, world, local_rank):
     tV = torch.from_numpy(hV.T).pin_memory(); hV = tV.numpy().T
     tcp = torch.from_numpy(hcp).pin_memory(); hcp = tcp.numpy()
     tri = torch.from_numpy(hri).pin_memory(); hri = tri.numpy()
+    hA = None
+    if galerkin:
+        tA = torch.from_numpy(inp.fetch_operator()).pin_memory(); hA = tA.numpy()
 
     pin_out = {}
 
@@ -502,7 +536,7 @@ def run_b200_sharded(a, rank, world, local_rank):
         return pin_out[key]
 
     def step_e2e():
-        i2 = Input(ctx, hV, hcp, hri, None)
+        i2 = Input(ctx, hV, hcp, hri, hA)
         h2 = build(i2)
         d2h = 0
         for lvl in range(h2.num_levels):
@@ -539,18 +573,18 @@ def run_b200_sharded(a, rank, world, local_rank):
     peak, peak_src = measured_peak()
     for i in infos:
         i.setdefault("nnz_ac", 0)
-    total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if k != "galerkin") for i in infos)
+    total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if k != "galerkin" or galerkin) for i in infos)
     achieved = total_bytes / (ms * 1e-3) / 1e9
     line = {"metric": METRIC, "value": n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": False,
+            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": galerkin,
                        "l2": "256 MB flush write between timed steps; inputs exceed the 126 MB L2",
                        "multi_gpu": (f"row-sharded over {world} ranks: owned ranges of fine vertices, replicated level "
                                      f"graph, {exchanges} NCCL all-gathers ({xbytes / 1e6:.1f} MB gathered per rank) per build")
                        if world > 1 else "single GPU through the sharded driver (world 1)",
                        "verts_per_gpu": n // world,
-                       "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "sampler_rounds", "parent_rounds")}
+                       "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_ac", "sampler_rounds", "parent_rounds")}
                                   for i in infos]},
             "clocks": clk, "gpu_launches": int(launches), "phase_ms": phase_ms,
             "e2e": {"value": n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
@@ -558,6 +592,8 @@ def run_b200_sharded(a, rank, world, local_rank):
             "roofline": {"bound": "hbm", "kernel": "whole sharded build (all stages, all levels, exchanges included)",
                          "achieved": achieved / world, "peak": peak, "peak_source": peak_src, "unit": "GB/s per GPU",
                          "frac": achieved / world / peak, "traffic": None, "algorithmic_bytes": int(total_bytes)}}
+    if vc is not None:
+        line["vcycle"] = vc
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

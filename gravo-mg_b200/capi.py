@@ -286,8 +286,9 @@ class Input:
         self.h2d_bytes = pts.nbytes + colptr.nbytes + rowidx.nbytes + (a.nbytes if a is not None else 0)
 
     @classmethod
-    def torus(cls, ctx, nu, nv, R=1.0, r=0.3, amplitude=0.2, seed=42):
-        """The noisy torus grid of configs C3/C5 generated on the device (gmg_generate_torus)."""
+    def torus(cls, ctx, nu, nv, R=1.0, r=0.3, amplitude=0.2, seed=42, mass_shift=None):
+        """The noisy torus grid of configs C3/C5 generated on the device (gmg_generate_torus); with mass_shift
+        also its system matrix, cotangent Laplacian + mass_shift * lumped mass (gmg_input_torus_operator)."""
         self = cls.__new__(cls)
         self.ctx = ctx
         h = C.c_void_p()
@@ -297,7 +298,18 @@ class Input:
         self.h = h
         self.n, self.nnz = nu * nv, 7 * nu * nv
         self.h2d_bytes = 0
+        if mass_shift is not None:
+            ctx.lib.gmg_input_torus_operator.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_double]
+            ctx._check(ctx.lib.gmg_input_torus_operator(ctx.h, h, nu, nv, float(mass_shift)))
         return self
+
+    def fetch_operator(self):
+        """A values (nnz) of an input that has them, copied back to the host."""
+        lib = self.ctx.lib
+        lib.gmg_input_fetch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        val = np.empty(self.nnz, dtype=np.float64)
+        self.ctx._check(lib.gmg_input_fetch(self.ctx.h, self.h, 3, val.ctypes.data_as(C.c_void_p)))
+        return val
 
     def fetch_arrays(self):
         """(points (n,3) F-order, colptr, rowidx) copied back to the host."""

@@ -114,6 +114,9 @@ int gmg_create(int device, void* cuda_stream, gmg_ctx** out) {
         GMG_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         uint64_t threshold = UINT64_MAX;
         GMG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+        size_t free_b = 0, total_b = 0;
+        GMG_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        c->cache_limit = total_b / 5 * 2;
         *out = c;
         return GMG_OK;
     } catch (const Error& e) {
@@ -126,11 +129,22 @@ void gmg_destroy(gmg_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     release_kept(c);
+    c->trim();
     cudaStreamSynchronize(c->stream);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+/* Device memory parked for reuse by this context goes back to the driver's pool; *cached_bytes (optional)
+ * receives how much that was. */
+int gmg_trim(gmg_ctx* c, int64_t* cached_bytes) {
+    if (!c) return GMG_ERR_STATE;
+    cudaSetDevice(c->device);
+    if (cached_bytes) *cached_bytes = int64_t(c->cached_bytes);
+    c->trim();
+    return GMG_OK;
 }
 
 const char* gmg_last_error(const gmg_ctx* c) { return c ? c->last_error.c_str() : g_create_error.c_str(); }

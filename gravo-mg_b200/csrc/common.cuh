@@ -6,6 +6,10 @@
 // feeds a comparison that decides an integer output or must agree with the reference to 1e-12.
 #pragma once
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+
 #include <cuda_runtime.h>
 #include <cooperative_groups.h>
 
@@ -13,6 +17,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/gravomg_b200.h"
@@ -59,35 +64,81 @@ struct gmg_ctx {
     void* keep[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int64_t keep_n[6] = {0, 0, 0, 0, 0, 0};
     int keep_kind = 0;  // 0 none, 1 sparse (inner,val), 2 triangles (tri,normal,fan)
+    // Released device buffers, by size class, for reuse by later allocations on this context's stream.
+    // cudaMallocAsync's own pool keeps the memory too, but with mixed multi-GB sizes it re-maps physical
+    // chunks on most allocations (measured here: ~0.4 ms per allocation, 8.5 ms/GB when it has to grow); a
+    // build repeats the same sizes level after level and call after call, so exact-class reuse costs nothing.
+    std::unordered_map<size_t, std::vector<void*>> cache;
+    size_t cached_bytes = 0;
+    size_t cache_limit = size_t(64) << 30;   // set to 40 % of the device's memory at creation
+    void trim() {   // give everything cached back to the driver's pool
+        for (auto& kv : cache)
+            for (void* q : kv.second) cudaFreeAsync(q, stream);
+        cache.clear();
+        cached_bytes = 0;
+    }
 };
 
 namespace gmg {
 
 // Stream-ordered device buffer (cudaMallocAsync pool): allocation and release cost no device sync.
+// Size class of a request: the next multiple of 1/8 of the largest power of two not above it (<= 12.5 % slack).
+inline size_t size_class(size_t bytes) {
+    if (bytes < 512) bytes = 512;
+    size_t p2 = size_t(1) << (63 - __builtin_clzll((unsigned long long)bytes));
+    const size_t step = p2 / 8;
+    return (bytes + step - 1) / step * step;
+}
+
+// The buffers live on the context's single stream, so handing a released block to the next request of the
+// same class is stream-ordered by construction (what cudaFreeAsync + cudaMallocAsync would give, minus the
+// driver's re-mapping). A context must outlive its buffers.
 template <typename T> struct DevBuf {
     T* p = nullptr;
     int64_t n = 0;
     cudaStream_t s = nullptr;
+    gmg_ctx* ctx = nullptr;
+    size_t cap = 0;             // bytes of the underlying block (its size class)
     DevBuf() {}
     DevBuf(gmg_ctx* c, int64_t count) { alloc(c, count); }
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n), s(o.s) { o.p = nullptr; o.n = 0; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n), s(o.s), ctx(o.ctx), cap(o.cap) { o.p = nullptr; o.n = 0; }
     DevBuf& operator=(DevBuf&& o) noexcept {
-        if (this != &o) { release(); p = o.p; n = o.n; s = o.s; o.p = nullptr; o.n = 0; }
+        if (this != &o) { release(); p = o.p; n = o.n; s = o.s; ctx = o.ctx; cap = o.cap; o.p = nullptr; o.n = 0; }
         return *this;
     }
     ~DevBuf() { release(); }
     void alloc(gmg_ctx* c, int64_t count) {
         release();
-        s = c->stream; n = count;
-        GMG_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&p), sizeof(T) * size_t(count > 0 ? count : 1), s));
+        s = c->stream; n = count; ctx = c;
+        cap = size_class(sizeof(T) * size_t(count > 0 ? count : 1));
+        auto it = c->cache.find(cap);
+        if (it != c->cache.end() && !it->second.empty()) {
+            p = static_cast<T*>(it->second.back());
+            it->second.pop_back();
+            c->cached_bytes -= cap;
+            return;
+        }
+        cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&p), cap, s);
+        if (e == cudaErrorMemoryAllocation) {       // out of memory with blocks parked in the cache: drop them, retry
+            cudaGetLastError();
+            c->trim();
+            cudaStreamSynchronize(s);
+            e = cudaMallocAsync(reinterpret_cast<void**>(&p), cap, s);
+        }
+        if (e != cudaSuccess) { p = nullptr; n = 0; }
+        GMG_CUDA(e);
     }
     void release() {
-        if (p) cudaFreeAsync(p, s);
+        if (p) {
+            ctx->cache[cap].push_back(p);
+            ctx->cached_bytes += cap;
+            if (ctx->cached_bytes > ctx->cache_limit) ctx->trim();
+        }
         p = nullptr; n = 0;
     }
-    T* detach() { T* q = p; p = nullptr; n = 0; return q; }
+    T* detach() { T* q = p; p = nullptr; n = 0; return q; }   // the caller frees it with cudaFreeAsync
     void upload(const T* host, int64_t count) {
         if (count > 0) GMG_CUDA(cudaMemcpyAsync(p, host, sizeof(T) * size_t(count), cudaMemcpyHostToDevice, s));
     }
@@ -120,6 +171,25 @@ inline void points_to_host(gmg_ctx* c, const double* dev, int64_t n, double* hos
 }
 
 inline void sync(gmg_ctx* c) { GMG_CUDA(cudaStreamSynchronize(c->stream)); }
+
+// GMG_TRACE=1 in the environment: wall-clock milliseconds between marks, each mark synchronising the
+// stream (diagnostic only; changes the timing it reports on, never the results).
+struct Trace {
+    gmg_ctx* c;
+    const char* what;
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    Trace(gmg_ctx* ctx, const char* name) : c(ctx), what(name), on(getenv("GMG_TRACE") != nullptr) {
+        if (on) { cudaStreamSynchronize(c->stream); t0 = std::chrono::steady_clock::now(); }
+    }
+    void mark(const char* label) {
+        if (!on) return;
+        cudaStreamSynchronize(c->stream);
+        const auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[gmg] %s: %s %.3f ms\n", what, label, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
 
 #define GMG_LAUNCH(ctx, kernel, grid, block, smem, ...)                         \
     do {                                                                        \

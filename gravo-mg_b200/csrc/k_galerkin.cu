@@ -20,6 +20,9 @@
 // Algorithmic bytes: symbolic 12n + 4nnzA + 8nnzP + 4m; numeric 12n + 12nnzA + 24nnzP + 4m + 12nnzAc.
 #include "stages.h"
 
+#include <cstdio>
+#include <cstdlib>
+
 namespace gmg {
 
 // ---- R = P^T ------------------------------------------------------------------------------------
@@ -47,11 +50,26 @@ __global__ void __launch_bounds__(kBlock) transpose_fill_kernel(int32_t rows, co
         tval[pos] = val[k];
     }
 }
+// One warp per row: rows of up to 32 entries (the usual case: ~22 fine rows per coarse column) are rank-sorted
+// in registers -- every lane holds one entry and counts the smaller keys with shuffles; keys within a row are
+// distinct, so the ranks are a permutation. Longer rows fall back to an insertion sort by lane 0.
 __global__ void __launch_bounds__(kBlock) sort_rows_kernel(int32_t rows, const int32_t* __restrict__ ptr,
                                                            int32_t* __restrict__ idx, double* __restrict__ val) {
-    const int64_t r = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int64_t r = (int64_t(blockIdx.x) * kBlock + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (r >= rows) return;
-    const int32_t b = ptr[r], e = ptr[r + 1];
+    const int32_t b = ptr[r], e = ptr[r + 1], k = e - b;
+    if (k <= 32) {
+        const bool have = lane < k;
+        const int32_t key = have ? idx[b + lane] : 0x7fffffff;
+        const double v = have ? val[b + lane] : 0.0;
+        int32_t rank = 0;
+        for (int j = 0; j < k; ++j) rank += __shfl_sync(0xffffffffu, key, j) < key ? 1 : 0;
+        __syncwarp();
+        if (have) { idx[b + rank] = key; val[b + rank] = v; }
+        return;
+    }
+    if (lane != 0) return;
     for (int32_t i = b + 1; i < e; ++i) {
         const int32_t x = idx[i]; const double v = val[i];
         int32_t j = i - 1;
@@ -67,17 +85,21 @@ void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, i
     R.rowptr.alloc(c, int64_t(R.rows) + 1);
     DevBuf<int32_t> count(c, int64_t(R.rows) + 1);
     DevBuf<int64_t> total(c, 1);
+    Trace tr(c, "transpose");
     count.zero();
     if (P.nnz > 0) GMG_LAUNCH(c, count_columns_kernel, div_up(P.nnz, kBlock), kBlock, 0, P.nnz, P.colidx.p, c_lo, c_hi, count.p);
     exclusive_scan_i32(c, count.p, R.rowptr.p, int64_t(R.rows) + 1, all ? nullptr : total.p);
     R.nnz = P.nnz;
     if (!all) { total.download(&R.nnz, 1); sync(c); }
+    tr.mark("count + scan");
     R.colidx.alloc(c, R.nnz);
     R.val.alloc(c, R.nnz);
     count.zero();
     if (P.rows > 0) GMG_LAUNCH(c, transpose_fill_kernel, div_up(P.rows, kBlock), kBlock, 0, P.rows, P.rowptr.p, P.colidx.p,
                                P.val.p, c_lo, c_hi, R.rowptr.p, count.p, R.colidx.p, R.val.p);
-    if (R.rows > 0) GMG_LAUNCH(c, sort_rows_kernel, div_up(R.rows, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
+    tr.mark("fill");
+    if (R.rows > 0) GMG_LAUNCH(c, sort_rows_kernel, div_up(int64_t(R.rows) * 32, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
+    tr.mark("sort rows");
 }
 
 // ---- SpGEMM -------------------------------------------------------------------------------------
@@ -292,7 +314,9 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     if (m == 0) { Ac.colptr.zero(); Ac.rowidx.alloc(c, 0); Ac.val.alloc(c, 0); Ac.nnz = 0; return; }
     DeviceCsr R_local;
     DeviceCsr& R = keep_R ? *keep_R : R_local;
+    Trace tr(c, "galerkin");
     transpose_csr(c, P, R, c_lo, c_hi);
+    tr.mark("transpose");
     DevBuf<int32_t> count(c, int64_t(m) + 1), flags(c, 4), overflow(c, m);
     DevBuf<int64_t> total(c, 1);
     count.zero(); flags.zero();
@@ -305,6 +329,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     flags.download(hf, 4);
     sync(c);
     const int32_t n_over = hf[1];
+    if (getenv("GMG_TRACE")) fprintf(stderr, "[gmg] galerkin: %d outer vectors, %d to the block-wide table\n", m, n_over);
     const int ogrid = n_over < 4 * c->sm_count ? n_over : 4 * c->sm_count;
     if (n_over > 0) {
         GMG_LAUNCH(c, galerkin_block_kernel<false>, ogrid, kBlock, 0, a, n_over);
@@ -315,6 +340,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     exclusive_scan_i32(c, count.p, Ac.colptr.p, int64_t(m) + 1, total.p);
     total.download(&Ac.nnz, 1);
     sync(c);
+    tr.mark("symbolic");
     GMG_REQUIRE(Ac.nnz < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: A_c exceeds 32-bit indexing");
     Ac.rowidx.alloc(c, Ac.nnz);
     Ac.val.alloc(c, Ac.nnz);
@@ -322,6 +348,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     a.out_ptr = Ac.colptr.p; a.out_idx = Ac.rowidx.p; a.out_val = Ac.val.p;
     GMG_LAUNCH(c, galerkin_warp_kernel<true>, grid, kBlock, 0, a);
     if (n_over > 0) GMG_LAUNCH(c, galerkin_block_kernel<true>, ogrid, kBlock, 0, a, n_over);
+    tr.mark("numeric");
 }
 
 }  // namespace gmg

@@ -106,36 +106,18 @@ __global__ void __launch_bounds__(kBlock) mark_children_kernel(int32_t n, int32_
     if (P >= p_lo && P < p_hi) { need[f] = 1; need[P] = 1; }
 }
 
-// Volumes of the ranks' slices of a row-major packed array: offsets (device, exclusive scan over `count`
-// items, count + 1 entries) read at the rank boundaries (multiples of `chunk`). Returns the largest, rounded
-// up to 32 elements; bounds[r] is where rank r's slice starts. One host round trip.
-int64_t rank_volumes(gmg_shard* s, const int32_t* offsets, int64_t count, int32_t chunk, std::vector<int64_t>& vol,
-                     std::vector<int32_t>& bounds) {
+// Where the ranks' slices of a row-major packed array start: offsets (device, exclusive scan over `count`
+// items, count + 1 entries) read at the rank boundaries (multiples of `chunk`). off[world] is the total.
+// One host round trip.
+void rank_offsets(gmg_shard* s, const int32_t* offsets, int64_t count, int32_t chunk, std::vector<int64_t>& off) {
     gmg_ctx* c = s->ctx;
-    bounds.assign(size_t(s->world) + 1, 0);
+    std::vector<int32_t> b(size_t(s->world) + 1, 0);
     for (int r = 0; r <= s->world; ++r) {
         const int64_t at = std::min<int64_t>(count, int64_t(r) * chunk);
-        GMG_CUDA(cudaMemcpyAsync(&bounds[size_t(r)], offsets + at, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        GMG_CUDA(cudaMemcpyAsync(&b[size_t(r)], offsets + at, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
     }
     sync(c);
-    vol.assign(size_t(s->world), 0);
-    int64_t most = 1;
-    for (int r = 0; r < s->world; ++r) {
-        vol[size_t(r)] = bounds[size_t(r) + 1] - bounds[size_t(r)];
-        most = std::max<int64_t>(most, vol[size_t(r)]);
-    }
-    return round_up(most, 32);
-}
-
-// the ranks' slices of an exchange buffer, concatenated
-template <typename T>
-void concat_slices(gmg_shard* s, const T* xbuf, int64_t slice, const std::vector<int64_t>& vol, T* out) {
-    int64_t at = 0;
-    for (int r = 0; r < s->world; ++r) {
-        const int64_t k = vol[size_t(r)];
-        if (k > 0) GMG_CUDA(cudaMemcpyAsync(out + at, xbuf + slice * r, sizeof(T) * size_t(k), cudaMemcpyDeviceToDevice, s->ctx->stream));
-        at += k;
-    }
+    off.assign(b.begin(), b.end());
 }
 
 __global__ void __launch_bounds__(kBlock) row_counts_kernel(int32_t rows, const int32_t* __restrict__ ptr, int32_t* __restrict__ cnt) {
@@ -289,28 +271,21 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 DevBuf<int64_t> total(c, 1);
                 GMG_CUDA(cudaMemsetAsync(s->ccnt.p + s->m, 0, sizeof(int32_t), c->stream));   // scan sentinel
                 exclusive_scan_i32(c, s->ccnt.p, s->rowoff.p, int64_t(s->m) + 1, total.p);
-                std::vector<int32_t> bounds;
-                s->rows_max = rank_volumes(s, s->rowoff.p, s->m, s->cchunk, s->rank_rows, bounds);
-                s->xQ.alloc(c, s->rows_max * s->world);
-                s->xt.alloc(c, s->rows_max * s->world);
+                rank_offsets(s, s->rowoff.p, s->m, s->cchunk, s->rows_off);
+                s->rows_are_ac = false;
+                s->xQ.alloc(c, s->rows_off.back());
+                s->xt.alloc(c, s->rows_off.back());
                 const int32_t own = s->chi - s->clo;
                 if (own > 0)
                     GMG_LAUNCH(c, pack_rows_kernel, div_up(int64_t(own) * 8, kBlock), kBlock, 0, s->clo, s->chi, s->rows.boff.p,
-                               s->ccnt.p, s->rowoff.p, bounds[size_t(s->rank)], s->rows.sQ.p, s->rows.st.p,
-                               s->xQ.p + s->rows_max * s->rank, s->xt.p + s->rows_max * s->rank);
+                               s->ccnt.p, s->rowoff.p, 0, s->rows.sQ.p, s->rows.st.p, s->xQ.p, s->xt.p);
                 s->rows = CoarseRows();
-                io[0] = s->rows_max;
+                io[0] = s->rows_off.back();
                 break;
             }
             case GMG_PH_COARSE_ASSEMBLE: {  // after the packed rows have been gathered
-                // concatenate the rank slices into the global row-major arrays (rowoff addresses them)
-                const int64_t total = [&] { int64_t t = 0; for (auto v : s->rank_rows) t += v; return t; }();
-                DevBuf<int32_t> allQ(c, total);
-                DevBuf<double> allt(c, total);
-                concat_slices(s, s->xQ.p, s->rows_max, s->rank_rows, allQ.p);
-                concat_slices(s, s->xt.p, s->rows_max, s->rank_rows, allt.p);
                 gmg_shard::Done& L = *s->cur;
-                coarse_assemble(c, s->m, s->rowoff.p, s->ccnt.p, allQ.p, allt.p, L.coarse, s->status.dev.p + StageStatus::kCoarseAsym);
+                coarse_assemble(c, s->m, s->rowoff.p, s->ccnt.p, s->xQ.p, s->xt.p, L.coarse, s->status.dev.p + StageStatus::kCoarseAsym);
                 L.info.nnz_c = L.coarse.nnz;
                 s->xQ = DevBuf<int32_t>(); s->xt = DevBuf<double>();
                 // replicated cheap stages
@@ -351,30 +326,25 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 DevBuf<int64_t> total(c, 1);
                 GMG_CUDA(cudaMemsetAsync(s->pcnt.p + s->n, 0, sizeof(int32_t), c->stream));     // scan sentinel
                 exclusive_scan_i32(c, s->pcnt.p, s->Pfull.rowptr.p, int64_t(s->n) + 1, total.p);
-                std::vector<int32_t> bounds;
-                s->p_max = rank_volumes(s, s->Pfull.rowptr.p, s->n, s->chunk, s->rank_p, bounds);
-                GMG_REQUIRE(s->rank_p[size_t(s->rank)] == L.P.nnz, GMG_ERR_STATE, "gathered row counts disagree with the owned rows of P");
-                s->xPc.alloc(c, s->p_max * s->world);
-                s->xPv.alloc(c, s->p_max * s->world);
+                rank_offsets(s, s->Pfull.rowptr.p, s->n, s->chunk, s->p_off);
+                const int64_t mine = s->p_off[size_t(s->rank) + 1] - s->p_off[size_t(s->rank)];
+                GMG_REQUIRE(mine == L.P.nnz, GMG_ERR_STATE, "gathered row counts disagree with the owned rows of P");
+                s->Pfull.nnz = s->p_off.back();
+                s->Pfull.colidx.alloc(c, s->Pfull.nnz);
+                s->Pfull.val.alloc(c, s->Pfull.nnz);
                 if (L.P.nnz > 0) {
-                    GMG_CUDA(cudaMemcpyAsync(s->xPc.p + s->p_max * s->rank, L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
-                    GMG_CUDA(cudaMemcpyAsync(s->xPv.p + s->p_max * s->rank, L.P.val.p, sizeof(double) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(s->Pfull.colidx.p + s->p_off[size_t(s->rank)], L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(s->Pfull.val.p + s->p_off[size_t(s->rank)], L.P.val.p, sizeof(double) * size_t(L.P.nnz), cudaMemcpyDeviceToDevice, c->stream));
                 }
-                io[0] = s->p_max;
+                io[0] = s->Pfull.nnz;
                 break;
             }
             case GMG_PH_GALERKIN_ROWS: {    // after the rows of P have been gathered: the owned outer vectors of A_c
                 gmg_shard::Done& L = *s->cur;
-                int64_t nnz_p = 0;
-                for (auto v : s->rank_p) nnz_p += v;
-                s->Pfull.nnz = nnz_p;
-                s->Pfull.colidx.alloc(c, nnz_p);
-                s->Pfull.val.alloc(c, nnz_p);
-                concat_slices(s, s->xPc.p, s->p_max, s->rank_p, s->Pfull.colidx.p);
-                concat_slices(s, s->xPv.p, s->p_max, s->rank_p, s->Pfull.val.p);
-                s->xPc = DevBuf<int32_t>(); s->xPv = DevBuf<double>();
+                Trace tr(c, "galerkin_rows");
                 L.clo = s->clo; L.chi = s->chi;
                 galerkin(c, s->a_n, s->a_colptr, s->a_rowidx, s->a_val, s->Pfull, s->ac_own, s->clo, s->chi, &L.R);
+                tr.mark("transpose + SpGEMM");
                 s->Pfull = DeviceCsr();
                 // entries per owned outer vector -> the count exchange buffer (the coarse-graph counts are done with)
                 s->ccnt.zero();
@@ -388,31 +358,25 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 DevBuf<int64_t> total(c, 1);
                 GMG_CUDA(cudaMemsetAsync(s->ccnt.p + s->m, 0, sizeof(int32_t), c->stream));
                 exclusive_scan_i32(c, s->ccnt.p, L.Ac.colptr.p, int64_t(s->m) + 1, total.p);
-                std::vector<int32_t> bounds;
-                s->ac_max = rank_volumes(s, L.Ac.colptr.p, s->m, s->cchunk, s->rank_ac, bounds);
-                GMG_REQUIRE(s->rank_ac[size_t(s->rank)] == s->ac_own.nnz, GMG_ERR_STATE, "gathered counts disagree with the owned part of A_c");
-                s->xQ.alloc(c, s->ac_max * s->world);
-                s->xt.alloc(c, s->ac_max * s->world);
+                rank_offsets(s, L.Ac.colptr.p, s->m, s->cchunk, s->rows_off);
+                s->rows_are_ac = true;
+                const int64_t at = s->rows_off[size_t(s->rank)];
+                GMG_REQUIRE(s->rows_off[size_t(s->rank) + 1] - at == s->ac_own.nnz, GMG_ERR_STATE, "gathered counts disagree with the owned part of A_c");
+                L.Ac.nnz = s->rows_off.back();
+                L.Ac.rowidx.alloc(c, L.Ac.nnz);
+                L.Ac.val.alloc(c, L.Ac.nnz);
                 if (s->ac_own.nnz > 0) {
-                    GMG_CUDA(cudaMemcpyAsync(s->xQ.p + s->ac_max * s->rank, s->ac_own.rowidx.p, sizeof(int32_t) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
-                    GMG_CUDA(cudaMemcpyAsync(s->xt.p + s->ac_max * s->rank, s->ac_own.val.p, sizeof(double) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(L.Ac.rowidx.p + at, s->ac_own.rowidx.p, sizeof(int32_t) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
+                    GMG_CUDA(cudaMemcpyAsync(L.Ac.val.p + at, s->ac_own.val.p, sizeof(double) * size_t(s->ac_own.nnz), cudaMemcpyDeviceToDevice, c->stream));
                 }
                 s->ac_own = DeviceCsc();
-                s->rows_max = s->ac_max;        // slice length reported for ROWS_ID / ROWS_VAL
-                io[0] = s->ac_max;
+                io[0] = L.Ac.nnz;
                 break;
             }
             case GMG_PH_GALERKIN_ASSEMBLE: {    // after the owned outer vectors have been gathered
                 gmg_shard::Done& L = *s->cur;
-                int64_t nnz = 0;
-                for (auto v : s->rank_ac) nnz += v;
-                L.Ac.nnz = nnz;
-                L.Ac.rowidx.alloc(c, nnz);
-                L.Ac.val.alloc(c, nnz);
-                concat_slices(s, s->xQ.p, s->ac_max, s->rank_ac, L.Ac.rowidx.p);
-                concat_slices(s, s->xt.p, s->ac_max, s->rank_ac, L.Ac.val.p);
-                s->xQ = DevBuf<int32_t>(); s->xt = DevBuf<double>();
-                L.info.nnz_ac = nnz;
+                s->rows_are_ac = false;
+                L.info.nnz_ac = L.Ac.nnz;
                 s->a_n = s->m; s->a_colptr = L.Ac.colptr.p; s->a_rowidx = L.Ac.rowidx.p; s->a_val = L.Ac.val.p;
                 break;
             }
@@ -455,14 +419,31 @@ int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, i
         case GMG_XB_PRED: *ptr = s->pred.p; *elem_bytes = 4; *slice = s->chunk; break;
         case GMG_XB_PARENTS: *ptr = s->parents.p; *elem_bytes = 4; *slice = s->chunk; break;
         case GMG_XB_COARSE_COUNT: *ptr = s->ccnt.p; *elem_bytes = 4; *slice = s->cchunk; break;
-        case GMG_XB_ROWS_ID: *ptr = s->xQ.p; *elem_bytes = 4; *slice = s->rows_max; break;
-        case GMG_XB_ROWS_VAL: *ptr = s->xt.p; *elem_bytes = 8; *slice = s->rows_max; break;
+        case GMG_XB_ROWS_ID: case GMG_XB_ROWS_VAL: case GMG_XB_P_COL: case GMG_XB_P_VAL:
+            return GMG_ERR_INVALID;      /* variable-size slices: gmg_shard_buffer_v */
         case GMG_XB_LEN_PARTIAL: *ptr = s->len_partial.p; *elem_bytes = 8; *slice = s->gchunk; break;
         case GMG_XB_P_COUNT: *ptr = s->pcnt.p; *elem_bytes = 4; *slice = s->chunk; break;
-        case GMG_XB_P_COL: *ptr = s->xPc.p; *elem_bytes = 4; *slice = s->p_max; break;
-        case GMG_XB_P_VAL: *ptr = s->xPv.p; *elem_bytes = 8; *slice = s->p_max; break;
         default: return GMG_ERR_INVALID;
     }
+    return GMG_OK;
+}
+
+/* Exchange buffers whose slices differ in size (ROWS_ID, ROWS_VAL, P_COL, P_VAL): rank r owns elements
+ * [offsets[r], offsets[r + 1]) of the buffer; `offsets` receives world + 1 entries. */
+int gmg_shard_buffer_v(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* offsets) {
+    if (!s || !ptr || !elem_bytes || !offsets) return GMG_ERR_STATE;
+    const std::vector<int64_t>* off = nullptr;
+    switch (which) {
+        case GMG_XB_ROWS_ID:
+            *ptr = s->rows_are_ac ? (void*)s->cur->Ac.rowidx.p : (void*)s->xQ.p; *elem_bytes = 4; off = &s->rows_off; break;
+        case GMG_XB_ROWS_VAL:
+            *ptr = s->rows_are_ac ? (void*)s->cur->Ac.val.p : (void*)s->xt.p; *elem_bytes = 8; off = &s->rows_off; break;
+        case GMG_XB_P_COL: *ptr = s->Pfull.colidx.p; *elem_bytes = 4; off = &s->p_off; break;
+        case GMG_XB_P_VAL: *ptr = s->Pfull.val.p; *elem_bytes = 8; off = &s->p_off; break;
+        default: return GMG_ERR_INVALID;
+    }
+    if (off->size() != size_t(s->world) + 1) return GMG_ERR_STATE;
+    for (int r = 0; r <= s->world; ++r) offsets[r] = (*off)[size_t(r)];
     return GMG_OK;
 }
 

@@ -37,10 +37,12 @@ struct gmg_shard {
     DevBuf<int32_t> ccnt;            // exchange: distinct neighbours per coarse row, cchunk * world (+1)
     CoarseRows rows;
     DevBuf<int32_t> rowoff;          // exclusive scan of ccnt over ALL rows (m + 1) = global row-major offsets
-    int64_t rows_max = 0;            // largest per-rank row volume: slice length of the two buffers below
-    DevBuf<int32_t> xQ;              // exchange: packed rows (neighbour ids), rows_max * world
-    DevBuf<double> xt;               // exchange: packed rows (values)
-    std::vector<int64_t> rank_rows;  // entries per rank
+    // Variable-size exchanges (packed coarse rows, rows of P, outer vectors of A_c): the exchange buffer IS the
+    // final row-major array; rank r owns elements [v_off[r], v_off[r + 1]) of it (gmg_shard_buffer_v).
+    DevBuf<int32_t> xQ;              // exchange: packed coarse rows (neighbour ids), all ranks
+    DevBuf<double> xt;               // exchange: packed coarse rows (values)
+    std::vector<int64_t> rows_off;   // world + 1 element offsets of xQ / xt, or of A_c's arrays while those are exchanged
+    bool rows_are_ac = false;        // ROWS_ID / ROWS_VAL currently name the arrays of A_c
     StageStatus status;
     // Galerkin side (build_galerkin): the level's system matrix (replicated, pattern = any) and the exchange
     int32_t a_n = 0;
@@ -48,14 +50,9 @@ struct gmg_shard {
     const int32_t* a_rowidx = nullptr;
     const double* a_val = nullptr;
     DevBuf<int32_t> pcnt;            // exchange: entries per row of P, chunk * world (+1)
-    DeviceCsr Pfull;                 // all rows of P (transient)
-    int64_t p_max = 0;               // largest per-rank P volume: slice length of xPc / xPv
-    DevBuf<int32_t> xPc;             // exchange: the ranks' colidx arrays
-    DevBuf<double> xPv;              // exchange: the ranks' value arrays
-    std::vector<int64_t> rank_p;
+    DeviceCsr Pfull;                 // all rows of P (transient); colidx / val are exchange buffers (P_COL / P_VAL)
+    std::vector<int64_t> p_off;      // world + 1 element offsets of the ranks' rows in Pfull.colidx / val
     DeviceCsc ac_own;                // the owned outer vectors of A_c, indexed from clo
-    int64_t ac_max = 0;
-    std::vector<int64_t> rank_ac;
     // finished levels: replicated coarse data + the owned rows of P
     struct Done {
         gmg_level_info info{};

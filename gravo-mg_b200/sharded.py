@@ -33,6 +33,7 @@ from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, 
 PHASE_NAMES = ["level_begin", "sampler_build", "sampler_round", "sampler_check", "samples", "parents_pull", "parents_check",
                "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end",
                "radius", "p_count", "p_pack", "galerkin_rows", "galerkin_pack", "galerkin_assemble"]
+V_BUFFERS = (XB_ROWS_ID, XB_ROWS_VAL, XB_P_COL, XB_P_VAL)      # slices of different sizes (packed rows)
 BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val", "len_partial",
                 "p_count", "p_col", "p_val"]
 
@@ -76,6 +77,23 @@ class TorchComm:
         self.dist.all_gather_into_tensor(full, mine, group=self.group)
         self.bytes_gathered += int(full.numel())
 
+    def all_gather_v(self, full, byte_offsets):
+        """Slices of different sizes: rank r's slice is full[byte_offsets[r]:byte_offsets[r+1]] and already in
+        place; every other slice is received into place (a list all_gather: grouped broadcasts under NCCL)."""
+        views = [full[byte_offsets[r]:byte_offsets[r + 1]] for r in range(self.world)]
+        sizes = {int(v.numel()) for v in views}
+        if len(sizes) == 1 and int(full.numel()) == self.world * next(iter(sizes)):
+            self.dist.all_gather_into_tensor(full, views[self.rank], group=self.group)
+        else:
+            try:
+                self.dist.all_gather(views, views[self.rank], group=self.group)
+            except (RuntimeError, ValueError):
+                for r in range(self.world):        # a backend without uneven all_gather: one broadcast per owner
+                    if views[r].numel():
+                        self.dist.broadcast(views[r], src=self.dist.get_global_rank(self.group, r) if self.group else r,
+                                            group=self.group)
+        self.bytes_gathered += int(full.numel())
+
 
 class ShardRank:
     """One rank's gmg_shard handle."""
@@ -100,6 +118,18 @@ class ShardRank:
     def phase(self, ph):
         self.ctx._check(self.ctx.lib.gmg_shard_phase(self.ctx.h, self.h, C.c_int(ph), self.io))
         return self.io
+
+    def buffer_v(self, which):
+        """(device pointer, byte offsets of the ranks' slices [world + 1]) of a variable-size exchange buffer."""
+        lib = self.ctx.lib
+        lib.gmg_shard_buffer_v.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int32),
+                                           C.POINTER(C.c_int64)]
+        ptr, eb = C.c_void_p(), C.c_int32()
+        off = (C.c_int64 * (self.world + 1))()
+        rc = lib.gmg_shard_buffer_v(self.h, C.c_int(which), C.byref(ptr), C.byref(eb), off)
+        if rc != 0:
+            raise GmgError(rc, "gmg_shard_buffer_v")
+        return ptr.value, [int(o) * int(eb.value) for o in off]
 
     def buffer(self, which):
         """(device pointer, bytes per slice) of an exchange buffer."""
@@ -163,7 +193,33 @@ class ShardedHierarchy:
     def _gather(self, which):
         return self._timed("gather_" + BUFFER_NAMES[which], lambda: self._gather_now(which))
 
+    def _gather_v(self, which):
+        t = self.torch
+        bufs = [s.buffer_v(which) for s in self.shards]
+        off = bufs[0][1]
+        total = off[-1]
+        self.exchanges += 1
+        self.exchange_bytes += total
+        if total == 0:
+            return
+        if not self.same_stream:
+            t.cuda.synchronize()
+        if self.comm is not None:
+            self.comm.all_gather_v(device_bytes_as_tensor(bufs[0][0], total, self.device), off)
+        else:
+            views = [device_bytes_as_tensor(p, total, self.device) for p, _ in bufs]
+            for src, shard in enumerate(self.shards):
+                r = shard.rank
+                if off[r + 1] > off[r]:
+                    for dst in range(len(views)):
+                        if dst != src:
+                            views[dst][off[r]:off[r + 1]].copy_(views[src][off[r]:off[r + 1]])
+        if not self.same_stream:
+            t.cuda.synchronize()
+
     def _gather_now(self, which):
+        if which in V_BUFFERS:
+            return self._gather_v(which)
         t = self.torch
         bufs = [s.buffer(which) for s in self.shards]
         slice_bytes = bufs[0][1]
@@ -342,6 +398,7 @@ class HaloPlan:
     def __init__(self, ghost, recv_counts, send_idx, send_counts):
         self.ghost, self.recv_counts, self.send_idx, self.send_counts = ghost, recv_counts, send_idx, send_counts
         self.volume = sum(sum(c) for c in send_counts)
+        self.empty_everywhere = False      # set by the solver once every rank's volume is known
 
     def select(self, keep_ghost, keep_send):
         """Sub-plan over the entries flagged by the boolean tensors (same rule on both sides of a pair)."""
@@ -432,6 +489,13 @@ class ShardedSolver:
             if l + 1 < self.num_levels:
                 self.plan_r.append(self._plan(l, HP_R))
                 self.plan_p.append(self._plan(l, HP_P))
+        # an exchange nobody has anything to send in is skipped by every rank (one all-reduce decides, here)
+        plans = self.plan_a + [p for per in self.plan_colour for p in per] + self.plan_r + self.plan_p
+        vol = torch.tensor([p.volume for p in plans], dtype=torch.int64, device=self.device)
+        if self.comm is not None:
+            self.comm.dist.all_reduce(vol, group=self.comm.group)
+        for p, v in zip(plans, vol.tolist()):
+            p.empty_everywhere = v == 0
         self.last_ms = 0.0
 
     # ---- plumbing --------------------------------------------------------------------------------------
@@ -486,6 +550,8 @@ class ShardedSolver:
     def _exchange(self, plan, level, which):
         """Owner values -> ghost slots of vector `which` of `level`, for the entries of `plan`."""
         t = self.torch
+        if plan.empty_everywhere:
+            return
         vecs = [self._vec(k, level, which) for k in range(len(self.h))]
         self._fence()
         self.exchanges += 1
@@ -535,17 +601,38 @@ class ShardedSolver:
             total = float(v.item())
         return float(np.sqrt(total))
 
-    def vcycle(self, b, x0=None, cycles=1, pre=2, post=2, coarse_sweeps=50):
-        """b, x0: the WHOLE right-hand side / start vector (every rank passes the same). Returns (x, residuals):
-        x holds the owned entries of the ranks this process runs (everything under the loop-back), NaN elsewhere."""
+    def rhs_from_solution(self, xstar):
+        """b = A x* on the owned rows, formed on the device (xstar: host array or device tensor, the WHOLE vector).
+        Use vcycle(None, ...) afterwards."""
         t = self.torch
         n = self.geom[0][0]["n"]
-        hb = t.from_numpy(np.ascontiguousarray(b, dtype=np.float64))
-        hx = t.zeros(n, dtype=t.float64) if x0 is None else t.from_numpy(np.ascontiguousarray(x0, dtype=np.float64))
+        src = xstar if isinstance(xstar, t.Tensor) else t.from_numpy(np.ascontiguousarray(xstar, dtype=np.float64))
         self._fence()
         for k in range(len(self.h)):
-            self._vec(k, 0, SV_B)[:n].copy_(hb)
-            self._vec(k, 0, SV_X)[:n].copy_(hx)
+            self._vec(k, 0, SV_X)[:n].copy_(src)
+            self._vec(k, 0, SV_B).zero_()
+        self._fence()
+        self._op(0, SO_RESIDUAL)                       # r = 0 - A x*
+        self._fence()
+        for k in range(len(self.h)):
+            g = self.geom[0][k]
+            self._vec(k, 0, SV_B)[g["lo"]:g["hi"]] = -self._vec(k, 0, SV_R)[g["lo"]:g["hi"]]
+        self._fence()
+
+    def vcycle(self, b, x0=None, cycles=1, pre=2, post=2, coarse_sweeps=50, fetch=True):
+        """b, x0: the WHOLE right-hand side / start vector (every rank passes the same); b = None keeps the
+        right-hand side already on the device (rhs_from_solution). Returns (x, residuals): x holds the owned
+        entries of the ranks this process runs (everything under the loop-back), NaN elsewhere (None if not fetch)."""
+        t = self.torch
+        n = self.geom[0][0]["n"]
+        self._fence()
+        for k in range(len(self.h)):
+            if b is not None:
+                self._vec(k, 0, SV_B)[:n].copy_(t.from_numpy(np.ascontiguousarray(b, dtype=np.float64)))
+            if x0 is None:
+                self._vec(k, 0, SV_X).zero_()
+            else:
+                self._vec(k, 0, SV_X)[:n].copy_(t.from_numpy(np.ascontiguousarray(x0, dtype=np.float64)))
         self._fence()
         res = [self._residual_norm()]
         e0, e1 = t.cuda.Event(enable_timing=True), t.cuda.Event(enable_timing=True)
@@ -558,6 +645,8 @@ class ShardedSolver:
             t.cuda.synchronize()
             self.last_ms += e0.elapsed_time(e1)
             res.append(self._residual_norm())
+        if not fetch:
+            return None, np.array(res)
         x = np.full(n, np.nan)
         for k in range(len(self.h)):
             g = self.geom[0][k]

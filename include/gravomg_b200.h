@@ -64,6 +64,9 @@ enum { GMG_SAMPLER_EXACT = 0, GMG_SAMPLER_PARALLEL = 1 };
 
 int gmg_create(int device, void* cuda_stream, gmg_ctx** out);
 void gmg_destroy(gmg_ctx* ctx);
+/* The context parks released device buffers for reuse by later calls (a build repeats the same sizes).
+ * gmg_trim hands them back to the driver's pool; *cached_bytes (optional) = how much was parked. */
+int gmg_trim(gmg_ctx* ctx, int64_t* cached_bytes);
 const char* gmg_last_error(const gmg_ctx* ctx);
 /* milliseconds spent in kernels of the most recent compute call, measured with CUDA events on the
  * context's stream (excludes host<->device copies) */
@@ -144,9 +147,12 @@ void gmg_input_destroy(gmg_input* in);
  * torus grid of configs C3/C5 (nu x nv vertices, vertex (i,j) = i*nv + j, quads split on the same
  * diagonal, positions displaced by amplitude * h * splitmix64 noise; pattern = adjacency + diagonal).
  * gmg_input_fetch copies an array back to the host: 0 points (f64[3n], column-major n x 3),
- * 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]). */
+ * 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]), 3 A values (f64[nnz]).
+ * gmg_input_torus_operator adds the system matrix of C3/C5 to such an input: cotangent Laplacian +
+ * mass_shift * lumped mass on the same pattern. */
 int gmg_generate_torus(gmg_ctx* ctx, int32_t nu, int32_t nv, double R, double r, double amplitude, uint64_t seed,
                        gmg_input** out);
+int gmg_input_torus_operator(gmg_ctx* ctx, gmg_input* in, int32_t nu, int32_t nv, double mass_shift);
 int gmg_input_fetch(gmg_ctx* ctx, const gmg_input* in, int which, void* host_out);
 int gmg_input_size(const gmg_input* in, int64_t* n, int64_t* nnz);
 
@@ -268,6 +274,9 @@ int gmg_shard_phase(gmg_ctx* ctx, gmg_shard* s, int phase, int64_t* io);
 /* exchange buffer: device pointer, element size, slice length in elements; the buffer holds
  * slice * world elements and rank r owns [r * slice, (r + 1) * slice) */
 int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* slice);
+/* ROWS_ID, ROWS_VAL, P_COL, P_VAL have slices of different sizes (packed rows): the buffer is the final
+ * row-major array itself and rank r owns elements [offsets[r], offsets[r + 1]) (world + 1 entries). */
+int gmg_shard_buffer_v(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* offsets);
 int gmg_shard_num_levels(const gmg_shard* s);
 int gmg_shard_level_info(const gmg_shard* s, int level, gmg_level_info* out, int64_t* row_lo, int64_t* row_hi);
 /* array ids of gmg_hierarchy_array; replicated arrays are complete on every rank, the P arrays hold

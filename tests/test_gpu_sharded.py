@@ -138,6 +138,13 @@ def test_device_torus_generator(ctx):
     pts, cp, ri = inp.fetch_arrays()
     assert np.array_equal(cp, A.indptr) and np.array_equal(ri, A.indices)
     assert np.abs(pts - V).max() < 1e-15
+    # the system matrix of C3/C5 on the same pattern (cotangent Laplacian + 1e-3 lumped mass)
+    inp_a = capi.Input.torus(ctx, nu, nv, mass_shift=1e-3)
+    want = meshgen.cotangent_laplacian(pts, F, mass_shift=1e-3)
+    got = inp_a.fetch_operator()
+    assert np.array_equal(want.indices, ri)
+    assert np.abs(got - want.data).max() <= 1e-11 * np.abs(want.data).max()
+    inp_a.close()
     # and it feeds the build
     h = capi.Hierarchy(ctx, inp, 3, sampler_mode=capi.SAMPLER_PARALLEL)
     assert h.num_levels == 2 and h.info[0]["m"] > 0

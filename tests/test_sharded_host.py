@@ -51,6 +51,14 @@ def _worker(rank, world, port, count, q):
             for r in range(world):
                 _, rlo, rhi = partition(count, world, r)
                 ok = ok and np.array_equal(got[rlo * elem:rhi * elem], ref[rlo * elem:rhi * elem].astype(np.uint8))
+        # slices of different sizes (packed rows): received in place around the rank's own slice
+        sizes = [(7 * r + 3) % 11 * 8 for r in range(world)]          # bytes per rank, some empty
+        off = np.concatenate([[0], np.cumsum(sizes)]).astype(int).tolist()
+        ref = ((np.arange(off[-1], dtype=np.int64) * 13 + 5) % 241).astype(np.uint8)
+        full = torch.zeros(off[-1], dtype=torch.uint8)
+        full[off[rank]:off[rank + 1]] = torch.from_numpy(ref[off[rank]:off[rank + 1]])
+        comm.all_gather_v(full, off)
+        ok = ok and np.array_equal(full.numpy(), ref)
         ok = ok and comm.bytes_gathered > 0
         q.put((rank, bool(ok)))
     finally:
