@@ -433,7 +433,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     import torch.distributed as dist
     from gravomg_b200 import capi
     from gravomg_b200.capi import Context, Input
-    from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm
+    from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
@@ -518,7 +518,7 @@ def run_b200_sharded(a, rank, world, local_rank):
         sv.close()
     hp.close()
 
-    # end to end: host buffers -> device (every rank uploads the whole mesh), build, owned rows of P -> host
+    # end to end: host buffers -> device (each rank its own slice, all-gathered over NVLink), build, owned rows of P -> host
     hV, hcp, hri = inp.fetch_arrays()
     tV = torch.from_numpy(hV.T).pin_memory(); hV = tV.numpy().T
     tcp = torch.from_numpy(hcp).pin_memory(); hcp = tcp.numpy()
@@ -536,7 +536,10 @@ def run_b200_sharded(a, rank, world, local_rank):
         return pin_out[key]
 
     def step_e2e():
-        i2 = Input(ctx, hV, hcp, hri, hA)
+        if world > 1:       # each rank uploads its own slice over PCIe; NVLink all-gathers complete the mesh
+            i2, _ = upload_sharded(ctx, comm, hV, hcp, hri, hA)
+        else:
+            i2 = Input(ctx, hV, hcp, hri, hA)
         h2 = build(i2)
         d2h = 0
         for lvl in range(h2.num_levels):

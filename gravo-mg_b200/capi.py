@@ -286,6 +286,31 @@ class Input:
         self.h2d_bytes = pts.nbytes + colptr.nbytes + rowidx.nbytes + (a.nbytes if a is not None else 0)
 
     @classmethod
+    def device_empty(cls, ctx, n, nnz, with_a=False):
+        """Arrays allocated on the device, to be filled by the caller (sharded.upload_sharded) and committed."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        h = C.c_void_p()
+        ctx.lib.gmg_input_create_device.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.POINTER(C.c_void_p)]
+        ctx._check(ctx.lib.gmg_input_create_device(ctx.h, n, nnz, 1 if with_a else 0, C.byref(h)))
+        self.h = h
+        self.n, self.nnz = int(n), int(nnz)
+        self.h2d_bytes = 0
+        return self
+
+    def device_ptr(self, which):
+        ptr = C.c_void_p()
+        self.ctx.lib.gmg_input_device_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        rc = self.ctx.lib.gmg_input_device_ptr(self.h, which, C.byref(ptr))
+        if rc != 0:
+            raise GmgError(rc, "gmg_input_device_ptr")
+        return ptr.value
+
+    def commit(self):
+        self.ctx.lib.gmg_input_commit.argtypes = [C.c_void_p, C.c_void_p]
+        self.ctx._check(self.ctx.lib.gmg_input_commit(self.ctx.h, self.h))
+
+    @classmethod
     def torus(cls, ctx, nu, nv, R=1.0, r=0.3, amplitude=0.2, seed=42, mass_shift=None):
         """The noisy torus grid of configs C3/C5 generated on the device (gmg_generate_torus); with mass_shift
         also its system matrix, cotangent Laplacian + mass_shift * lumped mass (gmg_input_torus_operator)."""

@@ -68,6 +68,50 @@ int gmg_input_create(gmg_ctx* c, int64_t n, const double* points, int64_t ld, co
     });
 }
 
+/* An input whose arrays the CALLER fills on the device (row-sharded upload: each rank copies its own slice from
+ * the host and the slices are all-gathered over NVLink instead of every rank pulling the whole mesh over PCIe).
+ * gmg_input_commit checks the pattern once the arrays are complete. */
+int gmg_input_create_device(gmg_ctx* c, int64_t n, int64_t nnz, int with_a, gmg_input** out) {
+    if (!out) return GMG_ERR_INVALID;
+    *out = nullptr;
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(n >= 0 && n < (int64_t(1) << 31) / 3, GMG_ERR_INVALID, "vertex count too large for 32-bit indices");
+        GMG_REQUIRE(nnz >= 0 && nnz < (int64_t(1) << 31), GMG_ERR_INVALID, "entry count too large for 32-bit offsets");
+        std::unique_ptr<gmg_input> in(new gmg_input());
+        in->ctx = c; in->n = int32_t(n); in->nnz = nnz;
+        in->pts.alloc(c, 3 * n); in->colptr.alloc(c, n + 1); in->rowidx.alloc(c, nnz);
+        if (with_a) { in->a_val.alloc(c, nnz); in->has_a = true; }
+        sync(c);
+        *out = in.release();
+    });
+}
+
+/* which: 0 points (f64[3n]: x | y | z), 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]), 3 A values (f64[nnz]) */
+int gmg_input_device_ptr(gmg_input* in, int which, void** ptr) {
+    if (!in || !ptr) return GMG_ERR_STATE;
+    switch (which) {
+        case 0: *ptr = in->pts.p; break;
+        case 1: *ptr = in->colptr.p; break;
+        case 2: *ptr = in->rowidx.p; break;
+        case 3: if (!in->has_a) return GMG_ERR_STATE; *ptr = in->a_val.p; break;
+        default: return GMG_ERR_INVALID;
+    }
+    return GMG_OK;
+}
+
+int gmg_input_commit(gmg_ctx* c, gmg_input* in) {
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(in, GMG_ERR_STATE, "null input");
+        int32_t ends[2] = {-1, -1};
+        GMG_CUDA(cudaMemcpyAsync(&ends[0], in->colptr.p, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        GMG_CUDA(cudaMemcpyAsync(&ends[1], in->colptr.p + in->n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        sync(c);
+        GMG_REQUIRE(ends[0] == 0 && ends[1] == in->nnz, GMG_ERR_INVALID, "bad colptr");
+        check_pattern(c, in->n, in->colptr.p, in->rowidx.p, true);
+        sync(c);
+    });
+}
+
 void gmg_input_destroy(gmg_input* in) {
     if (!in) return;
     cudaSetDevice(in->ctx->device);

@@ -79,20 +79,72 @@ class TorchComm:
 
     def all_gather_v(self, full, byte_offsets):
         """Slices of different sizes: rank r's slice is full[byte_offsets[r]:byte_offsets[r+1]] and already in
-        place; every other slice is received into place (a list all_gather: grouped broadcasts under NCCL)."""
-        views = [full[byte_offsets[r]:byte_offsets[r + 1]] for r in range(self.world)]
-        sizes = {int(v.numel()) for v in views}
-        if len(sizes) == 1 and int(full.numel()) == self.world * next(iter(sizes)):
-            self.dist.all_gather_into_tensor(full, views[self.rank], group=self.group)
+        place. The slices are nearly equal (contiguous ranges of rows), so they travel as ONE equal-size
+        all_gather_into_tensor through a padded staging tensor and are copied into place; NCCL's list
+        all_gather with uneven sizes (grouped broadcasts) measured 2.4x slower on 8 B200."""
+        import torch
+        sizes = [byte_offsets[r + 1] - byte_offsets[r] for r in range(self.world)]
+        if len(set(sizes)) == 1 and int(full.numel()) == self.world * sizes[0]:
+            self.dist.all_gather_into_tensor(full, full[byte_offsets[self.rank]:byte_offsets[self.rank + 1]], group=self.group)
         else:
-            try:
-                self.dist.all_gather(views, views[self.rank], group=self.group)
-            except (RuntimeError, ValueError):
-                for r in range(self.world):        # a backend without uneven all_gather: one broadcast per owner
-                    if views[r].numel():
-                        self.dist.broadcast(views[r], src=self.dist.get_global_rank(self.group, r) if self.group else r,
-                                            group=self.group)
+            smax = (max(sizes) + 15) // 16 * 16
+            staging = torch.empty(self.world * smax, dtype=torch.uint8, device=full.device)
+            mine = staging[self.rank * smax:(self.rank + 1) * smax]
+            mine[:sizes[self.rank]].copy_(full[byte_offsets[self.rank]:byte_offsets[self.rank + 1]])
+            self.dist.all_gather_into_tensor(staging, mine, group=self.group)
+            for r in range(self.world):
+                if r != self.rank and sizes[r]:
+                    full[byte_offsets[r]:byte_offsets[r + 1]].copy_(staging[r * smax:r * smax + sizes[r]])
         self.bytes_gathered += int(full.numel())
+
+
+def upload_sharded(ctx, comm, points, colptr, rowidx, a_val=None, device=None):
+    """Row-sharded upload of a level-0 problem every rank holds on the host: each rank copies only the slice
+    of its own vertices over PCIe (host -> device) and the slices are all-gathered over NVLink, so the whole
+    mesh crosses PCIe once per BOX instead of once per GPU. Only the owned slices of the host arrays are read.
+    Returns (capi.Input, bytes this rank copied from the host)."""
+    import torch
+    n, nnz = int(colptr.shape[0]) - 1, int(rowidx.shape[0])
+    world, rank = comm.world, comm.rank
+    device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    inp = capi.Input.device_empty(ctx, n, nnz, with_a=a_val is not None)
+    bounds = [partition(n, world, r)[1] for r in range(world)] + [n]
+    lo, hi = bounds[rank], bounds[rank + 1]
+    h2d = 0
+
+    def put(dst, src_np):
+        nonlocal h2d
+        t = torch.from_numpy(src_np)
+        dst.copy_(t.view(torch.uint8) if t.dtype != torch.uint8 else t, non_blocking=True)
+        h2d += src_np.nbytes
+
+    # positions: x | y | z, each coordinate a gather of its own
+    pts = device_bytes_as_tensor(inp.device_ptr(0), 24 * n, device)
+    for k in range(3):
+        col = np.ascontiguousarray(points[lo:hi, k])
+        off = [8 * (k * n + b) for b in bounds]
+        put(pts[off[rank]:off[rank + 1]], col.view(np.uint8))
+        comm.all_gather_v(pts, off)
+    # colptr: entries [lo, hi) per rank, the last rank also owns entry n
+    cp = device_bytes_as_tensor(inp.device_ptr(1), 4 * (n + 1), device)
+    off = [4 * b for b in bounds]
+    off[-1] = 4 * (n + 1)
+    last = hi + 1 if rank == world - 1 else hi
+    put(cp[off[rank]:off[rank + 1]], np.ascontiguousarray(colptr[lo:last]).view(np.uint8))
+    comm.all_gather_v(cp, off)
+    # entries: slices start where the ranks' first columns start (host colptr is complete on every rank)
+    e_off = [int(colptr[b]) for b in bounds]
+    ri = device_bytes_as_tensor(inp.device_ptr(2), 4 * nnz, device)
+    put(ri[4 * e_off[rank]:4 * e_off[rank + 1]], np.ascontiguousarray(rowidx[e_off[rank]:e_off[rank + 1]]).view(np.uint8))
+    comm.all_gather_v(ri, [4 * e for e in e_off])
+    if a_val is not None:
+        av = device_bytes_as_tensor(inp.device_ptr(3), 8 * nnz, device)
+        put(av[8 * e_off[rank]:8 * e_off[rank + 1]], np.ascontiguousarray(a_val[e_off[rank]:e_off[rank + 1]]).view(np.uint8))
+        comm.all_gather_v(av, [8 * e for e in e_off])
+    torch.cuda.current_stream().synchronize()       # the copies ran on torch's stream; commit runs on the context's
+    inp.commit()
+    inp.h2d_bytes = h2d
+    return inp, h2d
 
 
 class ShardRank:

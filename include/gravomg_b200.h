@@ -142,6 +142,14 @@ typedef struct gmg_input gmg_input;
 int gmg_input_create(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
                      const int32_t* rowidx, const double* A_val, gmg_input** out);
 void gmg_input_destroy(gmg_input* in);
+/* Row-sharded upload [not in reference]: an input whose arrays the caller fills ON THE DEVICE -- each rank
+ * copies its own slice from the host and the slices are all-gathered over NVLink, instead of every rank
+ * pulling the whole mesh over PCIe (gravo-mg_b200/sharded.py upload_sharded). gmg_input_device_ptr: 0 points
+ * (f64[3n]: x | y | z), 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]), 3 A values (f64[nnz]).
+ * gmg_input_commit validates the completed arrays (same checks as gmg_input_create). */
+int gmg_input_create_device(gmg_ctx* ctx, int64_t n, int64_t nnz, int with_a, gmg_input** out);
+int gmg_input_device_ptr(gmg_input* in, int which, void** ptr);
+int gmg_input_commit(gmg_ctx* ctx, gmg_input* in);
 
 /* Level-0 problems generated on the device [not in reference; the step before the hot path]: the noisy
  * torus grid of configs C3/C5 (nu x nv vertices, vertex (i,j) = i*nv + j, quads split on the same

@@ -18,7 +18,7 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 from gravomg_b200 import capi, meshgen
-from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm
+from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
 
 name = sys.argv[1] if len(sys.argv) > 1 else "C3"
 scale = float(sys.argv[2]) if len(sys.argv) > 2 else 0.05
@@ -55,8 +55,14 @@ for mode in (capi.SAMPLER_PARALLEL, capi.SAMPLER_EXACT) if name != "C3" else (ca
     print(f"rank {rank}/{world} mode {mode}: {single.num_levels} levels, n={V.shape[0]}, exchanges {sh.exchanges}, "
           f"sharded {sh.build_ms:.2f} ms vs single {single.build_ms:.2f} ms, mismatches so far {bad}", flush=True)
     sh.close(); single.close()
-# Galerkin operators and the V-cycle
-inp_a = capi.Input(ctx, V, A.indptr, A.indices, A.data)
+# Galerkin operators and the V-cycle, on an input uploaded slice by slice and completed over NVLink
+inp_a, h2d = upload_sharded(ctx, TorchComm(), V, A.indptr, A.indices, A.data)
+pts_d, cp_d, ri_d = inp_a.fetch_arrays()
+if not (np.array_equal(pts_d, V) and np.array_equal(cp_d, A.indptr) and np.array_equal(ri_d, A.indices)
+        and np.array_equal(inp_a.fetch_operator(), A.data)):
+    bad += 1
+    print(f"rank {rank}: sharded upload differs from the host arrays", flush=True)
+print(f"rank {rank}: sharded upload copied {h2d / 1e6:.1f} MB of {(V.nbytes + A.indptr.nbytes + A.indices.nbytes + A.data.nbytes) / 1e6:.1f} MB from the host", flush=True)
 single = capi.Hierarchy(ctx, inp_a, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=3, build_galerkin=True)
 sh = ShardedHierarchy(ctx, inp_a, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=capi.SAMPLER_PARALLEL, seed=3,
                       build_galerkin=True)
