@@ -40,13 +40,18 @@ def parse():
     ap.add_argument("--workload", default=None, help="C1|C2|C3|C4 (single GPU) or T<millions> (torus; sharded when N>1)")
     ap.add_argument("--per-gpu-mverts", type=float, default=12.5, help="default N>1 workload: torus vertices per GPU (millions)")
     ap.add_argument("--scale", type=float, default=1.0)
-    ap.add_argument("--sampler", default="exact", choices=["exact", "parallel"])
+    ap.add_argument("--sampler", default=None, choices=["exact", "parallel"],
+                    help="default: exact on one GPU (the reference's sample set), parallel for the row-sharded build "
+                         "(the exact greedy order is a cross-rank dependency chain; SURVEY.md 8(e))")
     ap.add_argument("--galerkin", type=int, default=0, help="1: also A_c = P^T A P on every level (config C3)")
     ap.add_argument("--vcycle", type=int, default=0, help="1 (with --galerkin 1): one V-cycle Poisson solve and an SpMV, timed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
+    world = max(a.gpus, int(os.environ.get("WORLD_SIZE", "1")))
     if a.workload is None:
-        a.workload = "C2" if a.gpus == 1 else f"T{a.per_gpu_mverts * a.gpus:g}"
+        a.workload = "C2" if world == 1 else f"T{a.per_gpu_mverts * world:g}"
+    if a.sampler is None:
+        a.sampler = "parallel" if (world > 1 or a.workload.startswith("T")) else "exact"
     return a
 
 
