@@ -295,13 +295,16 @@ def run_b200(a, rank, world, local_rank):
 
     def step_e2e():
         i2 = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
-        h = Hierarchy(ctx, i2, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin))
-        d2h = 0
-        for lvl in range(h.num_levels):
-            nl, nzp = h.info[lvl]["n"], h.info[lvl]["nnz_p"]
-            for which, cnt, dt in ((capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32),
-                                   (capi.H_P_VAL, nzp, np.float64)):
-                d2h += h.fetch(lvl, which, out=pinned_out((lvl, which), cnt, dt)).nbytes
+        # every level's P leaves the device on the copy stream as soon as the level is complete, while the
+        # next level builds; the step ends when the last copy has landed in the pinned result buffers
+        def stream_out(lvl, info):
+            nl, nzp = info["n"], info["nnz_p"]
+            return [(which, pinned_out((lvl, which), cnt, dt)[:cnt])
+                    for which, cnt, dt in ((capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32),
+                                           (capi.H_P_VAL, nzp, np.float64))]
+        h = Hierarchy(ctx, i2, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin), stream_out=stream_out)
+        ctx.copy_sync()
+        d2h = h.streamed_bytes
         nb = i2.h2d_bytes
         h.close(); i2.close()
         return nb, d2h

@@ -118,6 +118,18 @@ class Context:
         if rc != 0:
             raise GmgError(rc, self.lib.gmg_last_error(self.h).decode())
 
+    def copy_sync(self):
+        """Wait for the copies issued on the copy stream (Hierarchy(stream_out=...))."""
+        self.lib.gmg_copy_sync.argtypes = [C.c_void_p]
+        self._check(self.lib.gmg_copy_sync(self.h))
+
+    def trim(self):
+        """Return the device buffers this context has parked for reuse; returns how many bytes that was."""
+        n = C.c_int64()
+        self.lib.gmg_trim.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+        self._check(self.lib.gmg_trim(self.h, C.byref(n)))
+        return int(n.value)
+
     @property
     def last_kernel_ms(self):
         return float(self.lib.gmg_last_kernel_ms(self.h))
@@ -242,10 +254,13 @@ class Context:
 
 
 # ---- resident hierarchy builder (gmg_hierarchy_*) ------------------------------------------------
+LEVEL_CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_void_p, C.c_int)
+
+
 class HierarchyOptions(C.Structure):
     _fields_ = [("levels", C.c_int32), ("ratio", C.c_double), ("weighting", C.c_int32), ("sampler_mode", C.c_int32),
                 ("seed", C.c_uint64), ("radius_policy", C.c_int32), ("radius_override", _f64p),
-                ("build_galerkin", C.c_int32)]
+                ("build_galerkin", C.c_int32), ("on_level", LEVEL_CALLBACK), ("user", C.c_void_p)]
 
 
 class LevelInfo(C.Structure):
@@ -362,7 +377,10 @@ class Hierarchy:
     """levels-1 prolongations (and optionally Galerkin operators) built and kept on the device."""
 
     def __init__(self, ctx, inp, levels, ratio=8.0, weighting=BARYCENTRIC, sampler_mode=SAMPLER_EXACT, seed=42,
-                 radius_policy=0, radius_override=None, build_galerkin=False):
+                 radius_policy=0, radius_override=None, build_galerkin=False, stream_out=None):
+        """stream_out(level, info) -> [(array id, pinned 1-D numpy array), ...]: called as soon as a level is
+        complete on the device; the listed arrays are copied out on the context's copy stream while the next
+        level builds (gmg_hierarchy_fetch_async). Wait with ctx.copy_sync() before reading them."""
         self.ctx = ctx
         ro = None
         if radius_override is not None:
@@ -371,6 +389,21 @@ class Hierarchy:
         self._ro = ro
         opt = HierarchyOptions(levels, ratio, weighting, sampler_mode, seed, radius_policy,
                                _p(ro, _f64p) if ro is not None else None, 1 if build_galerkin else 0)
+        self.streamed_bytes = 0
+        if stream_out is not None:
+            lib = ctx.lib
+            lib.gmg_hierarchy_level_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+            lib.gmg_hierarchy_fetch_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+
+            def on_level(_user, hptr, level):
+                li = LevelInfo()
+                if lib.gmg_hierarchy_level_info(hptr, level, C.byref(li)) != 0:
+                    return
+                for which, out in stream_out(level, li.as_dict()):
+                    if lib.gmg_hierarchy_fetch_async(ctx.h, hptr, level, which, out.ctypes.data_as(C.c_void_p)) == 0:
+                        self.streamed_bytes += out.nbytes
+            self._cb = LEVEL_CALLBACK(on_level)          # keep the trampoline alive for the duration of the build
+            opt.on_level = self._cb
         h = C.c_void_p()
         ctx._check(ctx.lib.gmg_hierarchy_build(ctx.h, inp.h, C.byref(opt), C.byref(h)))
         self.h = h

@@ -70,10 +70,11 @@ template <typename F> static int guarded(gmg_ctx* c, F&& body) {
         return GMG_OK;
     } catch (const Error& e) {
         c->last_error = e.what;
-        cudaStreamSynchronize(c->stream);
+        abort_sync(c);
         return e.status;
     } catch (const std::exception& e) {
         c->last_error = e.what();
+        abort_sync(c);
         return GMG_ERR_INVALID;
     }
 }
@@ -114,6 +115,7 @@ int gmg_create(int device, void* cuda_stream, gmg_ctx** out) {
         GMG_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         uint64_t threshold = UINT64_MAX;
         GMG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+        GMG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&c->stage), kStageBytes, cudaHostAllocMapped));
         size_t free_b = 0, total_b = 0;
         GMG_CUDA(cudaMemGetInfo(&free_b, &total_b));
         c->cache_limit = total_b / 5 * 2;
@@ -133,6 +135,8 @@ void gmg_destroy(gmg_ctx* c) {
     cudaStreamSynchronize(c->stream);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->stage) cudaFreeHost(c->stage);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }

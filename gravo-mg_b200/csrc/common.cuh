@@ -9,6 +9,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 #include <cuda_runtime.h>
 #include <cooperative_groups.h>
@@ -55,6 +56,7 @@ struct gmg_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t copy_stream = nullptr;   // device -> host copies that overlap the build (created on first use)
     int sm_count = 148;
     std::string last_error;
     double last_kernel_ms = 0.0;
@@ -71,6 +73,15 @@ struct gmg_ctx {
     std::unordered_map<size_t, std::vector<void*>> cache;
     size_t cached_bytes = 0;
     size_t cache_limit = size_t(64) << 30;   // set to 40 % of the device's memory at creation
+    // Small device -> host reads (counts, flags, the per-level status block) go through a MAPPED pinned page that
+    // a tiny kernel writes: no copy-engine descriptor, no implicit host block (cudaMemcpyAsync into pageable
+    // memory returns only when the copy is done) and no queueing behind a bulk copy on the copy stream.
+    // sync() hands the staged bytes to their destinations.
+    unsigned char* stage = nullptr;
+    size_t stage_used = 0;
+    struct Pending { void* dst; size_t off, bytes; };
+    std::vector<Pending> pending;
+    void drop_pending() { pending.clear(); stage_used = 0; }
     void trim() {   // give everything cached back to the driver's pool
         for (auto& kv : cache)
             for (void* q : kv.second) cudaFreeAsync(q, stream);
@@ -82,6 +93,11 @@ struct gmg_ctx {
 namespace gmg {
 
 // Stream-ordered device buffer (cudaMallocAsync pool): allocation and release cost no device sync.
+constexpr size_t kStageBytes = 8192;
+static __global__ void stage_copy_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int words) {
+    for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
+}
+
 // Size class of a request: the next multiple of 1/8 of the largest power of two not above it (<= 12.5 % slack).
 inline size_t size_class(size_t bytes) {
     if (bytes < 512) bytes = 512;
@@ -143,7 +159,19 @@ template <typename T> struct DevBuf {
         if (count > 0) GMG_CUDA(cudaMemcpyAsync(p, host, sizeof(T) * size_t(count), cudaMemcpyHostToDevice, s));
     }
     void download(T* host, int64_t count) const {
-        if (count > 0) GMG_CUDA(cudaMemcpyAsync(host, p, sizeof(T) * size_t(count), cudaMemcpyDeviceToHost, s));
+        if (count <= 0) return;
+        const size_t bytes = sizeof(T) * size_t(count);
+        if (ctx && ctx->stage && bytes <= 512 && bytes % 4 == 0 && ctx->stage_used + bytes <= kStageBytes) {
+            const size_t off = ctx->stage_used;
+            ctx->stage_used += (bytes + 15) / 16 * 16;
+            stage_copy_kernel<<<1, 64, 0, s>>>(reinterpret_cast<const uint32_t*>(p), reinterpret_cast<uint32_t*>(ctx->stage + off),
+                                               int(bytes / 4));
+            GMG_CUDA(cudaGetLastError());
+            ++ctx->launches;
+            ctx->pending.push_back({host, off, bytes});     // delivered by sync()
+            return;
+        }
+        GMG_CUDA(cudaMemcpyAsync(host, p, bytes, cudaMemcpyDeviceToHost, s));
     }
     void zero() { GMG_CUDA(cudaMemsetAsync(p, 0, sizeof(T) * size_t(n > 0 ? n : 1), s)); }
 };
@@ -170,7 +198,18 @@ inline void points_to_host(gmg_ctx* c, const double* dev, int64_t n, double* hos
                                      c->stream));
 }
 
-inline void sync(gmg_ctx* c) { GMG_CUDA(cudaStreamSynchronize(c->stream)); }
+inline void sync(gmg_ctx* c) {
+    const cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess)
+        for (const auto& q : c->pending) memcpy(q.dst, c->stage + q.off, q.bytes);
+    c->drop_pending();
+    GMG_CUDA(e);
+}
+// after an error: wait for the stream and forget staged reads whose destinations may be gone
+inline void abort_sync(gmg_ctx* c) {
+    cudaStreamSynchronize(c->stream);
+    c->drop_pending();
+}
 
 // GMG_TRACE=1 in the environment: wall-clock milliseconds between marks, each mark synchronising the
 // stream (diagnostic only; changes the timing it reports on, never the results).

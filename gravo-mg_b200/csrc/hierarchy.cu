@@ -39,10 +39,11 @@ template <typename F> static int guarded_h(gmg_ctx* c, F&& body) {
         return GMG_OK;
     } catch (const Error& e) {
         c->last_error = e.what;
-        cudaStreamSynchronize(c->stream);
+        abort_sync(c);
         return e.status;
     } catch (const std::exception& e) {
         c->last_error = e.what();
+        abort_sync(c);
         return GMG_ERR_INVALID;
     }
 }
@@ -232,6 +233,9 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             pts = L->coarse_pts.p; colptr = L->coarse.colptr.p; rowidx = L->coarse.rowidx.p; val = L->coarse.val.p;
             if (opt->build_galerkin) { a_n = m; a_colptr = L->Ac.colptr.p; a_rowidx = L->Ac.rowidx.p; a_val = L->Ac.val.p; }
             h->levels.push_back(std::move(L));
+            // the level is complete on the device (the status fetch above synchronised): let the caller start
+            // copying it out on the copy stream while the next level builds
+            if (opt->on_level) opt->on_level(opt->user, h.get(), int(h->levels.size()) - 1);
         }
         cudaEventRecord(c->ev1, c->stream);
         cudaEventSynchronize(c->ev1);
@@ -256,50 +260,75 @@ int gmg_hierarchy_level_info(const gmg_hierarchy* h, int level, gmg_level_info* 
     return GMG_OK;
 }
 
-int gmg_hierarchy_fetch(gmg_ctx* c, const gmg_hierarchy* h, int level, int which, void* out) {
-    return guarded_h(c, [&] {
-        GMG_REQUIRE(h && level >= 0 && level < int(h->levels.size()), GMG_ERR_STATE, "no such level");
-        const Level& L = *h->levels[size_t(level)];
-        const int64_t n = L.info.n, m = L.info.m, T = L.info.T;
-        auto copy = [&](const void* dev, size_t bytes) {
-            if (bytes) GMG_CUDA(cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
-        };
-        auto copy_wide = [&](const int32_t* dev, int64_t count) {
-            DevBuf<int64_t> w(c, count);
-            widen_i32(c, dev, w.p, count);
-            copy(w.p, sizeof(int64_t) * size_t(count));
-            sync(c);
-        };
-        switch (which) {
-            case GMG_H_SAMPLES: copy_wide(L.samples.p, m); break;
-            case GMG_H_PARENTS: copy_wide(L.parents.p, n); break;
-            case GMG_H_COARSE_COLPTR: copy(L.coarse.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
-            case GMG_H_COARSE_ROWIDX: copy(L.coarse.rowidx.p, sizeof(int32_t) * size_t(L.coarse.nnz)); break;
-            case GMG_H_COARSE_VAL: copy(L.coarse.val.p, sizeof(double) * size_t(L.coarse.nnz)); break;
-            case GMG_H_COARSE_POINTS: copy(L.coarse_pts.p, sizeof(double) * size_t(3 * m)); break;
-            case GMG_H_TRIANGLES: copy_wide(L.tri.tri.p, 3 * T); break;
-            case GMG_H_NORMALS: copy(L.tri.normal.p, sizeof(double) * size_t(3 * T)); break;
-            case GMG_H_FAN_PTR: copy_wide(L.tri.fan_ptr.p, m + 1); break;
-            case GMG_H_FAN: copy_wide(L.tri.fan_tri.p, 3 * T); break;
-            case GMG_H_P_ROWPTR: copy(L.P.rowptr.p, sizeof(int32_t) * size_t(n + 1)); break;
-            case GMG_H_P_COLIDX: copy(L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz)); break;
-            case GMG_H_P_VAL: copy(L.P.val.p, sizeof(double) * size_t(L.P.nnz)); break;
-            case GMG_H_AC_COLPTR:
-                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
-                copy(L.Ac.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
-            case GMG_H_AC_ROWIDX:
-                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
-                copy(L.Ac.rowidx.p, sizeof(int32_t) * size_t(L.Ac.nnz)); break;
-            case GMG_H_AC_VAL:
-                GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
-                copy(L.Ac.val.p, sizeof(double) * size_t(L.Ac.nnz)); break;
-            case GMG_H_FINE_VAL:
-                GMG_REQUIRE(level == 0, GMG_ERR_STATE, "fine values exist on level 0 only");
-                copy(h->fine_val.p, sizeof(double) * size_t(h->fine_nnz)); break;
-            default: GMG_REQUIRE(false, GMG_ERR_INVALID, "unknown array id");
-        }
+namespace {
+
+// device -> host copy of one array of a level. async: on the context's copy stream, no synchronisation (the
+// caller waits with gmg_copy_sync); arrays that are widened to int64 on the way out are not available there.
+void fetch_level_array(gmg_ctx* c, const gmg_hierarchy* h, int level, int which, void* out, bool async) {
+    GMG_REQUIRE(h && level >= 0 && level < int(h->levels.size()), GMG_ERR_STATE, "no such level");
+    const Level& L = *h->levels[size_t(level)];
+    const int64_t n = L.info.n, m = L.info.m, T = L.info.T;
+    cudaStream_t stream = c->stream;
+    if (async) {
+        if (!c->copy_stream) GMG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        stream = c->copy_stream;
+    }
+    auto copy = [&](const void* dev, size_t bytes) {
+        if (bytes) GMG_CUDA(cudaMemcpyAsync(out, dev, bytes, cudaMemcpyDeviceToHost, stream));
+    };
+    auto copy_wide = [&](const int32_t* dev, int64_t count) {
+        GMG_REQUIRE(!async, GMG_ERR_INVALID, "int64 outputs (samples, parents, triangles, fans) have no asynchronous fetch");
+        DevBuf<int64_t> w(c, count);
+        widen_i32(c, dev, w.p, count);
+        copy(w.p, sizeof(int64_t) * size_t(count));
         sync(c);
-    });
+    };
+    switch (which) {
+        case GMG_H_SAMPLES: copy_wide(L.samples.p, m); break;
+        case GMG_H_PARENTS: copy_wide(L.parents.p, n); break;
+        case GMG_H_COARSE_COLPTR: copy(L.coarse.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
+        case GMG_H_COARSE_ROWIDX: copy(L.coarse.rowidx.p, sizeof(int32_t) * size_t(L.coarse.nnz)); break;
+        case GMG_H_COARSE_VAL: copy(L.coarse.val.p, sizeof(double) * size_t(L.coarse.nnz)); break;
+        case GMG_H_COARSE_POINTS: copy(L.coarse_pts.p, sizeof(double) * size_t(3 * m)); break;
+        case GMG_H_TRIANGLES: copy_wide(L.tri.tri.p, 3 * T); break;
+        case GMG_H_NORMALS: copy(L.tri.normal.p, sizeof(double) * size_t(3 * T)); break;
+        case GMG_H_FAN_PTR: copy_wide(L.tri.fan_ptr.p, m + 1); break;
+        case GMG_H_FAN: copy_wide(L.tri.fan_tri.p, 3 * T); break;
+        case GMG_H_P_ROWPTR: copy(L.P.rowptr.p, sizeof(int32_t) * size_t(n + 1)); break;
+        case GMG_H_P_COLIDX: copy(L.P.colidx.p, sizeof(int32_t) * size_t(L.P.nnz)); break;
+        case GMG_H_P_VAL: copy(L.P.val.p, sizeof(double) * size_t(L.P.nnz)); break;
+        case GMG_H_AC_COLPTR:
+            GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+            copy(L.Ac.colptr.p, sizeof(int32_t) * size_t(m + 1)); break;
+        case GMG_H_AC_ROWIDX:
+            GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+            copy(L.Ac.rowidx.p, sizeof(int32_t) * size_t(L.Ac.nnz)); break;
+        case GMG_H_AC_VAL:
+            GMG_REQUIRE(L.Ac.colptr.p, GMG_ERR_STATE, "hierarchy was built without the Galerkin operator");
+            copy(L.Ac.val.p, sizeof(double) * size_t(L.Ac.nnz)); break;
+        case GMG_H_FINE_VAL:
+            GMG_REQUIRE(level == 0, GMG_ERR_STATE, "fine values exist on level 0 only");
+            copy(h->fine_val.p, sizeof(double) * size_t(h->fine_nnz)); break;
+        default: GMG_REQUIRE(false, GMG_ERR_INVALID, "unknown array id");
+    }
+    if (!async) sync(c);
+}
+
+}  // namespace
+
+int gmg_hierarchy_fetch(gmg_ctx* c, const gmg_hierarchy* h, int level, int which, void* out) {
+    return guarded_h(c, [&] { fetch_level_array(c, h, level, which, out, false); });
+}
+
+/* The same copy on the context's copy stream, not waited for: meant to be called from the on_level callback
+ * of gmg_hierarchy_build (the level is complete by then), so that a finished level leaves the device while the
+ * next one builds. `out` should be pinned host memory. gmg_copy_sync waits for every such copy. */
+int gmg_hierarchy_fetch_async(gmg_ctx* c, const gmg_hierarchy* h, int level, int which, void* out) {
+    return guarded_h(c, [&] { fetch_level_array(c, h, level, which, out, true); });
+}
+
+int gmg_copy_sync(gmg_ctx* c) {
+    return guarded_h(c, [&] { if (c->copy_stream) GMG_CUDA(cudaStreamSynchronize(c->copy_stream)); });
 }
 
 }  // extern "C"

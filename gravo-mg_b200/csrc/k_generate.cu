@@ -113,10 +113,11 @@ template <typename F> int guarded_g(gmg_ctx* c, F&& body) {
         return GMG_OK;
     } catch (const Error& e) {
         c->last_error = e.what;
-        cudaStreamSynchronize(c->stream);
+        abort_sync(c);
         return e.status;
     } catch (const std::exception& e) {
         c->last_error = e.what();
+        abort_sync(c);
         return GMG_ERR_INVALID;
     }
 }

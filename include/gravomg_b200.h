@@ -174,6 +174,11 @@ typedef struct {
                                 1: divisor = number of off-diagonal entries */
     const double* radius_override; /* optional host array [levels-1]; entries > 0 replace the computed radius */
     int32_t build_galerkin;  /* 1: also A_c = P^T A P on every level (needs A_val) */
+    /* optional: called on the building thread as soon as a level is complete on the device, with the
+     * hierarchy under construction (valid for gmg_hierarchy_level_info / gmg_hierarchy_fetch_async of levels
+     * <= level only). Lets a finished level leave the device while the next one builds. */
+    void (*on_level)(void* user, gmg_hierarchy* h, int level);
+    void* user;
 } gmg_hierarchy_options;
 
 typedef struct {
@@ -217,6 +222,12 @@ typedef enum {
     GMG_H_FINE_VAL = 16       /* f64[nnz] level-0 only: the toEdgeDistanceMatrix values */
 } gmg_hierarchy_array;
 int gmg_hierarchy_fetch(gmg_ctx* ctx, const gmg_hierarchy* h, int level, int which, void* out);
+/* The same copy on the context's COPY stream, not waited for (arrays without an int64 conversion only: the
+ * coarse graph, points, normals, P, A_c, fine values). Call it from gmg_hierarchy_options.on_level so a
+ * finished level leaves the device while the next one builds; `out` should be pinned host memory.
+ * gmg_copy_sync waits for every such copy. */
+int gmg_hierarchy_fetch_async(gmg_ctx* ctx, const gmg_hierarchy* h, int level, int which, void* out);
+int gmg_copy_sync(gmg_ctx* ctx);
 
 /* ------------------------------------------------------------------------------------------------
  * SpMV, multicolour Gauss-Seidel and the V-cycle that validates a hierarchy [not in reference;

@@ -163,3 +163,31 @@ def test_parallel_sampler_statistics(ctx, orc):
                 for k2 in range(A.indptr[j], A.indptr[j + 1]):
                     t = A.indices[k2]
                     if d + val[k2] < radius and t != s: assert not sel_mask[t]
+
+
+def test_levels_streamed_out_during_the_build(ctx):
+    """on_level / gmg_hierarchy_fetch_async: P of every level copied out on the copy stream while the next level
+    builds must equal the ordinary fetch after the build."""
+    import torch
+    from gravomg_b200 import capi
+    cfg = meshgen.make_config("C3", 0.01)
+    V, A = cfg["V"], cfg["A"]
+    inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+    got = {}
+
+    def stream_out(level, info):
+        bufs = [(capi.H_P_ROWPTR, torch.empty(info["n"] + 1, dtype=torch.int32).pin_memory().numpy()),
+                (capi.H_P_COLIDX, torch.empty(info["nnz_p"], dtype=torch.int32).pin_memory().numpy()),
+                (capi.H_P_VAL, torch.empty(info["nnz_p"], dtype=torch.float64).pin_memory().numpy())]
+        got[level] = bufs
+        return bufs
+
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, stream_out=stream_out)
+    ctx.copy_sync()
+    assert sorted(got) == list(range(h.num_levels)) and h.streamed_bytes > 0
+    for lvl, bufs in got.items():
+        for which, arr in bufs:
+            assert np.array_equal(arr, h.fetch(lvl, which)), (lvl, which)
+    # int64 outputs are converted on the way out and have no asynchronous path
+    h.close(); inp.close()
+    assert ctx.trim() >= 0
