@@ -65,10 +65,6 @@ def build(verbose=False, force=False):
     return LIB
 
 
-if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
-
-
 FACADE_DIR = os.path.join(HERE, "facade")
 FACADE_TEST = os.path.join(LIBDIR, "facade_test")
 
@@ -92,3 +88,8 @@ def build_facade_test():
     if r.returncode != 0:
         raise RuntimeError(f"facade build failed:\n{r.stdout}\n{r.stderr}")
     return FACADE_TEST
+
+
+if __name__ == "__main__":
+    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    print(build_facade_test())        # links against the library and bakes in the header's struct layouts
