@@ -77,7 +77,8 @@ def build_facade_test():
         return None
     root = os.path.dirname(HERE)
     srcs = [src, os.path.join(FACADE_DIR, "gravomg_facade.cpp"), os.path.join(FACADE_DIR, "facade_extras.cpp")]
-    deps = srcs + [LIB, os.path.join(FACADE_DIR, "include", "gravomg", "b200_facade.h")]
+    deps = srcs + [LIB, os.path.join(FACADE_DIR, "include", "gravomg", "b200_facade.h"),
+                   os.path.join(root, "include", "gravomg_b200.h")]
     if os.path.exists(FACADE_TEST) and os.path.getmtime(FACADE_TEST) > max(os.path.getmtime(d) for d in deps):
         return FACADE_TEST
     cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(FACADE_DIR, "include"),
