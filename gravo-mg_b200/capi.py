@@ -517,6 +517,20 @@ class Solver:
                                                        _p(res, _f64p)))
         return x, res
 
+    def pcg(self, b, x0=None, rel_tol=1e-8, max_iter=100, sweeps=2, coarse_sweeps=20):
+        """Conjugate gradients preconditioned by one symmetric V(sweeps, sweeps) cycle. Returns (x, residual
+        norms [iterations + 1])."""
+        b = _f64(b)
+        x = np.zeros_like(b) if x0 is None else np.array(x0, dtype=np.float64)
+        res = np.zeros(max_iter + 1, dtype=np.float64)
+        it = C.c_int(0)
+        lib = self.ctx.lib
+        lib.gmg_solver_pcg.argtypes = [C.c_void_p, C.c_void_p, _f64p, _f64p, C.c_double, C.c_int, C.c_int, C.c_int,
+                                       C.POINTER(C.c_int), _f64p]
+        self.ctx._check(lib.gmg_solver_pcg(self.ctx.h, self.h, _p(b, _f64p), _p(x, _f64p), rel_tol, max_iter, sweeps,
+                                           coarse_sweeps, C.byref(it), _p(res, _f64p)))
+        return x, res[:it.value + 1]
+
     def close(self):
         if C is None:
             return

@@ -193,6 +193,39 @@ __global__ void __launch_bounds__(kBlock) sumsq_partial_kernel(int32_t n, const 
     __syncthreads();
     if (threadIdx.x == 0) { double t = 0.0; for (int w = 0; w < kBlock / 32; ++w) t += ws[w]; partial[blockIdx.x] = t; }
 }
+__global__ void __launch_bounds__(kBlock) dot_partial_kernel(int32_t n, const double* __restrict__ x, const double* __restrict__ y,
+                                                             double* __restrict__ partial) {
+    __shared__ double ws[kBlock / 32];
+    double s = 0.0;
+    for (int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x; i < n; i += int64_t(gridDim.x) * kBlock) s += x[i] * y[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) { double t = 0.0; for (int w = 0; w < kBlock / 32; ++w) t += ws[w]; partial[blockIdx.x] = t; }
+}
+// fixed grid and fixed summation order: the same inputs give the same bits
+double dot(gmg_ctx* c, int32_t n, const double* x, const double* y) {
+    if (n == 0) return 0.0;
+    const int blocks = std::min(div_up(n, kBlock), 1024);
+    DevBuf<double> partial(c, blocks);
+    GMG_LAUNCH(c, dot_partial_kernel, blocks, kBlock, 0, n, x, y, partial.p);
+    std::vector<double> h(size_t(blocks), 0.0);
+    partial.download(h.data(), blocks);
+    sync(c);
+    double t = 0.0;
+    for (double v : h) t += v;
+    return t;
+}
+
+__global__ void __launch_bounds__(kBlock) xpby_kernel(int32_t n, const double* __restrict__ x, double b, double* __restrict__ y) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n) y[i] = x[i] + b * y[i];
+}
+void xpby(gmg_ctx* c, int32_t n, const double* x, double b, double* y) {
+    if (n > 0) GMG_LAUNCH(c, xpby_kernel, div_up(n, kBlock), kBlock, 0, n, x, b, y);
+}
+
 double norm2(gmg_ctx* c, int32_t n, const double* x) {
     if (n == 0) return 0.0;
     const int blocks = std::min(div_up(n, kBlock), 1024);

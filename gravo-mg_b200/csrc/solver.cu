@@ -52,10 +52,13 @@ struct Timer {
     }
 };
 
-void vcycle(gmg_ctx* c, gmg_solver* s, size_t l, int pre, int post, int coarse_sweeps) {
+// symmetric: the coarsest level sweeps forward then backward, so that with pre == post the cycle is a
+// symmetric operator (what conjugate gradients needs of its preconditioner)
+void vcycle(gmg_ctx* c, gmg_solver* s, size_t l, int pre, int post, int coarse_sweeps, bool symmetric = false) {
     SolverLevel& L = *s->levels[l];
     if (l + 1 == s->levels.size()) {
         gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, coarse_sweeps, false);
+        if (symmetric) gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, coarse_sweeps, true);
         return;
     }
     SolverLevel& C = *s->levels[l + 1];
@@ -63,7 +66,7 @@ void vcycle(gmg_ctx* c, gmg_solver* s, size_t l, int pre, int post, int coarse_s
     spmv(c, L.n, L.outer, L.inner, L.val, L.x.p, L.r.p, -1.0, L.b.p);                     // r = b - A x
     spmv(c, C.n, L.R.rowptr.p, L.R.colidx.p, L.R.val.p, L.r.p, C.b.p, 1.0, nullptr);      // b_c = P^T r
     C.x.zero();
-    vcycle(c, s, l + 1, pre, post, coarse_sweeps);
+    vcycle(c, s, l + 1, pre, post, coarse_sweeps, symmetric);
     spmv(c, L.n, L.P->rowptr.p, L.P->colidx.p, L.P->val.p, C.x.p, L.x.p, 1.0, L.x.p);     // x += P e
     gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, post, true);
 }
@@ -161,6 +164,58 @@ int gmg_solver_vcycle(gmg_ctx* c, gmg_solver* s, const double* b, double* x, int
         }
         c->last_kernel_ms = total_ms;
         F.x.download(x, F.n);
+        sync(c);
+    });
+}
+
+/* Conjugate gradients on A x = b preconditioned by one symmetric V(sweeps, sweeps) cycle from a zero guess.
+ * Stops when ||b - A x||_2 <= rel_tol * ||b||_2 or after max_iter iterations. residual_out (optional,
+ * max_iter + 1 entries) receives the residual norm before the first and after every iteration. */
+int gmg_solver_pcg(gmg_ctx* c, gmg_solver* s, const double* b, double* x, double rel_tol, int max_iter, int sweeps,
+                   int coarse_sweeps, int* iterations_out, double* residual_out) {
+    return guarded_s(c, [&] {
+        GMG_REQUIRE(s && b && x && max_iter >= 0 && sweeps >= 1, GMG_ERR_INVALID, "bad arguments");
+        SolverLevel& F = *s->levels[0];
+        const int32_t n = F.n;
+        DevBuf<double> sol(c, n), res(c, n), p(c, n), Ap(c, n), rhs(c, n);
+        rhs.upload(b, n);
+        sol.upload(x, n);
+        spmv(c, n, F.outer, F.inner, F.val, sol.p, res.p, -1.0, rhs.p);            // r = b - A x
+        const double bnorm = norm2(c, n, rhs.p);
+        double rnorm = norm2(c, n, res.p);
+        if (residual_out) residual_out[0] = rnorm;
+        auto precondition = [&] {                                                   // F.x = M^-1 res
+            GMG_CUDA(cudaMemcpyAsync(F.b.p, res.p, sizeof(double) * size_t(n), cudaMemcpyDeviceToDevice, c->stream));
+            F.x.zero();
+            vcycle(c, s, 0, sweeps, sweeps, coarse_sweeps, true);
+        };
+        Timer t(c);
+        int it = 0;
+        double rz = 0.0;
+        if (rnorm > rel_tol * bnorm) {
+            precondition();
+            GMG_CUDA(cudaMemcpyAsync(p.p, F.x.p, sizeof(double) * size_t(n), cudaMemcpyDeviceToDevice, c->stream));
+            rz = dot(c, n, res.p, F.x.p);
+        }
+        while (it < max_iter && rnorm > rel_tol * bnorm) {
+            spmv(c, n, F.outer, F.inner, F.val, p.p, Ap.p, 1.0, nullptr);
+            const double pAp = dot(c, n, p.p, Ap.p);
+            GMG_REQUIRE(pAp > 0.0, GMG_ERR_INVALID, "pcg: the operator is not positive definite along the search direction");
+            const double alpha = rz / pAp;
+            axpy(c, n, alpha, p.p, sol.p);
+            axpy(c, n, -alpha, Ap.p, res.p);
+            rnorm = norm2(c, n, res.p);
+            ++it;
+            if (residual_out) residual_out[it] = rnorm;
+            if (rnorm <= rel_tol * bnorm) break;
+            precondition();
+            const double rz_new = dot(c, n, res.p, F.x.p);
+            xpby(c, n, F.x.p, rz_new / rz, p.p);                                    // p = z + beta p
+            rz = rz_new;
+        }
+        t.stop();
+        if (iterations_out) *iterations_out = it;
+        sol.download(x, n);
         sync(c);
     });
 }

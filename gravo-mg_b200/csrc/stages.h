@@ -176,6 +176,8 @@ void gauss_seidel(gmg_ctx* c, const Colouring& col, const int32_t* outer, const 
 void gauss_seidel_rows(gmg_ctx* c, const int32_t* rows, int32_t count, const int32_t* outer, const int32_t* inner,
                        const double* val, const double* b, double* x);
 double norm2(gmg_ctx* c, int32_t n, const double* x);
+double dot(gmg_ctx* c, int32_t n, const double* x, const double* y);
+void xpby(gmg_ctx* c, int32_t n, const double* x, double b, double* y);     // y = x + b * y
 
 // index conversions at the ABI boundary (std::vector<Eigen::Index> is int64, device indices int32)
 void narrow_i64(gmg_ctx* c, const int64_t* in, int32_t* out, int64_t n, int64_t upper, int32_t* d_flag);

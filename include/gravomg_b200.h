@@ -253,7 +253,13 @@ void gmg_solver_destroy(gmg_solver* s);
  * ||b - A x||_2 before the first and after every cycle. */
 int gmg_solver_vcycle(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, int cycles, int pre, int post,
                       int coarse_sweeps, double* residual_out);
-/* device milliseconds of the last gmg_spmv / gmg_solver_vcycle are available through gmg_last_kernel_ms */
+/* Conjugate gradients on A x = b preconditioned by one SYMMETRIC V(sweeps, sweeps) cycle from a zero guess (post
+ * sweeps in reverse colour order; the coarsest level sweeps forward then backward). Stops when
+ * ||b - A x||_2 <= rel_tol * ||b||_2 or after max_iter iterations; residual_out (optional, max_iter + 1
+ * entries) receives the residual norm before the first and after every iteration. */
+int gmg_solver_pcg(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, double rel_tol, int max_iter, int sweeps,
+                   int coarse_sweeps, int* iterations_out, double* residual_out);
+/* device milliseconds of the last gmg_spmv / gmg_solver_vcycle / gmg_solver_pcg: gmg_last_kernel_ms */
 
 /* ------------------------------------------------------------------------------------------------
  * Row-sharded hierarchy build [not in reference; one process per GPU]. Fine vertices are split into

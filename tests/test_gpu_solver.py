@@ -61,3 +61,27 @@ def test_vcycle_poisson(ctx):
     factors = res[1:] / res[:-1]
     assert factors.max() < 0.9
     s.close(); h.close(); inp.close()
+
+
+def test_pcg_with_vcycle_preconditioner(ctx):
+    """Conjugate gradients preconditioned by one symmetric V(2,2) cycle on the SPD torus operator: converges to
+    1e-10 in a few tens of iterations (plain CG needs hundreds), to the solution scipy's direct solve gives."""
+    import scipy.sparse.linalg as spla
+    from gravomg_b200.capi import Input, Hierarchy, Solver
+    cfg = meshgen.make_config("C3", 0.01)
+    V, A = cfg["V"], cfg["A"]
+    xstar = np.sin(3 * V[:, 0]) * np.cos(2 * V[:, 1]) + V[:, 2]
+    b = A @ xstar
+    inp = Input(ctx, V, A.indptr, A.indices, A.data)
+    h = Hierarchy(ctx, inp, cfg["levels"], build_galerkin=True)
+    s = Solver(ctx, inp, h)
+    x, res = s.pcg(b, rel_tol=1e-10, max_iter=60)
+    assert len(res) - 1 <= 40, len(res)
+    assert res[-1] <= 1e-10 * np.linalg.norm(b)
+    assert np.abs(A @ x - b).max() <= 10 * res[-1]
+    ref = spla.spsolve(A.tocsc(), b)
+    assert np.abs(x - ref).max() <= 1e-6 * np.abs(ref).max()
+    # the preconditioner matters: unpreconditioned CG is nowhere near after the same number of iterations
+    _, info = spla.cg(A, b, rtol=1e-10, maxiter=len(res) - 1)
+    assert info != 0
+    s.close(); h.close(); inp.close()

@@ -72,3 +72,19 @@ def test_edge_cases(orc):
     prp, pci, pva, rc = orc.construct_prolongation(V, cpts, ccp, cri, cval, par, 0)
     assert rc == 0 and list(np.diff(prp)) == [2, 2, 1, 2]
     assert np.allclose(np.add.reduceat(pva, prp[:-1]), 1.0)
+
+
+def test_headless_ply_dump(tmp_path):
+    """gravo-mg_b200/dump.py write_ply: the header counts and the body must round-trip (the viewer replacement)."""
+    import numpy as np
+    from gravomg_b200.dump import write_ply
+    pts = np.array([[0., 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1.5]])
+    tris = np.array([[0, 1, 2], [0, 2, 3]])
+    p = tmp_path / "t.ply"
+    write_ply(str(p), pts, tris, {"parent": np.array([0, 0, 1, 1])})
+    lines = p.read_text().splitlines()
+    assert lines[0] == "ply" and "element vertex 4" in lines and "element face 2" in lines
+    body = lines[lines.index("end_header") + 1:]
+    assert len(body) == 6
+    assert np.allclose([float(v) for v in body[3].split()], [0, 0, 1.5, 1])
+    assert body[5].split() == ["3", "0", "2", "3"]
