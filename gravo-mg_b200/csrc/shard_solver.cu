@@ -7,7 +7,9 @@
 //                    the single-GPU sweep in (colour, row) order);
 //     residual       r = b - A x on owned rows;
 //     restriction    b_c = R r on the owned coarse rows (R = the owned rows of P^T, kept by the build);
-//     prolongation   x += P e on the owned fine rows.
+//     prolongation   x += P e on the owned fine rows;
+//     coarsest level every rank gathers the whole right-hand side and sweeps ALL rows redundantly: finishing a
+//                    small level on every GPU is cheaper than exchanging its halos colour by colour.
 // Between them the HOST exchanges ghost entries (gravo-mg_b200/sharded.py: packed all-to-all over
 // NCCL / NVLink; a loop-back between virtual ranks in the single-GPU tests). This file exposes what the
 // host needs for that: the byte mask of the entries an operator's owned rows read outside the owned
@@ -214,6 +216,10 @@ int gmg_shard_solver_op(gmg_ctx* c, gmg_shard_solver* s, int level, int op, int 
                 break;
             }
             case GMG_SO_ZERO_X: L.x.zero(); break;
+            case GMG_SO_GS_ALL:       // `arg` sweeps over ALL rows: a small level every rank solves redundantly
+                GMG_REQUIRE(arg >= 0, GMG_ERR_INVALID, "negative sweep count");
+                gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, arg, false);
+                break;
             case GMG_SO_SUMSQ_R: {
                 GMG_REQUIRE(out, GMG_ERR_INVALID, "null output");
                 const double nr = norm2(c, own, L.r.p + L.lo);

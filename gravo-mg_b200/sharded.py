@@ -431,7 +431,7 @@ class ShardedHierarchy:
 # ---- row-sharded smoothing / V-cycle -----------------------------------------------------------------
 (SV_X, SV_B, SV_R, SV_COLOUR, SV_MASK) = range(5)
 (HP_A, HP_R, HP_P) = range(3)
-(SO_GS_COLOUR, SO_RESIDUAL, SO_RESTRICT, SO_PROLONG, SO_ZERO_X, SO_SUMSQ_R) = range(6)
+(SO_GS_COLOUR, SO_RESIDUAL, SO_RESTRICT, SO_PROLONG, SO_ZERO_X, SO_SUMSQ_R, SO_GS_ALL) = range(7)
 
 
 def halo_counts(ghost, chunk, world):
@@ -628,9 +628,29 @@ class ShardedSolver:
                 self._op(level, SO_GS_COLOUR, col)
                 self._exchange(self.plan_colour[level][col], level, SV_X)
 
+    def _gather_vector(self, level, which):
+        """All-gather the owned slices of a full-length vector (slice = the level's split, rank r owns slice r)."""
+        t = self.torch
+        chunk = self.geom[level][0]["chunk"]
+        vecs = [self._vec(k, level, which)[:chunk * self.world] for k in range(len(self.h))]
+        self._fence()
+        self.exchanges += 1
+        self.exchange_bytes += 8 * chunk * self.world
+        if self.comm is not None:
+            self.comm.all_gather_inplace(vecs[0].view(t.uint8), 8 * chunk)
+        else:
+            for src, r in enumerate(self.ranks):
+                for dst in range(len(vecs)):
+                    if dst != src:
+                        vecs[dst][r * chunk:(r + 1) * chunk].copy_(vecs[src][r * chunk:(r + 1) * chunk])
+        self._fence()
+
     def _vcycle(self, level, pre, post, coarse_sweeps):
         if level + 1 == self.num_levels:
-            self._smooth(level, coarse_sweeps, False)
+            # the coarsest level is small: every rank gathers the whole right-hand side and solves it redundantly
+            # (same kernel, same rows, same order as the single-GPU cycle) instead of exchanging halos per colour
+            self._gather_vector(level, SV_B)
+            self._op(level, SO_GS_ALL, coarse_sweeps)
             return
         self._smooth(level, pre, False)
         self._op(level, SO_RESIDUAL)
@@ -638,7 +658,8 @@ class ShardedSolver:
         self._op(level, SO_RESTRICT)
         self._op(level + 1, SO_ZERO_X)
         self._vcycle(level + 1, pre, post, coarse_sweeps)
-        self._exchange(self.plan_p[level], level + 1, SV_X)
+        if level + 2 < self.num_levels:                 # the coarsest level's x is already whole on every rank
+            self._exchange(self.plan_p[level], level + 1, SV_X)
         self._op(level, SO_PROLONG)
         self._exchange(self.plan_a[level], level, SV_X)
         self._smooth(level, post, True)

@@ -313,6 +313,7 @@ int gmg_shard_fetch(gmg_ctx* ctx, const gmg_shard* s, int level, int which, void
  * keeps full-length vectors per level (levels = prolongations + 1); only the owned entries [lo, hi) and the
  * ghost entries its rows read are valid. An op acts on the owned rows; between ops the HOST exchanges
  * ghost entries (packed all-to-all over NCCL in gravo-mg_b200/sharded.py), guided by the halo masks.
+ *   Coarsest level: all-gather b, GS_ALL (every rank solves it whole; no halo exchange).
  *   V-cycle on level l:  for each colour k { GS_COLOUR(k) ; exchange x over the ghosts of colour k } (pre
  *   sweeps) ; RESIDUAL ; exchange r over pattern R ; RESTRICT ; ZERO_X(l+1) ; recurse ; exchange x(l+1) over
  *   pattern P ; PROLONG ; exchange x over pattern A ; post sweeps in reverse colour order.
@@ -320,7 +321,8 @@ int gmg_shard_fetch(gmg_ctx* ctx, const gmg_shard* s, int level, int which, void
 typedef struct gmg_shard_solver gmg_shard_solver;
 enum { GMG_SV_X = 0, GMG_SV_B, GMG_SV_R, GMG_SV_COLOUR, GMG_SV_MASK };
 enum { GMG_HP_A = 0, GMG_HP_R, GMG_HP_P };
-enum { GMG_SO_GS_COLOUR = 0, GMG_SO_RESIDUAL, GMG_SO_RESTRICT, GMG_SO_PROLONG, GMG_SO_ZERO_X, GMG_SO_SUMSQ_R };
+enum { GMG_SO_GS_COLOUR = 0, GMG_SO_RESIDUAL, GMG_SO_RESTRICT, GMG_SO_PROLONG, GMG_SO_ZERO_X, GMG_SO_SUMSQ_R,
+       GMG_SO_GS_ALL };
 /* `shard` and `in` must outlive the solver */
 int gmg_shard_solver_create(gmg_ctx* ctx, const gmg_shard* shard, const gmg_input* in, gmg_shard_solver** out);
 void gmg_shard_solver_destroy(gmg_shard_solver* s);
@@ -335,7 +337,9 @@ int gmg_shard_solver_vector(gmg_shard_solver* s, int level, int which, void** pt
  * *space = number of entries of that mask. */
 int gmg_shard_solver_halo_mask(gmg_ctx* ctx, gmg_shard_solver* s, int level, int pattern, int64_t* space);
 /* One operator on the owned rows. GS_COLOUR: arg = colour. RESIDUAL: r = b - A x. RESTRICT: b(level+1) = R r.
- * PROLONG: x += P x(level+1). ZERO_X: x = 0 (all entries). SUMSQ_R: *out = sum over owned rows of r^2. */
+ * PROLONG: x += P x(level+1). ZERO_X: x = 0 (all entries). SUMSQ_R: *out = sum over owned rows of r^2.
+ * GS_ALL: arg sweeps over ALL rows (the coarsest level, after the host has all-gathered b: X, B and R hold
+ * slice * world entries, rank r owning slice r, so an in-place all-gather of the owned slices completes them). */
 int gmg_shard_solver_op(gmg_ctx* ctx, gmg_shard_solver* s, int level, int op, int arg, double* out);
 
 #ifdef __cplusplus
