@@ -65,6 +65,8 @@ def main():
             name = r[idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("gmg::", "")
             rd = to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]])
             wr = to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]])
+            if name in js:      # several launches of one kernel: keep the first (level 0, the largest)
+                continue
             js[name] = {"dram_bytes": int(rd + wr),
                         "time_us": to_us(r[idx["gpu__time_duration.sum"]], units[idx["gpu__time_duration.sum"]])}
         with open(sys.argv[4], "w") as f:
