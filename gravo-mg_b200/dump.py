@@ -28,7 +28,6 @@ def dump_hierarchy(h, fine_points, outdir):
     """capi.Hierarchy -> outdir/level<k>_{coarse_points,parents,samples,P_rowptr,P_colidx,P_val,projected}.npy and
     outdir/level<k>_coarse.ply (coarse points + Voronoi triangles) / level<k>_fine.ply (fine points coloured by
     parent). Returns the list of files written."""
-    from . import capi
     os.makedirs(outdir, exist_ok=True)
     written = []
     pts = np.asarray(fine_points)

@@ -21,7 +21,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
-from .capi import (Context, GmgError, HierarchyOptions, LevelInfo, _f64p, _i32, _i32p, _p, _pts,
+from .capi import (GmgError, HierarchyOptions, LevelInfo, _f64p, _p,
                    H_SAMPLES, H_PARENTS, H_COARSE_COLPTR, H_COARSE_ROWIDX, H_COARSE_VAL, H_COARSE_POINTS, H_TRIANGLES,
                    H_NORMALS, H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL, H_AC_COLPTR, H_AC_ROWIDX, H_AC_VAL)
 

@@ -1,7 +1,6 @@
 #!/usr/bin/env python
 """Per-build stage times of repeated hierarchy builds (diagnostic): python tools/diag_stage_times.py C3 exact 6"""
 import os, sys, time
-import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from gravomg_b200 import meshgen, capi
