@@ -510,6 +510,7 @@ class ShardedSolver:
         lib.gmg_shard_solver_halo_mask.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int64)]
         lib.gmg_shard_solver_op.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]
         self.ranks = [s.rank for s in sh.shards]
+        self._vec_cache = {}
         self.h = []
         for s in sh.shards:
             h = C.c_void_p()
@@ -556,6 +557,14 @@ class ShardedSolver:
             self.torch.cuda.synchronize()
 
     def _vec(self, k, level, which):
+        key = (k, level, which)
+        hit = self._vec_cache.get(key)
+        if hit is None:
+            hit = self._vec_cache[key] = self._vec_wrap(k, level, which)
+        return hit
+
+    def _vec_wrap(self, k, level, which):
+        """A solver vector as a torch tensor aliasing the library's device memory (stable for the solver's life)."""
         t = self.torch
         ptr = C.c_void_p()
         rc = self.ctx.lib.gmg_shard_solver_vector(self.h[k], C.c_int(level), C.c_int(which), C.byref(ptr))
