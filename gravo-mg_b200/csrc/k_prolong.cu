@@ -18,6 +18,8 @@
 // Algorithmic bytes: 32n + 12nnzP + 32m + 4nnz_c + 48T.
 #include "stages.h"
 
+#include <algorithm>
+
 namespace gmg {
 
 struct ProlongArgs {
@@ -102,7 +104,12 @@ __device__ __forceinline__ void emit_row(const ProlongArgs& a, int32_t f, const 
     for (int i = 0; i < k; ++i) { a.row_col[3 * r + i] = c[i]; a.row_val[3 * r + i] = v[i]; }
 }
 
-__global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a) {
+// Common case, one thread per fine vertex: degree-0 / degree-1 parents and the first-hit walk over the parent's fan.
+// A vertex that lies in none of the fan's triangles (a few per cent) is appended to `fallback` and finished by
+// prolong_fallback_kernel: keeping the rare edge / three-nearest fallbacks out of this kernel keeps its registers
+// and code size down.
+__global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a, int32_t* __restrict__ fallback,
+                                                                 int32_t* __restrict__ fallback_count) {
     const int64_t gid = int64_t(a.f_lo) + int64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (gid >= a.f_hi) return;
     const int32_t f = int32_t(gid);
@@ -125,11 +132,9 @@ __global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a) 
         return;
     }
     const int32_t fb = __ldg(a.fan_ptr + c), fe = __ldg(a.fan_ptr + c + 1);
-    const int32_t F = fe - fb;
-    unsigned long long bits = 0ull;   // 2 flag bits per fan triangle, used when F <= 32
-    for (int32_t i = 0; i < F; ++i) {                                                     // :356
-        const int32_t k1 = __ldg(a.fan_o1 + fb + i), k2 = __ldg(a.fan_o2 + fb + i);
-        const int64_t t = __ldg(a.fan_tri + fb + i);
+    for (int32_t i = fb; i < fe; ++i) {                                                   // :356
+        const int32_t k1 = __ldg(a.fan_o1 + i), k2 = __ldg(a.fan_o2 + i);
+        const int64_t t = __ldg(a.fan_tri + i);
         const V3 nn{__ldg(a.normal + 3 * t), __ldg(a.normal + 3 * t + 1), __ldg(a.normal + 3 * t + 2)};
         double bary[3]; bool b1, b2;
         if (in_triangle(p, pc, ld3(a.cp, a.m, k1), ld3(a.cp, a.m, k2), nn, bary, b1, b2)) {   // :374-380
@@ -140,62 +145,86 @@ __global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a) 
             emit_row(a, f, ids, w, 3);
             return;
         }
-        if (i < 32) bits |= (unsigned long long)(b1 ? 1 : 0) << (2 * i) | (unsigned long long)(b2 ? 1 : 0) << (2 * i + 1);
     }
     warp_count(a.stats + 0);
-    // First fallback (:407-448): smallest never-flagged key with a usable first-seen value.
-    int32_t best = 0x7fffffff;
-    for (int32_t i = 0; i < F; ++i) {
-        for (int s = 0; s < 2; ++s) {
-            const int32_t k = __ldg((s ? a.fan_o2 : a.fan_o1) + fb + i);
-            if (k >= best) continue;
-            bool bad = false;
-            for (int32_t j = 0; j < F && !bad; ++j) {
-                const int32_t j1 = __ldg(a.fan_o1 + fb + j), j2 = __ldg(a.fan_o2 + fb + j);
-                if (j1 != k && j2 != k) continue;
-                bool b1, b2;
-                if (F <= 32) { b1 = (bits >> (2 * j)) & 1; b2 = (bits >> (2 * j + 1)) & 1; }
-                else {
-                    const int64_t t = __ldg(a.fan_tri + fb + j);
-                    const V3 nn{__ldg(a.normal + 3 * t), __ldg(a.normal + 3 * t + 1), __ldg(a.normal + 3 * t + 2)};
-                    double bary[3];
-                    in_triangle(p, pc, ld3(a.cp, a.m, j1), ld3(a.cp, a.m, j2), nn, bary, b1, b2);
-                }
-                // the map is keyed by vertex: tri[1] and tri[2] may name the same key (:43-48)
-                bad = (j1 == k && b1) || (j2 == k && b2);
-            }
-            if (!bad && edge_value_usable(p, pc, ld3(a.cp, a.m, k))) best = k;
+    fallback[warp_append(fallback_count)] = f;
+}
+
+// The vertices the walk above found no triangle for (grid-stride over the list; its length is read on the device).
+__global__ void __launch_bounds__(kBlock) prolong_fallback_kernel(ProlongArgs a, const int32_t* __restrict__ fallback,
+                                                                  const int32_t* __restrict__ fallback_count) {
+    const int32_t count = *fallback_count;
+    for (int64_t r = int64_t(blockIdx.x) * kBlock + threadIdx.x; r < count; r += int64_t(gridDim.x) * kBlock) {
+        const int32_t f = fallback[r];
+        const int32_t c = __ldg(a.parents + f);
+        const V3 p = ld3(a.fp, a.n, f), pc = ld3(a.cp, a.m, c);
+        const int32_t cb = __ldg(a.c_colptr + c), ce = __ldg(a.c_colptr + c + 1);
+        const int32_t fb = __ldg(a.fan_ptr + c), fe = __ldg(a.fan_ptr + c + 1);
+        const int32_t F = fe - fb;
+        int32_t ids[3]; double w[3];
+        // the edge-side flags of the walk that failed (2 bits per fan triangle, kept when F <= 32)
+        unsigned long long bits = 0ull;
+        for (int32_t i = 0; i < F && i < 32; ++i) {
+            const int64_t t = __ldg(a.fan_tri + fb + i);
+            const V3 nn{__ldg(a.normal + 3 * t), __ldg(a.normal + 3 * t + 1), __ldg(a.normal + 3 * t + 2)};
+            double bary[3]; bool b1, b2;
+            in_triangle(p, pc, ld3(a.cp, a.m, __ldg(a.fan_o1 + fb + i)), ld3(a.cp, a.m, __ldg(a.fan_o2 + fb + i)), nn, bary, b1, b2);
+            bits |= (unsigned long long)(b1 ? 1 : 0) << (2 * i) | (unsigned long long)(b2 ? 1 : 0) << (2 * i + 1);
         }
+        // First fallback (:407-448): smallest never-flagged key with a usable first-seen value.
+        int32_t best = 0x7fffffff;
+        for (int32_t i = 0; i < F; ++i) {
+            for (int s = 0; s < 2; ++s) {
+                const int32_t k = __ldg((s ? a.fan_o2 : a.fan_o1) + fb + i);
+                if (k >= best) continue;
+                bool bad = false;
+                for (int32_t j = 0; j < F && !bad; ++j) {
+                    const int32_t j1 = __ldg(a.fan_o1 + fb + j), j2 = __ldg(a.fan_o2 + fb + j);
+                    if (j1 != k && j2 != k) continue;
+                    bool b1, b2;
+                    if (F <= 32) { b1 = (bits >> (2 * j)) & 1; b2 = (bits >> (2 * j + 1)) & 1; }
+                    else {
+                        const int64_t t = __ldg(a.fan_tri + fb + j);
+                        const V3 nn{__ldg(a.normal + 3 * t), __ldg(a.normal + 3 * t + 1), __ldg(a.normal + 3 * t + 2)};
+                        double bary[3];
+                        in_triangle(p, pc, ld3(a.cp, a.m, j1), ld3(a.cp, a.m, j2), nn, bary, b1, b2);
+                    }
+                    // the map is keyed by vertex: tri[1] and tri[2] may name the same key (:43-48)
+                    bad = (j1 == k && b1) || (j2 == k && b2);
+                }
+                if (!bad && edge_value_usable(p, pc, ld3(a.cp, a.m, k))) best = k;
+            }
+        }
+        if (best != 0x7fffffff) {                                                         // :422-448
+            warp_count(a.stats + 1);
+            const double w2 = edge_weight(p, pc, ld3(a.cp, a.m, best));
+            ids[0] = c; ids[1] = best;
+            if (a.weighting == GMG_BARYCENTRIC) { w[0] = 1. - w2; w[1] = w2; }
+            else if (a.weighting == GMG_UNIFORM) { w[0] = w[1] = 1. / 2; }
+            else inverse_distance_weights(a.cp, a.m, p, ids, 2, w);
+            emit_row(a, f, ids, w, 2);
+            continue;
+        }
+        // Second fallback (:449-483): the two nearest coarse neighbours of c by (distance, index), plus c.
+        warp_count(a.stats + 2);
+        double d1 = 0, d2 = 0; int32_t i1 = -1, i2 = -1;
+        for (int32_t k = cb; k < ce; ++k) {
+            const int32_t nb = __ldg(a.c_rowidx + k);
+            if (nb == c) continue;                                                        // :462
+            const double d = norm(p - ld3(a.cp, a.m, nb));
+            // std::pair operator< : (d, nb) < (d1, i1)
+            if (i1 < 0 || d < d1 || (!(d1 < d) && nb < i1)) { d2 = d1; i2 = i1; d1 = d; i1 = nb; }
+            else if (i2 < 0 || d < d2 || (!(d2 < d) && nb < i2)) { d2 = d; i2 = nb; }
+        }
+        if (i2 < 0) {  // fewer than two non-self neighbours: out-of-range read in the reference (:472)
+            warp_count(a.stats + 3);
+            ids[0] = c; w[0] = 1.0; emit_row(a, f, ids, w, 1);
+            continue;
+        }
+        ids[0] = c; ids[1] = i1; ids[2] = i2;
+        inverse_distance_weights(a.cp, a.m, p, ids, 3, w);                                // :478
+        emit_row(a, f, ids, w, 3);
     }
-    if (best != 0x7fffffff) {                                                             // :422-448
-        warp_count(a.stats + 1);
-        const double w2 = edge_weight(p, pc, ld3(a.cp, a.m, best));
-        ids[0] = c; ids[1] = best;
-        if (a.weighting == GMG_BARYCENTRIC) { w[0] = 1. - w2; w[1] = w2; }
-        else if (a.weighting == GMG_UNIFORM) { w[0] = w[1] = 1. / 2; }
-        else inverse_distance_weights(a.cp, a.m, p, ids, 2, w);
-        emit_row(a, f, ids, w, 2);
-        return;
-    }
-    // Second fallback (:449-483): the two nearest coarse neighbours of c by (distance, index), plus c.
-    warp_count(a.stats + 2);
-    double d1 = 0, d2 = 0; int32_t i1 = -1, i2 = -1;
-    for (int32_t k = cb; k < ce; ++k) {
-        const int32_t nb = __ldg(a.c_rowidx + k);
-        if (nb == c) continue;                                                            // :462
-        const double d = norm(p - ld3(a.cp, a.m, nb));
-        // std::pair operator< : (d, nb) < (d1, i1)
-        if (i1 < 0 || d < d1 || (!(d1 < d) && nb < i1)) { d2 = d1; i2 = i1; d1 = d; i1 = nb; }
-        else if (i2 < 0 || d < d2 || (!(d2 < d) && nb < i2)) { d2 = d; i2 = nb; }
-    }
-    if (i2 < 0) {  // fewer than two non-self neighbours: out-of-range read in the reference (:472)
-        warp_count(a.stats + 3);
-        ids[0] = c; w[0] = 1.0; emit_row(a, f, ids, w, 1);
-        return;
-    }
-    ids[0] = c; ids[1] = i1; ids[2] = i2;
-    inverse_distance_weights(a.cp, a.m, p, ids, 3, w);                                    // :478
-    emit_row(a, f, ids, w, 3);
 }
 
 __global__ void __launch_bounds__(kBlock) prolong_compact_kernel(int32_t n, const int32_t* __restrict__ rowptr,
@@ -228,7 +257,13 @@ void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, cons
     P.rowptr.zero();
     ProlongArgs a{f_lo, f_hi, n_all, m, fine_pts, coarse_pts, c_colptr, c_rowidx, parents, tr.fan_ptr.p, tr.fan_tri.p, tr.fan_o1.p,
                   tr.fan_o2.p, tr.normal.p, weighting, P.rowptr.p, row_col.p, row_val.p, dstats};
-    if (n > 0) GMG_LAUNCH(c, prolong_rows_kernel, div_up(n, kBlock), kBlock, 0, a);
+    if (n > 0) {
+        DevBuf<int32_t> fallback(c, n);
+        int32_t* fallback_count = st->dev.p + StageStatus::kProlongFallback;      // zeroed with the status block
+        GMG_LAUNCH(c, prolong_rows_kernel, div_up(n, kBlock), kBlock, 0, a, fallback.p, fallback_count);
+        const int grid = std::min(div_up(n, kBlock), 2 * c->sm_count);
+        GMG_LAUNCH(c, prolong_fallback_kernel, grid, kBlock, 0, a, fallback.p, fallback_count);
+    }
     exclusive_scan_i32(c, P.rowptr.p, P.rowptr.p, int64_t(n) + 1, total);
     // rows hold at most three entries: the arrays are sized 3n, so the host need not know nnz yet
     P.colidx.alloc(c, 3 * int64_t(n));

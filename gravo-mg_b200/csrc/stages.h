@@ -30,6 +30,7 @@ void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* 
 // and checks it before returning, which is the old behaviour.
 struct StageStatus {
     enum : int { kZeroEdge = 0, kNoOffer = 1, kParentRounds = 2, kCoarseHardOverflow = 3, kCoarseAsym = 4,
+                 kProlongFallback = 5 /* rows handed to the fallback kernel */,
                  kProlongStats = 8 /* 4 x uint64 */, kProlongNnz = 16 /* int64 */, kWords = 32 };
     DevBuf<int32_t> dev;
     int32_t host[kWords] = {0};
