@@ -346,6 +346,7 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 L.clo = s->clo; L.chi = s->chi;
                 galerkin(c, s->a_n, s->a_colptr, s->a_rowidx, s->a_val, s->Pfull, s->ac_own, s->clo, s->chi, &L.R);
                 tr.mark("transpose + SpGEMM");
+                if (s->level >= 1 && s->n <= kKeepWholeP) L.Pfull = std::move(s->Pfull);
                 s->Pfull = DeviceCsr();
                 // entries per owned outer vector -> the count exchange buffer (the coarse-graph counts are done with)
                 s->ccnt.zero();

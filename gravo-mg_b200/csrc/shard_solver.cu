@@ -8,8 +8,10 @@
 //     residual       r = b - A x on owned rows;
 //     restriction    b_c = R r on the owned coarse rows (R = the owned rows of P^T, kept by the build);
 //     prolongation   x += P e on the owned fine rows;
-//     coarsest level every rank gathers the whole right-hand side and sweeps ALL rows redundantly: finishing a
-//                    small level on every GPU is cheaper than exchanging its halos colour by colour.
+//     small levels   from the first level below a size threshold down (always at least the coarsest) every rank
+//                    gathers the whole right-hand side and runs the rest of the cycle redundantly with the
+//                    single-GPU kernels (the build keeps P whole there): finishing a small level on every GPU
+//                    is cheaper than exchanging its halos colour by colour.
 // Between them the HOST exchanges ghost entries (gravo-mg_b200/sharded.py: packed all-to-all over
 // NCCL / NVLink; a loop-back between virtual ranks in the single-GPU tests). This file exposes what the
 // host needs for that: the byte mask of the entries an operator's owned rows read outside the owned
@@ -29,6 +31,9 @@ struct SLevel {
     std::vector<int32_t> own_lo, own_hi;   // per colour: the owned part of the colour's bucket (positions in col.rows)
     const DeviceCsr* R = nullptr;     // owned rows of P^T towards the next level (local outer index)
     const DeviceCsr* P = nullptr;     // owned rows of P from the next level (local outer index)
+    bool replicated = false;          // this level and every coarser one run whole on every rank
+    const DeviceCsr* Pfull = nullptr; // replicated, not the coarsest: all rows of P from the next level
+    DeviceCsr Rfull;                  // ... and its transpose
     DevBuf<double> x, b, r;
     DevBuf<uint8_t> mask;
 };
@@ -82,11 +87,31 @@ __global__ void __launch_bounds__(kBlock) halo_mask_kernel(int32_t count, const 
     }
 }
 
+// the rest of a V-cycle from a replicated level down: the single-GPU cycle (csrc/solver.cu), on all rows
+void vcycle_all(gmg_ctx* c, gmg_shard_solver* s, size_t l, int pre, int post, int coarse_sweeps) {
+    SLevel& L = *s->levels[l];
+    if (l + 1 == s->levels.size()) {
+        gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, coarse_sweeps, false);
+        return;
+    }
+    SLevel& C = *s->levels[l + 1];
+    gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, pre, false);
+    spmv(c, L.n, L.outer, L.inner, L.val, L.x.p, L.r.p, -1.0, L.b.p);
+    spmv(c, C.n, L.Rfull.rowptr.p, L.Rfull.colidx.p, L.Rfull.val.p, L.r.p, C.b.p, 1.0, nullptr);
+    C.x.zero();
+    vcycle_all(c, s, l + 1, pre, post, coarse_sweeps);
+    spmv(c, L.n, L.Pfull->rowptr.p, L.Pfull->colidx.p, L.Pfull->val.p, C.x.p, L.x.p, 1.0, L.x.p);
+    gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, post, true);
+}
+
 }  // namespace
 
 extern "C" {
 
-int gmg_shard_solver_create(gmg_ctx* c, const gmg_shard* sh, const gmg_input* in, gmg_shard_solver** out) {
+/* replicate_below: levels >= 1 with at most this many vertices (and every coarser one) run whole on every
+ * rank; the coarsest level always does. */
+int gmg_shard_solver_create(gmg_ctx* c, const gmg_shard* sh, const gmg_input* in, int64_t replicate_below,
+                            gmg_shard_solver** out) {
     if (!out) return GMG_ERR_INVALID;
     *out = nullptr;
     return guarded_v(c, [&] {
@@ -121,6 +146,12 @@ int gmg_shard_solver_create(gmg_ctx* c, const gmg_shard* sh, const gmg_input* in
             L->x.alloc(c, n_pad); L->b.alloc(c, n_pad); L->r.alloc(c, n_pad);
             L->x.zero(); L->b.zero(); L->r.zero();
             L->mask.alloc(c, n_pad);
+            if (l == nl) L->replicated = true;
+            else if (l >= 1 && L->n <= replicate_below && sh->done[l]->Pfull.rowptr.p) {
+                L->replicated = true;
+                L->Pfull = &sh->done[l]->Pfull;
+                transpose_csr(c, *L->Pfull, L->Rfull);
+            }
             s->levels.push_back(std::move(L));
         }
         sync(c);
@@ -140,7 +171,7 @@ int gmg_shard_solver_num_levels(const gmg_shard_solver* s) { return s ? int(s->l
 int gmg_shard_solver_level(const gmg_shard_solver* s, int level, int64_t* io) {
     if (!s || !io || level < 0 || level >= int(s->levels.size())) return GMG_ERR_STATE;
     const SLevel& L = *s->levels[size_t(level)];
-    io[0] = L.n; io[1] = L.lo; io[2] = L.hi; io[3] = L.chunk; io[4] = L.col.num_colours;
+    io[0] = L.n; io[1] = L.lo; io[2] = L.hi; io[3] = L.chunk; io[4] = L.col.num_colours; io[5] = L.replicated ? 1 : 0;
     return GMG_OK;
 }
 
@@ -219,6 +250,10 @@ int gmg_shard_solver_op(gmg_ctx* c, gmg_shard_solver* s, int level, int op, int 
             case GMG_SO_GS_ALL:       // `arg` sweeps over ALL rows: a small level every rank solves redundantly
                 GMG_REQUIRE(arg >= 0, GMG_ERR_INVALID, "negative sweep count");
                 gauss_seidel(c, L.col, L.outer, L.inner, L.val, L.b.p, L.x.p, arg, false);
+                break;
+            case GMG_SO_VCYCLE_ALL:   // arg = pre | post << 8 | coarse_sweeps << 16: the rest of the cycle, on all rows
+                GMG_REQUIRE(L.replicated && arg >= 0, GMG_ERR_INVALID, "level is not replicated");
+                vcycle_all(c, s, size_t(level), arg & 0xff, (arg >> 8) & 0xff, arg >> 16);
                 break;
             case GMG_SO_SUMSQ_R: {
                 GMG_REQUIRE(out, GMG_ERR_INVALID, "null output");

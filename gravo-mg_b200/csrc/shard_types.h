@@ -3,6 +3,10 @@
 
 #include "hierarchy_types.h"
 
+// Levels >= 1 with at most this many fine vertices keep the gathered P whole (36 B per row): the row-sharded
+// V-cycle can then run them on every rank without any halo exchange.
+constexpr int64_t kKeepWholeP = 4000000;
+
 struct gmg_shard {
     gmg_ctx* ctx = nullptr;
     int rank = 0, world = 1;
@@ -65,6 +69,8 @@ struct gmg_shard {
         int32_t clo = 0, chi = 0;    // owned coarse vertices
         int32_t chunk = 0, cchunk = 0;   // slice lengths of the fine / coarse splits (owner of vertex j = j / chunk)
         DeviceCsr R;                 // build_galerkin: rows [clo, chi) of P^T (restriction of the owned coarse rows)
+        DeviceCsr Pfull;             // build_galerkin, small levels (see kKeepWholeP): ALL rows of P, for a solver
+                                     // that finishes the small levels redundantly on every rank
         DeviceCsc Ac;                // build_galerkin: A_c, replicated
     };
     std::vector<std::unique_ptr<Done>> done;

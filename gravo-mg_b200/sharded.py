@@ -431,7 +431,7 @@ class ShardedHierarchy:
 # ---- row-sharded smoothing / V-cycle -----------------------------------------------------------------
 (SV_X, SV_B, SV_R, SV_COLOUR, SV_MASK) = range(5)
 (HP_A, HP_R, HP_P) = range(3)
-(SO_GS_COLOUR, SO_RESIDUAL, SO_RESTRICT, SO_PROLONG, SO_ZERO_X, SO_SUMSQ_R, SO_GS_ALL) = range(7)
+(SO_GS_COLOUR, SO_RESIDUAL, SO_RESTRICT, SO_PROLONG, SO_ZERO_X, SO_SUMSQ_R, SO_GS_ALL, SO_VCYCLE_ALL) = range(8)
 
 
 def halo_counts(ghost, chunk, world):
@@ -495,13 +495,15 @@ class ShardedSolver:
     owned rows (gmg_shard_solver_op); ghost entries move between ranks as packed all-to-all exchanges
     (torch.distributed all_to_all_single over NCCL, or the loop-back between virtual ranks)."""
 
-    def __init__(self, sh, inp):
+    def __init__(self, sh, inp, replicate_below=2_000_000):
+        """replicate_below: levels >= 1 with at most this many vertices, and every coarser one, are finished
+        whole on every rank (gather the right-hand side once, no halo exchange below); 0 = only the coarsest."""
         import torch
         self.torch, self.sh, self.ctx, self._inp = torch, sh, sh.ctx, inp
         self.comm, self.world, self.device = sh.comm, sh.world, sh.device
         self.same_stream = sh.same_stream
         lib = self.ctx.lib
-        lib.gmg_shard_solver_create.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+        lib.gmg_shard_solver_create.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
         lib.gmg_shard_solver_destroy.argtypes = [C.c_void_p]
         lib.gmg_shard_solver_destroy.restype = None
         lib.gmg_shard_solver_num_levels.argtypes = [C.c_void_p]
@@ -514,7 +516,7 @@ class ShardedSolver:
         self.h = []
         for s in sh.shards:
             h = C.c_void_p()
-            self.ctx._check(lib.gmg_shard_solver_create(self.ctx.h, s.h, inp.h, C.byref(h)))
+            self.ctx._check(lib.gmg_shard_solver_create(self.ctx.h, s.h, inp.h, int(replicate_below), C.byref(h)))
             self.h.append(h)
         self.num_levels = int(lib.gmg_shard_solver_num_levels(self.h[0]))
         self.exchanges = 0
@@ -525,7 +527,8 @@ class ShardedSolver:
             g = []
             for h in self.h:
                 self.ctx._check(lib.gmg_shard_solver_level(h, C.c_int(l), io))
-                g.append(dict(n=int(io[0]), lo=int(io[1]), hi=int(io[2]), chunk=int(io[3]), colours=int(io[4])))
+                g.append(dict(n=int(io[0]), lo=int(io[1]), hi=int(io[2]), chunk=int(io[3]), colours=int(io[4]),
+                              replicated=bool(io[5])))
             self.geom.append(g)
         self._fence()
         # halo plans: per level the operator's ghosts split by colour, the restriction's and the prolongation's
@@ -655,11 +658,12 @@ class ShardedSolver:
         self._fence()
 
     def _vcycle(self, level, pre, post, coarse_sweeps):
-        if level + 1 == self.num_levels:
-            # the coarsest level is small: every rank gathers the whole right-hand side and solves it redundantly
-            # (same kernel, same rows, same order as the single-GPU cycle) instead of exchanging halos per colour
+        if self.geom[level][0]["replicated"]:
+            # a small level (at least the coarsest): every rank gathers the whole right-hand side and finishes the
+            # cycle redundantly (same kernels, same rows, same order as the single-GPU cycle) instead of exchanging
+            # halos colour by colour
             self._gather_vector(level, SV_B)
-            self._op(level, SO_GS_ALL, coarse_sweeps)
+            self._op(level, SO_VCYCLE_ALL, pre | (post << 8) | (coarse_sweeps << 16))
             return
         self._smooth(level, pre, False)
         self._op(level, SO_RESIDUAL)
@@ -667,7 +671,7 @@ class ShardedSolver:
         self._op(level, SO_RESTRICT)
         self._op(level + 1, SO_ZERO_X)
         self._vcycle(level + 1, pre, post, coarse_sweeps)
-        if level + 2 < self.num_levels:                 # the coarsest level's x is already whole on every rank
+        if not self.geom[level + 1][0]["replicated"]:    # a replicated level's x is already whole on every rank
             self._exchange(self.plan_p[level], level + 1, SV_X)
         self._op(level, SO_PROLONG)
         self._exchange(self.plan_a[level], level, SV_X)

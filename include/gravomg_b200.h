@@ -313,7 +313,8 @@ int gmg_shard_fetch(gmg_ctx* ctx, const gmg_shard* s, int level, int which, void
  * keeps full-length vectors per level (levels = prolongations + 1); only the owned entries [lo, hi) and the
  * ghost entries its rows read are valid. An op acts on the owned rows; between ops the HOST exchanges
  * ghost entries (packed all-to-all over NCCL in gravo-mg_b200/sharded.py), guided by the halo masks.
- *   Coarsest level: all-gather b, GS_ALL (every rank solves it whole; no halo exchange).
+ *   First replicated level (small levels, at least the coarsest): all-gather b, VCYCLE_ALL with
+ *   arg = pre | post << 8 | coarse_sweeps << 16 (every rank finishes the cycle whole; no halo exchange).
  *   V-cycle on level l:  for each colour k { GS_COLOUR(k) ; exchange x over the ghosts of colour k } (pre
  *   sweeps) ; RESIDUAL ; exchange r over pattern R ; RESTRICT ; ZERO_X(l+1) ; recurse ; exchange x(l+1) over
  *   pattern P ; PROLONG ; exchange x over pattern A ; post sweeps in reverse colour order.
@@ -322,12 +323,16 @@ typedef struct gmg_shard_solver gmg_shard_solver;
 enum { GMG_SV_X = 0, GMG_SV_B, GMG_SV_R, GMG_SV_COLOUR, GMG_SV_MASK };
 enum { GMG_HP_A = 0, GMG_HP_R, GMG_HP_P };
 enum { GMG_SO_GS_COLOUR = 0, GMG_SO_RESIDUAL, GMG_SO_RESTRICT, GMG_SO_PROLONG, GMG_SO_ZERO_X, GMG_SO_SUMSQ_R,
-       GMG_SO_GS_ALL };
+       GMG_SO_GS_ALL, GMG_SO_VCYCLE_ALL };
 /* `shard` and `in` must outlive the solver */
-int gmg_shard_solver_create(gmg_ctx* ctx, const gmg_shard* shard, const gmg_input* in, gmg_shard_solver** out);
+/* replicate_below: levels >= 1 with at most this many vertices (the build keeps P whole up to 4 M), and
+ * every coarser one, run whole on every rank: no halo exchange below that level. The coarsest always does. */
+int gmg_shard_solver_create(gmg_ctx* ctx, const gmg_shard* shard, const gmg_input* in, int64_t replicate_below,
+                            gmg_shard_solver** out);
 void gmg_shard_solver_destroy(gmg_shard_solver* s);
 int gmg_shard_solver_num_levels(const gmg_shard_solver* s);
-/* io (>= 8 int64) = {n, lo, hi, slice length of the level's split (owner of vertex j = j / slice), colours} */
+/* io (>= 8 int64) = {n, lo, hi, slice length of the level's split (owner of vertex j = j / slice), colours,
+ * 1 if the level is replicated} */
 int gmg_shard_solver_level(const gmg_shard_solver* s, int level, int64_t* io);
 /* device pointer of a level's vector: X, B, R f64[max(n, slice * world)]; COLOUR int32[n]; MASK uint8[same as X] */
 int gmg_shard_solver_vector(gmg_shard_solver* s, int level, int which, void** ptr);
@@ -339,7 +344,9 @@ int gmg_shard_solver_halo_mask(gmg_ctx* ctx, gmg_shard_solver* s, int level, int
 /* One operator on the owned rows. GS_COLOUR: arg = colour. RESIDUAL: r = b - A x. RESTRICT: b(level+1) = R r.
  * PROLONG: x += P x(level+1). ZERO_X: x = 0 (all entries). SUMSQ_R: *out = sum over owned rows of r^2.
  * GS_ALL: arg sweeps over ALL rows (the coarsest level, after the host has all-gathered b: X, B and R hold
- * slice * world entries, rank r owning slice r, so an in-place all-gather of the owned slices completes them). */
+ * slice * world entries, rank r owning slice r, so an in-place all-gather of the owned slices completes them).
+ * VCYCLE_ALL (replicated levels only): the rest of the V-cycle from this level down on ALL rows, after the host
+ * has all-gathered b; arg = pre | post << 8 | coarse_sweeps << 16. */
 int gmg_shard_solver_op(gmg_ctx* ctx, gmg_shard_solver* s, int level, int op, int arg, double* out);
 
 #ifdef __cplusplus

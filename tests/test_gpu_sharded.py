@@ -83,8 +83,8 @@ def test_sharded_galerkin_equals_single_gpu(ctx, name, scale, world):
     sh.close(); h.close(); inp.close()
 
 
-@pytest.mark.parametrize("world", [2, 5])
-def test_sharded_vcycle_equals_single_gpu(ctx, world):
+@pytest.mark.parametrize("world,replicate_below", [(2, 0), (5, 0), (3, 2_000_000), (4, 5_000)])
+def test_sharded_vcycle_equals_single_gpu(ctx, world, replicate_below):
     """Row-sharded multicolour Gauss-Seidel / V-cycle with halo exchanges of ghost entries (packed all-to-all;
     loop-back here) against the single-GPU V-cycle on the same hierarchy: same colouring, same (colour, row)
     sweep order, so the iterates agree to rounding (A_c's accumulation order is the only difference)."""
@@ -99,8 +99,11 @@ def test_sharded_vcycle_equals_single_gpu(ctx, world):
     x_ref, res_ref = ref.vcycle(b, cycles=3, pre=2, post=2, coarse_sweeps=20)
     sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_PARALLEL,
                           seed=5, build_galerkin=True)
-    sv = ShardedSolver(sh, inp)
+    sv = ShardedSolver(sh, inp, replicate_below=replicate_below)
     assert sv.num_levels == h.num_levels + 1
+    flags = [g[0]["replicated"] for g in sv.geom]
+    assert flags[0] is False and flags[-1] is True and flags == sorted(flags)      # a suffix of the levels
+    assert sum(flags) == (1 if replicate_below == 0 else sum(1 for g in sv.geom[1:] if g[0]["n"] <= replicate_below) or 1)
     x, res = sv.vcycle(b, cycles=3, pre=2, post=2, coarse_sweeps=20)
     assert not np.isnan(x).any()
     assert np.abs(res - res_ref).max() <= 1e-9 * res_ref[0], (res, res_ref)
