@@ -58,3 +58,34 @@ def test_meshgen_is_deterministic_and_symmetric():
     u = meshgen.uniform_pm1(42, np.arange(5, dtype=np.uint64), 1)
     assert np.all((u >= -1) & (u < 1))
     assert np.array_equal(u, meshgen.uniform_pm1(42, np.arange(5, dtype=np.uint64), 1))
+
+
+def test_ctypes_structs_match_the_c_header(tmp_path):
+    """The ctypes mirrors of the C structs must have the header's layout (a stale mirror reads garbage past the
+    end of a smaller struct): compile a C program against include/gravomg_b200.h and compare sizes and offsets."""
+    import ctypes as C
+    import os
+    import subprocess
+    from gravomg_b200 import capi
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "layout.c"
+    src.write_text('''#include <stdio.h>
+#include <stddef.h>
+#include "gravomg_b200.h"
+int main(void) {
+    printf("%zu %zu %zu %zu %zu\\n", sizeof(gmg_hierarchy_options), offsetof(gmg_hierarchy_options, radius_override),
+           offsetof(gmg_hierarchy_options, build_galerkin), offsetof(gmg_hierarchy_options, on_level),
+           offsetof(gmg_hierarchy_options, user));
+    printf("%zu %zu %zu\\n", sizeof(gmg_level_info), offsetof(gmg_level_info, radius), offsetof(gmg_level_info, stage_ms));
+    printf("%zu\\n", sizeof(gmg_prolongation_stats));
+    return 0;
+}
+''')
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c11", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    got = [int(v) for v in out]
+    O, L = capi.HierarchyOptions, capi.LevelInfo
+    want = [C.sizeof(O), O.radius_override.offset, O.build_galerkin.offset, O.on_level.offset, O.user.offset,
+            C.sizeof(L), L.radius.offset, L.stage_ms.offset, C.sizeof(capi.ProlongationStats)]
+    assert got == want, (got, want)
