@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--workload", default=None, help="C1|C2|C3|C4 (single GPU) or T<millions> (torus; sharded when N>1)")
     ap.add_argument("--per-gpu-mverts", type=float, default=12.5, help="default N>1 workload: torus vertices per GPU (millions)")
     ap.add_argument("--scale", type=float, default=1.0)
-    ap.add_argument("--sampler", default=None, choices=["exact", "parallel"],
+    ap.add_argument("--sampler", default=None, choices=["exact", "parallel", "hashed"],
                     help="default: exact on one GPU (the reference's sample set), parallel for the row-sharded build "
                          "(the exact greedy order is a cross-rank dependency chain; SURVEY.md 8(e))")
     ap.add_argument("--galerkin", type=int, default=0, help="1: also A_c = P^T A P on every level (config C3)")
@@ -255,7 +255,7 @@ def run_b200(a, rank, world, local_rank):
     V, A = cfg["V"], cfg["A"]
     levels = LEVELS[a.workload]
     n = V.shape[0]
-    mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
+    mode = {"exact": capi.SAMPLER_EXACT, "parallel": capi.SAMPLER_PARALLEL, "hashed": capi.SAMPLER_HASHED}[a.sampler]
 
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)         # a real stream shared by the library and the timing events
@@ -455,7 +455,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     nu, nv = torus_dims(a.workload)
     n = nu * nv
     levels = 4
-    mode = capi.SAMPLER_EXACT if a.sampler == "exact" else capi.SAMPLER_PARALLEL
+    mode = {"exact": capi.SAMPLER_EXACT, "parallel": capi.SAMPLER_PARALLEL, "hashed": capi.SAMPLER_HASHED}[a.sampler]
     galerkin = bool(a.galerkin or a.vcycle)
     # the whole mesh, resident on every rank (with its system matrix when A_c is asked for)
     inp = Input.torus(ctx, nu, nv, mass_shift=1e-3 if galerkin else None)

@@ -24,7 +24,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgravomg_b200.so")
 
 BARYCENTRIC, UNIFORM, INVDIST = 0, 1, 2
-SAMPLER_EXACT, SAMPLER_PARALLEL = 0, 1
+SAMPLER_EXACT, SAMPLER_PARALLEL, SAMPLER_HASHED = 0, 1, 2
 
 STATUS_NAMES = {0: "GMG_OK", 1: "GMG_ERR_CUDA", 2: "GMG_ERR_INVALID", 3: "GMG_ERR_FALLBACK_RATIO",
                 4: "GMG_ERR_ZERO_LENGTH_EDGE", 5: "GMG_ERR_ASYMMETRIC", 6: "GMG_ERR_STATE", 7: "GMG_ERR_NCCL"}

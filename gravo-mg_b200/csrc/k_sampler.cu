@@ -38,44 +38,74 @@ namespace gmg {
 constexpr int kLanes = 8;    // lanes cooperating on one vertex in the build kernel (mesh columns hold ~7 entries)
 constexpr int kStage = 16;   // later-path targets a lane can stage in shared memory
 
-// Invertible mixing of k-bit integers: xor-seed, then (odd multiply, xorshift by ceil(k/2)) twice and a
-// last odd multiply, all modulo 2^k. Every step is a bijection on k bits; the xorshift is its own
-// inverse because twice the shift is >= k.
+// Precedence order. EXACT: rank(v) = v. Otherwise a vertex is cut into (super-tile, offset) = (v >> tshift,
+// v & (2^tshift - 1)) and the SUPER-TILE number goes through a seeded invertible mixing of kt-bit integers:
+// xor-seed, then (odd multiply, xorshift by ceil(kt/2)) twice and a last odd multiply, all modulo 2^kt; every
+// step is a bijection on kt bits and the xorshift is its own inverse because twice the shift is >= kt.
+//   GMG_SAMPLER_HASHED    tshift = 0: every vertex hashed, dependency depth O(log n)
+//   GMG_SAMPLER_PARALLEL  tshift = ceil(log2(n / 4)): the reference's index-order sweep restarted in 2-4
+//                         super-tiles taken in hashed order (why: DESIGN.md section 4, "sampler orders")
 struct Order {
     uint32_t mask, shift, seed;
     uint32_t c1, c2, c3, i1, i2, i3;   // odd multipliers and their inverses modulo 2^32
+    uint32_t tshift;                   // log2 of the super-tile size
+    uint32_t kbits;                    // bits of a rank (kt + tshift); ranks live in [0, 2^kbits)
 };
 __host__ __device__ __forceinline__ uint32_t order_rank(const Order& o, uint32_t v) {
-    uint32_t x = (v ^ o.seed) & o.mask;
+    uint32_t x = ((v >> o.tshift) ^ o.seed) & o.mask;
     x = (x * o.c1) & o.mask; x ^= x >> o.shift;
     x = (x * o.c2) & o.mask; x ^= x >> o.shift;
-    return (x * o.c3) & o.mask;
+    x = (x * o.c3) & o.mask;
+    return (x << o.tshift) | (v & ((1u << o.tshift) - 1u));
 }
 __host__ __device__ __forceinline__ uint32_t order_unrank(const Order& o, uint32_t r) {
-    uint32_t x = (r * o.i3) & o.mask;
+    uint32_t x = ((r >> o.tshift) * o.i3) & o.mask;
     x ^= x >> o.shift; x = (x * o.i2) & o.mask;
     x ^= x >> o.shift; x = (x * o.i1) & o.mask;
-    return (x ^ o.seed) & o.mask;
+    x = (x ^ o.seed) & o.mask;
+    return (x << o.tshift) | (r & ((1u << o.tshift) - 1u));
 }
 static uint32_t inverse_odd(uint32_t c) {       // Newton iteration for c^-1 modulo 2^32
     uint32_t x = c;
     for (int i = 0; i < 5; ++i) x *= 2u - c * x;
     return x;
 }
-static Order make_order(int32_t n, uint64_t seed) {
+static int ceil_log2(int64_t v) { int k = 0; while ((int64_t(1) << k) < v) ++k; return k; }
+static Order make_order(int32_t n, uint64_t seed, int mode) {
     Order o{};
-    int k = 1;
-    while ((int64_t(1) << k) < int64_t(n)) ++k;
-    o.mask = k >= 32 ? 0xFFFFFFFFu : ((1u << k) - 1u);
-    o.shift = uint32_t((k + 1) / 2);
+    if (mode == GMG_SAMPLER_EXACT) {            // identity; only kbits is read
+        o.kbits = uint32_t(ceil_log2(n > 1 ? n : 2));
+        return o;
+    }
+    o.tshift = mode == GMG_SAMPLER_PARALLEL ? uint32_t(ceil_log2((int64_t(n) + 3) / 4)) : 0u;
+    const int64_t tiles = (int64_t(n) + (int64_t(1) << o.tshift) - 1) >> o.tshift;
+    const int kt = ceil_log2(tiles);
+    o.mask = kt >= 32 ? 0xFFFFFFFFu : ((1u << kt) - 1u);
+    o.shift = uint32_t((kt + 1) / 2);
+    if (o.shift == 0) o.shift = 1;
     const uint64_t z = (seed + 0x9E3779B97F4A7C15ull) * 0xBF58476D1CE4E5B9ull;
     o.seed = uint32_t(z >> 32) & o.mask;
     o.c1 = 0x9E3779B1u; o.c2 = 0x85EBCA6Bu | 1u; o.c3 = 0xC2B2AE35u | 1u;
     o.i1 = inverse_odd(o.c1); o.i2 = inverse_odd(o.c2); o.i3 = inverse_odd(o.c3);
+    o.kbits = uint32_t(kt) + o.tshift;
+    if (o.kbits == 0) o.kbits = 1;
     return o;
 }
 
-enum : int32_t { kUndecided = 0, kIn = 1, kOut = 2 };
+// ---- the flow's state, all indexed by RANK (so that a tile of consecutive tickets is contiguous) -----------
+// wext[r]   preceding covering paths into r from vertices of OTHER flow tiles; bit 31 = knocked OUT by a selected
+//           vertex of another tile. Only ever changed by fire-and-forget reductions (atomicSub / atomicOr).
+// cint[r]   preceding covering paths from vertices of r's OWN flow tile (decremented in shared memory)
+// lst       later coverees of every vertex as rank | (multiplicity - 1) << kbits: duplicates are merged (a mesh
+//           vertex has ~24 later paths but ~8 distinct later coverees), same-tile targets first
+// lcnt[r]   entries of the list | same-tile entries << 16 (0xFFFF: list not partitioned nor merged, see the build kernel)
+constexpr int kTileLog = 12;
+constexpr int kTile = 1 << kTileLog;          // ranks per flow tile
+constexpr int kFlowThreads = 1024;
+constexpr int kOwn = kTile / kFlowThreads;    // ranks per thread
+constexpr int kListCap = 49152;               // same-tile list entries (uint16) a block can stage
+constexpr uint32_t kOutFlag = 0x80000000u;
+constexpr uint32_t kUnpartitioned = 0xFFFFu;
 
 struct SamplerArgs {
     int32_t n;
@@ -84,18 +114,23 @@ struct SamplerArgs {
     const double* len;
     double radius;
     Order order;
-    int32_t* state;
-    int32_t* cnt;
-    long long* lptr;             // start of the later-coveree list of every vertex
-    int32_t* lcnt;               // its length (paths, duplicates kept)
-    int32_t* lst;                // the lists
+    uint32_t* wext;
+    uint32_t* cint;
+    long long* lptr;             // start of the later-coveree list of every rank
+    uint32_t* lcnt;
+    uint32_t* lst;               // the lists
     unsigned long long* cursor;  // bump allocator over lst
-    unsigned int* ticket;        // next ticket of the flow kernel
-    unsigned int tickets;        // n (exact) or 2^k (parallel)
+    unsigned int* ticket;        // next tile of the flow kernel
+    unsigned int tiles;          // flow tiles: ceil(ranks / kTile)
+    uint8_t* res;                // [ranks] 1 = selected
+    int32_t* flags;              // [0] a vertex has more than 65535 list entries
 };
 
 template <int MODE> __device__ __forceinline__ uint32_t rank_of(const SamplerArgs& a, int32_t v) {
     return MODE == GMG_SAMPLER_EXACT ? uint32_t(v) : order_rank(a.order, uint32_t(v));
+}
+template <int MODE> __device__ __forceinline__ uint32_t vertex_of(const SamplerArgs& a, uint32_t r) {
+    return MODE == GMG_SAMPLER_EXACT ? r : order_unrank(a.order, r);
 }
 
 // Walk every covering path out of `self` and call f(target) for each path whose target differs
@@ -129,37 +164,77 @@ __device__ __forceinline__ void for_each_covered(const SamplerArgs& a, int32_t s
     }
 }
 
+// One walk of every two-hop neighbourhood (8 lanes per vertex): counts the preceding covering paths (same flow
+// tile / other tiles) and writes the LATER coverees as a merged list. The lanes stage their later targets in
+// shared memory; the group then merges duplicates (an entry keeps a multiplicity, capped by the bits a rank
+// leaves free in 32) and writes same-tile targets first. A vertex with a lane that outgrows its stage (> 16
+// later paths on one first-hop edge: rare) walks again and writes its paths raw, flagged kUnpartitioned.
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     static_assert(kBlock / kLanes == 32, "one warp scans the group totals");
     __shared__ int32_t s_group[kBlock / kLanes];
     __shared__ unsigned long long s_base;
-    __shared__ int32_t s_stage[kBlock][kStage + 1];   // +1: conflict-free lane-private rows
+    __shared__ uint32_t s_stage[kBlock][kStage + 1];   // +1: conflict-free lane-private rows
+    __shared__ uint8_t s_mult[kBlock][kStage];         // 0: merged into an earlier entry, else its multiplicity
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t i = int32_t(gid / kLanes);
     const int sub = threadIdx.x % kLanes;
     const int g = threadIdx.x / kLanes;
     const bool active = i < a.n;
-    int32_t prev = 0, later = 0;
+    int32_t prev_in = 0, prev_ext = 0, later = 0;
+    uint32_t ri = 0;
     if (active) {
-        const uint32_t ri = rank_of<MODE>(a, i);
-        int32_t* stage = s_stage[threadIdx.x];
+        ri = rank_of<MODE>(a, i);
+        uint32_t* stage = s_stage[threadIdx.x];
         for_each_covered(a, i, sub, [&](int32_t t) {
-            if (rank_of<MODE>(a, t) < ri) ++prev;
-            else { if (later < kStage) stage[later] = t; ++later; }
+            const uint32_t rt = rank_of<MODE>(a, t);
+            if (rt < ri) { if ((rt >> kTileLog) == (ri >> kTileLog)) ++prev_in; else ++prev_ext; }
+            else { if (later < kStage) stage[later] = rt; ++later; }
         });
     }
-    const bool overflow = __any_sync(0xffffffffu, later > kStage);   // per warp; re-walk is rare
-    const unsigned group_over = __ballot_sync(0xffffffffu, later > kStage) & (0xFFu << ((threadIdx.x & 31) & ~(kLanes - 1)));
+    const int lane = threadIdx.x & 31;
+    const unsigned gmask = 0xFFu << (lane & ~(kLanes - 1));
+    const bool group_over = (__ballot_sync(0xffffffffu, later > kStage) & gmask) != 0;
 #pragma unroll
-    for (int d = kLanes / 2; d > 0; d >>= 1) prev += __shfl_xor_sync(0xffffffffu, prev, d, kLanes);
-    int32_t incl = later;
+    for (int d = kLanes / 2; d > 0; d >>= 1) {
+        prev_in += __shfl_xor_sync(0xffffffffu, prev_in, d, kLanes);
+        prev_ext += __shfl_xor_sync(0xffffffffu, prev_ext, d, kLanes);
+    }
+    // merge duplicates within the group: entry (lane, e) survives when the number of equal entries before it
+    // in (lane, position) order is a multiple of the cap, and then stands for up to `cap` of them
+    const uint32_t cap = 1u << (32u - a.order.kbits < 4u ? 32u - a.order.kbits : 4u);
+    int32_t kept = 0, kept_in = 0;
+    int32_t cnts[kLanes];
+#pragma unroll
+    for (int l2 = 0; l2 < kLanes; ++l2) cnts[l2] = __shfl_sync(0xffffffffu, later, (lane & ~(kLanes - 1)) + l2);
+    __syncwarp();
+    if (!group_over) {
+        const uint32_t* stage = s_stage[threadIdx.x];
+        for (int32_t e = 0; e < later; ++e) {
+            const uint32_t x = stage[e];
+            uint32_t ordinal = 0, total = 0;
+#pragma unroll
+            for (int l2 = 0; l2 < kLanes; ++l2) {
+                const uint32_t* row = s_stage[(threadIdx.x & ~(kLanes - 1)) + l2];
+                for (int32_t p = 0; p < cnts[l2]; ++p)
+                    if (row[p] == x) { ++total; if (l2 < sub || (l2 == sub && p < e)) ++ordinal; }
+            }
+            const bool keep = (ordinal & (cap - 1u)) == 0u;
+            const uint32_t mult = keep ? (total - ordinal < cap ? total - ordinal : cap) : 0u;
+            s_mult[threadIdx.x][e] = uint8_t(mult);
+            if (keep) { ++kept; if ((x >> kTileLog) == (ri >> kTileLog)) ++kept_in; }
+        }
+    }
+    const int32_t own = group_over ? later : kept;
+    int32_t incl = own, incl_in = kept_in;
 #pragma unroll
     for (int d = 1; d < kLanes; d <<= 1) {
         const int32_t t = __shfl_up_sync(0xffffffffu, incl, d, kLanes);
-        if (sub >= d) incl += t;
+        const int32_t t2 = __shfl_up_sync(0xffffffffu, incl_in, d, kLanes);
+        if (sub >= d) { incl += t; incl_in += t2; }
     }
     const int32_t group_total = __shfl_sync(0xffffffffu, incl, kLanes - 1, kLanes);
+    const int32_t group_in = __shfl_sync(0xffffffffu, incl_in, kLanes - 1, kLanes);
     if (sub == 0) s_group[g] = group_total;
     __syncthreads();
     if (threadIdx.x < 32) {
@@ -176,86 +251,205 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     __syncthreads();
     if (!active) return;
     const long long start = (long long)s_base + s_group[g];
-    int32_t* dst = a.lst + start + (incl - later);
-    if (!(overflow && group_over)) {
-        const int32_t* stage = s_stage[threadIdx.x];
-        for (int32_t w = 0; w < later; ++w) dst[w] = stage[w];
+    if (!group_over) {
+        // same-tile targets first: [start, start + group_in), the others behind them
+        uint32_t* dst_in = a.lst + start + (incl_in - kept_in);
+        uint32_t* dst_ext = a.lst + start + group_in + ((incl - kept) - (incl_in - kept_in));
+        const uint32_t* stage = s_stage[threadIdx.x];
+        for (int32_t e = 0; e < later; ++e) {
+            const uint32_t mult = s_mult[threadIdx.x][e];
+            if (!mult) continue;
+            const uint32_t x = stage[e];
+            const uint32_t packed = x | ((mult - 1u) << a.order.kbits);
+            if ((x >> kTileLog) == (ri >> kTileLog)) *dst_in++ = packed; else *dst_ext++ = packed;
+        }
     } else {                                          // some lane of this vertex outgrew its stage: walk again
-        const uint32_t ri = rank_of<MODE>(a, i);
-        int32_t w = 0;
-        for_each_covered(a, i, sub, [&](int32_t t) { if (!(rank_of<MODE>(a, t) < ri)) dst[w++] = t; });
+        uint32_t* dst = a.lst + start + (incl - own);
+        for_each_covered(a, i, sub, [&](int32_t t) {
+            const uint32_t rt = rank_of<MODE>(a, t);
+            if (!(rt < ri)) *dst++ = rt;
+        });
     }
     if (sub == 0) {
-        a.lptr[i] = start;
-        a.lcnt[i] = group_total;
-        a.cnt[i] = prev;
-        a.state[i] = prev == 0 ? kIn : kUndecided;
+        if (group_total > 0xFFFF || group_in >= int32_t(kUnpartitioned)) a.flags[0] = 1;
+        a.lptr[ri] = start;
+        a.lcnt[ri] = uint32_t(group_total) | ((group_over ? kUnpartitioned : uint32_t(group_in)) << 16);
+        a.cint[ri] = uint32_t(prev_in);
+        a.wext[ri] = uint32_t(prev_ext);
     }
 }
 
+// The flow: a vertex is IN once every preceding coverer is OUT (both path counters at 0), OUT once a preceding
+// coverer is IN. A block takes flow TILES (kTile consecutive ranks) by ticket, so every tile that precedes a
+// running tile is running or done and the waits below always end. Inside a tile the decisions travel through
+// SHARED memory: the tile's same-tile lists are staged there once (they are static), the same-tile counters
+// live there, and a round -- every thread looks at its undecided ranks, a newly decided rank applies its
+// same-tile list -- costs two barriers instead of a round trip through L2. That is what the index order of a
+// coherent numbering needs: on a row-major 10000 x 1000 grid a tile is four rows, its preceding coverers sit in
+// the tile before it, and the dependency chain (24,000 steps at level 0) is walked at shared-memory speed.
+// What crosses tiles goes through the global words: a selected rank ORs the OUT bit into its later coverees, a
+// rejected one subtracts its multiplicity, both without a return value; the owner of a rank polls one word.
+// With a hashed order nearly every target is in another tile and the kernel is a coalesced poll / push loop.
 template <int MODE>
-__global__ void __launch_bounds__(kBlock) sampler_flow_kernel(SamplerArgs a) {
-    const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerArgs a) {
+    extern __shared__ unsigned char smem_raw[];
+    int32_t* s_rem = reinterpret_cast<int32_t*>(smem_raw);                       // kTile same-tile path counters
+    uint16_t* s_list = reinterpret_cast<uint16_t*>(s_rem + kTile);               // kListCap staged entries
+    uint8_t* s_hit = reinterpret_cast<uint8_t*>(s_list + kListCap);              // kTile: knocked OUT inside the tile
+    __shared__ int32_t s_warp[kFlowThreads / 32];
+    __shared__ unsigned int s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
+    const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
     for (;;) {
-        unsigned int base = 0;
-        if (lane == 0) base = atomicAdd(a.ticket, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= a.tickets) break;
-        // The warp polls its 32 state words TOGETHER (one coalesced request per poll in index order):
-        // with per-lane polling, 300k waiting lanes saturate the L2 request rate on deep dependency chains
-        // and slow the very atomics they are waiting for.
-        const unsigned int r = base + lane;
-        uint32_t v = 0;
-        bool pending = r < a.tickets;
-        if (pending) { v = MODE == GMG_SAMPLER_EXACT ? r : order_unrank(a.order, r); pending = v < uint32_t(a.n); }
-        long long p = 0;
-        int32_t c = 0;
-        if (pending) { p = a.lptr[v]; c = a.lcnt[v]; }
+        __syncthreads();                                   // everybody is done with the previous tile's shared state
+        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+        __syncthreads();
+        const unsigned int tile = s_tile;
+        if (tile >= a.tiles) break;
+        const uint32_t t0 = tile << kTileLog;
+        // ---- static data of the tile's ranks; rank i of the tile belongs to thread i % kFlowThreads
+        long long ptr[kOwn];
+        uint32_t tot[kOwn], nin[kOwn], soff[kOwn];
+        uint8_t st[kOwn];              // 0 undecided, 1 IN, 2 OUT; | 4 same-tile list applied; | 8 other-tile list applied
+        int32_t mine = 0;              // same-tile list entries this thread wants to stage
+#pragma unroll
+        for (int q = 0; q < kOwn; ++q) {
+            const int i = tid + q * kFlowThreads;
+            const uint64_t r = uint64_t(t0) + uint64_t(i);
+            const bool valid = r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n);
+            ptr[q] = 0; tot[q] = 0; nin[q] = 0; st[q] = 2 | 4 | 8;
+            int32_t rem = 0;
+            if (valid) {
+                const uint32_t lc = a.lcnt[r];
+                ptr[q] = a.lptr[r]; tot[q] = lc & 0xFFFFu; nin[q] = lc >> 16; st[q] = 0;
+                rem = int32_t(a.cint[r]);
+                if (nin[q] != kUnpartitioned) mine += int32_t(nin[q]);
+            }
+            s_rem[i] = rem;
+            s_hit[i] = 0;
+        }
+        // shared-memory segments for the same-tile parts of the lists: block-wide exclusive scan over the threads
+        {
+            int32_t s = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int32_t t = __shfl_up_sync(0xffffffffu, s, d);
+                if (lane >= d) s += t;
+            }
+            if (lane == 31) s_warp[warp] = s;
+            __syncthreads();
+            if (warp == 0) {
+                const int32_t v = s_warp[lane];
+                int32_t w = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int32_t t = __shfl_up_sync(0xffffffffu, w, d);
+                    if (lane >= d) w += t;
+                }
+                s_warp[lane] = w - v;
+            }
+            __syncthreads();
+            int32_t off = s_warp[warp] + (s - mine);
+#pragma unroll
+            for (int q = 0; q < kOwn; ++q) {
+                const int32_t want = ((st[q] & 3) == 0 && nin[q] != kUnpartitioned) ? int32_t(nin[q]) : 0;
+                soff[q] = (want > 0 && off + want <= kListCap) ? uint32_t(off) : 0xFFFFFFFFu;
+                off += want;
+            }
+        }
+        // ---- stage the same-tile lists as uint16: offset in the tile | (multiplicity - 1) << 12
+#pragma unroll
+        for (int q = 0; q < kOwn; ++q) {
+            if (soff[q] == 0xFFFFFFFFu) continue;
+            for (uint32_t e = 0; e < nin[q]; ++e) {
+                const uint32_t x = a.lst[ptr[q] + e];
+                s_list[soff[q] + e] = uint16_t(((x & rmask) - t0) | ((x >> a.order.kbits) << kTileLog));
+            }
+        }
+        __syncthreads();
+        // ---- the flow
         unsigned ns = 0;
-        while (__any_sync(0xffffffffu, pending)) {
-            const int32_t st = pending ? *(volatile int32_t*)(a.state + v) : kUndecided;
-            if (pending && st != kUndecided) {
-                pending = false;
-                if (st == kIn) {
-                    // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); later
-                    // coverees of an IN vertex are undecided or already OUT, never IN
-                    for (int32_t k = 0; k < c; k += 4) {
-                        int32_t t[4];
+        for (;;) {
+            uint32_t ext[kOwn];
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) t[u] = k + u < c ? a.lst[p + k + u] : -1;
+            for (int q = 0; q < kOwn; ++q)
+                ext[q] = (st[q] & 3) == 0 ? *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads) : 0u;
+            for (;;) {                                          // rounds inside the tile, shared memory only
+                bool changed = false;
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) if (t[u] >= 0) *(volatile int32_t*)(a.state + t[u]) = kOut;
+                for (int q = 0; q < kOwn; ++q) {
+                    const int i = tid + q * kFlowThreads;
+                    if ((st[q] & 3) == 0) {
+                        if ((ext[q] & kOutFlag) || *(volatile uint8_t*)(s_hit + i)) { st[q] |= 2; changed = true; }
+                        else if (ext[q] == 0u && *(volatile int32_t*)(s_rem + i) == 0) { st[q] |= 1; changed = true; }
                     }
-                } else {
-                    for (int32_t k = 0; k < c; k += 4) {
-                        int32_t t[4], old[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) t[u] = k + u < c ? a.lst[p + k + u] : -1;
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) old[u] = t[u] >= 0 ? atomicSub(a.cnt + t[u], 1) : 0;
-                        // every preceding coverer of t is OUT, so nobody can mark t OUT: t is selected (:25-28)
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) if (old[u] == 1) *(volatile int32_t*)(a.state + t[u]) = kIn;
+                    if ((st[q] & 3) != 0 && !(st[q] & 4)) {
+                        st[q] |= 4;
+                        const bool in = (st[q] & 3) == 1;
+                        if (soff[q] != 0xFFFFFFFFu) {
+                            for (uint32_t e = 0; e < nin[q]; ++e) {
+                                const uint32_t y = s_list[soff[q] + e];
+                                const uint32_t t = y & (kTile - 1);
+                                // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a
+                                // rejected one releases its later coverees
+                                if (in) *(volatile uint8_t*)(s_hit + t) = 1;
+                                else atomicSub(s_rem + t, int32_t(y >> kTileLog) + 1);
+                            }
+                        } else {
+                            // list not staged (no room, or not partitioned): same-tile targets straight from the list
+                            const uint32_t cnt = nin[q] == kUnpartitioned ? tot[q] : nin[q];
+                            for (uint32_t e = 0; e < cnt; ++e) {
+                                const uint32_t x = a.lst[ptr[q] + e];
+                                const uint32_t rt = x & rmask;
+                                if ((rt >> kTileLog) != tile) continue;
+                                if (in) *(volatile uint8_t*)(s_hit + (rt - t0)) = 1;
+                                else atomicSub(s_rem + (rt - t0), int32_t(x >> a.order.kbits) + 1);
+                            }
+                        }
                     }
                 }
-                ns = 0;
-            } else if (ns) {
-                __nanosleep(ns);
+                if (!__syncthreads_or(changed)) break;
             }
-            ns = ns == 0 ? 32 : (ns < 512 ? ns << 1 : ns);
+            // ---- what leaves the tile, and the result
+            bool progress = false, all = true;
+#pragma unroll
+            for (int q = 0; q < kOwn; ++q) {
+                if ((st[q] & 3) == 0) { all = false; continue; }
+                if (st[q] & 8) continue;
+                st[q] |= 8;
+                progress = true;
+                const bool in = (st[q] & 3) == 1;
+                const bool raw = nin[q] == kUnpartitioned;
+                for (uint32_t e = raw ? 0u : nin[q]; e < tot[q]; ++e) {
+                    const uint32_t x = a.lst[ptr[q] + e];
+                    const uint32_t rt = x & rmask;
+                    if (raw && (rt >> kTileLog) == tile) continue;
+                    if (in) atomicOr(a.wext + rt, kOutFlag);
+                    else atomicSub(a.wext + rt, (x >> a.order.kbits) + 1u);
+                }
+                a.res[t0 + tid + q * kFlowThreads] = in ? 1 : 0;
+            }
+            if (__syncthreads_and(all)) break;
+            if (__syncthreads_or(progress)) ns = 0;
+            else { ns = ns == 0 ? 64 : (ns < 1024 ? ns << 1 : ns); __nanosleep(ns); }
         }
     }
 }
 
-__global__ void __launch_bounds__(kBlock) flag_in_kernel(int32_t n, const int32_t* __restrict__ state,
-                                                         int32_t* __restrict__ flag) {
+__global__ void __launch_bounds__(kBlock) sampler_init_kernel(uint64_t ranks, uint8_t* __restrict__ res) {
     const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (i < n) flag[i] = state[i] == kIn ? 1 : 0;
+    if (uint64_t(i) < ranks) res[i] = 0;
 }
-__global__ void __launch_bounds__(kBlock) compact_kernel(int32_t n, const int32_t* __restrict__ state,
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) flag_in_kernel(SamplerArgs a, int32_t* __restrict__ flag) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < a.n) flag[i] = a.res[rank_of<MODE>(a, int32_t(i))] ? 1 : 0;
+}
+__global__ void __launch_bounds__(kBlock) compact_kernel(int32_t n, const int32_t* __restrict__ flag,
                                                          const int32_t* __restrict__ pos, int32_t* __restrict__ out) {
     const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (i < n && state[i] == kIn) out[pos[i]] = int32_t(i);
+    if (i < n && flag[i]) out[pos[i]] = int32_t(i);
 }
 
 // sum over columns of deg^2: with nnz it bounds the number of covering paths
@@ -273,15 +467,18 @@ void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned lo
     if (n > 0) GMG_LAUNCH(c, degree_square_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, d_out);
 }
 
-template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a) {
+constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint16_t) * kListCap + kTile;
+
+template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, int32_t* flag) {
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
+    GMG_CUDA(cudaFuncSetAttribute(sampler_flow_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFlowSmem)));
     int per_sm = 0;
-    GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_flow_kernel<MODE>, kBlock, 0));
+    GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_flow_kernel<MODE>, kFlowThreads, kFlowSmem));
     GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "sampler flow kernel does not fit on an SM");
     int grid = per_sm * c->sm_count;
-    const int needed = div_up(int64_t(a.tickets), kBlock);
-    if (grid > needed) grid = needed;
-    GMG_LAUNCH(c, sampler_flow_kernel<MODE>, grid < 1 ? 1 : grid, kBlock, 0, a);
+    if (grid > int(a.tiles)) grid = int(a.tiles);
+    GMG_LAUNCH(c, sampler_flow_kernel<MODE>, grid < 1 ? 1 : grid, kFlowThreads, kFlowSmem, a);
+    GMG_LAUNCH(c, flag_in_kernel<MODE>, div_up(a.n, kBlock), kBlock, 0, a, flag);
 }
 
 int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, const double* len,
@@ -289,9 +486,10 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
                     int64_t path_bound) {
     if (stats) stats->rounds = 0;
     if (n == 0) { selection.alloc(c, 0); return 0; }
-    GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL, GMG_ERR_INVALID, "unknown sampler mode");
+    GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL || mode == GMG_SAMPLER_HASHED, GMG_ERR_INVALID,
+                "unknown sampler mode");
     // bound on the later-path lists: every path has a mirror image, exactly one of the two is "later"
-    DevBuf<unsigned long long> cursor(c, 3);          // [0] list cursor, [1] sum deg^2, [2] ticket counter
+    DevBuf<unsigned long long> cursor(c, 4);          // [0] list cursor, [1] sum deg^2, [2] tile ticket, [3] flags
     cursor.zero();
     if (path_bound < 0) {
         degree_square_sum(c, n, colptr, cursor.p + 1);
@@ -303,25 +501,35 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
         path_bound = int64_t(hsq[1]) + nnz;
     }
     const int64_t list_cap = path_bound / 2 + 1;
-    DevBuf<int32_t> state(c, n), cnt(c, n), lcnt(c, n), lst(c, list_cap);
-    DevBuf<long long> lptr(c, n);
-    const Order order = make_order(n, seed);
-    const unsigned int tickets = mode == GMG_SAMPLER_EXACT ? unsigned(n) : (order.mask == 0xFFFFFFFFu ? 0xFFFFFFFFu : order.mask + 1u);
-    SamplerArgs a{n, colptr, rowidx, len, radius, order, state.p, cnt.p, lptr.p, lcnt.p, lst.p, cursor.p,
-                  reinterpret_cast<unsigned int*>(cursor.p + 2), tickets};
-    if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a);
-    else run_sampler<GMG_SAMPLER_PARALLEL>(c, a);
-    // ascending compaction of the IN flags (cnt is reused as the flag/offset array)
+    const Order order = make_order(n, seed, mode);
+    const uint64_t ranks = mode == GMG_SAMPLER_EXACT ? uint64_t(n) : (uint64_t(1) << order.kbits);
+    GMG_REQUIRE(ranks <= (uint64_t(1) << 31), GMG_ERR_INVALID, "fastDiscSample: too many vertices for 32-bit ranks");
+    DevBuf<uint32_t> wext(c, int64_t(ranks)), cint(c, int64_t(ranks)), lcnt(c, int64_t(ranks)), lst(c, list_cap);
+    DevBuf<long long> lptr(c, int64_t(ranks));
+    DevBuf<uint8_t> res(c, int64_t(ranks));
+    DevBuf<int32_t> flag(c, n);
+    GMG_LAUNCH(c, sampler_init_kernel, div_up(int64_t(ranks), kBlock), kBlock, 0, ranks, res.p);
+    SamplerArgs a{n, colptr, rowidx, len, radius, order, wext.p, cint.p, lptr.p, lcnt.p, lst.p, cursor.p,
+                  reinterpret_cast<unsigned int*>(cursor.p + 2), unsigned((ranks + kTile - 1) >> kTileLog), res.p,
+                  reinterpret_cast<int32_t*>(cursor.p + 3)};
+    if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, flag.p);
+    else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, flag.p);
+    // ascending compaction of the IN flags
     DevBuf<int64_t> total(c, 1);
-    GMG_LAUNCH(c, flag_in_kernel, div_up(n, kBlock), kBlock, 0, n, state.p, cnt.p);
-    exclusive_scan_i32(c, cnt.p, cnt.p, n, total.p);
+    DevBuf<int32_t> pos(c, n);
+    exclusive_scan_i32(c, flag.p, pos.p, n, total.p);
     int64_t m = 0;
+    unsigned long long hflags = 0;
     total.download(&m, 1);
+    GMG_CUDA(cudaMemcpyAsync(&hflags, cursor.p + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     sync(c);
+    GMG_REQUIRE((hflags & 0xFFFFFFFFull) == 0, GMG_ERR_INVALID, "fastDiscSample: a vertex covers more than 65535 later vertices");
     selection.alloc(c, m);
-    GMG_LAUNCH(c, compact_kernel, div_up(n, kBlock), kBlock, 0, n, state.p, cnt.p, selection.p);
+    GMG_LAUNCH(c, compact_kernel, div_up(n, kBlock), kBlock, 0, n, flag.p, pos.p, selection.p);
     return int32_t(m);
 }
+
+enum : int32_t { kUndecided = 0, kIn = 1, kOut = 2 };   // the row-sharded variant's replicated state bytes
 
 // ---------------------------------------------------------------------------------------------
 // Row-sharded variant (one rank owns the vertices [lo, hi); the state array is replicated and
@@ -387,9 +595,9 @@ __global__ void __launch_bounds__(kBlock) shard_build_kernel(SamplerArgs a, int3
     __syncthreads();
     if (!active) return;
     const long long start = (long long)s_base + s_group[g];
-    int32_t* dst = a.lst + start + (incl - prev);
+    uint32_t* dst = a.lst + start + (incl - prev);
     int32_t w = 0;
-    for_each_covered(a, i, sub, [&](int32_t t) { if (rank_of<MODE>(a, t) < ri) dst[w++] = t; });
+    for_each_covered(a, i, sub, [&](int32_t t) { if (rank_of<MODE>(a, t) < ri) dst[w++] = uint32_t(t); });
     if (sub == 0) {
         a.lptr[i - lo] = start;
         a.lcnt[i - lo] = group_total;
@@ -451,22 +659,26 @@ __global__ void __launch_bounds__(kBlock) compact8_kernel(int32_t n, const uint8
 
 void shard_sampler_build(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const int32_t* colptr, const int32_t* rowidx,
                          const double* len, double radius, int mode, uint64_t seed, uint8_t* state8, ShardSampler& out) {
-    GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL, GMG_ERR_INVALID, "unknown sampler mode");
+    GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL || mode == GMG_SAMPLER_HASHED, GMG_ERR_INVALID,
+                "unknown sampler mode");
+    // the pull rounds need a shallow dependency depth: the row-sharded build hashes every vertex in both
+    // non-exact modes (the super-tile sweeps of GMG_SAMPLER_PARALLEL are as deep as the index order)
+    if (mode == GMG_SAMPLER_PARALLEL) mode = GMG_SAMPLER_HASHED;
     out.lo = lo; out.hi = hi;
     const int32_t own = hi - lo;
     out.lptr.alloc(c, own); out.lcnt.alloc(c, own);
     if (own <= 0) { out.lst.alloc(c, 0); return; }
     DevBuf<unsigned long long> cursor(c, 2);
     cursor.zero();
-    SamplerArgs a{n, colptr, rowidx, len, radius, make_order(n, seed), nullptr, nullptr, out.lptr.p, out.lcnt.p, nullptr,
-                  cursor.p, nullptr, 0};
+    SamplerArgs a{n, colptr, rowidx, len, radius, make_order(n, seed, mode), nullptr, nullptr, out.lptr.p,
+                  reinterpret_cast<uint32_t*>(out.lcnt.p), nullptr, cursor.p, nullptr, 0, nullptr, nullptr};
     if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_EXACT>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     else GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_PARALLEL>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     unsigned long long hb[2];
     cursor.download(hb, 2);
     sync(c);
     out.lst.alloc(c, int64_t(hb[1]) + 1);
-    a.lst = out.lst.p;
+    a.lst = reinterpret_cast<uint32_t*>(out.lst.p);
     const int grid = div_up(int64_t(own) * kLanes, kBlock);
     if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_build_kernel<GMG_SAMPLER_EXACT>, grid, kBlock, 0, a, lo, hi, state8);
     else GMG_LAUNCH(c, shard_build_kernel<GMG_SAMPLER_PARALLEL>, grid, kBlock, 0, a, lo, hi, state8);

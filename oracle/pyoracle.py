@@ -157,6 +157,57 @@ class Oracle:
         nnz = int(rowptr[n])
         return rowptr, self._take(col, nnz, np.int32), self._take(val, nnz, np.float64), rc
 
+    # ---- parts the reference lacks (oracle/solver_oracle.c; only in the plain-C library) ---------------
+    def _solver_lib(self):
+        if self.kind == "orc":
+            return self.lib
+        if not hasattr(self, "_orc_lib"):
+            if not os.path.exists(_PATHS["orc"]):
+                build()
+            self._orc_lib = C.CDLL(_PATHS["orc"])
+        return self._orc_lib
+
+    def galerkin(self, a_ptr, a_idx, a_val, p_rowptr, p_colidx, p_val, m):
+        """A_c = P^T A P by outer vector (structural pattern, sorted inner indices): (ptr, idx, val)."""
+        lib = self._solver_lib()
+        a_ptr, a_idx, a_val = self._csc(a_ptr, a_idx, a_val)
+        p_rowptr, p_colidx, p_val = self._csc(p_rowptr, p_colidx, p_val)
+        n = a_ptr.shape[0] - 1
+        optr = np.empty(m + 1, dtype=np.int32)
+        oi, ov = _i32p(), _f64p()
+        lib.orc_galerkin(C.c_int64(n), _p(a_ptr, _i32p), _p(a_idx, _i32p), _p(a_val, _f64p), C.c_int64(m),
+                         _p(p_rowptr, _i32p), _p(p_colidx, _i32p), _p(p_val, _f64p), _p(optr, _i32p),
+                         C.byref(oi), C.byref(ov))
+        nnz = int(optr[m])
+        lib.orc_solver_free.argtypes = [C.c_void_p]
+
+        def take(ptr, ty, dt):
+            out = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ty)), shape=(max(nnz, 1),))[:nnz].copy()
+            lib.orc_solver_free(C.cast(ptr, C.c_void_p))
+            return out.astype(dt, copy=False)
+        return optr, take(oi, C.c_int32, np.int32), take(ov, C.c_double, np.float64)
+
+    def spmv(self, outer, inner, val, x):
+        lib = self._solver_lib()
+        outer, inner, val = self._csc(outer, inner, val)
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = outer.shape[0] - 1
+        y = np.empty(n, dtype=np.float64)
+        lib.orc_spmv(C.c_int64(n), _p(outer, _i32p), _p(inner, _i32p), _p(val, _f64p), _p(x, _f64p), _p(y, _f64p))
+        return y
+
+    def gauss_seidel(self, outer, inner, val, b, x, rows, sweeps=1):
+        """Gauss-Seidel sweeps in the row order `rows` (the multicolour kernel's (colour, row) order)."""
+        lib = self._solver_lib()
+        outer, inner, val = self._csc(outer, inner, val)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.array(x, dtype=np.float64)
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        n = outer.shape[0] - 1
+        lib.orc_gauss_seidel(C.c_int64(n), _p(outer, _i32p), _p(inner, _i32p), _p(val, _f64p), _p(b, _f64p),
+                             _p(rows, _i32p), C.c_int(sweeps), _p(x, _f64p))
+        return x
+
     def projected_points(self, rowptr, colidx, val, coarse_points):
         cp = fpoints(coarse_points); m = cp.shape[0]
         rowptr = np.ascontiguousarray(rowptr, dtype=np.int32); n = rowptr.shape[0] - 1

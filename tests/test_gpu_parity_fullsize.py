@@ -1,0 +1,184 @@
+"""Parity of the CUDA path with the CPU checker at BASELINE.json's REAL sizes (not scaled-down stand-ins):
+
+  * C2 (2,621,442-vertex noisy icosphere, 4 levels) and C3 (10,000,000-vertex noisy torus, 4 levels, A_c on every
+    level), exact sampler: every integer output and every floating-point output of the reference path bit-exact
+    against the reference's own code (oracle/_ref, unmodified sources on the Eigen shim) or its plain-C
+    restatement (pinned to it bit-for-bit by tests/test_oracle.py); A_c against the CPU product with PATTERN
+    EQUALITY and values within 1e-12.
+  * every parallel-sampler configuration pinned by SEEDING (north star: "bit-exact when seeded with the reference's
+    own sample sets" -- and conversely the reference's assignParents ... constructProlongation accept any sample
+    set): the GPU's sample set of every level goes into the checker, everything downstream must match bit for bit.
+  * the parallel sampler itself by the literal north-star criterion: sample count and coverage radius within 2 % of
+    the reference's greedy order, on the torus, the kNN cloud and the icosphere.
+
+These are the bugs that only show at size: shared-memory table overflow paths, fans of more than 32 triangles,
+the sampler's staged-list overflow, 32-bit offsets.
+"""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from gravomg_b200 import capi, meshgen
+from pipeline import run_level, assert_level_equal
+
+pytestmark = pytest.mark.gpu
+
+KEYS = "sel par ccp cri cval cpts tri nrm fptr fan prp pci pva".split()
+
+
+@pytest.fixture(scope="module")
+def cpu():
+    """The reference's own code where its library travelled with the repo, else the plain-C restatement."""
+    from oracle.pyoracle import Oracle, available, build
+    if available("ref"):
+        return Oracle("ref")
+    if not available("orc"):
+        build()
+    return Oracle("orc")
+
+
+@pytest.fixture(scope="module")
+def orc_fast():
+    from oracle.pyoracle import Oracle, available, build
+    if not available("orc"):
+        build()
+    return Oracle("orc")
+
+
+def assert_galerkin_equal(got, want, what):
+    """Pattern equality (structural, un-pruned, sorted) and values within 1e-12 of the column's largest entry;
+    returns the number of entries that differ in any bit."""
+    gp, gi, gv = got
+    wp, wi, wv = want
+    assert np.array_equal(gp, wp), f"{what}: outer pointers differ ({gp[-1]} vs {wp[-1]} entries)"
+    assert np.array_equal(gi, wi), f"{what}: inner indices differ in {np.count_nonzero(gi != wi)} places"
+    col = np.repeat(np.arange(len(wp) - 1), np.diff(wp))
+    colmax = np.zeros(len(wp) - 1)
+    np.maximum.at(colmax, col, np.abs(wv))
+    err = np.abs(gv - wv)
+    bad = err > 1e-12 * colmax[col]
+    assert not bad.any(), f"{what}: {np.count_nonzero(bad)} values off by more than 1e-12 (max rel {np.max(err / colmax[col]):.3e})"
+    return int(np.count_nonzero(gv != wv))
+
+
+def check_hierarchy(ctx, be, V, A, levels, mode, galerkin, what, seed=42, galerkin_be=None):
+    """Build on the GPU, replay every level on the CPU with the GPU's radius (and, for the parallel sampler, the
+    GPU's sample set) and compare everything."""
+    inp = capi.Input(ctx, V, A.indptr, A.indices, A.data if galerkin else None)
+    h = capi.Hierarchy(ctx, inp, levels, sampler_mode=mode, build_galerkin=galerkin, seed=seed)
+    assert h.num_levels == levels - 1
+    pts, cp, ri = V, A.indptr, A.indices
+    val = be.to_edge_distance_matrix(cp, ri, pts)
+    assert np.array_equal(val, h.fetch(0, capi.H_FINE_VAL)), f"{what}: toEdgeDistanceMatrix differs"
+    a_cur = (A.indptr, A.indices, A.data)
+    bitdiff = 0
+    for lvl in range(h.num_levels):
+        g = h.level_arrays(lvl)
+        w = run_level(be, pts, cp, ri, val, radius=g["radius"],
+                      samples=None if mode == capi.SAMPLER_EXACT else g["sel"])
+        assert_level_equal(g, w, keys=KEYS, what=f"{what} level {lvl} ")
+        if galerkin:
+            m = len(g["sel"])
+            want = (galerkin_be or be).galerkin(*a_cur, g["prp"], g["pci"], g["pva"], m)
+            got = (h.fetch(lvl, capi.H_AC_COLPTR), h.fetch(lvl, capi.H_AC_ROWIDX), h.fetch(lvl, capi.H_AC_VAL))
+            bitdiff += assert_galerkin_equal(got, want, f"{what} level {lvl} A_c")
+            a_cur = want
+        pts, cp, ri, val = w["cpts"], w["ccp"], w["cri"], w["cval"]
+    info = h.info
+    h.close(); inp.close()
+    return info, bitdiff
+
+
+def test_c2_full_size_bit_exact(ctx, cpu):
+    cfg = meshgen.make_config("C2")
+    assert cfg["V"].shape[0] == 2_621_442
+    info, bitdiff = check_hierarchy(ctx, cpu, cfg["V"], cfg["A"], cfg["levels"], capi.SAMPLER_EXACT, True, "C2 full")
+    assert [i["n"] for i in info][0] == 2_621_442 and len(info) == 3
+    assert bitdiff == 0, f"A_c values agree to 1e-12 but {bitdiff} are not bit-identical"
+
+
+def test_c3_full_size_bit_exact_with_galerkin(ctx, orc_fast):
+    """The north star's target sentence: the 10 M-vertex surface, 4 levels, P and A_c at every level, matching
+    the reference's indices exactly and its values within 1e-12 (here: bit-exact)."""
+    cfg = meshgen.make_config("C3")
+    assert cfg["V"].shape[0] == 10_000_000
+    info, bitdiff = check_hierarchy(ctx, orc_fast, cfg["V"], cfg["A"], cfg["levels"], capi.SAMPLER_EXACT, True, "C3 full")
+    assert len(info) == 3 and info[0]["nnz_ac"] > 0
+    assert bitdiff == 0, f"A_c values agree to 1e-12 but {bitdiff} are not bit-identical"
+
+
+@pytest.mark.parametrize("name,scale,mode", [("C3", 1.0, capi.SAMPLER_PARALLEL), ("C3", 0.25, capi.SAMPLER_HASHED),
+                                             ("C4", 0.1, capi.SAMPLER_PARALLEL), ("C4", 0.1, capi.SAMPLER_HASHED),
+                                             ("C2", 1.0, capi.SAMPLER_HASHED)])
+def test_parallel_sampler_pinned_by_seeding(ctx, orc_fast, name, scale, mode):
+    """PARALLEL: index-order sweeps restarted in a few super-tiles; HASHED: every vertex hashed (the order the
+    row-sharded build uses). Neither set can come out of the reference, but everything after the sampler can."""
+    cfg = meshgen.make_config(name, scale)
+    info, _ = check_hierarchy(ctx, orc_fast, cfg["V"], cfg["A"], cfg["levels"], mode, name != "C4",
+                              f"{name} x{scale} sampler mode {mode}", seed=7)
+    assert all(i["m"] > 0 for i in info)
+
+
+def coverage_radius(be, V, cp, ri, sel):
+    """max over vertices of the distance to its parent's sample"""
+    par = be.assign_parents(V, cp, ri, sel)
+    return float(np.linalg.norm(V - V[sel[par]], axis=1).max())
+
+
+@pytest.mark.parametrize("name,scale", [("C3", 1.0), ("C3", 0.1), ("C4", 0.1), ("C2", 0.25)])
+def test_parallel_sampler_statistics_literal(ctx, orc_fast, name, scale):
+    """BASELINE.json: "the parallel sampler, which cannot reproduce the sequential greedy order, is additionally
+    validated by coverage-radius and sample-count statistics within 2% of the reference". Literal: both within 2 %.
+    GMG_SAMPLER_PARALLEL is what is validated here. Hashing every vertex (GMG_SAMPLER_HASHED) is statistically
+    the same thing on unordered inputs but packs an index-coherent grid 28 % more loosely than the reference's
+    row-by-row sweep; test_hashed_sampler_statistics records that."""
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    val = orc_fast.to_edge_distance_matrix(A.indptr, A.indices, V)
+    edges, _ = orc_fast.extract_edges(A.indptr, A.indices, val)
+    radius = 2.0 * orc_fast.average_edge_length(V, edges)
+    ref_sel = orc_fast.fast_disc_sample(V, A.indptr, A.indices, radius)
+    par_sel = ctx.fast_disc_sample(V, A.indptr, A.indices, radius, mode=capi.SAMPLER_PARALLEL, seed=7)
+    assert np.all(np.diff(par_sel) > 0)
+    r_ref = coverage_radius(orc_fast, V, A.indptr, A.indices, ref_sel)
+    r_par = coverage_radius(orc_fast, V, A.indptr, A.indices, par_sel)
+    d_count = (len(par_sel) - len(ref_sel)) / len(ref_sel)
+    d_cov = (r_par - r_ref) / r_ref
+    print(f"{name} x{scale}: count {len(par_sel)} vs {len(ref_sel)} ({100 * d_count:+.2f} %), coverage radius "
+          f"{r_par:.6g} vs {r_ref:.6g} ({100 * d_cov:+.2f} %)")
+    assert abs(d_count) <= 0.02, f"sample count off by {100 * d_count:+.2f} %"
+    assert abs(d_cov) <= 0.02, f"coverage radius off by {100 * d_cov:+.2f} %"
+    # a maximal independent set of the covering relation whatever the order: the reference rule, run in the
+    # order that puts the parallel set first, must select exactly that set
+    n = V.shape[0]
+    first = np.zeros(n, dtype=bool); first[par_sel] = True
+    perm = np.concatenate([par_sel, np.flatnonzero(~first)])
+    inv = np.empty(n, dtype=np.int64); inv[perm] = np.arange(n)
+    Ap = sp.csc_matrix((np.ones(A.nnz), A.indices, A.indptr), shape=(n, n))[perm][:, perm].tocsc()
+    Ap.sort_indices()
+    again = orc_fast.fast_disc_sample(np.asfortranarray(V[perm]), Ap.indptr.astype(np.int32), Ap.indices.astype(np.int32), radius)
+    assert np.array_equal(again, np.arange(len(par_sel))), "the parallel set is not a maximal independent set of the covering relation"
+
+
+@pytest.mark.parametrize("name,scale,count_tol", [("C4", 0.1, 0.02), ("C2", 0.25, 0.02), ("C3", 0.1, None)])
+def test_hashed_sampler_statistics(ctx, orc_fast, name, scale, count_tol):
+    """The fully hashed order: within 2 % on point clouds and subdivision orders. On the row-major torus it is a
+    valid maximal independent set of the same covering relation with a LOOSER packing than the reference's
+    row-by-row sweep (measured -28 % samples); that gap is recorded, not hidden: the assertion there is only that
+    it stays a looser packing (fewer samples, coverage radius still below the sampling radius)."""
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    val = orc_fast.to_edge_distance_matrix(A.indptr, A.indices, V)
+    edges, _ = orc_fast.extract_edges(A.indptr, A.indices, val)
+    radius = 2.0 * orc_fast.average_edge_length(V, edges)
+    ref_sel = orc_fast.fast_disc_sample(V, A.indptr, A.indices, radius)
+    sel = ctx.fast_disc_sample(V, A.indptr, A.indices, radius, mode=capi.SAMPLER_HASHED, seed=7)
+    r_ref = coverage_radius(orc_fast, V, A.indptr, A.indices, ref_sel)
+    r_sel = coverage_radius(orc_fast, V, A.indptr, A.indices, sel)
+    d_count = (len(sel) - len(ref_sel)) / len(ref_sel)
+    print(f"{name} x{scale} hashed: count {len(sel)} vs {len(ref_sel)} ({100 * d_count:+.2f} %), coverage radius "
+          f"{r_sel:.6g} vs {r_ref:.6g} ({100 * (r_sel - r_ref) / r_ref:+.2f} %)")
+    if count_tol is not None:
+        assert abs(d_count) <= count_tol and abs(r_sel - r_ref) <= 0.02 * r_ref
+    else:
+        assert -0.40 < d_count < 0.0 and r_sel < radius
