@@ -41,17 +41,26 @@ def parse():
     ap.add_argument("--per-gpu-mverts", type=float, default=12.5, help="default N>1 workload: torus vertices per GPU (millions)")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--sampler", default=None, choices=["exact", "parallel", "hashed"],
-                    help="default: exact on one GPU (the reference's sample set), parallel for the row-sharded build "
-                         "(the exact greedy order is a cross-rank dependency chain; SURVEY.md 8(e))")
-    ap.add_argument("--galerkin", type=int, default=0, help="1: also A_c = P^T A P on every level (config C3)")
-    ap.add_argument("--vcycle", type=int, default=0, help="1 (with --galerkin 1): one V-cycle Poisson solve and an SpMV, timed")
+                    help="default: exact on one GPU (the reference's sample set, the parity mode), hashed for the row-sharded "
+                         "build (the exact greedy order is a cross-rank dependency chain; SURVEY.md 8(e))")
+    ap.add_argument("--galerkin", type=int, default=None, help="1: also A_c = P^T A P on every level (default: 1 for C3 and the torus family)")
+    ap.add_argument("--vcycle", type=int, default=None, help="1 (with --galerkin 1): one V-cycle Poisson solve and an SpMV, timed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-scale", type=float, default=None, help="size of the in-line CPU baseline sample (default: the workload itself, which also gives the parity check)")
     a = ap.parse_args()
     world = max(a.gpus, int(os.environ.get("WORLD_SIZE", "1")))
     if a.workload is None:
-        a.workload = "C2" if world == 1 else f"T{a.per_gpu_mverts * world:g}"
+        # N = 1: config C3, the largest single-GPU configuration of BASELINE.json and the north star's target
+        # (10 M-vertex torus, P and A_c at every level, one V-cycle). N > 1: the same family row-sharded, 12.5 M
+        # vertices per GPU (N = 8 is the 100 M-vertex mesh of config C5).
+        a.workload = "C3" if world == 1 else f"T{a.per_gpu_mverts * world:g}"
+    torus = a.workload == "C3" or a.workload.startswith("T")
+    if a.galerkin is None:
+        a.galerkin = 1 if torus else 0
+    if a.vcycle is None:
+        a.vcycle = 1 if (torus and a.galerkin) else 0
     if a.sampler is None:
-        a.sampler = "parallel" if (world > 1 or a.workload.startswith("T")) else "exact"
+        a.sampler = "hashed" if (world > 1 or a.workload.startswith("T")) else "exact"
     return a
 
 
@@ -66,11 +75,19 @@ def workload_name(a):
     if a.workload.startswith("T"):
         nu, nv = torus_dims(a.workload)
         return f"noisy torus {nu}x{nv} ({nu * nv:,} verts, C5 family), 4 levels, ratio 8, generated on the device"
-    base = {"C1": "icosphere 6 subdivisions (40,962 verts), 3 levels",
-            "C2": "icosphere 9 subdivisions + vertex noise (2,621,442 verts), 4 levels, ratio 8",
-            "C3": "noisy torus 10000x1000 (10,000,000 verts), 4 levels, ratio 8",
-            "C4": "kNN k=8 sphere cloud 20M points, 4 levels"}[a.workload]
+    base = {"C1": "C1: icosphere 6 subdivisions (40,962 verts), 3 levels",
+            "C2": "C2: icosphere 9 subdivisions + vertex noise (2,621,442 verts), 4 levels, ratio 8",
+            "C3": "C3: anisotropic noisy torus 10000x1000 (10,000,000 verts), 4 levels, ratio 8",
+            "C4": "C4: kNN k=8 sphere cloud 20M points, 4 levels"}[a.workload]
+    if a.galerkin:
+        base += ", P + Galerkin A_c at every level"
     return base if a.scale == 1.0 else f"{base} [scaled x{a.scale}]"
+
+
+def bench_config(a, world):
+    """The `config` object; identical in the B200 arm and the reference arm."""
+    return {"workload": workload_name(a), "sampler": a.sampler, "galerkin": bool(a.galerkin), "vcycle": bool(a.vcycle),
+            "n_gpus": world}
 
 
 # ---- clocks sampler (B200_PROFILING.md recipe) ---------------------------------------------------
@@ -172,7 +189,9 @@ def measured_peak():
 # kernels of each stage (for roofline.traffic: DRAM bytes per launch from the committed ncu --set full capture)
 STAGE_KERNELS = {"edge_lengths": ["edge_length_kernel"], "sampling": ["sampler_build_kernel<0>", "sampler_flow_kernel<0>"],
                  "parents": ["parents_sweep_kernel", "parents_pred_kernel"], "coarse_edges": ["coarse_rows_warp_kernel"],
-                 "prolongation_rows": ["prolong_rows_kernel"]}
+                 "prolongation_rows": ["prolong_rows_kernel"], "galerkin_numeric": ["galerkin_warp_kernel<1>"],
+                 "galerkin_symbolic": ["galerkin_warp_kernel<0>"],
+                 "galerkin_transpose": ["count_columns_kernel", "transpose_fill_kernel"]}
 
 
 def ncu_traffic(workload, stage):
@@ -188,52 +207,141 @@ def ncu_traffic(workload, stage):
 
 
 # ---- CPU arm: the reference's own code on the host cores ---------------------------------------------
-def cpu_hierarchy_seconds(V, A, levels):
-    """One hierarchy build with the reference's CPU implementation (unmodified sources on the Eigen
-    shim when oracle/_ref exists, else the plain-C port). Single thread: the reference has no threading."""
+CPU_STAGES = ["edge_lengths", "sampling", "parents", "coarse_edges", "coarse_points", "triangle_fans", "prolongation_rows",
+              "galerkin"]
+
+
+def cpu_hierarchy(V, A, levels, galerkin=False, radii=None, kind=None):
+    """One hierarchy build with the reference's CPU implementation (the UNMODIFIED sources on the Eigen shim when
+    oracle/_ref exists, else the plain-C port), one thread: the reference has no threading. The call order is the
+    demo's (test/main.cpp:68-121) looped over levels; A_c = P^T A P, which the reference does not contain, is our
+    single-thread CSR product (oracle/solver_oracle.c). Returns (per-level results, per-stage seconds, total
+    seconds, kind). radii: use these sampling radii (the GPU's, so that the two hierarchies can be compared bit
+    for bit; averageEdgeLength is still computed and timed)."""
     from oracle.pyoracle import Oracle, available
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from pipeline import run_hierarchy
-    kind = "ref" if available("ref") else "orc"
+    kind = kind or ("ref" if available("ref") else "orc")
     be = Oracle(kind)
-    t0 = time.perf_counter()
-    run_hierarchy(be, V, A, levels)
-    return time.perf_counter() - t0, ("reference" if kind == "ref" else "port")
+    sec = {k: 0.0 for k in CPU_STAGES}
+
+    def timed(stage, fn, *args):
+        t0 = time.perf_counter()
+        r = fn(*args)
+        sec[stage] += time.perf_counter() - t0
+        return r
+
+    t_all = time.perf_counter()
+    pts, cp, ri = V, A.indptr, A.indices
+    val = timed("edge_lengths", be.to_edge_distance_matrix, cp, ri, pts)
+    a_cur = (A.indptr, A.indices, A.data)
+    res = []
+    for lvl in range(levels - 1):
+        r = {}
+        edges, _ = timed("edge_lengths", be.extract_edges, cp, ri, val)
+        r["radius_cpu"] = np.cbrt(8.0) * timed("edge_lengths", be.average_edge_length, pts, edges)
+        del edges
+        r["radius"] = r["radius_cpu"] if radii is None else radii[lvl]
+        r["sel"] = timed("sampling", be.fast_disc_sample, pts, cp, ri, r["radius"])
+        m = len(r["sel"])
+        r["par"] = timed("parents", be.assign_parents, pts, cp, ri, r["sel"])
+        r["ccp"], r["cri"], r["cval"] = timed("coarse_edges", be.extract_coarse_edges, cp, ri, val, m, r["par"])
+        r["cpts"] = timed("coarse_points", be.coarse_from_mean_of_fine_children, pts, cp, ri, r["par"], m)
+        # constructProlongation calls constructVoronoiTriangles itself (src/multigrid.cpp:272); the demo's own extra
+        # call (test/main.cpp:107) only feeds the viewer and is timed as the triangle stage
+        r["tri"], r["nrm"], r["fptr"], r["fan"] = timed("triangle_fans", be.construct_voronoi_triangles, r["cpts"],
+                                                        r["ccp"], r["cri"], r["cval"])
+        pr = timed("prolongation_rows", be.construct_prolongation, pts, r["cpts"], r["ccp"], r["cri"], r["cval"], r["par"], 0)
+        r["prp"], r["pci"], r["pva"] = pr[0], pr[1], pr[2]
+        if galerkin:
+            r["ac"] = timed("galerkin", be.galerkin, *a_cur, r["prp"], r["pci"], r["pva"], m)
+            a_cur = r["ac"]
+        res.append(r)
+        pts, cp, ri, val = r["cpts"], r["ccp"], r["cri"], r["cval"]
+    return res, sec, time.perf_counter() - t_all, ("reference" if kind == "ref" else "port")
+
+
+def compare_with_cpu(h, capi, cpu_levels, galerkin):
+    """Bit-exact comparison of a GPU hierarchy (exact sampler) with the CPU run on the same input and radii."""
+    keys = "sel par ccp cri cval cpts tri nrm fptr fan prp pci pva".split()
+    out = {"levels": len(cpu_levels), "arrays": 0, "mismatches": []}
+    ac_err = 0.0
+    for lvl, w in enumerate(cpu_levels):
+        g = h.level_arrays(lvl)
+        for k in keys:
+            x, y = np.asarray(g[k]), np.asarray(w[k])
+            out["arrays"] += 1
+            if x.shape != y.shape or not np.array_equal(x, y):
+                out["mismatches"].append(f"L{lvl}.{k}")
+        rel = abs(g["radius"] - w["radius_cpu"]) / w["radius_cpu"]
+        if rel > 1e-12:
+            out["mismatches"].append(f"L{lvl}.radius({rel:.1e})")
+        if galerkin:
+            gp, gi, gv = h.fetch(lvl, capi.H_AC_COLPTR), h.fetch(lvl, capi.H_AC_ROWIDX), h.fetch(lvl, capi.H_AC_VAL)
+            wp, wi, wv = w["ac"]
+            out["arrays"] += 3
+            if not (np.array_equal(gp, wp) and np.array_equal(gi, wi)):
+                out["mismatches"].append(f"L{lvl}.A_c pattern")
+            else:
+                ac_err = max(ac_err, float(np.abs(gv - wv).max(initial=0.0) / np.abs(wv).max()))
+                if ac_err > 1e-12:
+                    out["mismatches"].append(f"L{lvl}.A_c values({ac_err:.1e})")
+                out.setdefault("ac_bit_identical", True)
+                out["ac_bit_identical"] = out["ac_bit_identical"] and bool(np.array_equal(gv, wv))
+    out["ac_max_rel_err"] = ac_err
+    return out
+
+
+def cpu_solver_seconds(A, levels_cpu):
+    """Single-thread CSR SpMV and one Gauss-Seidel sweep on the level-0 operator (oracle/solver_oracle.c), timed."""
+    from oracle.pyoracle import Oracle
+    be = Oracle("orc")
+    n = A.shape[0]
+    x = np.linspace(0.0, 1.0, n)
+    t0 = time.perf_counter(); be.spmv(A.indptr, A.indices, A.data, x); t_spmv = time.perf_counter() - t0
+    rows = np.arange(n, dtype=np.int32)
+    t0 = time.perf_counter(); be.gauss_seidel(A.indptr, A.indices, A.data, x, np.zeros(n), rows, 1); t_gs = time.perf_counter() - t0
+    return {"spmv_s": t_spmv, "spmv_gbs": (20 * n + 12 * A.nnz) / t_spmv / 1e9, "gauss_seidel_sweep_s": t_gs,
+            "what": "single-thread CSR kernels of ours (the reference has none), level-0 operator"}
 
 
 def run_reference(a, rank, world):
+    """The reference arm: same config, metric and unit as the B200 arm; every step is one whole hierarchy build by
+    the reference's CPU code on a BOUNDED sample of the workload (the full C3 build takes about 100 s per step on one
+    core; the reference is single-threaded), sized so that steps + warmup fit a few minutes."""
     if rank != 0:
         return
     from gravomg_b200 import meshgen
-    name = workload_name(a)
+    config = bench_config(a, world)
     if a.workload.startswith("T"):      # the torus family: the CPU sample is the C3 generator at a bounded size
         nu, nv = torus_dims(a.workload)
-        a.scale = nu * nv / 10_000_000.0
-        a.workload = "C3"
-    # bounded sample: every step about 10-25 s of CPU work and the whole run within a few minutes
-    # (the reference builds ~0.13-0.4 Mverts/s on one core, depending on the mesh)
-    per_step_s = min(25.0, 150.0 / max(1, a.steps + a.warmup))
-    full_n = {"C1": 40962, "C2": 2621442, "C3": 10_000_000, "C4": 20_000_000}[a.workload] * a.scale
-    scale = a.scale
-    while full_n * (scale / a.scale) / 0.13e6 > per_step_s and scale > 1e-5:
-        scale /= 4.0
-    cfg = meshgen.make_config(a.workload, scale)
+        full_n, gen = nu * nv, "C3"
+    else:
+        full_n, gen = {"C1": 40962, "C2": 2621442, "C3": 10_000_000, "C4": 20_000_000}[a.workload] * a.scale, a.workload
+    per_step_s = max(2.0, 240.0 / max(1, a.steps + a.warmup))
+    rate = 0.10e6 if a.galerkin else 0.2e6          # verts per second of the CPU build, conservative
+    target_n = min(full_n, per_step_s * rate)
+    base_n = {"C1": 40962, "C2": 2621442, "C3": 10_000_000, "C4": 20_000_000}[gen]
+    scale = min(1.0, target_n / base_n)
+    if gen in ("C1", "C2"):             # icospheres come in subdivision steps: round the scale to a power of 4
+        scale = min(1.0, 4.0 ** np.floor(np.log(max(scale, 1e-6)) / np.log(4.0)))
+    cfg = meshgen.make_config(gen, scale)
     V, A = cfg["V"], cfg["A"]
     n = V.shape[0]
-    times, kind = [], "port"
+    times, kind, sec_acc = [], "port", None
     for s in range(a.warmup + a.steps):
-        dt, kind = cpu_hierarchy_seconds(V, A, LEVELS[a.workload])
+        _, sec, dt, kind = cpu_hierarchy(V, A, LEVELS[gen], galerkin=bool(a.galerkin))
         if s >= a.warmup:
             times.append(dt)
+            sec_acc = sec if sec_acc is None else {k: sec_acc[k] + v for k, v in sec.items()}
     ms = 1e3 * float(np.mean(times))
     value = n / (ms * 1e-3) / 1e6
-    sample = f"{a.workload} at scale {scale:g}: {n} verts, {LEVELS[a.workload]} levels, whole hierarchy per step"
+    sample = (f"{gen} generator at scale {scale:g}: {n} verts, {LEVELS[gen]} levels, whole hierarchy"
+              f"{' + A_c every level' if a.galerkin else ''} per step; reference sources on the Eigen shim, -O2, 1 thread")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mverts/s", "n_gpus": a.gpus,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": name, "sampler": "exact (sequential greedy)", "cpu_sample_verts": n},
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
             "cpu_baseline": {"value": value, "unit": "Mverts/s", "cores": 1, "kind": kind, "sample": sample,
-                             "host_cores": os.cpu_count()},
+                             "host_cores": os.cpu_count(), "sample_verts": n,
+                             "stage_seconds": {k: round(v / max(1, a.steps), 4) for k, v in (sec_acc or {}).items()}},
             "e2e": {"value": value, "unit": "Mverts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -255,7 +363,8 @@ def run_b200(a, rank, world, local_rank):
     V, A = cfg["V"], cfg["A"]
     levels = LEVELS[a.workload]
     n = V.shape[0]
-    mode = {"exact": capi.SAMPLER_EXACT, "parallel": capi.SAMPLER_PARALLEL, "hashed": capi.SAMPLER_HASHED}[a.sampler]
+    MODES = {"exact": capi.SAMPLER_EXACT, "parallel": capi.SAMPLER_PARALLEL, "hashed": capi.SAMPLER_HASHED}
+    mode = MODES[a.sampler]
 
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)         # a real stream shared by the library and the timing events
@@ -280,9 +389,8 @@ def run_b200(a, rank, world, local_rank):
 
     inp = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
 
-    def step_resident():
-        h = Hierarchy(ctx, inp, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin))
-        return h
+    def step_resident(m=mode):
+        return Hierarchy(ctx, inp, levels, sampler_mode=m, build_galerkin=bool(a.galerkin))
 
     # pinned result buffers, allocated once and reused like a caller's own output arrays (rows of P hold <= 3 entries)
     pin_out = {}
@@ -295,13 +403,14 @@ def run_b200(a, rank, world, local_rank):
 
     def step_e2e():
         i2 = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
-        # every level's P leaves the device on the copy stream as soon as the level is complete, while the
+        # every level's P (and A_c) leaves the device on the copy stream as soon as the level is complete, while the
         # next level builds; the step ends when the last copy has landed in the pinned result buffers
         def stream_out(lvl, info):
-            nl, nzp = info["n"], info["nnz_p"]
-            return [(which, pinned_out((lvl, which), cnt, dt)[:cnt])
-                    for which, cnt, dt in ((capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32),
-                                           (capi.H_P_VAL, nzp, np.float64))]
+            nl, nzp, m, nzac = info["n"], info["nnz_p"], info["m"], info["nnz_ac"]
+            want = [(capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32), (capi.H_P_VAL, nzp, np.float64)]
+            if a.galerkin:
+                want += [(capi.H_AC_COLPTR, m + 1, np.int32), (capi.H_AC_ROWIDX, nzac, np.int32), (capi.H_AC_VAL, nzac, np.float64)]
+            return [(which, pinned_out((lvl, which), cnt, dt)[:cnt]) for which, cnt, dt in want]
         h = Hierarchy(ctx, i2, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin), stream_out=stream_out)
         ctx.copy_sync()
         d2h = h.streamed_bytes
@@ -309,39 +418,48 @@ def run_b200(a, rank, world, local_rank):
         h.close(); i2.close()
         return nb, d2h
 
-    for _ in range(a.warmup):
-        step_resident().close()
-    barrier()
+    def timed_builds(m, steps, warmup):
+        for _ in range(warmup):
+            step_resident(m).close()
+        barrier()
+        l0 = ctx.launch_count
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        infos, acc, gacc = None, None, None
+        for s_ in range(steps):
+            flush.fill_(s_ & 0xFF)                        # flush L2 between timed iterations
+            torch.cuda.synchronize()
+            ev[s_][0].record(stream)
+            h = step_resident(m)
+            ev[s_][1].record(stream)
+            torch.cuda.synchronize()
+            infos = h.info
+            sm = np.array([i["stage_ms"] for i in h.info])
+            gm = np.array([i["galerkin_ms"] for i in h.info])
+            acc = sm if acc is None else acc + sm
+            gacc = gm if gacc is None else gacc + gm
+            h.close()
+        barrier()
+        ms_ = float(np.mean([e0.elapsed_time(e1) for e0, e1 in ev]))
+        return ms_, infos, acc / steps, gacc / steps, ctx.launch_count - l0
+
     clocks = ClockSampler(local_rank)
     clocks.start()
-    launches0 = ctx.launch_count
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
-    infos = None
-    stage_acc = None
-    barrier()
-    for s in range(a.steps):
-        flush.fill_(s & 0xFF)                        # flush L2 between timed iterations
-        torch.cuda.synchronize()
-        ev[s][0].record(stream)
-        h = step_resident()
-        ev[s][1].record(stream)
-        torch.cuda.synchronize()
-        infos = h.info
-        sm = np.array([i["stage_ms"] for i in h.info])
-        stage_acc = sm if stage_acc is None else stage_acc + sm
-        h.close()
-    barrier()
-    launches = ctx.launch_count - launches0
+    ms, infos, stage_ms, gal_ms, launches = timed_builds(mode, a.steps, a.warmup)
     clk = clocks.stop()
-    ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in ev]))
-    stage_ms = stage_acc / a.steps                   # [level][stage]
+    # the other sampler order beside it (fewer steps): exact is the parity mode, parallel the throughput mode
+    other = None
+    other_name = "parallel" if a.sampler == "exact" else "exact"
+    if a.scale == 1.0 or a.workload != "C4":
+        o_ms, o_infos, _, _, _ = timed_builds(MODES[other_name], max(1, min(a.steps, 5)), 2)
+        other = {"sampler": other_name, "ms_per_step": o_ms, "value": n / (o_ms * 1e-3) / 1e6, "unit": "Mverts/s",
+                 "coarse_sizes": [i["m"] for i in o_infos]}
 
-    # end-to-end through the C ABI with host buffers: H2D of the inputs + build + D2H of every P
+    # end-to-end through the C ABI with host buffers: H2D of the inputs + build + D2H of every P (and A_c)
     e2e_ms, h2d, d2h = [], 0, 0
     step_e2e()
     barrier()
-    for s in range(max(1, min(a.steps, 3))):
-        flush.fill_(s)
+    for s_ in range(max(1, min(a.steps, 5))):
+        flush.fill_(s_)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         h2d, d2h = step_e2e()
@@ -359,42 +477,55 @@ def run_b200(a, rank, world, local_rank):
         return
 
     peak, peak_src = measured_peak()
-    # dominant stage at level 0 (the level that holds ~7/8 of the work)
     names = capi.STAGE_NAMES
-    dom = int(np.argmax(stage_ms[0]))
-    bytes0 = stage_bytes(infos[0])[names[dom]]
-    achieved = bytes0 / (stage_ms[0][dom] * 1e-3) / 1e9
-    traffic, traffic_src = ncu_traffic(a.workload, names[dom]) if a.scale == 1.0 and a.sampler == "exact" else (None, None)
+    # the dominant kernel group at level 0 (the level that holds ~7/8 of the work); the Galerkin stage is split
+    # into its transpose, symbolic and numeric parts, each with its own algorithmic bytes
+    i0 = infos[0]
+    sb = stage_bytes(i0)
+    cand = {names[s_]: (float(stage_ms[0][s_]), sb[names[s_]]) for s_ in range(8)}
+    if a.galerkin:
+        n0, nnz0, m0, nzp, nzac = i0["n"], i0["nnz"], i0["m"], i0["nnz_p"], i0["nnz_ac"]
+        cand["galerkin_transpose"] = (float(gal_ms[0][0]), 12 * nzp + 4 * m0 + 12 * nzp)
+        cand["galerkin_symbolic"] = (float(gal_ms[0][1]), 12 * n0 + 4 * nnz0 + 8 * nzp + 4 * m0)
+        cand["galerkin_numeric"] = (float(gal_ms[0][2]), 12 * n0 + 12 * nnz0 + 24 * nzp + 4 * m0 + 12 * nzac)
+    dom = max(cand, key=lambda k: cand[k][0])
+    dom_ms, bytes0 = cand[dom]
+    achieved = bytes0 / (dom_ms * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(a.workload, dom) if a.scale == 1.0 else (None, None)
     total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if (k != "galerkin" or a.galerkin)) for i in infos)
+    config = bench_config(a, world)
+    config.update({"l2": "256 MB flush write between timed steps; inputs (>200 MB) exceed the 126 MB L2",
+                   "multi_gpu": "replicas only (one independent build per rank)" if world > 1 else "single GPU",
+                   "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_p", "nnz_ac", "sampler_rounds",
+                                                  "parent_rounds")} for i in infos]})
     line = {"metric": METRIC, "value": world * n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world,
-            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": bool(a.galerkin),
-                       "l2": "256 MB flush write between timed steps; inputs (>200 MB) exceed the 126 MB L2",
-                       "multi_gpu": "replicas only (one independent build per rank)" if world > 1 else "single GPU",
-                       "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_p", "sampler_rounds",
-                                                      "parent_rounds")} for i in infos]},
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "value_is": f"{a.sampler} sampler" + (" (the reference's own sample sets; the parity mode)" if a.sampler == "exact" else ""),
+            "other_sampler": other,
             "clocks": clk, "gpu_launches": int(launches),
             "e2e": {"value": world * n / (e2e * 1e-3) / 1e6, "unit": "Mverts/s", "ms_per_step": e2e,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "roofline": {"bound": "hbm",
-                         "kernel": f"level-0 stage '{names[dom]}' ({' + '.join(STAGE_KERNELS.get(names[dom], [names[dom]]))})",
+                         "kernel": f"level-0 '{dom}' ({' + '.join(STAGE_KERNELS.get(dom, [dom]))})",
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
-                         "algorithmic_bytes": int(bytes0), "stage_ms": float(stage_ms[0][dom]),
+                         "algorithmic_bytes": int(bytes0), "stage_ms": dom_ms,
+                         "per_stage_frac": {k: round(v[1] / (v[0] * 1e-3) / 1e9 / peak, 4) for k, v in cand.items() if v[0] > 0},
                          "whole_build": {"algorithmic_bytes": int(total_bytes),
                                          "achieved": total_bytes / (ms * 1e-3) / 1e9,
                                          "frac": total_bytes / (ms * 1e-3) / 1e9 / peak}},
-            "stage_ms": {f"L{l}": {names[s]: round(float(stage_ms[l][s]), 4) for s in range(9)}
+            "stage_ms": {f"L{l}": {names[s_]: round(float(stage_ms[l][s_]), 4) for s_ in range(9)}
                          for l in range(len(infos))}}
     if a.galerkin:
         # SpGEMM (P^T A P) of level 0 against the HBM roofline, from the build's own stage events
-        gi = names.index("galerkin")
-        gb = stage_bytes(infos[0])["galerkin"]
-        gms = float(stage_ms[0][gi])
+        gb = sb["galerkin"]
+        gms = float(stage_ms[0][names.index("galerkin")])
         line["spgemm"] = {"ms": gms, "algorithmic_bytes": int(gb), "achieved": gb / (gms * 1e-3) / 1e9, "unit": "GB/s",
-                          "frac": gb / (gms * 1e-3) / 1e9 / peak, "nnz_ac": int(infos[0]["nnz_ac"]),
-                          "what": "level-0 transpose + symbolic + numeric passes of A_c = P^T A P"}
+                          "frac": gb / (gms * 1e-3) / 1e9 / peak, "nnz_ac": int(i0["nnz_ac"]),
+                          "transpose_ms": float(gal_ms[0][0]), "symbolic_ms": float(gal_ms[0][1]), "numeric_ms": float(gal_ms[0][2]),
+                          "what": "level-0 transpose + symbolic + numeric passes of A_c = P^T A P (bytes: symbolic + numeric formulas of SURVEY.md 8(d))"}
+    h_exact = None
     if a.galerkin and a.vcycle:
         from gravomg_b200.capi import Solver, spmv
         h = Hierarchy(ctx, inp, levels, sampler_mode=mode, build_galerkin=True)
@@ -407,29 +538,55 @@ def run_b200(a, rank, world, local_rank):
         for _ in range(5):
             spmv(ctx, A.indptr, A.indices, A.data, xs)
             sp_ms.append(ctx.last_kernel_ms)
-        sb = 20 * n + 12 * A.nnz
+        sbytes = 20 * n + 12 * A.nnz
         sms = float(np.median(sp_ms))
-        line["spmv"] = {"ms": sms, "algorithmic_bytes": int(sb), "achieved": sb / (sms * 1e-3) / 1e9, "unit": "GB/s",
-                        "frac": sb / (sms * 1e-3) / 1e9 / peak, "what": "y = A x on the level-0 operator, device time"}
+        line["spmv"] = {"ms": sms, "algorithmic_bytes": int(sbytes), "achieved": sbytes / (sms * 1e-3) / 1e9, "unit": "GB/s",
+                        "frac": sbytes / (sms * 1e-3) / 1e9 / peak, "what": "y = A x on the level-0 operator, device time"}
         sol = Solver(ctx, inp, h)
         sol.vcycle(bvec, cycles=1)                                             # warm-up (colourings are built here)
         x1, res = sol.vcycle(bvec, cycles=1, pre=2, post=2)
         line["vcycle"] = {"ms": ctx.last_kernel_ms, "residual_before": float(res[0]), "residual_after": float(res[1]),
                           "reduction": float(res[1] / res[0]), "what": "one V(2,2) cycle on A x = b, multicolour Gauss-Seidel, "
                           "b = A x*, x* smooth; device time of the cycle"}
-        sol.close(); h.close()
+        sol.close()
+        if a.sampler == "exact":
+            h_exact = h
+        else:
+            h.close()
     if not a.no_cpu_baseline:
-        # bounded sample of the same workload on the host cores (about 10-30 s of CPU work)
-        scale = a.scale
-        while n * scale / a.scale / 0.25e6 > 30.0:
-            scale /= 4.0
-        c2 = cfg if scale == a.scale else meshgen.make_config(a.workload, scale)
-        dt, kind = cpu_hierarchy_seconds(c2["V"], c2["A"], levels)
+        # the reference's CPU code on the host cores, on the SAME workload at the same size by default: that run is
+        # then also the parity check (GPU hierarchy, exact sampler, against the CPU one: every array, bit for bit)
+        cscale = a.scale if a.cpu_scale is None else a.cpu_scale
+        same = cscale == a.scale
+        c2 = cfg if same else meshgen.make_config(a.workload, cscale)
+        radii = None
+        if same:
+            if h_exact is None:
+                h_exact = Hierarchy(ctx, inp, levels, sampler_mode=capi.SAMPLER_EXACT, build_galerkin=bool(a.galerkin))
+            radii = [i["radius"] for i in h_exact.info]
+        cpu_levels, sec, dt, kind = cpu_hierarchy(c2["V"], c2["A"], levels, galerkin=bool(a.galerkin), radii=radii)
         nn = c2["V"].shape[0]
         line["cpu_baseline"] = {"value": nn / dt / 1e6, "unit": "Mverts/s", "cores": 1, "kind": kind,
                                 "host_cores": os.cpu_count(), "seconds": dt,
-                                "sample": f"{a.workload} at scale {scale:g}: {nn} verts, whole {levels}-level hierarchy, "
-                                          f"one run, reference source on Eigen shim, -O2, 1 thread"}
+                                "stage_seconds": {k: round(v, 3) for k, v in sec.items()},
+                                "sample": f"{a.workload} at scale {cscale:g}: {nn} verts, whole {levels}-level hierarchy"
+                                          f"{' + A_c every level (our single-thread CSR product)' if a.galerkin else ''}, "
+                                          f"one run, reference sources on the Eigen shim, -O2, 1 thread"}
+        if a.galerkin:
+            line["cpu_baseline"]["solver"] = cpu_solver_seconds(c2["A"], cpu_levels)
+        if same:
+            try:
+                par = compare_with_cpu(h_exact, capi, cpu_levels, bool(a.galerkin))
+                line["parity_checked"] = len(par["mismatches"]) == 0
+                line["parity"] = par
+            except Exception as e:                                  # a failed comparison must not hide the numbers
+                line["parity_checked"] = False
+                line["parity"] = {"error": repr(e)}
+        else:
+            line["parity_checked"] = False
+            line["parity"] = {"skipped": "the CPU sample is a different size (--cpu-scale)"}
+    if h_exact is not None:
+        h_exact.close()
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -589,7 +746,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     line = {"metric": METRIC, "value": n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sampler": a.sampler, "galerkin": galerkin,
+            "config": {**bench_config(a, world),
                        "l2": "256 MB flush write between timed steps; inputs exceed the 126 MB L2",
                        "multi_gpu": (f"row-sharded over {world} ranks: owned ranges of fine vertices, replicated level "
                                      f"graph, {exchanges} NCCL all-gathers ({xbytes / 1e6:.1f} MB gathered per rank) per build")

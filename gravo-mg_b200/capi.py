@@ -266,7 +266,8 @@ class HierarchyOptions(C.Structure):
 class LevelInfo(C.Structure):
     _fields_ = [("n", C.c_int64), ("nnz", C.c_int64), ("m", C.c_int64), ("nnz_c", C.c_int64), ("T", C.c_int64),
                 ("nnz_p", C.c_int64), ("nnz_ac", C.c_int64), ("radius", C.c_double), ("sampler_rounds", C.c_int32),
-                ("parent_rounds", C.c_int32), ("stats", ProlongationStats), ("stage_ms", C.c_double * 9)]
+                ("parent_rounds", C.c_int32), ("stats", ProlongationStats), ("stage_ms", C.c_double * 9),
+                ("galerkin_ms", C.c_double * 3)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_p", "nnz_ac", "radius",
@@ -275,6 +276,7 @@ class LevelInfo(C.Structure):
         d["edges_found"] = self.stats.edges_found
         d["fallback_count"] = self.stats.fallback_count
         d["stage_ms"] = list(self.stage_ms)
+        d["galerkin_ms"] = list(self.galerkin_ms)
         return d
 
 

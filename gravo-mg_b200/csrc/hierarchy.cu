@@ -220,13 +220,16 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             status.raise_coarse();
             status.raise_prolong(n);
             // stage 8: Galerkin coarse operator
+            StageClock gclk(c);
             if (opt->build_galerkin) {
-                galerkin(c, a_n, a_colptr, a_rowidx, a_val, L->P, L->Ac);
+                for (int s = 0; s < 4; ++s) { cudaEvent_t e; GMG_CUDA(cudaEventCreate(&e)); gclk.ev.push_back(e); }
+                galerkin(c, a_n, a_colptr, a_rowidx, a_val, L->P, L->Ac, 0, -1, nullptr, gclk.ev.data());
                 L->info.nnz_ac = L->Ac.nnz;
             }
             clk.mark();
             sync(c);
             for (int s = 0; s < 9; ++s) L->info.stage_ms[s] = clk.ms(size_t(s));
+            for (int s = 0; s < 3; ++s) L->info.galerkin_ms[s] = opt->build_galerkin ? gclk.ms(size_t(s)) : 0.0;
 
             // next level's fine inputs
             n = m; nnz = L->coarse.nnz;

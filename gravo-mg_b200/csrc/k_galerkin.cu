@@ -8,15 +8,23 @@
 // which is exactly (P^T A P)(j,i) with A(l,k) read from outer vector k. No symmetry of A is assumed.
 //
 // One warp per coarse outer index i, in two steps that share the warp's shared memory:
-//   step 1  c(l) = sum_k P(k,i) * A(l,k)   R = P^T (CSR) lists the fine k with P(k,i) stored; 8 lanes per k
-//                                          walk A's outer vector k into a hash keyed by the FINE index l
-//   step 2  out(j) = sum_l c(l) * P(l,j)   one lane per distinct l adds the <= 3 entries of P's row l into a
-//                                          hash keyed by the COARSE index j
-// Grouping by l first means every row of P is expanded once per distinct l (~45 per coarse row) and not
-// once per (k, l) pair (~160): about 290 hash insertions per coarse row instead of 470. Pass 1 (symbolic)
-// runs both steps on keys only and counts distinct j, a scan sizes the result, pass 2 (numeric)
-// accumulates values, sorts the keys and writes the outer vector. Rows that outgrow the warp's tables go
-// to a block-wide single-table version of the plain triple loop.
+//   step 1  c(l) = sum_k P(k,i) * A(l,k)   R = P^T lists the fine k with P(k,i) stored (sorted ascending in shared
+//                                          memory); the products (k, q), q over A's outer vector k, are taken 32 at a
+//                                          time, one per lane, in (k, q) order
+//   step 2  out(j) = sum_l c(l) * P(l,j)   the distinct l sorted ascending, 32 per round, one per lane; entry t = 0, 1, 2
+//                                          of every row of P in turn
+// Grouping by l first means every row of P is expanded once per distinct l (~45 per coarse row) and not once per
+// (k, l) pair (~160). Keys are found with a shared-memory hash (atomicCAS on the key only). VALUES are accumulated
+// WITHOUT atomics: shared-memory atomicAdd(double) is a compare-and-swap loop on this architecture (ATOMS.CAST.SPIN
+// in the SASS; the first version spent 86 % of its time there). Instead the lanes of one group of 32 that hold the
+// same key find each other with __match_any_sync, the lowest lane adds the group's values in lane order and does a
+// plain read-modify-write of the slot -- distinct keys own distinct slots. The summation order is therefore FIXED
+// (products in (k, q) order, then l ascending; inside a group of 32 equal keys are summed first), the result is
+// reproducible bit for bit, and the CPU checker (oracle/solver_oracle.c) follows the same association.
+// Pass 1 (symbolic) runs both steps on keys only and counts distinct j, a scan sizes the result, pass 2 (numeric)
+// computes the values, sorts the keys and writes the outer vector. Rows that outgrow the warp's tables (more than
+// 64 rows of P per column, 192 distinct l or 96 distinct j) go to a block-wide single-table version of the plain
+// triple loop with atomics (not bit-reproducible; none on the BASELINE meshes).
 // Algorithmic bytes: symbolic 12n + 4nnzA + 8nnzP + 4m; numeric 12n + 12nnzA + 24nnzP + 4m + 12nnzAc.
 #include "stages.h"
 
@@ -78,7 +86,7 @@ __global__ void __launch_bounds__(kBlock) sort_rows_kernel(int32_t rows, const i
     }
 }
 
-void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, int32_t c_hi) {
+void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, int32_t c_hi, bool sort_rows) {
     if (c_hi < 0) c_hi = P.cols;
     const bool all = c_lo == 0 && c_hi == P.cols;
     R.rows = c_hi - c_lo; R.cols = P.rows;
@@ -98,7 +106,7 @@ void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, i
     if (P.rows > 0) GMG_LAUNCH(c, transpose_fill_kernel, div_up(P.rows, kBlock), kBlock, 0, P.rows, P.rowptr.p, P.colidx.p,
                                P.val.p, c_lo, c_hi, R.rowptr.p, count.p, R.colidx.p, R.val.p);
     tr.mark("fill");
-    if (R.rows > 0) GMG_LAUNCH(c, sort_rows_kernel, div_up(int64_t(R.rows) * 32, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
+    if (R.rows > 0 && sort_rows) GMG_LAUNCH(c, sort_rows_kernel, div_up(int64_t(R.rows) * 32, kBlock), kBlock, 0, R.rows, R.rowptr.p, R.colidx.p, R.val.p);
     tr.mark("sort rows");
 }
 
@@ -198,93 +206,202 @@ __device__ __forceinline__ int hash_insert(int32_t* keys, int32_t key, int32_t* 
     return -1;
 }
 
-// Two-step row for ONE WARP (see the header comment). scount[0], scount[1]: distinct fine / coarse keys.
-template <bool NUMERIC, int FSLOTS, int SLOTS>
-__device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int32_t i, int lane, int32_t* fkeys,
-                                                      double* fvals, int32_t* keys, double* vals, int32_t* scount) {
-    for (int s = lane; s < FSLOTS; s += 32) { fkeys[s] = -1; if (NUMERIC) fvals[s] = 0.0; }
-    for (int s = lane; s < SLOTS; s += 32) { keys[s] = -1; if (NUMERIC) vals[s] = 0.0; }
-    if (lane < 2) scount[lane] = 0;
-    __syncwarp();
-    // step 1: fine-keyed
-    constexpr int kSub = 8;
-    bool full = false;
+constexpr int kGWarpSlots = 128;
+constexpr int kGFineSlots = 256;
+constexpr int kGBlockSlots = 2048;
+constexpr int kGMaxR = 64;            // rows of P per coarse column the warp path stages
+
+struct GalerkinWarpSmem {
+    int32_t fkeys[kGFineSlots];
+    int32_t keys[kGWarpSlots];
+    int32_t rk[kGMaxR];               // fine rows k of R's row i, ascending
+    int32_t rbase[kGMaxR + 1];        // exclusive scan of the lengths of A's outer vectors k
+    int32_t scount[2];                // distinct fine / coarse keys
+};
+struct GalerkinWarpVals {
+    double fvals[kGFineSlots];
+    double vals[kGWarpSlots];
+    double rp[kGMaxR];                // P(k, i)
+};
+
+// Add v to acc[slot] for every lane with valid == true; lanes holding the same key are summed first, in lane
+// order, by the lowest of them (see the header comment). All 32 lanes must call.
+__device__ __forceinline__ void group_accumulate(bool valid, int32_t key, int slot, double v, double* acc, int lane) {
+    const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : -1 - lane);
+    const bool leader = valid && (__ffs(grp) - 1) == lane;
+    const int longest = __reduce_max_sync(0xffffffffu, valid ? __popc(grp) : 0);
+    unsigned rest = grp;
+    double partial = 0.0;
+    for (int it = 0; it < longest; ++it) {
+        const int src = rest ? __ffs(rest) - 1 : lane;
+        const double o = __shfl_sync(0xffffffffu, v, src);
+        if (rest) partial = it == 0 ? o : partial + o;
+        rest &= rest - 1;
+    }
+    if (leader) acc[slot] = acc[slot] + partial;
+}
+
+// Two-step row for ONE WARP (see the header comment).
+template <bool NUMERIC>
+__device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int32_t i, int lane, GalerkinWarpSmem& sm,
+                                                      GalerkinWarpVals* sv) {
     const int32_t rb = __ldg(a.r_ptr + i), re = __ldg(a.r_ptr + i + 1);
-    for (int32_t e = rb + lane / kSub; e < re; e += 32 / kSub) {
-        const int32_t k = __ldg(a.r_col + e);
-        const double pki = NUMERIC ? __ldg(a.r_val + e) : 0.0;
-        const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
-        for (int32_t q = ab + lane % kSub; q < ae; q += kSub) {
-            const int s = hash_insert<FSLOTS>(fkeys, __ldg(a.a_idx + q), scount);
-            if (s < 0) { full = true; break; }
-            if (NUMERIC) atomicAdd(fvals + s, pki * __ldg(a.a_val + q));
+    const int32_t nr = re - rb;
+    if (nr > kGMaxR) return false;
+    for (int s = lane; s < kGFineSlots; s += 32) { sm.fkeys[s] = -1; if (NUMERIC) sv->fvals[s] = 0.0; }
+    for (int s = lane; s < kGWarpSlots; s += 32) { sm.keys[s] = -1; if (NUMERIC) sv->vals[s] = 0.0; }
+    if (lane < 2) sm.scount[lane] = 0;
+    // ---- R's row: sorted by fine row (the transpose fills it in arrival order), with the scan of the lengths of
+    //      A's outer vectors, which numbers the products
+    {
+        int32_t k0 = 0x7fffffff, k1 = 0x7fffffff;
+        double p0 = 0.0, p1 = 0.0;
+        if (lane < nr) { k0 = __ldg(a.r_col + rb + lane); if (NUMERIC) p0 = __ldg(a.r_val + rb + lane); }
+        if (lane + 32 < nr) { k1 = __ldg(a.r_col + rb + lane + 32); if (NUMERIC) p1 = __ldg(a.r_val + rb + lane + 32); }
+        sm.rbase[lane] = k0; sm.rbase[lane + 32] = k1;        // scratch: the unsorted keys
+        __syncwarp();
+        int32_t rank0 = 0, rank1 = 0;
+        for (int32_t e = 0; e < nr; ++e) { const int32_t o = sm.rbase[e]; rank0 += o < k0 ? 1 : 0; rank1 += o < k1 ? 1 : 0; }
+        __syncwarp();
+        if (lane < nr) { sm.rk[rank0] = k0; if (NUMERIC) sv->rp[rank0] = p0; }
+        if (lane + 32 < nr) { sm.rk[rank1] = k1; if (NUMERIC) sv->rp[rank1] = p1; }
+        __syncwarp();
+        // lengths, inclusive scan over 64 entries held two per lane (entry 2*lane, 2*lane + 1)
+        const int32_t e0 = 2 * lane, e1 = 2 * lane + 1;
+        int32_t d0 = 0, d1 = 0;
+        if (e0 < nr) { const int32_t k = sm.rk[e0]; d0 = __ldg(a.a_ptr + k + 1) - __ldg(a.a_ptr + k); }
+        if (e1 < nr) { const int32_t k = sm.rk[e1]; d1 = __ldg(a.a_ptr + k + 1) - __ldg(a.a_ptr + k); }
+        int32_t incl = d0 + d1;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        sm.rbase[e0] = incl - d0 - d1;
+        sm.rbase[e1] = incl - d1;
+        if (lane == 31) sm.rbase[kGMaxR] = incl;
+        __syncwarp();
+    }
+    const int32_t np = sm.rbase[kGMaxR];
+    // ---- step 1: fine-keyed, 32 products per sub-step
+    bool full = false;
+    for (int32_t p0 = 0; p0 < np; p0 += 32) {
+        const int32_t pos = p0 + lane;
+        const bool valid = pos < np;
+        int32_t l = 0;
+        double w = 0.0;
+        int slot = -1;
+        if (valid) {
+            int32_t lo = 0, hi = nr;                 // last e with rbase[e] <= pos
+            while (hi - lo > 1) { const int32_t mid = (lo + hi) >> 1; if (sm.rbase[mid] <= pos) lo = mid; else hi = mid; }
+            const int32_t k = sm.rk[lo];
+            const int32_t q = __ldg(a.a_ptr + k) + (pos - sm.rbase[lo]);
+            l = __ldg(a.a_idx + q);
+            if (NUMERIC) w = sv->rp[lo] * __ldg(a.a_val + q);
+            slot = hash_insert<kGFineSlots>(sm.fkeys, l, sm.scount);
+            if (slot < 0) full = true;
+        }
+        if (NUMERIC) {
+            group_accumulate(valid && slot >= 0, l, slot, w, sv->fvals, lane);
+            __syncwarp();
         }
     }
     __syncwarp();
-    if (__any_sync(0xffffffffu, full) || scount[0] > FSLOTS * 3 / 4) return false;
+    if (__any_sync(0xffffffffu, full) || sm.scount[0] > kGFineSlots * 3 / 4) return false;
     // compact the occupied fine slots to the front (in place, chunk read before chunk written)
     int32_t kf = 0;
-    for (int s0 = 0; s0 < FSLOTS; s0 += 32) {
-        const int32_t key = fkeys[s0 + lane];
-        const double v = NUMERIC ? fvals[s0 + lane] : 0.0;
+    for (int s0 = 0; s0 < kGFineSlots; s0 += 32) {
+        const int32_t key = sm.fkeys[s0 + lane];
+        const double v = NUMERIC ? sv->fvals[s0 + lane] : 0.0;
         const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
         __syncwarp();
-        if (key >= 0) { const int pos = kf + __popc(occ & ((1u << lane) - 1u)); fkeys[pos] = key; if (NUMERIC) fvals[pos] = v; }
+        if (key >= 0) { const int pos = kf + __popc(occ & ((1u << lane) - 1u)); sm.fkeys[pos] = key; if (NUMERIC) sv->fvals[pos] = v; }
         kf += __popc(occ);
         __syncwarp();
     }
-    // step 2: coarse-keyed, one lane per distinct fine index
-    for (int32_t f = lane; f < kf; f += 32) {
-        const int32_t l = fkeys[f];
-        const double cl = NUMERIC ? fvals[f] : 0.0;
-        const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
-        for (int32_t t = pb; t < pe; ++t) {
-            const int s = hash_insert<SLOTS>(keys, __ldg(a.p_col + t), scount + 1);
-            if (s < 0) { full = true; break; }
-            if (NUMERIC) atomicAdd(vals + s, cl * __ldg(a.p_val + t));
+    if (NUMERIC) {
+        // sort the distinct fine indices ascending (through registers: rank every entry, then write it back)
+        constexpr int kPer = kGFineSlots * 3 / 4 / 32;      // entries per lane
+        int32_t key[kPer], rank[kPer];
+        double val[kPer];
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int f = lane + 32 * u;
+            key[u] = f < kf ? sm.fkeys[f] : 0x7fffffff;
+            val[u] = f < kf ? sv->fvals[f] : 0.0;
+            rank[u] = 0;
+        }
+        for (int32_t f = 0; f < kf; ++f) {
+            const int32_t o = sm.fkeys[f];
+#pragma unroll
+            for (int u = 0; u < kPer; ++u) rank[u] += o < key[u] ? 1 : 0;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < kPer; ++u)
+            if (lane + 32 * u < kf) { sm.fkeys[rank[u]] = key[u]; sv->fvals[rank[u]] = val[u]; }
+        __syncwarp();
+    }
+    // ---- step 2: coarse-keyed, one lane per distinct fine index, entry t of every row of P in turn
+    for (int32_t f0 = 0; f0 < kf; f0 += 32) {
+        const int32_t f = f0 + lane;
+        int32_t pb = 0, pe = 0;
+        double cl = 0.0;
+        if (f < kf) {
+            const int32_t l = sm.fkeys[f];
+            pb = __ldg(a.p_ptr + l); pe = __ldg(a.p_ptr + l + 1);
+            if (NUMERIC) cl = sv->fvals[f];
+        }
+        const int32_t longest = __reduce_max_sync(0xffffffffu, pe - pb);
+        for (int32_t t = 0; t < longest; ++t) {
+            const bool valid = pb + t < pe;
+            int32_t j = 0;
+            int slot = -1;
+            if (valid) {
+                j = __ldg(a.p_col + pb + t);
+                slot = hash_insert<kGWarpSlots>(sm.keys, j, sm.scount + 1);
+                if (slot < 0) full = true;
+            }
+            if (NUMERIC) {
+                const double v = valid ? cl * __ldg(a.p_val + pb + t) : 0.0;
+                group_accumulate(valid && slot >= 0, j, slot, v, sv->vals, lane);
+                __syncwarp();
+            }
         }
     }
     __syncwarp();
-    const int32_t K = scount[1];
-    if (__any_sync(0xffffffffu, full) || K > SLOTS * 3 / 4) return false;
+    const int32_t K = sm.scount[1];
+    if (__any_sync(0xffffffffu, full) || K > kGWarpSlots * 3 / 4) return false;
     if (!NUMERIC) { if (lane == 0) a.out_count[i] = K; return true; }
     const int32_t off = __ldg(a.out_ptr + i);
     int32_t base = 0;
-    for (int s0 = 0; s0 < SLOTS; s0 += 32) {
-        const int32_t key = keys[s0 + lane];
-        const double v = vals[s0 + lane];
+    for (int s0 = 0; s0 < kGWarpSlots; s0 += 32) {
+        const int32_t key = sm.keys[s0 + lane];
+        const double v = sv->vals[s0 + lane];
         const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
         __syncwarp();
-        if (key >= 0) { const int pos = base + __popc(occ & ((1u << lane) - 1u)); keys[pos] = key; vals[pos] = v; }
+        if (key >= 0) { const int pos = base + __popc(occ & ((1u << lane) - 1u)); sm.keys[pos] = key; sv->vals[pos] = v; }
         base += __popc(occ);
         __syncwarp();
     }
     for (int s = lane; s < K; s += 32) {
-        const int32_t key = keys[s];
+        const int32_t key = sm.keys[s];
         int32_t rank = 0;
-        for (int s2 = 0; s2 < K; ++s2) rank += keys[s2] < key ? 1 : 0;
+        for (int s2 = 0; s2 < K; ++s2) rank += sm.keys[s2] < key ? 1 : 0;
         a.out_idx[off + rank] = key;
-        a.out_val[off + rank] = vals[s];
+        a.out_val[off + rank] = sv->vals[s];
     }
     return true;
 }
 
-constexpr int kGWarpSlots = 128;
-constexpr int kGFineSlots = 256;
-constexpr int kGBlockSlots = 2048;
-
 template <bool NUMERIC>
 __global__ void __launch_bounds__(kBlock) galerkin_warp_kernel(GalerkinArgs a) {
-    __shared__ int32_t fkeys[kBlock / 32][kGFineSlots];
-    __shared__ int32_t keys[kBlock / 32][kGWarpSlots];
-    __shared__ double fvals[NUMERIC ? kBlock / 32 : 1][NUMERIC ? kGFineSlots : 1];
-    __shared__ double vals[NUMERIC ? kBlock / 32 : 1][NUMERIC ? kGWarpSlots : 1];
-    __shared__ int32_t scount[kBlock / 32][2];
+    __shared__ GalerkinWarpSmem sm[kBlock / 32];
+    __shared__ GalerkinWarpVals sv[NUMERIC ? kBlock / 32 : 1];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t i = int64_t(blockIdx.x) * (kBlock / 32) + w;
     if (i >= a.m) return;
-    if (!galerkin_row_two_step<NUMERIC, kGFineSlots, kGWarpSlots>(a, int32_t(i), lane, fkeys[w], NUMERIC ? fvals[w] : nullptr,
-                                                                  keys[w], NUMERIC ? vals[w] : nullptr, scount[w])) {
+    if (!galerkin_row_two_step<NUMERIC>(a, int32_t(i), lane, sm[w], NUMERIC ? &sv[w] : nullptr)) {
         // symbolic pass records the overflow; the numeric pass skips rows already on the list
         if (!NUMERIC && lane == 0) { a.out_count[i] = 0; a.overflow[atomicAdd(a.flags + 1, 1)] = int32_t(i); }
     }
@@ -305,18 +422,25 @@ __global__ void __launch_bounds__(kBlock) galerkin_block_kernel(GalerkinArgs a, 
 }
 
 void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
-              const DeviceCsr& P, DeviceCsc& Ac, int32_t c_lo, int32_t c_hi, DeviceCsr* keep_R) {
+              const DeviceCsr& P, DeviceCsc& Ac, int32_t c_lo, int32_t c_hi, DeviceCsr* keep_R, cudaEvent_t* marks) {
     GMG_REQUIRE(P.rows == n, GMG_ERR_INVALID, "galerkin: P and A sizes disagree");
     if (c_hi < 0) c_hi = P.cols;
     const int32_t m = c_hi - c_lo;     // outer vectors computed here; Ac is indexed from c_lo
     Ac.n = m;
     Ac.colptr.alloc(c, int64_t(m) + 1);
-    if (m == 0) { Ac.colptr.zero(); Ac.rowidx.alloc(c, 0); Ac.val.alloc(c, 0); Ac.nnz = 0; return; }
+    if (m == 0) {
+        Ac.colptr.zero(); Ac.rowidx.alloc(c, 0); Ac.val.alloc(c, 0); Ac.nnz = 0;
+        if (marks) for (int s = 0; s < 4; ++s) cudaEventRecord(marks[s], c->stream);
+        return;
+    }
     DeviceCsr R_local;
     DeviceCsr& R = keep_R ? *keep_R : R_local;
     Trace tr(c, "galerkin");
-    transpose_csr(c, P, R, c_lo, c_hi);
+    if (marks) cudaEventRecord(marks[0], c->stream);
+    // the warp kernel sorts R's rows itself while it stages them; a restriction that is KEPT is sorted once here
+    transpose_csr(c, P, R, c_lo, c_hi, keep_R != nullptr);
     tr.mark("transpose");
+    if (marks) cudaEventRecord(marks[1], c->stream);
     DevBuf<int32_t> count(c, int64_t(m) + 1), flags(c, 4), overflow(c, m);
     DevBuf<int64_t> total(c, 1);
     count.zero(); flags.zero();
@@ -341,6 +465,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     total.download(&Ac.nnz, 1);
     sync(c);
     tr.mark("symbolic");
+    if (marks) cudaEventRecord(marks[2], c->stream);
     GMG_REQUIRE(Ac.nnz < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: A_c exceeds 32-bit indexing");
     Ac.rowidx.alloc(c, Ac.nnz);
     Ac.val.alloc(c, Ac.nnz);
@@ -349,6 +474,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     GMG_LAUNCH(c, galerkin_warp_kernel<true>, grid, kBlock, 0, a);
     if (n_over > 0) GMG_LAUNCH(c, galerkin_block_kernel<true>, ogrid, kBlock, 0, a, n_over);
     tr.mark("numeric");
+    if (marks) cudaEventRecord(marks[3], c->stream);
 }
 
 }  // namespace gmg

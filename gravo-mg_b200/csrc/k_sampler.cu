@@ -43,7 +43,7 @@ constexpr int kStage = 16;   // later-path targets a lane can stage in shared me
 // xor-seed, then (odd multiply, xorshift by ceil(kt/2)) twice and a last odd multiply, all modulo 2^kt; every
 // step is a bijection on kt bits and the xorshift is its own inverse because twice the shift is >= kt.
 //   GMG_SAMPLER_HASHED    tshift = 0: every vertex hashed, dependency depth O(log n)
-//   GMG_SAMPLER_PARALLEL  tshift = ceil(log2(n / 4)): the reference's index-order sweep restarted in 2-4
+//   GMG_SAMPLER_PARALLEL  tshift = ceil(log2(n / 3)): the reference's index-order sweep restarted in 2-3
 //                         super-tiles taken in hashed order (why: DESIGN.md section 4, "sampler orders")
 struct Order {
     uint32_t mask, shift, seed;
@@ -77,7 +77,7 @@ static Order make_order(int32_t n, uint64_t seed, int mode) {
         o.kbits = uint32_t(ceil_log2(n > 1 ? n : 2));
         return o;
     }
-    o.tshift = mode == GMG_SAMPLER_PARALLEL ? uint32_t(ceil_log2((int64_t(n) + 3) / 4)) : 0u;
+    o.tshift = mode == GMG_SAMPLER_PARALLEL ? uint32_t(ceil_log2((int64_t(n) + 2) / 3)) : 0u;
     const int64_t tiles = (int64_t(n) + (int64_t(1) << o.tshift) - 1) >> o.tshift;
     const int kt = ceil_log2(tiles);
     o.mask = kt >= 32 ? 0xFFFFFFFFu : ((1u << kt) - 1u);
@@ -103,7 +103,8 @@ constexpr int kTileLog = 12;
 constexpr int kTile = 1 << kTileLog;          // ranks per flow tile
 constexpr int kFlowThreads = 1024;
 constexpr int kOwn = kTile / kFlowThreads;    // ranks per thread
-constexpr int kListCap = 49152;               // same-tile list entries (uint16) a block can stage
+constexpr int kListCap = 40960;               // same-tile list entries (uint16) a block can stage
+constexpr int kExtCap = 16384;                // other-tile list entries (uint32) a block can stage
 constexpr uint32_t kOutFlag = 0x80000000u;
 constexpr uint32_t kUnpartitioned = 0xFFFFu;
 
@@ -124,7 +125,20 @@ struct SamplerArgs {
     unsigned int tiles;          // flow tiles: ceil(ranks / kTile)
     uint8_t* res;                // [ranks] 1 = selected
     int32_t* flags;              // [0] a vertex has more than 65535 list entries
+    unsigned long long* stats;   // [0] same-tile list entries, [1] all list entries (decides which flow kernel runs)
+    unsigned int* epoch;         // bumped by a tile after every push of other-tile effects: what waiting tiles watch
+    int force_lane;              // GMG_SAMPLER_HASHED: no tile ever holds two coverers, always the per-lane flow
 };
+
+// Which flow kernel runs is decided ON THE DEVICE from the build kernel's counts (no host round trip): the
+// tile-cooperative kernel pays off when at least a quarter of the list entries stay inside a flow tile, i.e.
+// when the precedence order is spatially coherent (grids, Morton orders, the coarse levels of such meshes).
+__device__ __forceinline__ bool use_lane_flow(const SamplerArgs& a) {
+    if (a.force_lane) return true;
+    const unsigned long long same = *(volatile unsigned long long*)(a.stats + 0);
+    const unsigned long long all = *(volatile unsigned long long*)(a.stats + 1);
+    return same * 4ull < all;
+}
 
 template <int MODE> __device__ __forceinline__ uint32_t rank_of(const SamplerArgs& a, int32_t v) {
     return MODE == GMG_SAMPLER_EXACT ? uint32_t(v) : order_rank(a.order, uint32_t(v));
@@ -176,6 +190,8 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     __shared__ unsigned long long s_base;
     __shared__ uint32_t s_stage[kBlock][kStage + 1];   // +1: conflict-free lane-private rows
     __shared__ uint8_t s_mult[kBlock][kStage];         // 0: merged into an earlier entry, else its multiplicity
+    __shared__ int32_t s_same;
+    if (threadIdx.x == 0) s_same = 0;
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t i = int32_t(gid / kLanes);
     const int sub = threadIdx.x % kLanes;
@@ -188,7 +204,7 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
         uint32_t* stage = s_stage[threadIdx.x];
         for_each_covered(a, i, sub, [&](int32_t t) {
             const uint32_t rt = rank_of<MODE>(a, t);
-            if (rt < ri) { if ((rt >> kTileLog) == (ri >> kTileLog)) ++prev_in; else ++prev_ext; }
+            if (rt < ri) { if (!a.force_lane && (rt >> kTileLog) == (ri >> kTileLog)) ++prev_in; else ++prev_ext; }
             else { if (later < kStage) stage[later] = rt; ++later; }
         });
     }
@@ -222,7 +238,7 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
             const bool keep = (ordinal & (cap - 1u)) == 0u;
             const uint32_t mult = keep ? (total - ordinal < cap ? total - ordinal : cap) : 0u;
             s_mult[threadIdx.x][e] = uint8_t(mult);
-            if (keep) { ++kept; if ((x >> kTileLog) == (ri >> kTileLog)) ++kept_in; }
+            if (keep) { ++kept; if (!a.force_lane && (x >> kTileLog) == (ri >> kTileLog)) ++kept_in; }
         }
     }
     const int32_t own = group_over ? later : kept;
@@ -237,6 +253,7 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     const int32_t group_in = __shfl_sync(0xffffffffu, incl_in, kLanes - 1, kLanes);
     if (sub == 0) s_group[g] = group_total;
     __syncthreads();
+    if (sub == 0 && group_in > 0) atomicAdd(&s_same, group_in);
     if (threadIdx.x < 32) {
         const int32_t v = s_group[threadIdx.x];
         int32_t s = v;
@@ -246,9 +263,10 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
             if (int(threadIdx.x) >= d) s += t;
         }
         s_group[threadIdx.x] = s - v;
-        if (threadIdx.x == 31) s_base = atomicAdd(a.cursor, (unsigned long long)s);
+        if (threadIdx.x == 31) { s_base = atomicAdd(a.cursor, (unsigned long long)s); if (s) atomicAdd(a.stats + 1, (unsigned long long)s); }
     }
     __syncthreads();
+    if (threadIdx.x == 0 && s_same > 0) atomicAdd(a.stats + 0, (unsigned long long)s_same);
     if (!active) return;
     const long long start = (long long)s_base + s_group[g];
     if (!group_over) {
@@ -261,7 +279,7 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
             if (!mult) continue;
             const uint32_t x = stage[e];
             const uint32_t packed = x | ((mult - 1u) << a.order.kbits);
-            if ((x >> kTileLog) == (ri >> kTileLog)) *dst_in++ = packed; else *dst_ext++ = packed;
+            if (!a.force_lane && (x >> kTileLog) == (ri >> kTileLog)) *dst_in++ = packed; else *dst_ext++ = packed;
         }
     } else {                                          // some lane of this vertex outgrew its stage: walk again
         uint32_t* dst = a.lst + start + (incl - own);
@@ -280,24 +298,33 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
 }
 
 // The flow: a vertex is IN once every preceding coverer is OUT (both path counters at 0), OUT once a preceding
-// coverer is IN. A block takes flow TILES (kTile consecutive ranks) by ticket, so every tile that precedes a
-// running tile is running or done and the waits below always end. Inside a tile the decisions travel through
-// SHARED memory: the tile's same-tile lists are staged there once (they are static), the same-tile counters
-// live there, and a round -- every thread looks at its undecided ranks, a newly decided rank applies its
-// same-tile list -- costs two barriers instead of a round trip through L2. That is what the index order of a
-// coherent numbering needs: on a row-major 10000 x 1000 grid a tile is four rows, its preceding coverers sit in
-// the tile before it, and the dependency chain (24,000 steps at level 0) is walked at shared-memory speed.
+// coverer is IN. Two kernels; which one does the work is decided on the device (use_lane_flow).
+//
+// (1) TILE flow, for spatially coherent orders. A block takes flow TILES (kTile consecutive ranks) by ticket, so
+// every tile that precedes a running tile is running or done and the waits below always end. Inside a tile the
+// decisions travel through SHARED memory: both halves of the tile's lists are staged there once (they are
+// static, so this happens BEFORE the tile has anything to wait for), the same-tile counters live there, and a
+// round -- every thread looks at its undecided ranks, a newly decided rank applies its same-tile list -- costs a
+// barrier instead of a round trip through L2. That is what the index order of a coherent numbering needs: on a
+// row-major 10000 x 1000 grid a tile is four rows, its preceding coverers sit in the tile before it, and the
+// dependency chain (24,000 steps at level 0) is walked at shared-memory speed.
 // What crosses tiles goes through the global words: a selected rank ORs the OUT bit into its later coverees, a
-// rejected one subtracts its multiplicity, both without a return value; the owner of a rank polls one word.
-// With a hashed order nearly every target is in another tile and the kernel is a coalesced poll / push loop.
+// rejected one subtracts its multiplicity, both without a return value. A tile that can make no progress does
+// not poll its 4096 words (148 waiting tiles doing that saturate the L2 and slow the one tile everybody waits
+// for): after every push a tile bumps ONE global epoch word, and a waiting tile watches that word only.
+//
+// (2) LANE flow, for incoherent orders (hashed priorities, subdivision orders): nearly every target sits in
+// another tile, the dependency depth is O(log n), and one rank per lane with no block-wide barriers is faster.
 template <int MODE>
 __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerArgs a) {
     extern __shared__ unsigned char smem_raw[];
     int32_t* s_rem = reinterpret_cast<int32_t*>(smem_raw);                       // kTile same-tile path counters
-    uint16_t* s_list = reinterpret_cast<uint16_t*>(s_rem + kTile);               // kListCap staged entries
+    uint32_t* s_ext = reinterpret_cast<uint32_t*>(s_rem + kTile);                // kExtCap staged other-tile entries
+    uint16_t* s_list = reinterpret_cast<uint16_t*>(s_ext + kExtCap);             // kListCap staged same-tile entries
     uint8_t* s_hit = reinterpret_cast<uint8_t*>(s_list + kListCap);              // kTile: knocked OUT inside the tile
-    __shared__ int32_t s_warp[kFlowThreads / 32];
-    __shared__ unsigned int s_tile;
+    __shared__ int32_t s_warp[2][kFlowThreads / 32];
+    __shared__ unsigned int s_tile, s_epoch;
+    if (use_lane_flow(a)) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
@@ -310,9 +337,9 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         const uint32_t t0 = tile << kTileLog;
         // ---- static data of the tile's ranks; rank i of the tile belongs to thread i % kFlowThreads
         long long ptr[kOwn];
-        uint32_t tot[kOwn], nin[kOwn], soff[kOwn];
+        uint32_t tot[kOwn], nin[kOwn], soff[kOwn], xoff[kOwn];
         uint8_t st[kOwn];              // 0 undecided, 1 IN, 2 OUT; | 4 same-tile list applied; | 8 other-tile list applied
-        int32_t mine = 0;              // same-tile list entries this thread wants to stage
+        int32_t mine = 0, mine_x = 0;  // same-tile / other-tile list entries this thread wants to stage
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
             const int i = tid + q * kFlowThreads;
@@ -324,57 +351,70 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 const uint32_t lc = a.lcnt[r];
                 ptr[q] = a.lptr[r]; tot[q] = lc & 0xFFFFu; nin[q] = lc >> 16; st[q] = 0;
                 rem = int32_t(a.cint[r]);
-                if (nin[q] != kUnpartitioned) mine += int32_t(nin[q]);
+                if (nin[q] != kUnpartitioned) { mine += int32_t(nin[q]); mine_x += int32_t(tot[q] - nin[q]); }
             }
             s_rem[i] = rem;
             s_hit[i] = 0;
         }
-        // shared-memory segments for the same-tile parts of the lists: block-wide exclusive scan over the threads
+        // shared-memory segments for the two halves of the lists: block-wide exclusive scans over the threads
         {
-            int32_t s = mine;
+            int32_t s = mine, sx = mine_x;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const int32_t t = __shfl_up_sync(0xffffffffu, s, d);
-                if (lane >= d) s += t;
+                const int32_t tx = __shfl_up_sync(0xffffffffu, sx, d);
+                if (lane >= d) { s += t; sx += tx; }
             }
-            if (lane == 31) s_warp[warp] = s;
+            if (lane == 31) { s_warp[0][warp] = s; s_warp[1][warp] = sx; }
             __syncthreads();
-            if (warp == 0) {
-                const int32_t v = s_warp[lane];
+            if (warp < 2) {
+                const int32_t v = s_warp[warp][lane];
                 int32_t w = v;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
                     const int32_t t = __shfl_up_sync(0xffffffffu, w, d);
                     if (lane >= d) w += t;
                 }
-                s_warp[lane] = w - v;
+                s_warp[warp][lane] = w - v;
             }
             __syncthreads();
-            int32_t off = s_warp[warp] + (s - mine);
+            int32_t off = s_warp[0][warp] + (s - mine), offx = s_warp[1][warp] + (sx - mine_x);
 #pragma unroll
             for (int q = 0; q < kOwn; ++q) {
-                const int32_t want = ((st[q] & 3) == 0 && nin[q] != kUnpartitioned) ? int32_t(nin[q]) : 0;
+                const bool part = (st[q] & 3) == 0 && nin[q] != kUnpartitioned;
+                const int32_t want = part ? int32_t(nin[q]) : 0, wantx = part ? int32_t(tot[q] - nin[q]) : 0;
                 soff[q] = (want > 0 && off + want <= kListCap) ? uint32_t(off) : 0xFFFFFFFFu;
-                off += want;
+                xoff[q] = (wantx > 0 && offx + wantx <= kExtCap) ? uint32_t(offx) : 0xFFFFFFFFu;
+                off += want; offx += wantx;
             }
         }
-        // ---- stage the same-tile lists as uint16: offset in the tile | (multiplicity - 1) << 12
+        // ---- stage the lists: same-tile entries as uint16 (offset in the tile | (multiplicity - 1) << 12), the
+        //      others as they are
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
-            if (soff[q] == 0xFFFFFFFFu) continue;
-            for (uint32_t e = 0; e < nin[q]; ++e) {
-                const uint32_t x = a.lst[ptr[q] + e];
-                s_list[soff[q] + e] = uint16_t(((x & rmask) - t0) | ((x >> a.order.kbits) << kTileLog));
-            }
+            if (soff[q] != 0xFFFFFFFFu)
+                for (uint32_t e = 0; e < nin[q]; ++e) {
+                    const uint32_t x = a.lst[ptr[q] + e];
+                    s_list[soff[q] + e] = uint16_t(((x & rmask) - t0) | ((x >> a.order.kbits) << kTileLog));
+                }
+            if (xoff[q] != 0xFFFFFFFFu)
+                for (uint32_t e = nin[q]; e < tot[q]; ++e) s_ext[xoff[q] + (e - nin[q])] = a.lst[ptr[q] + e];
         }
         __syncthreads();
         // ---- the flow
-        unsigned ns = 0;
-        for (;;) {
-            uint32_t ext[kOwn];
+        uint32_t ext[kOwn];
 #pragma unroll
-            for (int q = 0; q < kOwn; ++q)
-                ext[q] = (st[q] & 3) == 0 ? *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads) : 0u;
+        for (int q = 0; q < kOwn; ++q) ext[q] = (st[q] & 3) == 0 ? 1u : 0u;        // 1: not polled yet
+        unsigned int seen = 0;
+        for (;;) {
+            // the epoch is read BEFORE the words: a push that lands after this poll bumps it afterwards
+            if (tid == 0) s_epoch = *(volatile unsigned int*)a.epoch;
+            __syncthreads();
+            seen = s_epoch;
+            __threadfence();
+#pragma unroll
+            for (int q = 0; q < kOwn; ++q)      // a word that has reached 0 has no outside coverer left and stays 0
+                if ((st[q] & 3) == 0 && ext[q] != 0u) ext[q] = *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads);
             for (;;) {                                          // rounds inside the tile, shared memory only
                 bool changed = false;
 #pragma unroll
@@ -418,21 +458,84 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 if ((st[q] & 3) == 0) { all = false; continue; }
                 if (st[q] & 8) continue;
                 st[q] |= 8;
-                progress = true;
                 const bool in = (st[q] & 3) == 1;
                 const bool raw = nin[q] == kUnpartitioned;
-                for (uint32_t e = raw ? 0u : nin[q]; e < tot[q]; ++e) {
-                    const uint32_t x = a.lst[ptr[q] + e];
+                const uint32_t first = raw ? 0u : nin[q];
+                for (uint32_t e = first; e < tot[q]; ++e) {
+                    const uint32_t x = xoff[q] != 0xFFFFFFFFu ? s_ext[xoff[q] + (e - first)] : a.lst[ptr[q] + e];
                     const uint32_t rt = x & rmask;
                     if (raw && (rt >> kTileLog) == tile) continue;
+                    progress = true;
                     if (in) atomicOr(a.wext + rt, kOutFlag);
                     else atomicSub(a.wext + rt, (x >> a.order.kbits) + 1u);
                 }
                 a.res[t0 + tid + q * kFlowThreads] = in ? 1 : 0;
             }
+            if (progress) __threadfence();
+            const bool pushed = __syncthreads_or(progress);
+            if (pushed && tid == 0) atomicAdd(a.epoch, 1u);
             if (__syncthreads_and(all)) break;
-            if (__syncthreads_or(progress)) ns = 0;
-            else { ns = ns == 0 ? 64 : (ns < 1024 ? ns << 1 : ns); __nanosleep(ns); }
+            // nothing more to do until somebody pushes: watch the epoch word (one lane of the block)
+            if (tid == 0) {
+                unsigned ns = 32;
+                while (*(volatile unsigned int*)a.epoch == seen) { __nanosleep(ns); if (ns < 256) ns <<= 1; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) sampler_merge_counts_kernel(SamplerArgs a) {
+    if (!use_lane_flow(a)) return;
+    const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
+    const uint64_t r = uint64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n)) a.wext[r] += a.cint[r];
+}
+
+// One rank per lane, 32 consecutive ranks per warp ticket; the warp polls its 32 words together (one coalesced
+// request per poll). A decided lane applies its whole list with reductions that return nothing.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) sampler_lane_flow_kernel(SamplerArgs a) {
+    if (!use_lane_flow(a)) return;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
+    const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
+    for (;;) {
+        unsigned int base = 0;
+        if (lane == 0) base = atomicAdd(a.ticket + 1, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (uint64_t(base) >= ranks) break;
+        const uint64_t r = uint64_t(base) + lane;
+        bool pending = r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n);
+        long long p = 0;
+        uint32_t c = 0;
+        if (pending) { p = a.lptr[r]; c = a.lcnt[r] & 0xFFFFu; }
+        unsigned ns = 0;
+        while (__any_sync(0xffffffffu, pending)) {
+            const uint32_t w = pending ? *(volatile uint32_t*)(a.wext + r) : 1u;
+            if (pending && (w == 0u || (w & kOutFlag))) {
+                pending = false;
+                const bool in = w == 0u;
+                for (uint32_t k = 0; k < c; k += 4) {
+                    uint32_t x[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) x[u] = k + u < c ? a.lst[p + k + u] : 0xFFFFFFFFu;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (k + u >= c) continue;
+                        // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a rejected one
+                        // releases its later coverees (the last release selects: :25-28)
+                        if (in) atomicOr(a.wext + (x[u] & rmask), kOutFlag);
+                        else atomicSub(a.wext + (x[u] & rmask), (x[u] >> a.order.kbits) + 1u);
+                    }
+                }
+                a.res[r] = in ? 1 : 0;
+                ns = 0;
+            } else if (ns) {
+                __nanosleep(ns);
+            }
+            ns = ns == 0 ? 32 : (ns < 512 ? ns << 1 : ns);
         }
     }
 }
@@ -467,17 +570,25 @@ void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned lo
     if (n > 0) GMG_LAUNCH(c, degree_square_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, d_out);
 }
 
-constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint16_t) * kListCap + kTile;
+constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint32_t) * kExtCap + sizeof(uint16_t) * kListCap + kTile;
 
-template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, int32_t* flag) {
+template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, uint64_t ranks, int32_t* flag) {
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
+    // both flow kernels are launched; the one the build's counts do not select returns at once
     GMG_CUDA(cudaFuncSetAttribute(sampler_flow_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFlowSmem)));
     int per_sm = 0;
     GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_flow_kernel<MODE>, kFlowThreads, kFlowSmem));
     GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "sampler flow kernel does not fit on an SM");
     int grid = per_sm * c->sm_count;
     if (grid > int(a.tiles)) grid = int(a.tiles);
-    GMG_LAUNCH(c, sampler_flow_kernel<MODE>, grid < 1 ? 1 : grid, kFlowThreads, kFlowSmem, a);
+    if (!a.force_lane) GMG_LAUNCH(c, sampler_flow_kernel<MODE>, grid < 1 ? 1 : grid, kFlowThreads, kFlowSmem, a);
+    GMG_LAUNCH(c, sampler_merge_counts_kernel<MODE>, div_up(int64_t(ranks), kBlock), kBlock, 0, a);
+    GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_lane_flow_kernel<MODE>, kBlock, 0));
+    GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "sampler flow kernel does not fit on an SM");
+    grid = per_sm * c->sm_count;
+    const int needed = div_up(int64_t(ranks), kBlock);
+    if (grid > needed) grid = needed;
+    GMG_LAUNCH(c, sampler_lane_flow_kernel<MODE>, grid < 1 ? 1 : grid, kBlock, 0, a);
     GMG_LAUNCH(c, flag_in_kernel<MODE>, div_up(a.n, kBlock), kBlock, 0, a, flag);
 }
 
@@ -489,7 +600,8 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL || mode == GMG_SAMPLER_HASHED, GMG_ERR_INVALID,
                 "unknown sampler mode");
     // bound on the later-path lists: every path has a mirror image, exactly one of the two is "later"
-    DevBuf<unsigned long long> cursor(c, 4);          // [0] list cursor, [1] sum deg^2, [2] tile ticket, [3] flags
+    // [0] list cursor, [1] sum deg^2, [2] tickets (tile flow | lane flow), [3] flags | epoch, [4] same-tile entries, [5] all entries
+    DevBuf<unsigned long long> cursor(c, 6);
     cursor.zero();
     if (path_bound < 0) {
         degree_square_sum(c, n, colptr, cursor.p + 1);
@@ -511,9 +623,10 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     GMG_LAUNCH(c, sampler_init_kernel, div_up(int64_t(ranks), kBlock), kBlock, 0, ranks, res.p);
     SamplerArgs a{n, colptr, rowidx, len, radius, order, wext.p, cint.p, lptr.p, lcnt.p, lst.p, cursor.p,
                   reinterpret_cast<unsigned int*>(cursor.p + 2), unsigned((ranks + kTile - 1) >> kTileLog), res.p,
-                  reinterpret_cast<int32_t*>(cursor.p + 3)};
-    if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, flag.p);
-    else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, flag.p);
+                  reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, reinterpret_cast<unsigned int*>(cursor.p + 3) + 1,
+                  mode == GMG_SAMPLER_HASHED ? 1 : 0};
+    if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, ranks, flag.p);
+    else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, ranks, flag.p);
     // ascending compaction of the IN flags
     DevBuf<int64_t> total(c, 1);
     DevBuf<int32_t> pos(c, n);
@@ -671,7 +784,7 @@ void shard_sampler_build(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const in
     DevBuf<unsigned long long> cursor(c, 2);
     cursor.zero();
     SamplerArgs a{n, colptr, rowidx, len, radius, make_order(n, seed, mode), nullptr, nullptr, out.lptr.p,
-                  reinterpret_cast<uint32_t*>(out.lcnt.p), nullptr, cursor.p, nullptr, 0, nullptr, nullptr};
+                  reinterpret_cast<uint32_t*>(out.lcnt.p), nullptr, cursor.p, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 1};
     if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_EXACT>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     else GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_PARALLEL>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     unsigned long long hb[2];

@@ -154,10 +154,13 @@ void projected_points_dev(gmg_ctx* c, int32_t n, int32_t m, const int32_t* rowpt
 // the structural pattern is kept (no numerical pruning), inner indices ascending.
 // With [c_lo, c_hi) only those outer vectors are formed (Ac.n = c_hi - c_lo, indexed from c_lo): the
 // row-sharded build, where P is the whole operator and every rank forms the coarse rows it owns.
+// marks (optional): 4 events recorded before the transpose, after it, after the symbolic and after the numeric pass
 void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
-              const DeviceCsr& P, DeviceCsc& Ac, int32_t c_lo = 0, int32_t c_hi = -1, DeviceCsr* keep_R = nullptr);
+              const DeviceCsr& P, DeviceCsc& Ac, int32_t c_lo = 0, int32_t c_hi = -1, DeviceCsr* keep_R = nullptr,
+              cudaEvent_t* marks = nullptr);
 // R = P^T in CSR (rows = coarse columns [c_lo, c_hi) of P), fine indices ascending per row
-void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo = 0, int32_t c_hi = -1);
+// sort_rows = false leaves every row in arrival order (the Galerkin kernel sorts what it stages)
+void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo = 0, int32_t c_hi = -1, bool sort_rows = true);
 
 // ---- k_solver.cu ------------------------------------------------------------------------------
 struct Colouring {

@@ -204,7 +204,7 @@ class ShardedHierarchy:
     in production, all of them as virtual ranks with comm=None (loop-back on one GPU) in the tests."""
 
     def __init__(self, ctx, inp, levels, world, ranks, comm=None, ratio=8.0,
-                 weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_PARALLEL, seed=0, radius_policy=0,
+                 weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_HASHED, seed=0, radius_policy=0,
                  radius_override=None, device=None, profile=False, build_galerkin=False):
         import torch
         self.torch = torch

@@ -200,6 +200,8 @@ typedef struct {
        0 edge lengths+radius, 1 sampling, 2 parents, 3 cluster CSR, 4 coarse edges, 5 coarse points,
        6 triangle fans, 7 prolongation rows, 8 Galerkin */
     double stage_ms[9];
+    /* stage 8 split: transpose R = P^T, symbolic pass, numeric pass (0 unless build_galerkin) */
+    double galerkin_ms[3];
 } gmg_level_info;
 
 int gmg_hierarchy_build(gmg_ctx* ctx, const gmg_input* in, const gmg_hierarchy_options* opt, gmg_hierarchy** out);

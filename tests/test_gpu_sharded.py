@@ -26,8 +26,8 @@ def _single(ctx, V, A, levels, mode, radii=None):
 
 
 @pytest.mark.parametrize("name,scale,world,mode", [
-    ("C1", 1.0, 2, capi.SAMPLER_EXACT), ("C1", 1.0, 3, capi.SAMPLER_PARALLEL), ("C3", 0.004, 4, capi.SAMPLER_PARALLEL),
-    ("C4", 0.002, 2, capi.SAMPLER_PARALLEL), ("C3", 0.004, 8, capi.SAMPLER_EXACT)])
+    ("C1", 1.0, 2, capi.SAMPLER_EXACT), ("C1", 1.0, 3, capi.SAMPLER_HASHED), ("C3", 0.004, 4, capi.SAMPLER_HASHED),
+    ("C4", 0.002, 2, capi.SAMPLER_HASHED), ("C3", 0.004, 8, capi.SAMPLER_EXACT)])
 def test_sharded_equals_single_gpu(ctx, name, scale, world, mode):
     from gravomg_b200.sharded import ShardedHierarchy
     cfg = meshgen.make_config(name, scale)
@@ -61,8 +61,8 @@ def test_sharded_galerkin_equals_single_gpu(ctx, name, scale, world):
     cfg = meshgen.make_config(name, scale)
     V, A = cfg["V"], cfg["A"]
     inp = capi.Input(ctx, V, A.indptr, A.indices, A.data)
-    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=3, build_galerkin=True)
-    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_PARALLEL,
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_HASHED, seed=3, build_galerkin=True)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_HASHED,
                           seed=3, build_galerkin=True)
     assert sh.num_levels == h.num_levels
     Acur = A.tocsc()
@@ -94,10 +94,10 @@ def test_sharded_vcycle_equals_single_gpu(ctx, world, replicate_below):
     n = V.shape[0]
     b = A @ (np.sin(3 * V[:, 0]) * np.cos(2 * V[:, 1]) + V[:, 2])
     inp = capi.Input(ctx, V, A.indptr, A.indices, A.data)
-    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=5, build_galerkin=True)
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_HASHED, seed=5, build_galerkin=True)
     ref = capi.Solver(ctx, inp, h)
     x_ref, res_ref = ref.vcycle(b, cycles=3, pre=2, post=2, coarse_sweeps=20)
-    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_PARALLEL,
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_HASHED,
                           seed=5, build_galerkin=True)
     sv = ShardedSolver(sh, inp, replicate_below=replicate_below)
     assert sv.num_levels == h.num_levels + 1
@@ -149,6 +149,6 @@ def test_device_torus_generator(ctx):
     assert np.abs(got - want.data).max() <= 1e-11 * np.abs(want.data).max()
     inp_a.close()
     # and it feeds the build
-    h = capi.Hierarchy(ctx, inp, 3, sampler_mode=capi.SAMPLER_PARALLEL)
+    h = capi.Hierarchy(ctx, inp, 3, sampler_mode=capi.SAMPLER_HASHED)
     assert h.num_levels == 2 and h.info[0]["m"] > 0
     h.close(); inp.close()

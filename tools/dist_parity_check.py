@@ -32,7 +32,7 @@ cfg = meshgen.make_config(name, scale)
 V, A = cfg["V"], cfg["A"]
 inp = capi.Input(ctx, V, A.indptr, A.indices, None)
 bad = 0
-for mode in (capi.SAMPLER_PARALLEL, capi.SAMPLER_EXACT) if name != "C3" else (capi.SAMPLER_PARALLEL,):
+for mode in (capi.SAMPLER_HASHED, capi.SAMPLER_EXACT) if name != "C3" else (capi.SAMPLER_HASHED,):
     single = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=mode, seed=3)
     sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=mode, seed=3)
     assert sh.same_stream
@@ -63,8 +63,8 @@ if not (np.array_equal(pts_d, V) and np.array_equal(cp_d, A.indptr) and np.array
     bad += 1
     print(f"rank {rank}: sharded upload differs from the host arrays", flush=True)
 print(f"rank {rank}: sharded upload copied {h2d / 1e6:.1f} MB of {(V.nbytes + A.indptr.nbytes + A.indices.nbytes + A.data.nbytes) / 1e6:.1f} MB from the host", flush=True)
-single = capi.Hierarchy(ctx, inp_a, cfg["levels"], sampler_mode=capi.SAMPLER_PARALLEL, seed=3, build_galerkin=True)
-sh = ShardedHierarchy(ctx, inp_a, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=capi.SAMPLER_PARALLEL, seed=3,
+single = capi.Hierarchy(ctx, inp_a, cfg["levels"], sampler_mode=capi.SAMPLER_HASHED, seed=3, build_galerkin=True)
+sh = ShardedHierarchy(ctx, inp_a, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=capi.SAMPLER_HASHED, seed=3,
                       build_galerkin=True)
 for lvl in range(single.num_levels):
     want, got = single.galerkin(lvl), sh.galerkin(lvl)
