@@ -284,7 +284,8 @@ STAGE_NAMES = ["edge_lengths", "sampling", "parents", "cluster_csr", "coarse_edg
                "triangle_fans", "prolongation_rows", "galerkin"]
 
 (H_SAMPLES, H_PARENTS, H_COARSE_COLPTR, H_COARSE_ROWIDX, H_COARSE_VAL, H_COARSE_POINTS, H_TRIANGLES, H_NORMALS,
- H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL, H_AC_COLPTR, H_AC_ROWIDX, H_AC_VAL, H_FINE_VAL) = range(17)
+ H_FAN_PTR, H_FAN, H_P_ROWPTR, H_P_COLIDX, H_P_VAL, H_AC_COLPTR, H_AC_ROWIDX, H_AC_VAL, H_FINE_VAL,
+ H_PROJECTED) = range(18)
 
 
 class Input:
@@ -442,6 +443,7 @@ class Hierarchy:
             H_FAN_PTR: (m + 1, np.int64), H_FAN: (3 * T, np.int64), H_P_ROWPTR: (n + 1, np.int32),
             H_P_COLIDX: (i["nnz_p"], np.int32), H_P_VAL: (i["nnz_p"], np.float64), H_AC_COLPTR: (m + 1, np.int32),
             H_AC_ROWIDX: (i["nnz_ac"], np.int32), H_AC_VAL: (i["nnz_ac"], np.float64), H_FINE_VAL: (i["nnz"], np.float64),
+            H_PROJECTED: (3 * n, np.float64),
         }[which]
         if out is None:
             out = np.empty(max(shape_dtype[0], 1), dtype=shape_dtype[1])
@@ -452,6 +454,8 @@ class Hierarchy:
         out = out[:shape_dtype[0]]
         if which == H_COARSE_POINTS:
             return out.reshape((m, 3), order="F")
+        if which == H_PROJECTED:
+            return out.reshape((n, 3), order="F")
         if which in (H_TRIANGLES, H_NORMALS):
             return out.reshape(T, 3)
         return out
@@ -464,6 +468,10 @@ class Hierarchy:
                     cpts=f(level, H_COARSE_POINTS), tri=f(level, H_TRIANGLES), nrm=f(level, H_NORMALS),
                     fptr=f(level, H_FAN_PTR), fan=f(level, H_FAN), prp=f(level, H_P_ROWPTR),
                     pci=f(level, H_P_COLIDX), pva=f(level, H_P_VAL))
+
+    def projected_points(self, level):
+        """projectedPoints(P, coarse_points) of a level, computed on the device (src/multigrid.cpp:500-510)."""
+        return self.fetch(level, H_PROJECTED)
 
     def prolongation(self, level):
         import scipy.sparse as sp

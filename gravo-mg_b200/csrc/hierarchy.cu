@@ -312,6 +312,14 @@ void fetch_level_array(gmg_ctx* c, const gmg_hierarchy* h, int level, int which,
         case GMG_H_FINE_VAL:
             GMG_REQUIRE(level == 0, GMG_ERR_STATE, "fine values exist on level 0 only");
             copy(h->fine_val.p, sizeof(double) * size_t(h->fine_nnz)); break;
+        case GMG_H_PROJECTED: {
+            GMG_REQUIRE(!async, GMG_ERR_INVALID, "projected points are computed on the compute stream: no asynchronous fetch");
+            DevBuf<double> proj(c, 3 * n);
+            projected_points_dev(c, int32_t(n), int32_t(m), L.P.rowptr.p, L.P.colidx.p, L.P.val.p, L.coarse_pts.p, proj.p);
+            copy(proj.p, sizeof(double) * size_t(3 * n));
+            sync(c);
+            break;
+        }
         default: GMG_REQUIRE(false, GMG_ERR_INVALID, "unknown array id");
     }
     if (!async) sync(c);

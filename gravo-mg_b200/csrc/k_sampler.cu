@@ -179,66 +179,71 @@ __device__ __forceinline__ void for_each_covered(const SamplerArgs& a, int32_t s
 }
 
 // One walk of every two-hop neighbourhood (8 lanes per vertex): counts the preceding covering paths (same flow
-// tile / other tiles) and writes the LATER coverees as a merged list. The lanes stage their later targets in
-// shared memory; the group then merges duplicates (an entry keeps a multiplicity, capped by the bits a rank
-// leaves free in 32) and writes same-tile targets first. A vertex with a lane that outgrows its stage (> 16
-// later paths on one first-hop edge: rare) walks again and writes its paths raw, flagged kUnpartitioned.
+// tile / other tiles) and writes the LATER coverees as a merged list. A mesh vertex has ~24 later paths but only
+// ~8 distinct later coverees: every later target goes straight into a small per-vertex hash table in shared
+// memory (atomicCAS on the key, atomicAdd on its multiplicity -- both native on 32-bit shared words), and the
+// occupied slots are written out, same-tile targets first, an entry standing for up to `cap` paths (the bits a
+// rank leaves free in 32). A vertex with more distinct later coverees than the table holds (dense kNN graphs)
+// walks again and writes its paths raw, flagged kUnpartitioned.
+constexpr int kMergeSlots = 64;      // per vertex; a walk that fills more than 3/4 of them falls back to raw paths
+
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     static_assert(kBlock / kLanes == 32, "one warp scans the group totals");
+    static_assert(kMergeSlots % kLanes == 0, "the lanes of a group split the slots evenly");
     __shared__ int32_t s_group[kBlock / kLanes];
     __shared__ unsigned long long s_base;
-    __shared__ uint32_t s_stage[kBlock][kStage + 1];   // +1: conflict-free lane-private rows
-    __shared__ uint8_t s_mult[kBlock][kStage];         // 0: merged into an earlier entry, else its multiplicity
+    __shared__ uint32_t s_key[kBlock / kLanes][kMergeSlots];
+    __shared__ uint32_t s_cnt[kBlock / kLanes][kMergeSlots];
+    __shared__ int32_t s_used[kBlock / kLanes];        // occupied slots of the group's table (-1: overflowed)
     __shared__ int32_t s_same;
-    if (threadIdx.x == 0) s_same = 0;
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t i = int32_t(gid / kLanes);
     const int sub = threadIdx.x % kLanes;
     const int g = threadIdx.x / kLanes;
     const bool active = i < a.n;
+    for (int s = sub; s < kMergeSlots; s += kLanes) { s_key[g][s] = 0xFFFFFFFFu; s_cnt[g][s] = 0u; }
+    if (sub == 0) s_used[g] = 0;
+    if (threadIdx.x == 0) s_same = 0;
+    __syncthreads();
     int32_t prev_in = 0, prev_ext = 0, later = 0;
     uint32_t ri = 0;
     if (active) {
         ri = rank_of<MODE>(a, i);
-        uint32_t* stage = s_stage[threadIdx.x];
+        uint32_t* keys = s_key[g];
+        uint32_t* cnts = s_cnt[g];
         for_each_covered(a, i, sub, [&](int32_t t) {
             const uint32_t rt = rank_of<MODE>(a, t);
-            if (rt < ri) { if (!a.force_lane && (rt >> kTileLog) == (ri >> kTileLog)) ++prev_in; else ++prev_ext; }
-            else { if (later < kStage) stage[later] = rt; ++later; }
+            if (rt < ri) { if (!a.force_lane && (rt >> kTileLog) == (ri >> kTileLog)) ++prev_in; else ++prev_ext; return; }
+            ++later;
+            uint32_t h = (rt * 0x9E3779B1u) >> 16;
+            for (int probe = 0; probe < kMergeSlots; ++probe, ++h) {
+                const int sl = int(h & (kMergeSlots - 1));
+                const uint32_t prev = atomicCAS(keys + sl, 0xFFFFFFFFu, rt);
+                if (prev == 0xFFFFFFFFu) { if (atomicAdd(s_used + g, 1) >= kMergeSlots * 3 / 4) s_used[g] = -(1 << 20); }
+                if (prev == 0xFFFFFFFFu || prev == rt) { atomicAdd(cnts + sl, 1u); return; }
+            }
+            s_used[g] = -(1 << 20);                      // table full
         });
     }
     const int lane = threadIdx.x & 31;
-    const unsigned gmask = 0xFFu << (lane & ~(kLanes - 1));
-    const bool group_over = (__ballot_sync(0xffffffffu, later > kStage) & gmask) != 0;
+    __syncwarp();
+    const bool group_over = active && *(volatile int32_t*)(s_used + g) < 0;
 #pragma unroll
     for (int d = kLanes / 2; d > 0; d >>= 1) {
         prev_in += __shfl_xor_sync(0xffffffffu, prev_in, d, kLanes);
         prev_ext += __shfl_xor_sync(0xffffffffu, prev_ext, d, kLanes);
     }
-    // merge duplicates within the group: entry (lane, e) survives when the number of equal entries before it
-    // in (lane, position) order is a multiple of the cap, and then stands for up to `cap` of them
+    // entries this lane writes: its share of the table's slots, an entry per `cap` paths of a slot
     const uint32_t cap = 1u << (32u - a.order.kbits < 4u ? 32u - a.order.kbits : 4u);
     int32_t kept = 0, kept_in = 0;
-    int32_t cnts[kLanes];
-#pragma unroll
-    for (int l2 = 0; l2 < kLanes; ++l2) cnts[l2] = __shfl_sync(0xffffffffu, later, (lane & ~(kLanes - 1)) + l2);
-    __syncwarp();
-    if (!group_over) {
-        const uint32_t* stage = s_stage[threadIdx.x];
-        for (int32_t e = 0; e < later; ++e) {
-            const uint32_t x = stage[e];
-            uint32_t ordinal = 0, total = 0;
-#pragma unroll
-            for (int l2 = 0; l2 < kLanes; ++l2) {
-                const uint32_t* row = s_stage[(threadIdx.x & ~(kLanes - 1)) + l2];
-                for (int32_t p = 0; p < cnts[l2]; ++p)
-                    if (row[p] == x) { ++total; if (l2 < sub || (l2 == sub && p < e)) ++ordinal; }
-            }
-            const bool keep = (ordinal & (cap - 1u)) == 0u;
-            const uint32_t mult = keep ? (total - ordinal < cap ? total - ordinal : cap) : 0u;
-            s_mult[threadIdx.x][e] = uint8_t(mult);
-            if (keep) { ++kept; if (!a.force_lane && (x >> kTileLog) == (ri >> kTileLog)) ++kept_in; }
+    if (active && !group_over) {
+        for (int sl = sub; sl < kMergeSlots; sl += kLanes) {
+            const uint32_t x = s_key[g][sl];
+            if (x == 0xFFFFFFFFu) continue;
+            const int32_t pieces = int32_t((s_cnt[g][sl] + cap - 1u) / cap);
+            kept += pieces;
+            if (!a.force_lane && (x >> kTileLog) == (ri >> kTileLog)) kept_in += pieces;
         }
     }
     const int32_t own = group_over ? later : kept;
@@ -273,15 +278,18 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
         // same-tile targets first: [start, start + group_in), the others behind them
         uint32_t* dst_in = a.lst + start + (incl_in - kept_in);
         uint32_t* dst_ext = a.lst + start + group_in + ((incl - kept) - (incl_in - kept_in));
-        const uint32_t* stage = s_stage[threadIdx.x];
-        for (int32_t e = 0; e < later; ++e) {
-            const uint32_t mult = s_mult[threadIdx.x][e];
-            if (!mult) continue;
-            const uint32_t x = stage[e];
-            const uint32_t packed = x | ((mult - 1u) << a.order.kbits);
-            if (!a.force_lane && (x >> kTileLog) == (ri >> kTileLog)) *dst_in++ = packed; else *dst_ext++ = packed;
+        for (int sl = sub; sl < kMergeSlots; sl += kLanes) {
+            const uint32_t x = s_key[g][sl];
+            if (x == 0xFFFFFFFFu) continue;
+            const bool same = !a.force_lane && (x >> kTileLog) == (ri >> kTileLog);
+            for (uint32_t left = s_cnt[g][sl]; left > 0u;) {
+                const uint32_t mult = left < cap ? left : cap;
+                const uint32_t packed = x | ((mult - 1u) << a.order.kbits);
+                if (same) *dst_in++ = packed; else *dst_ext++ = packed;
+                left -= mult;
+            }
         }
-    } else {                                          // some lane of this vertex outgrew its stage: walk again
+    } else {                                          // more distinct later coverees than the table holds: walk again
         uint32_t* dst = a.lst + start + (incl - own);
         for_each_covered(a, i, sub, [&](int32_t t) {
             const uint32_t rt = rank_of<MODE>(a, t);
@@ -323,14 +331,16 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
     uint16_t* s_list = reinterpret_cast<uint16_t*>(s_ext + kExtCap);             // kListCap staged same-tile entries
     uint8_t* s_hit = reinterpret_cast<uint8_t*>(s_list + kListCap);              // kTile: knocked OUT inside the tile
     __shared__ int32_t s_warp[2][kFlowThreads / 32];
-    __shared__ unsigned int s_tile, s_epoch;
+    __shared__ unsigned int s_tile;
+    __shared__ unsigned int s_epoch;      // the last value of the global epoch word this block has looked at
+    __shared__ int32_t s_left;            // undecided ranks of the tile
     if (use_lane_flow(a)) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
     for (;;) {
         __syncthreads();                                   // everybody is done with the previous tile's shared state
-        if (tid == 0) s_tile = atomicAdd(a.ticket, 1u);
+        if (tid == 0) { s_tile = atomicAdd(a.ticket, 1u); s_left = 0; s_epoch = *(volatile unsigned int*)a.epoch << 1; }
         __syncthreads();
         const unsigned int tile = s_tile;
         if (tile >= a.tiles) break;
@@ -338,24 +348,26 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         // ---- static data of the tile's ranks; rank i of the tile belongs to thread i % kFlowThreads
         long long ptr[kOwn];
         uint32_t tot[kOwn], nin[kOwn], soff[kOwn], xoff[kOwn];
-        uint8_t st[kOwn];              // 0 undecided, 1 IN, 2 OUT; | 4 same-tile list applied; | 8 other-tile list applied
         int32_t mine = 0, mine_x = 0;  // same-tile / other-tile list entries this thread wants to stage
+        unsigned undecided = 0;        // bit q: rank q of this thread is not decided yet
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
             const int i = tid + q * kFlowThreads;
             const uint64_t r = uint64_t(t0) + uint64_t(i);
             const bool valid = r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n);
-            ptr[q] = 0; tot[q] = 0; nin[q] = 0; st[q] = 2 | 4 | 8;
+            ptr[q] = 0; tot[q] = 0; nin[q] = 0;
             int32_t rem = 0;
             if (valid) {
                 const uint32_t lc = a.lcnt[r];
-                ptr[q] = a.lptr[r]; tot[q] = lc & 0xFFFFu; nin[q] = lc >> 16; st[q] = 0;
+                ptr[q] = a.lptr[r]; tot[q] = lc & 0xFFFFu; nin[q] = lc >> 16;
+                undecided |= 1u << q;
                 rem = int32_t(a.cint[r]);
                 if (nin[q] != kUnpartitioned) { mine += int32_t(nin[q]); mine_x += int32_t(tot[q] - nin[q]); }
             }
             s_rem[i] = rem;
             s_hit[i] = 0;
         }
+        if (undecided) atomicAdd(&s_left, __popc(undecided));
         // shared-memory segments for the two halves of the lists: block-wide exclusive scans over the threads
         {
             int32_t s = mine, sx = mine_x;
@@ -381,7 +393,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             int32_t off = s_warp[0][warp] + (s - mine), offx = s_warp[1][warp] + (sx - mine_x);
 #pragma unroll
             for (int q = 0; q < kOwn; ++q) {
-                const bool part = (st[q] & 3) == 0 && nin[q] != kUnpartitioned;
+                const bool part = ((undecided >> q) & 1u) && nin[q] != kUnpartitioned;
                 const int32_t want = part ? int32_t(nin[q]) : 0, wantx = part ? int32_t(tot[q] - nin[q]) : 0;
                 soff[q] = (want > 0 && off + want <= kListCap) ? uint32_t(off) : 0xFFFFFFFFu;
                 xoff[q] = (wantx > 0 && offx + wantx <= kExtCap) ? uint32_t(offx) : 0xFFFFFFFFu;
@@ -401,86 +413,83 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 for (uint32_t e = nin[q]; e < tot[q]; ++e) s_ext[xoff[q] + (e - nin[q])] = a.lst[ptr[q] + e];
         }
         __syncthreads();
-        // ---- the flow
+        // ---- the flow: no barrier inside. Every thread spins over its undecided ranks; a decision is applied at
+        //      once (same-tile targets in shared memory, the others with reductions on the global words), and a
+        //      warp that pushed something bumps the global epoch word so that the tiles waiting on it look again.
         uint32_t ext[kOwn];
 #pragma unroll
-        for (int q = 0; q < kOwn; ++q) ext[q] = (st[q] & 3) == 0 ? 1u : 0u;        // 1: not polled yet
-        unsigned int seen = 0;
-        for (;;) {
-            // the epoch is read BEFORE the words: a push that lands after this poll bumps it afterwards
-            if (tid == 0) s_epoch = *(volatile unsigned int*)a.epoch;
-            __syncthreads();
-            seen = s_epoch;
-            __threadfence();
-#pragma unroll
-            for (int q = 0; q < kOwn; ++q)      // a word that has reached 0 has no outside coverer left and stays 0
-                if ((st[q] & 3) == 0 && ext[q] != 0u) ext[q] = *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads);
-            for (;;) {                                          // rounds inside the tile, shared memory only
-                bool changed = false;
-#pragma unroll
-                for (int q = 0; q < kOwn; ++q) {
-                    const int i = tid + q * kFlowThreads;
-                    if ((st[q] & 3) == 0) {
-                        if ((ext[q] & kOutFlag) || *(volatile uint8_t*)(s_hit + i)) { st[q] |= 2; changed = true; }
-                        else if (ext[q] == 0u && *(volatile int32_t*)(s_rem + i) == 0) { st[q] |= 1; changed = true; }
-                    }
-                    if ((st[q] & 3) != 0 && !(st[q] & 4)) {
-                        st[q] |= 4;
-                        const bool in = (st[q] & 3) == 1;
-                        if (soff[q] != 0xFFFFFFFFu) {
-                            for (uint32_t e = 0; e < nin[q]; ++e) {
-                                const uint32_t y = s_list[soff[q] + e];
-                                const uint32_t t = y & (kTile - 1);
-                                // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a
-                                // rejected one releases its later coverees
-                                if (in) *(volatile uint8_t*)(s_hit + t) = 1;
-                                else atomicSub(s_rem + t, int32_t(y >> kTileLog) + 1);
-                            }
-                        } else {
-                            // list not staged (no room, or not partitioned): same-tile targets straight from the list
-                            const uint32_t cnt = nin[q] == kUnpartitioned ? tot[q] : nin[q];
-                            for (uint32_t e = 0; e < cnt; ++e) {
-                                const uint32_t x = a.lst[ptr[q] + e];
-                                const uint32_t rt = x & rmask;
-                                if ((rt >> kTileLog) != tile) continue;
-                                if (in) *(volatile uint8_t*)(s_hit + (rt - t0)) = 1;
-                                else atomicSub(s_rem + (rt - t0), int32_t(x >> a.order.kbits) + 1);
-                            }
-                        }
-                    }
-                }
-                if (!__syncthreads_or(changed)) break;
+        for (int q = 0; q < kOwn; ++q) ext[q] = 1u;                    // 1: the global word has not been read yet
+        unsigned int seen = s_epoch - 1u;                              // forces the first read
+        unsigned idle = 0, watch = 0;
+        while (*(volatile int32_t*)&s_left > 0) {
+            // one thread of the block watches the epoch word (with a back-off while the block is making no progress)
+            if (tid == 0) {
+                // (every 4096th look also forces a fresh read of the words, whatever the epoch says: a lost
+                // wake-up must cost microseconds, never the kernel)
+                const unsigned int e = (*(volatile unsigned int*)a.epoch << 1) | ((++watch >> 12) & 1u);
+                if (e != *(volatile unsigned int*)&s_epoch) *(volatile unsigned int*)&s_epoch = e;
             }
-            // ---- what leaves the tile, and the result
-            bool progress = false, all = true;
+            const unsigned int now = *(volatile unsigned int*)&s_epoch;
+            if (now != seen) {
+                // the epoch was read BEFORE these words: a push that lands after this poll bumps it again
+                seen = now;
+                __threadfence();
+#pragma unroll
+                for (int q = 0; q < kOwn; ++q)     // a word that has reached 0 has no outside coverer left and stays 0
+                    if (((undecided >> q) & 1u) && ext[q] != 0u) ext[q] = *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads);
+            }
+            bool pushed = false, decided_any = false;
 #pragma unroll
             for (int q = 0; q < kOwn; ++q) {
-                if ((st[q] & 3) == 0) { all = false; continue; }
-                if (st[q] & 8) continue;
-                st[q] |= 8;
-                const bool in = (st[q] & 3) == 1;
+                if (!((undecided >> q) & 1u)) continue;
+                const int i = tid + q * kFlowThreads;
+                bool in;
+                if ((ext[q] & kOutFlag) || *(volatile uint8_t*)(s_hit + i)) in = false;
+                else if (ext[q] == 0u && *(volatile int32_t*)(s_rem + i) == 0) in = true;
+                else continue;
+                undecided &= ~(1u << q);
+                decided_any = true;
+                // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a rejected one releases
+                // its later coverees
                 const bool raw = nin[q] == kUnpartitioned;
+                if (soff[q] != 0xFFFFFFFFu) {
+                    for (uint32_t e = 0; e < nin[q]; ++e) {
+                        const uint32_t y = s_list[soff[q] + e];
+                        if (in) *(volatile uint8_t*)(s_hit + (y & (kTile - 1))) = 1;
+                        else atomicSub(s_rem + (y & (kTile - 1)), int32_t(y >> kTileLog) + 1);
+                    }
+                } else {
+                    // list not staged (no room, or not partitioned): same-tile targets straight from the list
+                    const uint32_t cnt = raw ? tot[q] : nin[q];
+                    for (uint32_t e = 0; e < cnt; ++e) {
+                        const uint32_t x = a.lst[ptr[q] + e];
+                        const uint32_t rt = x & rmask;
+                        if ((rt >> kTileLog) != tile) continue;
+                        if (in) *(volatile uint8_t*)(s_hit + (rt - t0)) = 1;
+                        else atomicSub(s_rem + (rt - t0), int32_t(x >> a.order.kbits) + 1);
+                    }
+                }
                 const uint32_t first = raw ? 0u : nin[q];
                 for (uint32_t e = first; e < tot[q]; ++e) {
                     const uint32_t x = xoff[q] != 0xFFFFFFFFu ? s_ext[xoff[q] + (e - first)] : a.lst[ptr[q] + e];
                     const uint32_t rt = x & rmask;
                     if (raw && (rt >> kTileLog) == tile) continue;
-                    progress = true;
+                    pushed = true;
                     if (in) atomicOr(a.wext + rt, kOutFlag);
                     else atomicSub(a.wext + rt, (x >> a.order.kbits) + 1u);
                 }
-                a.res[t0 + tid + q * kFlowThreads] = in ? 1 : 0;
+                a.res[t0 + i] = in ? 1 : 0;
+                atomicSub(&s_left, 1);
             }
-            if (progress) __threadfence();
-            const bool pushed = __syncthreads_or(progress);
-            if (pushed && tid == 0) atomicAdd(a.epoch, 1u);
-            if (__syncthreads_and(all)) break;
-            // nothing more to do until somebody pushes: watch the epoch word (one lane of the block)
-            if (tid == 0) {
-                unsigned ns = 32;
-                while (*(volatile unsigned int*)a.epoch == seen) { __nanosleep(ns); if (ns < 256) ns <<= 1; }
+            if (pushed) {                          // one bump per group of lanes that pushed together
+                __threadfence();
+                const cg::coalesced_group grp = cg::coalesced_threads();
+                if (grp.thread_rank() == 0) atomicAdd(a.epoch, 1u);
             }
-            __syncthreads();
+            // a thread that is done with the tile meets the block at the barrier; thread 0 stays: it is the watcher
+            if (!undecided && tid != 0) break;
+            if (decided_any) idle = 0;
+            else if (++idle > 8) __nanosleep(idle < 64 ? 20 : 100);
         }
     }
 }

@@ -56,6 +56,12 @@ __device__ __forceinline__ uint32_t prio(uint32_t v) {
     return v;
 }
 
+constexpr int kMaxColours = 1024;
+
+// A vertex that beats every uncoloured neighbour takes the SMALLEST colour none of its coloured neighbours has.
+// The used colours are collected 64 at a time (one bit mask per window of 64 colours; rows with more than 64
+// distinct neighbour colours -- Galerkin operators of kNN-32 clouds, deep coarse levels -- scan again for the next
+// window), so two adjacent rows can never share a colour. More than kMaxColours colours is reported.
 __global__ void __launch_bounds__(kBlock) colour_round_kernel(int32_t n, const int32_t* __restrict__ outer,
                                                               const int32_t* __restrict__ inner,
                                                               const int32_t* __restrict__ colour_in,
@@ -64,9 +70,10 @@ __global__ void __launch_bounds__(kBlock) colour_round_kernel(int32_t n, const i
     if (i >= n) return;
     if (colour_in[i] >= 0) { colour_out[i] = colour_in[i]; return; }
     const uint32_t pi = prio(uint32_t(i));
+    const int32_t b = __ldg(outer + i), e = __ldg(outer + i + 1);
     unsigned long long used = 0ull;
     bool wins = true;
-    for (int32_t k = __ldg(outer + i); k < __ldg(outer + i + 1); ++k) {
+    for (int32_t k = b; k < e; ++k) {
         const int32_t j = __ldg(inner + k);
         if (j == i) continue;
         const int32_t cj = colour_in[j];
@@ -74,14 +81,21 @@ __global__ void __launch_bounds__(kBlock) colour_round_kernel(int32_t n, const i
         const uint32_t pj = prio(uint32_t(j));
         if (pj > pi || (pj == pi && j > i)) { wins = false; break; }
     }
-    if (wins) {
-        int32_t cidx = __ffsll((long long)~used) - 1;       // smallest free colour (< 64)
-        if (cidx < 0) cidx = 63;
-        colour_out[i] = cidx;
-    } else {
-        colour_out[i] = -1;
-        *remaining = 1;
+    if (!wins) { colour_out[i] = -1; remaining[0] = 1; return; }
+    int32_t cidx = __ffsll((long long)~used) - 1;       // smallest free colour below 64, or -1
+    for (int32_t base = 64; cidx < 0 && base < kMaxColours; base += 64) {
+        used = 0ull;
+        for (int32_t k = b; k < e; ++k) {
+            const int32_t j = __ldg(inner + k);
+            if (j == i) continue;
+            const int32_t cj = colour_in[j] - base;
+            if (cj >= 0 && cj < 64) used |= 1ull << cj;
+        }
+        const int32_t f = __ffsll((long long)~used) - 1;
+        if (f >= 0) cidx = base + f;
     }
+    if (cidx < 0) { cidx = 0; remaining[1] = 1; }        // more than kMaxColours colours: reported by the caller
+    colour_out[i] = cidx;
 }
 
 __global__ void __launch_bounds__(kBlock) colour_hist_kernel(int32_t n, const int32_t* __restrict__ colour, int32_t* __restrict__ hist) {
@@ -107,27 +121,28 @@ void colour_graph(gmg_ctx* c, int32_t n, const int32_t* outer, const int32_t* in
     out.num_colours = 0;
     out.offsets.assign(1, 0);
     if (n == 0) return;
-    DevBuf<int32_t> a(c, n), b(c, n), remaining(c, 1);
+    DevBuf<int32_t> a(c, n), b(c, n), remaining(c, 2);
     GMG_CUDA(cudaMemsetAsync(a.p, 0xFF, sizeof(int32_t) * size_t(n), c->stream));
     int32_t* cur = a.p; int32_t* nxt = b.p;
     for (int round = 0; round < 4096; ++round) {
         remaining.zero();
         GMG_LAUNCH(c, colour_round_kernel, div_up(n, kBlock), kBlock, 0, n, outer, inner, cur, nxt, remaining.p);
-        int32_t h = 0;
-        remaining.download(&h, 1);
+        int32_t h[2] = {0, 0};
+        remaining.download(h, 2);
         sync(c);
+        GMG_REQUIRE(h[1] == 0, GMG_ERR_INVALID, "multicolour Gauss-Seidel: a row needs more than 1024 colours");
         std::swap(cur, nxt);
-        if (!h) break;
+        if (!h[0]) break;
     }
     GMG_CUDA(cudaMemcpyAsync(out.colour.p, cur, sizeof(int32_t) * size_t(n), cudaMemcpyDeviceToDevice, c->stream));
-    DevBuf<int32_t> hist(c, 64);
+    DevBuf<int32_t> hist(c, kMaxColours);
     hist.zero();
     GMG_LAUNCH(c, colour_hist_kernel, div_up(n, kBlock), kBlock, 0, n, out.colour.p, hist.p);
-    int32_t hh[64];
-    hist.download(hh, 64);
+    std::vector<int32_t> hh(kMaxColours, 0);
+    GMG_CUDA(cudaMemcpyAsync(hh.data(), hist.p, sizeof(int32_t) * kMaxColours, cudaMemcpyDeviceToHost, c->stream));
     sync(c);
     int nc = 0;
-    for (int k = 0; k < 64; ++k) if (hh[k] > 0) nc = k + 1;
+    for (int k = 0; k < kMaxColours; ++k) if (hh[k] > 0) nc = k + 1;
     out.num_colours = nc;
     out.offsets.assign(size_t(nc) + 1, 0);
     for (int k = 0; k < nc; ++k) out.offsets[size_t(k) + 1] = out.offsets[size_t(k)] + hh[k];

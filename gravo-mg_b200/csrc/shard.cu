@@ -382,14 +382,46 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 s->a_n = s->m; s->a_colptr = L.Ac.colptr.p; s->a_rowidx = L.Ac.rowidx.p; s->a_val = L.Ac.val.p;
                 break;
             }
-            case GMG_PH_LEVEL_END: {
+            case GMG_PH_LEVEL_STATUS: {        // this rank's deferred flags and counters into its slice of STATUS
                 gmg_shard::Done& L = *s->cur;
                 s->status.fetch(c);
                 finish_prolongation(s->status, L.P, &L.info.stats);
                 L.info.nnz_p = L.P.nnz;
-                s->status.raise_parents();
-                s->status.raise_coarse();
-                s->status.raise_prolong(s->hi - s->lo);
+                int64_t* w = s->status_host;
+                w[0] = s->status.host[StageStatus::kZeroEdge];
+                w[1] = s->status.host[StageStatus::kNoOffer];
+                w[2] = s->status.host[StageStatus::kCoarseHardOverflow];
+                w[3] = s->status.host[StageStatus::kCoarseAsym];
+                w[4] = s->status.host_i64(StageStatus::kProlongStats + 6);      // degenerate fan
+                w[5] = s->status.host_i64(StageStatus::kProlongStats + 4);      // fallback rows
+                w[6] = int64_t(s->hi) - int64_t(s->lo);                          // owned rows
+                w[7] = 0;
+                if (!s->xstatus.p) s->xstatus.alloc(c, 8 * int64_t(s->world));
+                GMG_CUDA(cudaMemcpyAsync(s->xstatus.p + 8 * int64_t(s->rank), w, sizeof(int64_t) * 8, cudaMemcpyHostToDevice, c->stream));
+                sync(c);
+                break;
+            }
+            case GMG_PH_LEVEL_END: {           // after STATUS has been gathered: the checks on the values of all ranks
+                gmg_shard::Done& L = *s->cur;
+                GMG_REQUIRE(s->xstatus.p, GMG_ERR_STATE, "LEVEL_END before LEVEL_STATUS");
+                std::vector<int64_t> all(size_t(8) * size_t(s->world));
+                GMG_CUDA(cudaMemcpyAsync(all.data(), s->xstatus.p, sizeof(int64_t) * all.size(), cudaMemcpyDeviceToHost, c->stream));
+                sync(c);
+                int64_t g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                for (int r = 0; r < s->world; ++r) {
+                    for (int k = 0; k < 5; ++k) g[k] |= all[size_t(8 * r + k)];
+                    g[5] += all[size_t(8 * r + 5)]; g[6] += all[size_t(8 * r + 6)];
+                }
+                StageStatus global;
+                global.host[StageStatus::kZeroEdge] = int32_t(g[0] != 0);
+                global.host[StageStatus::kNoOffer] = int32_t(g[1] != 0);
+                global.host[StageStatus::kCoarseHardOverflow] = int32_t(g[2] != 0);
+                global.host[StageStatus::kCoarseAsym] = int32_t(g[3] != 0);
+                memcpy(global.host + StageStatus::kProlongStats + 6, &g[4], sizeof(int64_t));
+                memcpy(global.host + StageStatus::kProlongStats + 4, &g[5], sizeof(int64_t));
+                global.raise_parents();
+                global.raise_coarse();
+                global.raise_prolong(g[6]);
                 L.clo = s->clo; L.chi = s->chi; L.chunk = s->chunk; L.cchunk = s->cchunk;
                 // keep what a consumer of the level needs; the rest goes back to the pool
                 L.samples = std::move(s->samples);
@@ -425,6 +457,7 @@ int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, i
             return GMG_ERR_INVALID;      /* variable-size slices: gmg_shard_buffer_v */
         case GMG_XB_LEN_PARTIAL: *ptr = s->len_partial.p; *elem_bytes = 8; *slice = s->gchunk; break;
         case GMG_XB_P_COUNT: *ptr = s->pcnt.p; *elem_bytes = 4; *slice = s->chunk; break;
+        case GMG_XB_STATUS: *ptr = s->xstatus.p; *elem_bytes = 8; *slice = 8; break;
         default: return GMG_ERR_INVALID;
     }
     return GMG_OK;

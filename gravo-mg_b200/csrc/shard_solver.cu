@@ -131,12 +131,12 @@ int gmg_shard_solver_create(gmg_ctx* c, const gmg_shard* sh, const gmg_input* in
             else { const auto& d = *sh->done[nl - 1]; L->lo = d.clo; L->hi = d.chi; L->chunk = d.cchunk; }
             colour_graph(c, L->n, L->outer, L->inner, L->col);
             const int nc = L->col.num_colours;
-            GMG_REQUIRE(nc <= 64, GMG_ERR_INVALID, "more than 64 colours");
+            GMG_REQUIRE(nc <= 1024, GMG_ERR_INVALID, "more than 1024 colours");
             L->own_lo.assign(size_t(nc), 0); L->own_hi.assign(size_t(nc), 0);
             if (nc > 0) {
                 auto d_off = to_device(c, L->col.offsets.data(), int64_t(nc) + 1);
                 DevBuf<int32_t> d_b(c, 2 * int64_t(nc));
-                GMG_LAUNCH(c, bucket_bounds_kernel, 1, 64, 0, nc, L->col.rows.p, d_off.p, L->lo, L->hi, d_b.p);
+                GMG_LAUNCH(c, bucket_bounds_kernel, 1, 1024, 0, nc, L->col.rows.p, d_off.p, L->lo, L->hi, d_b.p);
                 std::vector<int32_t> hb(size_t(2 * nc));
                 d_b.download(hb.data(), 2 * int64_t(nc));
                 sync(c);

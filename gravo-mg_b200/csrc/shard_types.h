@@ -48,6 +48,8 @@ struct gmg_shard {
     std::vector<int64_t> rows_off;   // world + 1 element offsets of xQ / xt, or of A_c's arrays while those are exchanged
     bool rows_are_ac = false;        // ROWS_ID / ROWS_VAL currently name the arrays of A_c
     StageStatus status;
+    DevBuf<int64_t> xstatus;         // exchange: 8 status words per rank (LEVEL_STATUS / LEVEL_END)
+    int64_t status_host[8] = {0};
     // Galerkin side (build_galerkin): the level's system matrix (replicated, pattern = any) and the exchange
     int32_t a_n = 0;
     const int32_t* a_colptr = nullptr;

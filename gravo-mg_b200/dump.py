@@ -33,8 +33,7 @@ def dump_hierarchy(h, fine_points, outdir):
     pts = np.asarray(fine_points)
     for lvl in range(h.num_levels):
         a = h.level_arrays(lvl)
-        P = h.prolongation(lvl)
-        proj = P @ a["cpts"]                                    # projectedPoints (src/multigrid.cpp:500-510)
+        proj = h.projected_points(lvl)                          # projectedPoints on the device (src/multigrid.cpp:500-510)
         for name, arr in (("coarse_points", a["cpts"]), ("parents", a["par"]), ("samples", a["sel"]),
                           ("P_rowptr", a["prp"]), ("P_colidx", a["pci"]), ("P_val", a["pva"]), ("projected", proj)):
             path = os.path.join(outdir, f"level{lvl}_{name}.npy")

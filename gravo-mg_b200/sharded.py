@@ -27,15 +27,16 @@ from .capi import (GmgError, HierarchyOptions, LevelInfo, _f64p, _p,
 
 (PH_LEVEL_BEGIN, PH_SAMPLER_BUILD, PH_SAMPLER_ROUND, PH_SAMPLER_CHECK, PH_SAMPLES, PH_PARENTS_PULL, PH_PARENTS_CHECK,
  PH_PARENTS_PRED, PH_PARENTS_RESOLVE, PH_COARSE_ROWS, PH_COARSE_PACK, PH_COARSE_ASSEMBLE, PH_PROLONG,
- PH_LEVEL_END, PH_RADIUS, PH_P_COUNT, PH_P_PACK, PH_GALERKIN_ROWS, PH_GALERKIN_PACK, PH_GALERKIN_ASSEMBLE) = range(20)
+ PH_LEVEL_END, PH_RADIUS, PH_P_COUNT, PH_P_PACK, PH_GALERKIN_ROWS, PH_GALERKIN_PACK, PH_GALERKIN_ASSEMBLE,
+ PH_LEVEL_STATUS) = range(21)
 (XB_STATE, XB_CHANGED, XB_DIST, XB_PRED, XB_PARENTS, XB_COARSE_COUNT, XB_ROWS_ID, XB_ROWS_VAL, XB_LEN_PARTIAL,
- XB_P_COUNT, XB_P_COL, XB_P_VAL) = range(12)
+ XB_P_COUNT, XB_P_COL, XB_P_VAL, XB_STATUS) = range(13)
 PHASE_NAMES = ["level_begin", "sampler_build", "sampler_round", "sampler_check", "samples", "parents_pull", "parents_check",
                "parents_pred", "parents_resolve", "coarse_rows", "coarse_pack", "coarse_assemble", "prolong", "level_end",
-               "radius", "p_count", "p_pack", "galerkin_rows", "galerkin_pack", "galerkin_assemble"]
+               "radius", "p_count", "p_pack", "galerkin_rows", "galerkin_pack", "galerkin_assemble", "level_status"]
 V_BUFFERS = (XB_ROWS_ID, XB_ROWS_VAL, XB_P_COL, XB_P_VAL)      # slices of different sizes (packed rows)
 BUFFER_NAMES = ["state", "changed", "dist", "pred", "parents", "coarse_count", "rows_id", "rows_val", "len_partial",
-                "p_count", "p_col", "p_val"]
+                "p_count", "p_col", "p_val", "status"]
 
 
 def partition(count, world, rank):
@@ -359,6 +360,9 @@ class ShardedHierarchy:
                 self._gather(XB_ROWS_ID)
                 self._gather(XB_ROWS_VAL)
                 self._phase(PH_GALERKIN_ASSEMBLE)
+            # the deferred checks of the level on the values of ALL ranks: every rank raises the same error together
+            self._phase(PH_LEVEL_STATUS)
+            self._gather(XB_STATUS)
             self._phase(PH_LEVEL_END)
 
     # ---- results -------------------------------------------------------------------------------------

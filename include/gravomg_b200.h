@@ -227,7 +227,10 @@ typedef enum {
     GMG_H_AC_COLPTR = 13,     /* int32[m+1]   A_c = P^T A P, compressed column-major like A */
     GMG_H_AC_ROWIDX = 14,     /* int32[nnz_ac] ascending per column, structural (un-pruned) pattern */
     GMG_H_AC_VAL = 15,        /* f64[nnz_ac] */
-    GMG_H_FINE_VAL = 16       /* f64[nnz] level-0 only: the toEdgeDistanceMatrix values */
+    GMG_H_FINE_VAL = 16,      /* f64[nnz] level-0 only: the toEdgeDistanceMatrix values */
+    GMG_H_PROJECTED = 17      /* f64[3n], column-major, ld = n: projectedPoints(P, coarse_points) = P X_c
+                                 (src/multigrid.cpp:500-510, test/main.cpp:147), computed on the device from the
+                                 resident P and coarse points when it is fetched */
 } gmg_hierarchy_array;
 int gmg_hierarchy_fetch(gmg_ctx* ctx, const gmg_hierarchy* h, int level, int which, void* out);
 /* The same copy on the context's COPY stream, not waited for (arrays without an int64 conversion only: the
@@ -284,7 +287,12 @@ int gmg_solver_pcg(gmg_ctx* ctx, gmg_solver* s, const double* b, double* x, doub
  *   SAMPLES -> io[0] = m ; repeat { PARENTS_PULL ; G(DIST) ; G(CHANGED) ; PARENTS_CHECK -> io[0] =
  *   improved vertices; stop at 0 } ; PARENTS_PRED ; G(PRED) ; PARENTS_RESOLVE ; G(PARENTS) ;
  *   COARSE_ROWS ; G(COARSE_COUNT) ; COARSE_PACK ; G(ROWS_ID) ; G(ROWS_VAL) ; COARSE_ASSEMBLE ;
- *   PROLONG ; [Galerkin, below] ; LEVEL_END -> io = {m, nnz_c, T, nnz_p of the owned rows, nnz_ac}.
+ *   PROLONG ; [Galerkin, below] ; LEVEL_STATUS ; G(STATUS) ; LEVEL_END -> io = {m, nnz_c, T, nnz_p of the owned rows,
+ *   nnz_ac}. LEVEL_STATUS puts the rank's deferred error flags and counters (zero-length edge, missing offer, coarse
+ *   overflow / asymmetry, degenerate fan, fallback rows, owned rows) into its slice of STATUS; LEVEL_END evaluates
+ *   the checks on the values of ALL ranks -- flags OR-ed, the fallback ratio of src/multigrid.cpp:488 over the whole
+ *   level -- so that every rank raises the same error together (a rank that left the loop alone would leave the
+ *   others waiting in the next all-gather) and the error behaviour equals the single-GPU build's.
  * With build_galerkin (A_c = P^T A P on every level, replicated because it is the next level's A):
  *   P_COUNT ; G(P_COUNT) ; P_PACK ; G(P_COL) ; G(P_VAL) ; GALERKIN_ROWS (transpose the owned coarse
  *   columns of P, two-pass SpGEMM on the owned outer vectors) ; G(COARSE_COUNT) ; GALERKIN_PACK ;
@@ -294,9 +302,10 @@ typedef struct gmg_shard gmg_shard;
 enum { GMG_PH_LEVEL_BEGIN = 0, GMG_PH_SAMPLER_BUILD, GMG_PH_SAMPLER_ROUND, GMG_PH_SAMPLER_CHECK, GMG_PH_SAMPLES,
        GMG_PH_PARENTS_PULL, GMG_PH_PARENTS_CHECK, GMG_PH_PARENTS_PRED, GMG_PH_PARENTS_RESOLVE, GMG_PH_COARSE_ROWS,
        GMG_PH_COARSE_PACK, GMG_PH_COARSE_ASSEMBLE, GMG_PH_PROLONG, GMG_PH_LEVEL_END, GMG_PH_RADIUS,
-       GMG_PH_P_COUNT, GMG_PH_P_PACK, GMG_PH_GALERKIN_ROWS, GMG_PH_GALERKIN_PACK, GMG_PH_GALERKIN_ASSEMBLE };
+       GMG_PH_P_COUNT, GMG_PH_P_PACK, GMG_PH_GALERKIN_ROWS, GMG_PH_GALERKIN_PACK, GMG_PH_GALERKIN_ASSEMBLE,
+       GMG_PH_LEVEL_STATUS };
 enum { GMG_XB_STATE = 0, GMG_XB_CHANGED, GMG_XB_DIST, GMG_XB_PRED, GMG_XB_PARENTS, GMG_XB_COARSE_COUNT, GMG_XB_ROWS_ID,
-       GMG_XB_ROWS_VAL, GMG_XB_LEN_PARTIAL, GMG_XB_P_COUNT, GMG_XB_P_COL, GMG_XB_P_VAL };
+       GMG_XB_ROWS_VAL, GMG_XB_LEN_PARTIAL, GMG_XB_P_COUNT, GMG_XB_P_COL, GMG_XB_P_VAL, GMG_XB_STATUS };
 /* `in` is the WHOLE level-0 problem, resident on this rank's device (the same on every rank); it must
  * outlive the shard */
 int gmg_shard_create(gmg_ctx* ctx, int rank, int world, const gmg_input* in, const gmg_hierarchy_options* opt,

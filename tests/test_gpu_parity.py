@@ -63,6 +63,8 @@ def test_resident_hierarchy_matches_oracle(ctx, orc, name, scale):
     for lvl, w in enumerate(want):
         g = h.level_arrays(lvl)
         assert_level_equal(g, w, keys=keys, what=f"{name} level {lvl} ")
+        # projectedPoints from the resident arrays (GMG_H_PROJECTED), bit-exact like the per-function call
+        assert np.array_equal(h.projected_points(lvl), orc.projected_points(w["prp"], w["pci"], w["pva"], w["cpts"]))
         # Galerkin operator: the structural (un-pruned) pattern must be EQUAL to the CPU product's, values within
         # 1e-12; scipy (which sums duplicates and keeps explicit zeros too) cross-checks the CPU product itself
         P = h.prolongation(lvl)

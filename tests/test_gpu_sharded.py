@@ -152,3 +152,27 @@ def test_device_torus_generator(ctx):
     h = capi.Hierarchy(ctx, inp, 3, sampler_mode=capi.SAMPLER_HASHED)
     assert h.num_levels == 2 and h.info[0]["m"] > 0
     h.close(); inp.close()
+
+
+def test_sharded_errors_are_raised_by_every_rank(ctx):
+    """A duplicate point in ONE rank's slice: the zero-length-edge flag is local to that rank's pull kernel, but the
+    level-end checks run on the statuses of all ranks (LEVEL_STATUS / G(STATUS) / LEVEL_END), so every rank --
+    here the first virtual rank, whose own slice is clean -- raises the same error instead of walking into the
+    next level's all-gather alone."""
+    cfg = meshgen.make_config("C3", 0.004)
+    V, A = np.array(cfg["V"], order="F"), cfg["A"]
+    n = V.shape[0]
+    world = 4
+    v = int(n * 0.6)                                   # a vertex of rank 2's slice
+    nb = A.indices[A.indptr[v]:A.indptr[v + 1]]
+    u = int(nb[nb != v][0])
+    assert n // 2 < min(u, v) and max(u, v) < 3 * n // 4
+    V[u] = V[v]
+    inp = capi.Input(ctx, V, A.indptr, A.indices, None)
+    with pytest.raises(capi.GmgError) as e:
+        ShardedHierarchy(ctx, inp, cfg["levels"], world, list(range(world)), comm=None, sampler_mode=capi.SAMPLER_HASHED, seed=7)
+    assert e.value.status == 4
+    with pytest.raises(capi.GmgError) as e:            # the single-GPU build reports the same thing
+        capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=capi.SAMPLER_HASHED, seed=7)
+    assert e.value.status == 4
+    inp.close()

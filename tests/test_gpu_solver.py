@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import scipy.sparse as sp
 
-from gravomg_b200 import meshgen
+from gravomg_b200 import capi, meshgen
 
 pytestmark = pytest.mark.gpu
 
@@ -85,3 +85,35 @@ def test_pcg_with_vcycle_preconditioner(ctx):
     _, info = spla.cg(A, b, rtol=1e-10, maxiter=len(res) - 1)
     assert info != 0
     s.close(); h.close(); inp.close()
+
+
+def test_colouring_is_proper_beyond_64_colours(ctx):
+    """Rows with far more than 64 neighbours (Galerkin operators of kNN-32 clouds, deep coarse levels): no stored
+    entry may join two rows of the same colour, or the 'multicolour' sweep is no longer a Gauss-Seidel sweep.
+    Checked on A_c of a kNN cloud and on a banded matrix whose rows need ~100 colours."""
+    import scipy.sparse as sp
+    from oracle.pyoracle import Oracle
+    cfg = meshgen.make_config("C4", 1500 / 20_000_000)
+    V, A0 = cfg["V"], cfg["A"]
+    inp = capi.Input(ctx, V, A0.indptr, A0.indices, A0.data + 0.0)
+    h = capi.Hierarchy(ctx, inp, 3, build_galerkin=True)
+    mats = [h.galerkin(0).tocsr()]
+    h.close(); inp.close()
+    n = 600
+    band = sp.diags([np.full(n - abs(k), -1.0 if k else 250.0) for k in range(-100, 101)], list(range(-100, 101)), format="csr")
+    mats.append(band)
+    for A in mats:
+        A = sp.csr_matrix(A); A.sort_indices()
+        n = A.shape[0]
+        A = A + sp.diags(np.asarray(np.abs(A).sum(axis=1)).ravel() + 1.0)           # diagonally dominant: the sweep is well defined
+        A = sp.csr_matrix(A); A.sort_indices()
+        b = np.ones(n)
+        x1, colours, nc = capi.gauss_seidel(ctx, A.indptr, A.indices, A.data, b, np.zeros(n), sweeps=2)
+        coo = A.tocoo()
+        off = coo.row != coo.col
+        assert colours.min() >= 0 and colours.max() == nc - 1
+        assert np.all(colours[coo.row[off]] != colours[coo.col[off]]), "two coupled rows share a colour"
+        order = np.lexsort((np.arange(n), colours)).astype(np.int32)
+        want = Oracle("orc").gauss_seidel(A.indptr, A.indices, A.data, b, np.zeros(n), order, sweeps=2)
+        assert np.abs(x1 - want).max() <= 1e-12 * np.abs(want).max()
+    assert nc > 64        # the banded matrix needs more colours than one 64-bit mask holds
