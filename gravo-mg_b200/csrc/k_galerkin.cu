@@ -222,23 +222,22 @@ struct GalerkinWarpVals {
     double fvals[kGFineSlots];
     double vals[kGWarpSlots];
     double rp[kGMaxR];                // P(k, i)
+    double xch[32];                   // group_accumulate's exchange
 };
 
 // Add v to acc[slot] for every lane with valid == true; lanes holding the same key are summed first, in lane
-// order, by the lowest of them (see the header comment). All 32 lanes must call.
-__device__ __forceinline__ void group_accumulate(bool valid, int32_t key, int slot, double v, double* acc, int lane) {
+// order, by the lowest of them (see the header comment). The values travel through 32 doubles of shared memory so
+// that only the group leaders loop. All 32 lanes must call.
+__device__ __forceinline__ void group_accumulate(bool valid, int32_t key, int slot, double v, double* acc, double* xch, int lane) {
     const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : -1 - lane);
-    const bool leader = valid && (__ffs(grp) - 1) == lane;
-    const int longest = __reduce_max_sync(0xffffffffu, valid ? __popc(grp) : 0);
-    unsigned rest = grp;
-    double partial = 0.0;
-    for (int it = 0; it < longest; ++it) {
-        const int src = rest ? __ffs(rest) - 1 : lane;
-        const double o = __shfl_sync(0xffffffffu, v, src);
-        if (rest) partial = it == 0 ? o : partial + o;
-        rest &= rest - 1;
+    xch[lane] = v;
+    __syncwarp();
+    if (valid && (__ffs(grp) - 1) == lane) {
+        double partial = v;
+        for (unsigned rest = grp & (grp - 1); rest; rest &= rest - 1) partial = partial + xch[__ffs(rest) - 1];
+        acc[slot] = acc[slot] + partial;
     }
-    if (leader) acc[slot] = acc[slot] + partial;
+    __syncwarp();
 }
 
 // Two-step row for ONE WARP (see the header comment).
@@ -266,44 +265,34 @@ __device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int
         if (lane < nr) { sm.rk[rank0] = k0; if (NUMERIC) sv->rp[rank0] = p0; }
         if (lane + 32 < nr) { sm.rk[rank1] = k1; if (NUMERIC) sv->rp[rank1] = p1; }
         __syncwarp();
-        // lengths, inclusive scan over 64 entries held two per lane (entry 2*lane, 2*lane + 1)
-        const int32_t e0 = 2 * lane, e1 = 2 * lane + 1;
-        int32_t d0 = 0, d1 = 0;
-        if (e0 < nr) { const int32_t k = sm.rk[e0]; d0 = __ldg(a.a_ptr + k + 1) - __ldg(a.a_ptr + k); }
-        if (e1 < nr) { const int32_t k = sm.rk[e1]; d1 = __ldg(a.a_ptr + k + 1) - __ldg(a.a_ptr + k); }
-        int32_t incl = d0 + d1;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        sm.rbase[e0] = incl - d0 - d1;
-        sm.rbase[e1] = incl - d1;
-        if (lane == 31) sm.rbase[kGMaxR] = incl;
-        __syncwarp();
     }
-    const int32_t np = sm.rbase[kGMaxR];
-    // ---- step 1: fine-keyed, 32 products per sub-step
+    // ---- step 1: fine-keyed. A sub-step takes 4 rows k of R (8 lanes each) and entries [q0, q0 + 8) of A's outer
+    //      vectors k; lane = 8 * (k's place among the 4) + (q - q0).
     bool full = false;
-    for (int32_t p0 = 0; p0 < np; p0 += 32) {
-        const int32_t pos = p0 + lane;
-        const bool valid = pos < np;
-        int32_t l = 0;
-        double w = 0.0;
-        int slot = -1;
-        if (valid) {
-            int32_t lo = 0, hi = nr;                 // last e with rbase[e] <= pos
-            while (hi - lo > 1) { const int32_t mid = (lo + hi) >> 1; if (sm.rbase[mid] <= pos) lo = mid; else hi = mid; }
-            const int32_t k = sm.rk[lo];
-            const int32_t q = __ldg(a.a_ptr + k) + (pos - sm.rbase[lo]);
-            l = __ldg(a.a_idx + q);
-            if (NUMERIC) w = sv->rp[lo] * __ldg(a.a_val + q);
-            slot = hash_insert<kGFineSlots>(sm.fkeys, l, sm.scount);
-            if (slot < 0) full = true;
+    constexpr int kSub = 8;
+    for (int32_t e0 = 0; e0 < nr; e0 += 32 / kSub) {
+        const int32_t e = e0 + lane / kSub;
+        int32_t ab = 0, ae = 0;
+        double pki = 0.0;
+        if (e < nr) {
+            const int32_t k = sm.rk[e];
+            ab = __ldg(a.a_ptr + k); ae = __ldg(a.a_ptr + k + 1);
+            if (NUMERIC) pki = sv->rp[e];
         }
-        if (NUMERIC) {
-            group_accumulate(valid && slot >= 0, l, slot, w, sv->fvals, lane);
-            __syncwarp();
+        const int32_t longest = __reduce_max_sync(0xffffffffu, ae - ab);
+        for (int32_t q0 = 0; q0 < longest; q0 += kSub) {
+            const int32_t q = ab + q0 + lane % kSub;
+            const bool valid = q < ae;
+            int32_t l = 0;
+            double w = 0.0;
+            int slot = -1;
+            if (valid) {
+                l = __ldg(a.a_idx + q);
+                if (NUMERIC) w = pki * __ldg(a.a_val + q);
+                slot = hash_insert<kGFineSlots>(sm.fkeys, l, sm.scount);
+                if (slot < 0) full = true;
+            }
+            if (NUMERIC) group_accumulate(valid && slot >= 0, l, slot, w, sv->fvals, sv->xch, lane);
         }
     }
     __syncwarp();
@@ -342,9 +331,12 @@ __device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int
             if (lane + 32 * u < kf) { sm.fkeys[rank[u]] = key[u]; sv->fvals[rank[u]] = val[u]; }
         __syncwarp();
     }
-    // ---- step 2: coarse-keyed, one lane per distinct fine index, entry t of every row of P in turn
-    for (int32_t f0 = 0; f0 < kf; f0 += 32) {
-        const int32_t f = f0 + lane;
+    // ---- step 2: coarse-keyed, one lane per distinct fine index, entry t of every row of P in turn. The sorted
+    //      fine indices are dealt out INTERLEAVED (round r takes f = lane * rounds + r): neighbouring fine rows
+    //      share their coarse columns, and lanes of one sub-step that hold the same column are summed one by one.
+    const int32_t rounds = (kf + 31) / 32;
+    for (int32_t r = 0; r < rounds; ++r) {
+        const int32_t f = lane * rounds + r;
         int32_t pb = 0, pe = 0;
         double cl = 0.0;
         if (f < kf) {
@@ -364,8 +356,7 @@ __device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int
             }
             if (NUMERIC) {
                 const double v = valid ? cl * __ldg(a.p_val + pb + t) : 0.0;
-                group_accumulate(valid && slot >= 0, j, slot, v, sv->vals, lane);
-                __syncwarp();
+                group_accumulate(valid && slot >= 0, j, slot, v, sv->vals, sv->xch, lane);
             }
         }
     }

@@ -126,9 +126,16 @@ struct SamplerArgs {
     uint8_t* res;                // [ranks] 1 = selected
     int32_t* flags;              // [0] a vertex has more than 65535 list entries
     unsigned long long* stats;   // [0] same-tile list entries, [1] all list entries (decides which flow kernel runs)
-    unsigned int* epoch;         // bumped by a tile after every push of other-tile effects: what waiting tiles watch
+    unsigned int* epoch;         // [tiles] word t is bumped by whoever pushed an effect INTO tile t: what a waiting tile watches
     int force_lane;              // GMG_SAMPLER_HASHED: no tile ever holds two coverers, always the per-lane flow
+    unsigned long long* dbg;     // GMG_SAMPLER_DEBUG: 8 words per tile (timeline of the tile flow), else null
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 
 // Which flow kernel runs is decided ON THE DEVICE from the build kernel's counts (no host round trip): the
 // tile-cooperative kernel pays off when at least a quarter of the list entries stay inside a flow tile, i.e.
@@ -319,7 +326,8 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
 // What crosses tiles goes through the global words: a selected rank ORs the OUT bit into its later coverees, a
 // rejected one subtracts its multiplicity, both without a return value. A tile that can make no progress does
 // not poll its 4096 words (148 waiting tiles doing that saturate the L2 and slow the one tile everybody waits
-// for): after every push a tile bumps ONE global epoch word, and a waiting tile watches that word only.
+// for): whoever pushes an effect into a tile bumps that tile's epoch word, and a waiting tile watches its own word
+// only -- a wake-up goes to the tile it concerns and to nobody else.
 //
 // (2) LANE flow, for incoherent orders (hashed priorities, subdivision orders): nearly every target sits in
 // another tile, the dependency depth is O(log n), and one rank per lane with no block-wide barriers is faster.
@@ -340,11 +348,13 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
     for (;;) {
         __syncthreads();                                   // everybody is done with the previous tile's shared state
-        if (tid == 0) { s_tile = atomicAdd(a.ticket, 1u); s_left = 0; s_epoch = *(volatile unsigned int*)a.epoch << 1; }
+        if (tid == 0) { s_tile = atomicAdd(a.ticket, 1u); s_left = 0; s_epoch = 0; }
         __syncthreads();
         const unsigned int tile = s_tile;
         if (tile >= a.tiles) break;
         const uint32_t t0 = tile << kTileLog;
+        const unsigned int* my_epoch = a.epoch + tile;
+        if (a.dbg && tid == 0) a.dbg[8 * tile + 0] = global_ns();
         // ---- static data of the tile's ranks; rank i of the tile belongs to thread i % kFlowThreads
         long long ptr[kOwn];
         uint32_t tot[kOwn], nin[kOwn], soff[kOwn], xoff[kOwn];
@@ -415,22 +425,27 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         __syncthreads();
         // ---- the flow: no barrier inside. Every thread spins over its undecided ranks; a decision is applied at
         //      once (same-tile targets in shared memory, the others with reductions on the global words), and a
-        //      warp that pushed something bumps the global epoch word so that the tiles waiting on it look again.
+        //      thread that pushed into other tiles bumps their epoch words so that they look again.
+        if (a.dbg && tid == 0) a.dbg[8 * tile + 1] = global_ns();
+        unsigned dbg_iter = 0, dbg_poll = 0;
+        bool dbg_first = true;
         uint32_t ext[kOwn];
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) ext[q] = 1u;                    // 1: the global word has not been read yet
-        unsigned int seen = s_epoch - 1u;                              // forces the first read
+        unsigned int seen = 0xFFFFFFFFu;                               // forces the first read
         unsigned idle = 0, watch = 0;
         while (*(volatile int32_t*)&s_left > 0) {
             // one thread of the block watches the epoch word (with a back-off while the block is making no progress)
-            if (tid == 0) {
+            if (tid == 0 && (dbg_iter & 3u) == 0u) {
                 // (every 4096th look also forces a fresh read of the words, whatever the epoch says: a lost
                 // wake-up must cost microseconds, never the kernel)
-                const unsigned int e = (*(volatile unsigned int*)a.epoch << 1) | ((++watch >> 12) & 1u);
+                const unsigned int e = ((*(volatile const unsigned int*)my_epoch << 1) | ((++watch >> 12) & 1u)) & 0x7FFFFFFFu;
                 if (e != *(volatile unsigned int*)&s_epoch) *(volatile unsigned int*)&s_epoch = e;
             }
+            ++dbg_iter;
             const unsigned int now = *(volatile unsigned int*)&s_epoch;
             if (now != seen) {
+                ++dbg_poll;
                 // the epoch was read BEFORE these words: a push that lands after this poll bumps it again
                 seen = now;
                 __threadfence();
@@ -438,7 +453,9 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 for (int q = 0; q < kOwn; ++q)     // a word that has reached 0 has no outside coverer left and stays 0
                     if (((undecided >> q) & 1u) && ext[q] != 0u) ext[q] = *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads);
             }
-            bool pushed = false, decided_any = false;
+            bool decided_any = false;
+            uint32_t wake[4];                      // tiles this thread pushed into during this pass
+            int nwake = 0;
 #pragma unroll
             for (int q = 0; q < kOwn; ++q) {
                 if (!((undecided >> q) & 1u)) continue;
@@ -449,6 +466,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 else continue;
                 undecided &= ~(1u << q);
                 decided_any = true;
+                if (a.dbg && dbg_first) { dbg_first = false; atomicMin(a.dbg + 8 * tile + 2, global_ns()); }
                 // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a rejected one releases
                 // its later coverees
                 const bool raw = nin[q] == kUnpartitioned;
@@ -473,24 +491,41 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 for (uint32_t e = first; e < tot[q]; ++e) {
                     const uint32_t x = xoff[q] != 0xFFFFFFFFu ? s_ext[xoff[q] + (e - first)] : a.lst[ptr[q] + e];
                     const uint32_t rt = x & rmask;
-                    if (raw && (rt >> kTileLog) == tile) continue;
-                    pushed = true;
+                    const uint32_t tt = rt >> kTileLog;
+                    if (raw && tt == tile) continue;
                     if (in) atomicOr(a.wext + rt, kOutFlag);
                     else atomicSub(a.wext + rt, (x >> a.order.kbits) + 1u);
+                    bool known = false;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) known = known || (u < nwake && wake[u] == tt);
+                    if (!known) {
+                        if (nwake == 4) {          // rare: flush what is noted so far (its pushes are fenced first)
+                            __threadfence();
+#pragma unroll
+                            for (int u = 0; u < 4; ++u) atomicAdd(a.epoch + wake[u], 1u);
+                            nwake = 0;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) if (u == nwake) wake[u] = tt;
+                        ++nwake;
+                    }
                 }
                 a.res[t0 + i] = in ? 1 : 0;
                 atomicSub(&s_left, 1);
             }
-            if (pushed) {                          // one bump per group of lanes that pushed together
+            if (nwake) {                           // the pushes first, then the wake-ups
                 __threadfence();
-                const cg::coalesced_group grp = cg::coalesced_threads();
-                if (grp.thread_rank() == 0) atomicAdd(a.epoch, 1u);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (u < nwake) atomicAdd(a.epoch + wake[u], 1u);
             }
             // a thread that is done with the tile meets the block at the barrier; thread 0 stays: it is the watcher
-            if (!undecided && tid != 0) break;
+            if (!undecided && tid != 0) { if (a.dbg) atomicMax(a.dbg + 8 * tile + 3, global_ns()); break; }
+            // no sleeping here: a waiting rank must react within one pass (the dependency chain of a row-major grid
+            // is tens of thousands of passes long); only a tile that has waited very long backs off
             if (decided_any) idle = 0;
-            else if (++idle > 8) __nanosleep(idle < 64 ? 20 : 100);
+            else if (++idle > 20000) __nanosleep(200);
         }
+        if (a.dbg && tid == 0) { a.dbg[8 * tile + 4] = dbg_iter; a.dbg[8 * tile + 5] = dbg_poll; a.dbg[8 * tile + 6] = global_ns(); a.dbg[8 * tile + 7] = blockIdx.x; }
     }
 }
 
@@ -629,11 +664,25 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     DevBuf<long long> lptr(c, int64_t(ranks));
     DevBuf<uint8_t> res(c, int64_t(ranks));
     DevBuf<int32_t> flag(c, n);
+    const unsigned ntiles = unsigned((ranks + kTile - 1) >> kTileLog);
+    DevBuf<unsigned int> epochs(c, int64_t(ntiles));
+    epochs.zero();
+    DevBuf<unsigned long long> dbg;
+    const bool debug = getenv("GMG_SAMPLER_DEBUG") != nullptr && mode != GMG_SAMPLER_HASHED;
+    if (debug) {
+        dbg.alloc(c, 8 * int64_t(ntiles));
+        GMG_CUDA(cudaMemsetAsync(dbg.p, 0, sizeof(unsigned long long) * 8 * size_t(ntiles), c->stream));
+        // first-decision slots start at the maximum (atomicMin)
+        std::vector<unsigned long long> init(size_t(8) * ntiles, 0ull);
+        for (unsigned t = 0; t < ntiles; ++t) init[size_t(8) * t + 2] = ~0ull;
+        GMG_CUDA(cudaMemcpyAsync(dbg.p, init.data(), sizeof(unsigned long long) * init.size(), cudaMemcpyHostToDevice, c->stream));
+        sync(c);
+    }
     GMG_LAUNCH(c, sampler_init_kernel, div_up(int64_t(ranks), kBlock), kBlock, 0, ranks, res.p);
     SamplerArgs a{n, colptr, rowidx, len, radius, order, wext.p, cint.p, lptr.p, lcnt.p, lst.p, cursor.p,
-                  reinterpret_cast<unsigned int*>(cursor.p + 2), unsigned((ranks + kTile - 1) >> kTileLog), res.p,
-                  reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, reinterpret_cast<unsigned int*>(cursor.p + 3) + 1,
-                  mode == GMG_SAMPLER_HASHED ? 1 : 0};
+                  reinterpret_cast<unsigned int*>(cursor.p + 2), ntiles, res.p,
+                  reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, epochs.p,
+                  mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr};
     if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, ranks, flag.p);
     else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, ranks, flag.p);
     // ascending compaction of the IN flags
@@ -646,6 +695,31 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     GMG_CUDA(cudaMemcpyAsync(&hflags, cursor.p + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     sync(c);
     GMG_REQUIRE((hflags & 0xFFFFFFFFull) == 0, GMG_ERR_INVALID, "fastDiscSample: a vertex covers more than 65535 later vertices");
+    if (debug) {        // timeline of the tile flow (diagnostic only)
+        std::vector<unsigned long long> h(size_t(8) * ntiles);
+        GMG_CUDA(cudaMemcpyAsync(h.data(), dbg.p, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost, c->stream));
+        sync(c);
+        if (h[6] != 0) {
+            unsigned long long t_begin = ~0ull, t_end = 0, iters = 0, polls = 0;
+            double active = 0.0, wait = 0.0;
+            for (unsigned t = 0; t < ntiles; ++t) {
+                const unsigned long long* w = h.data() + size_t(8) * t;
+                if (w[0] < t_begin) t_begin = w[0];
+                if (w[6] > t_end) t_end = w[6];
+                iters += w[4]; polls += w[5];
+                active += double(w[6] - w[2]); wait += double(w[2] - w[1]);
+            }
+            fprintf(stderr, "[gmg] sampler tile flow: n %d, %u tiles, %.3f ms; per tile: first decision -> done %.1f us, staged -> first decision %.1f us, "
+                            "%.0f spin iterations, %.0f polls\n", n, ntiles, double(t_end - t_begin) * 1e-6, active / ntiles * 1e-3,
+                    wait / ntiles * 1e-3, double(iters) / ntiles, double(polls) / ntiles);
+            for (unsigned t = 0; t < ntiles && t < 400; t += (t < 24 ? 1 : 47)) {
+                const unsigned long long* w = h.data() + size_t(8) * t;
+                fprintf(stderr, "[gmg]   tile %u block %llu: ticket %.1f staged %.1f first %.1f last-thread %.1f done %.1f us; iters %llu polls %llu\n", t, w[7],
+                        double(w[0] - t_begin) * 1e-3, double(w[1] - t_begin) * 1e-3, double(w[2] - t_begin) * 1e-3, double(w[3] - t_begin) * 1e-3,
+                        double(w[6] - t_begin) * 1e-3, w[4], w[5]);
+            }
+        }
+    }
     selection.alloc(c, m);
     GMG_LAUNCH(c, compact_kernel, div_up(n, kBlock), kBlock, 0, n, flag.p, pos.p, selection.p);
     return int32_t(m);
@@ -793,7 +867,7 @@ void shard_sampler_build(gmg_ctx* c, int32_t n, int32_t lo, int32_t hi, const in
     DevBuf<unsigned long long> cursor(c, 2);
     cursor.zero();
     SamplerArgs a{n, colptr, rowidx, len, radius, make_order(n, seed, mode), nullptr, nullptr, out.lptr.p,
-                  reinterpret_cast<uint32_t*>(out.lcnt.p), nullptr, cursor.p, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 1};
+                  reinterpret_cast<uint32_t*>(out.lcnt.p), nullptr, cursor.p, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 1, nullptr};
     if (mode == GMG_SAMPLER_EXACT) GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_EXACT>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     else GMG_LAUNCH(c, shard_path_bound_kernel<GMG_SAMPLER_PARALLEL>, div_up(own, kBlock), kBlock, 0, a, lo, hi, cursor.p + 1);
     unsigned long long hb[2];

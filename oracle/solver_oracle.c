@@ -14,8 +14,9 @@
  *                                         entries of A's outer vector k in stored (ascending) order
  *     out(j) = sum_l c(l) * P(l,j)        l ascending over the distinct l, entries of P's row l in stored order
  * with the SAME association as the CUDA kernel (gravo-mg_b200/csrc/k_galerkin.cu), which processes
- * the products 32 at a time and adds the partial sum of equal keys inside one group of 32 before it
- * touches the accumulator. Following that order makes the comparison bit-exact instead of 1e-12.
+ * the products one warp-wide window at a time (step 1: 4 rows k x 8 entries; step 2: 32 interleaved l, one
+ * entry of their rows of P) and adds the partial sum of equal keys inside a window before it touches the
+ * accumulator. Following that order makes the comparison bit-exact instead of 1e-12.
  *
  * Build: gcc -std=c11 -O2 -ffp-contract=off (no FMA contraction, no -march).
  */
@@ -92,17 +93,24 @@ void orc_galerkin(int64_t n, const int32_t* a_ptr, const int32_t* a_idx, const d
         }
         qsort(flist, kf, sizeof(int32_t), cmp_i32);
         for (size_t f = 0; f < kf; ++f) { fslot[flist[f]] = (int32_t)f; fval[f] = 0.0; }
-        /* step 1, values: the products in (k, q) order, 32 at a time */
+        /* step 1, values: a window holds 4 rows k of R (ascending) times entries [q0, q0 + 8) of A's outer vectors
+         * k, ordered (k, q) */
         int w = 0;
-        for (int32_t e = r_ptr[i]; e < r_ptr[i + 1]; ++e) {
-            const int32_t k = r_col[e];
-            const double pki = r_val[e];
-            for (int32_t q = a_ptr[k]; q < a_ptr[k + 1]; ++q) {
-                wkey[w] = a_idx[q]; wval[w] = pki * a_val[q]; ++w;
-                if (w == WINDOW) { window_accumulate(w, wkey, wval, fslot, fval); w = 0; }
+        for (int32_t e0 = r_ptr[i]; e0 < r_ptr[i + 1]; e0 += 4) {
+            const int32_t e1 = e0 + 4 < r_ptr[i + 1] ? e0 + 4 : r_ptr[i + 1];
+            int32_t longest = 0;
+            for (int32_t e = e0; e < e1; ++e) { const int32_t len = a_ptr[r_col[e] + 1] - a_ptr[r_col[e]]; if (len > longest) longest = len; }
+            for (int32_t q0 = 0; q0 < longest; q0 += 8) {
+                w = 0;
+                for (int32_t e = e0; e < e1; ++e) {
+                    const int32_t k = r_col[e];
+                    for (int32_t q = a_ptr[k] + q0; q < a_ptr[k + 1] && q < a_ptr[k] + q0 + 8; ++q) {
+                        wkey[w] = a_idx[q]; wval[w] = r_val[e] * a_val[q]; ++w;
+                    }
+                }
+                window_accumulate(w, wkey, wval, fslot, fval);
             }
         }
-        if (w) window_accumulate(w, wkey, wval, fslot, fval);
         /* step 2, keys: distinct coarse indices j, ascending */
         size_t kc = 0;
         for (size_t f = 0; f < kf; ++f) {
@@ -116,19 +124,29 @@ void orc_galerkin(int64_t n, const int32_t* a_ptr, const int32_t* a_idx, const d
         }
         qsort(clist, kc, sizeof(int32_t), cmp_i32);
         for (size_t s = 0; s < kc; ++s) { cslot[clist[s]] = (int32_t)s; cval[s] = 0.0; }
-        /* step 2, values: 32 distinct l per round (ascending); within a round entry t = 0, 1, 2 of every row of P
-         * in turn, each turn one window in l order */
-        for (size_t f0 = 0; f0 < kf; f0 += WINDOW) {
-            const size_t f1 = f0 + WINDOW < kf ? f0 + WINDOW : kf;
-            int32_t longest = 0;
-            for (size_t f = f0; f < f1; ++f) { const int32_t len = p_ptr[flist[f] + 1] - p_ptr[flist[f]]; if (len > longest) longest = len; }
-            for (int32_t t = 0; t < longest; ++t) {
-                w = 0;
-                for (size_t f = f0; f < f1; ++f) {
-                    const int32_t l = flist[f];
-                    if (p_ptr[l] + t < p_ptr[l + 1]) { wkey[w] = p_col[p_ptr[l] + t]; wval[w] = fval[f] * p_val[p_ptr[l] + t]; ++w; }
+        /* step 2, values: the sorted distinct l are dealt out interleaved over 32 lanes (round r takes
+         * f = lane * rounds + r); within a round entry t = 0, 1, 2 of every row of P in turn, each turn one window
+         * in lane order */
+        {
+            const size_t rounds = (kf + WINDOW - 1) / WINDOW;
+            for (size_t r = 0; r < rounds; ++r) {
+                int32_t longest = 0;
+                for (size_t lane = 0; lane < WINDOW; ++lane) {
+                    const size_t f = lane * rounds + r;
+                    if (f >= kf) continue;
+                    const int32_t len = p_ptr[flist[f] + 1] - p_ptr[flist[f]];
+                    if (len > longest) longest = len;
                 }
-                window_accumulate(w, wkey, wval, cslot, cval);
+                for (int32_t t = 0; t < longest; ++t) {
+                    w = 0;
+                    for (size_t lane = 0; lane < WINDOW; ++lane) {
+                        const size_t f = lane * rounds + r;
+                        if (f >= kf) continue;
+                        const int32_t l = flist[f];
+                        if (p_ptr[l] + t < p_ptr[l + 1]) { wkey[w] = p_col[p_ptr[l] + t]; wval[w] = fval[f] * p_val[p_ptr[l] + t]; ++w; }
+                    }
+                    window_accumulate(w, wkey, wval, cslot, cval);
+                }
             }
         }
         if (onnz + kc > ocap) { while (onnz + kc > ocap) ocap *= 2; oi = (int32_t*)realloc(oi, sizeof(int32_t) * ocap); ov = (double*)realloc(ov, sizeof(double) * ocap); }

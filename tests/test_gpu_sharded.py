@@ -159,6 +159,7 @@ def test_sharded_errors_are_raised_by_every_rank(ctx):
     level-end checks run on the statuses of all ranks (LEVEL_STATUS / G(STATUS) / LEVEL_END), so every rank --
     here the first virtual rank, whose own slice is clean -- raises the same error instead of walking into the
     next level's all-gather alone."""
+    from gravomg_b200.sharded import ShardedHierarchy
     cfg = meshgen.make_config("C3", 0.004)
     V, A = np.array(cfg["V"], order="F"), cfg["A"]
     n = V.shape[0]

@@ -88,3 +88,40 @@ def test_headless_ply_dump(tmp_path):
     assert len(body) == 6
     assert np.allclose([float(v) for v in body[3].split()], [0, 0, 1.5, 1])
     assert body[5].split() == ["3", "0", "2", "3"]
+
+
+@pytest.mark.parametrize("name,scale", [("C1", 1.0), ("C3", 0.004), ("C4", 0.001)])
+def test_solver_oracle_matches_scipy(orc, name, scale):
+    """The parts the reference lacks (oracle/solver_oracle.c): P^T A P with the structural pattern of an un-pruned
+    product and sorted indices, SpMV, Gauss-Seidel -- pinned against scipy / numpy, on every level of a hierarchy."""
+    import scipy.sparse as sp
+    cfg = meshgen.make_config(name, scale)
+    V, A = cfg["V"], cfg["A"]
+    res = run_hierarchy(orc, V, A, cfg["levels"])
+    Acur = A.tocsc()
+    for r in res:
+        n, m = len(r["par"]), len(r["sel"])
+        P = sp.csr_matrix((r["pva"], r["pci"], r["prp"]), shape=(n, m))
+        ptr, idx, val = orc.galerkin(Acur.indptr, Acur.indices, Acur.data, P.indptr, P.indices, P.data, m)
+        got = sp.csc_matrix((val, idx, ptr), shape=(m, m))
+        assert np.all(np.diff(ptr) >= 0) and got.has_sorted_indices
+        # structural pattern: every (j, i) reachable through stored entries of P, A, P -- with 0/1 matrices
+        ones = lambda M: sp.csr_matrix((np.ones(M.nnz), M.indices, M.indptr), shape=M.shape) if M.format == "csr" else \
+            sp.csc_matrix((np.ones(M.nnz), M.indices, M.indptr), shape=M.shape)
+        pat = (ones(P).T @ ones(Acur) @ ones(P)).tocsc()
+        pat.sort_indices()
+        assert np.array_equal(pat.indptr, ptr) and np.array_equal(pat.indices, idx)
+        want = (P.T @ Acur @ P).tocsc()
+        assert np.abs((got - want).tocoo().data).max(initial=0.0) <= 1e-13 * np.abs(want.data).max()
+        Acur = got
+    n = A.shape[0]
+    x = np.random.default_rng(1).standard_normal(n)
+    assert np.abs(orc.spmv(A.indptr, A.indices, A.data, x) - A.T @ x).max() <= 1e-12 * np.abs(A.T @ x).max()
+    As = (A + sp.identity(n)).tocsr(); As.sort_indices()
+    b = np.ones(n)
+    got = orc.gauss_seidel(As.indptr, As.indices, As.data, b, np.zeros(n), np.arange(n, dtype=np.int32), sweeps=2)
+    Lo = sp.tril(As, format="csr")
+    want = np.zeros(n)
+    for _ in range(2):
+        want = sp.linalg.spsolve_triangular(Lo, b - (As - Lo) @ want, lower=True)
+    assert np.abs(got - want).max() <= 1e-10 * np.abs(want).max()
