@@ -38,32 +38,50 @@ namespace gmg {
 constexpr int kLanes = 8;    // lanes cooperating on one vertex in the build kernel (mesh columns hold ~7 entries)
 constexpr int kStage = 16;   // later-path targets a lane can stage in shared memory
 
-// Precedence order. EXACT: rank(v) = v. Otherwise a vertex is cut into (super-tile, offset) = (v >> tshift,
-// v & (2^tshift - 1)) and the SUPER-TILE number goes through a seeded invertible mixing of kt-bit integers:
-// xor-seed, then (odd multiply, xorshift by ceil(kt/2)) twice and a last odd multiply, all modulo 2^kt; every
-// step is a bijection on kt bits and the xorshift is its own inverse because twice the shift is >= kt.
-//   GMG_SAMPLER_HASHED    tshift = 0: every vertex hashed, dependency depth O(log n)
-//   GMG_SAMPLER_PARALLEL  tshift = ceil(log2(n / 3)): the reference's index-order sweep restarted in 2-3
-//                         super-tiles taken in hashed order (why: DESIGN.md section 4, "sampler orders")
+// Precedence order.
+//   GMG_SAMPLER_EXACT     rank(v) = v: the reference's order.
+//   GMG_SAMPLER_HASHED    every vertex index goes through a seeded invertible mixing of k-bit integers: xor-seed,
+//                         then (odd multiply, xorshift by ceil(k/2)) twice and a last odd multiply, all modulo 2^k;
+//                         every step is a bijection on k bits and the xorshift is its own inverse because twice the
+//                         shift is >= k. Dependency depth O(log n).
+//   GMG_SAMPLER_PARALLEL  the reference's index-order sweep restarted in `supers` (3) contiguous SUPER-TILES of
+//                         `ssize` vertices (a multiple of the flow tile) that are swept CONCURRENTLY: the flow tiles
+//                         of the super-tiles are interleaved in the order, rank = ((flow tile in its super-tile) *
+//                         supers + super-tile) * kTile + offset. Every super-tile starts at once (its first rows
+//                         precede the last rows of its neighbour), so the dependency depth is a third of the index
+//                         order's; the packing is the reference's except along the seams (why: DESIGN.md section 4,
+//                         "sampler orders"). The seed is not used.
 struct Order {
     uint32_t mask, shift, seed;
     uint32_t c1, c2, c3, i1, i2, i3;   // odd multipliers and their inverses modulo 2^32
-    uint32_t tshift;                   // log2 of the super-tile size
-    uint32_t kbits;                    // bits of a rank (kt + tshift); ranks live in [0, 2^kbits)
+    uint32_t supers, ssize;            // PARALLEL: number and size of the super-tiles (supers == 0: HASHED)
+    uint32_t kbits;                    // bits of a rank; ranks live in [0, 2^kbits)
 };
+constexpr int kOrderTileLog = 12;      // = kTileLog of the tile flow kernel
 __host__ __device__ __forceinline__ uint32_t order_rank(const Order& o, uint32_t v) {
-    uint32_t x = ((v >> o.tshift) ^ o.seed) & o.mask;
+    if (o.supers) {
+        const uint32_t sup = (v >= o.ssize ? 1u : 0u) + (v >= 2u * o.ssize ? 1u : 0u);
+        const uint32_t inner = v - sup * o.ssize;
+        return (((inner >> kOrderTileLog) * o.supers + sup) << kOrderTileLog) | (inner & ((1u << kOrderTileLog) - 1u));
+    }
+    uint32_t x = (v ^ o.seed) & o.mask;
     x = (x * o.c1) & o.mask; x ^= x >> o.shift;
     x = (x * o.c2) & o.mask; x ^= x >> o.shift;
     x = (x * o.c3) & o.mask;
-    return (x << o.tshift) | (v & ((1u << o.tshift) - 1u));
+    return x;
 }
+// (a rank that stands for no vertex comes back as a value >= n)
 __host__ __device__ __forceinline__ uint32_t order_unrank(const Order& o, uint32_t r) {
-    uint32_t x = ((r >> o.tshift) * o.i3) & o.mask;
+    if (o.supers) {
+        const uint32_t q = r >> kOrderTileLog;
+        const uint32_t ft = q / o.supers, sup = q - ft * o.supers;
+        const uint32_t inner = (ft << kOrderTileLog) | (r & ((1u << kOrderTileLog) - 1u));
+        return inner < o.ssize ? sup * o.ssize + inner : 0xFFFFFFFFu;
+    }
+    uint32_t x = (r * o.i3) & o.mask;
     x ^= x >> o.shift; x = (x * o.i2) & o.mask;
     x ^= x >> o.shift; x = (x * o.i1) & o.mask;
-    x = (x ^ o.seed) & o.mask;
-    return (x << o.tshift) | (r & ((1u << o.tshift) - 1u));
+    return (x ^ o.seed) & o.mask;
 }
 static uint32_t inverse_odd(uint32_t c) {       // Newton iteration for c^-1 modulo 2^32
     uint32_t x = c;
@@ -77,9 +95,16 @@ static Order make_order(int32_t n, uint64_t seed, int mode) {
         o.kbits = uint32_t(ceil_log2(n > 1 ? n : 2));
         return o;
     }
-    o.tshift = mode == GMG_SAMPLER_PARALLEL ? uint32_t(ceil_log2((int64_t(n) + 2) / 3)) : 0u;
-    const int64_t tiles = (int64_t(n) + (int64_t(1) << o.tshift) - 1) >> o.tshift;
-    const int kt = ceil_log2(tiles);
+    if (mode == GMG_SAMPLER_PARALLEL) {
+        constexpr int64_t tile = int64_t(1) << kOrderTileLog;
+        const int64_t third = ((int64_t(n) + 2) / 3 + tile - 1) / tile * tile;
+        o.ssize = uint32_t(third);
+        o.supers = uint32_t((int64_t(n) + third - 1) / third);          // 3, fewer for a small n
+        o.kbits = uint32_t(ceil_log2(third * int64_t(o.supers)));
+        if (o.kbits == 0) o.kbits = 1;
+        return o;
+    }
+    const int kt = ceil_log2(n);
     o.mask = kt >= 32 ? 0xFFFFFFFFu : ((1u << kt) - 1u);
     o.shift = uint32_t((kt + 1) / 2);
     if (o.shift == 0) o.shift = 1;
@@ -87,7 +112,7 @@ static Order make_order(int32_t n, uint64_t seed, int mode) {
     o.seed = uint32_t(z >> 32) & o.mask;
     o.c1 = 0x9E3779B1u; o.c2 = 0x85EBCA6Bu | 1u; o.c3 = 0xC2B2AE35u | 1u;
     o.i1 = inverse_odd(o.c1); o.i2 = inverse_odd(o.c2); o.i3 = inverse_odd(o.c3);
-    o.kbits = uint32_t(kt) + o.tshift;
+    o.kbits = uint32_t(kt);
     if (o.kbits == 0) o.kbits = 1;
     return o;
 }
@@ -99,7 +124,7 @@ static Order make_order(int32_t n, uint64_t seed, int mode) {
 // lst       later coverees of every vertex as rank | (multiplicity - 1) << kbits: duplicates are merged (a mesh
 //           vertex has ~24 later paths but ~8 distinct later coverees), same-tile targets first
 // lcnt[r]   entries of the list | same-tile entries << 16 (0xFFFF: list not partitioned nor merged, see the build kernel)
-constexpr int kTileLog = 12;
+constexpr int kTileLog = kOrderTileLog;
 constexpr int kTile = 1 << kTileLog;          // ranks per flow tile
 constexpr int kFlowThreads = 1024;
 constexpr int kOwn = kTile / kFlowThreads;    // ranks per thread
@@ -126,9 +151,13 @@ struct SamplerArgs {
     uint8_t* res;                // [ranks] 1 = selected
     int32_t* flags;              // [0] a vertex has more than 65535 list entries
     unsigned long long* stats;   // [0] same-tile list entries, [1] all list entries (decides which flow kernel runs)
-    unsigned int* epoch;         // [tiles] word t is bumped by whoever pushed an effect INTO tile t: what a waiting tile watches
+    unsigned int* epoch;         // [tiles] tile flow: entries reserved in the mailbox of tile t
     int force_lane;              // GMG_SAMPLER_HASHED: no tile ever holds two coverers, always the per-lane flow
     unsigned long long* dbg;     // GMG_SAMPLER_DEBUG: 8 words per tile (timeline of the tile flow), else null
+    uint32_t* trace;             // GMG_SAMPLER_TRACE: 4 words per rank (ns since t0: queued, popped, ext popped, ext done), else null
+    const unsigned long long* trace_t0;
+    int fast_warps, group, xgroup, xsleep;   // tile flow shape (defaults kFastWarps, kGroup, kGroup, 64; GMG_FLOW_* env for tuning)
+    uint16_t* mbox;              // [tiles * kTile] tile flow: mailbox of every tile (rank offset | knocked-out << kTileLog), 0xFFFF = empty
 };
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -312,81 +341,130 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     }
 }
 
+__global__ void stamp_kernel(unsigned long long* out) { *out = global_ns(); }
+
 // The flow: a vertex is IN once every preceding coverer is OUT (both path counters at 0), OUT once a preceding
 // coverer is IN. Two kernels; which one does the work is decided on the device (use_lane_flow).
 //
-// (1) TILE flow, for spatially coherent orders. A block takes flow TILES (kTile consecutive ranks) by ticket, so
-// every tile that precedes a running tile is running or done and the waits below always end. Inside a tile the
-// decisions travel through SHARED memory: both halves of the tile's lists are staged there once (they are
-// static, so this happens BEFORE the tile has anything to wait for), the same-tile counters live there, and a
-// round -- every thread looks at its undecided ranks, a newly decided rank applies its same-tile list -- costs a
-// barrier instead of a round trip through L2. That is what the index order of a coherent numbering needs: on a
-// row-major 10000 x 1000 grid a tile is four rows, its preceding coverers sit in the tile before it, and the
-// dependency chain (24,000 steps at level 0) is walked at shared-memory speed.
-// What crosses tiles goes through the global words: a selected rank ORs the OUT bit into its later coverees, a
-// rejected one subtracts its multiplicity, both without a return value. A tile that can make no progress does
-// not poll its 4096 words (148 waiting tiles doing that saturate the L2 and slow the one tile everybody waits
-// for): whoever pushes an effect into a tile bumps that tile's epoch word, and a waiting tile watches its own word
-// only -- a wake-up goes to the tile it concerns and to nobody else.
+// (1) TILE flow, for spatially coherent orders. On a row-major 10000 x 1000 grid the dependency chain is tens of
+// thousands of decisions long and only a handful of vertices per tile can be decided at any moment, so what counts
+// is the latency of ONE decision step, not throughput. A block takes flow TILES (kTile consecutive ranks) by
+// ticket, so every tile that precedes a running tile is running or done and the waits below always end. Inside a
+// tile nothing polls: the tile is a WORK LIST in shared memory.
+//   * Both halves of the tile's lists are staged in shared memory once (they are static, so this happens before
+//     the tile has anything to wait for), next to one state word per rank: same-tile path counter | PENDING (the
+//     other-tile counter is not 0 yet) | DECIDED.
+//   * Whoever makes the atomic that leaves a word at "counter 0, not pending, not decided" queues that rank as
+//     IN; whoever first ORs DECIDED into a word queues it as OUT. Atomics on a word are totally ordered, so each
+//     rank is queued exactly once, by the operation that decided it, at the moment it is decided.
+//   * FAST warps pop the queue: the 32 lanes apply the popped rank's same-tile list in parallel (one shared-memory
+//     atomic each), queueing what that decides, and hand the rank on to the second queue.
+//   * EXT warps pop the second queue and apply the other-tile half with atomics on the global words. These return
+//     the old value: the lane that brings a word to 0, or sets its OUT bit first, appends the rank to the MAILBOX of
+//     the tile that owns it (<= 1 notification per rank). Two L2 round trips, kept away from the fast warps.
+//   * One WATCH warp reads the tile's own mailbox, 32 slots per look, and turns notifications into state-word
+//     atomics. A waiting tile therefore costs one L2 load per look, and is told exactly which ranks changed.
 //
 // (2) LANE flow, for incoherent orders (hashed priorities, subdivision orders): nearly every target sits in
-// another tile, the dependency depth is O(log n), and one rank per lane with no block-wide barriers is faster.
+// another tile, the dependency depth is O(log n), and one rank per lane with no block-wide structure is faster.
+constexpr int32_t kRemMask = 0x000FFFFF;      // same-tile preceding paths still undecided
+constexpr int32_t kPending = 1 << 20;         // the global word (other-tile preceding paths) has not reached 0
+constexpr int32_t kDecided = 1 << 21;         // queued as OUT, or not a vertex at all
+constexpr int32_t kSlow = 1 << 22;            // lists not staged (no room, or not partitioned): read from global memory
+constexpr uint32_t kEmpty = 0xFFFFu;          // queue / mailbox slot not written yet
+constexpr int kFastWarps = 16;                // warps 1 .. kFastWarps pop the tile's queue; warp 0 watches the mailbox
+constexpr int kGroup = 8;                     // lanes that apply one rank's list
+constexpr int kPtrLen = kTile + 2;            // prefix arrays (kTile + 1 used; even length keeps 4-byte alignment)
+
 template <int MODE>
 __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerArgs a) {
     extern __shared__ unsigned char smem_raw[];
-    int32_t* s_rem = reinterpret_cast<int32_t*>(smem_raw);                       // kTile same-tile path counters
-    uint32_t* s_ext = reinterpret_cast<uint32_t*>(s_rem + kTile);                // kExtCap staged other-tile entries
+    int32_t* s_state = reinterpret_cast<int32_t*>(smem_raw);                     // kTile state words
+    uint32_t* s_ext = reinterpret_cast<uint32_t*>(s_state + kTile);              // kExtCap staged other-tile entries
     uint16_t* s_list = reinterpret_cast<uint16_t*>(s_ext + kExtCap);             // kListCap staged same-tile entries
-    uint8_t* s_hit = reinterpret_cast<uint8_t*>(s_list + kListCap);              // kTile: knocked OUT inside the tile
+    uint16_t* s_lptr = s_list + kListCap;                                        // same-tile list of rank i: [s_lptr[i], s_lptr[i+1])
+    uint16_t* s_xptr = s_lptr + kPtrLen;                                         // other-tile list of rank i, likewise
+    uint16_t* s_queue = s_xptr + kPtrLen;                                        // decided ranks: offset | IN << kTileLog
+    uint16_t* s_xqueue = s_queue + kTile;                                        // ... whose other-tile half is still to apply
     __shared__ int32_t s_warp[2][kFlowThreads / 32];
     __shared__ unsigned int s_tile;
-    __shared__ unsigned int s_epoch;      // the last value of the global epoch word this block has looked at
-    __shared__ int32_t s_left;            // undecided ranks of the tile
+    // [0] vertices of the tile, [1] queued, [2] claimed, [3] vertices with an other-tile half, [4] queued, [5] claimed
+    __shared__ int32_t s_ctr[8];
     if (use_lane_flow(a)) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
+    const unsigned long long trace_t0 = a.trace ? *a.trace_t0 : 0ull;
+    auto push = [&](uint32_t t, uint32_t in) {
+        if (a.trace) a.trace[4 * (size_t(s_tile) * kTile + t) + 0] = uint32_t(global_ns() - trace_t0);
+        const int32_t slot = atomicAdd(&s_ctr[1], 1);
+        *(volatile uint16_t*)(s_queue + slot) = uint16_t(t | (in << kTileLog));
+    };
+    // a decrement of `mult` paths / a knock-out arriving at rank t of the tile
+    auto release = [&](uint32_t t, int32_t mult) {
+        const int32_t now = atomicSub(s_state + t, mult) - mult;
+        if ((now & (kRemMask | kPending | kDecided)) == 0) push(t, 1u);
+    };
+    auto knock_out = [&](uint32_t t) {
+        if (!(atomicOr(s_state + t, kDecided) & kDecided)) push(t, 0u);
+    };
     for (;;) {
         __syncthreads();                                   // everybody is done with the previous tile's shared state
-        if (tid == 0) { s_tile = atomicAdd(a.ticket, 1u); s_left = 0; s_epoch = 0; }
+        if (tid == 0) {
+            s_tile = atomicAdd(a.ticket, 1u);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s_ctr[k] = 0;
+        }
         __syncthreads();
         const unsigned int tile = s_tile;
         if (tile >= a.tiles) break;
         const uint32_t t0 = tile << kTileLog;
-        const unsigned int* my_epoch = a.epoch + tile;
-        if (a.dbg && tid == 0) a.dbg[8 * tile + 0] = global_ns();
-        // ---- static data of the tile's ranks; rank i of the tile belongs to thread i % kFlowThreads
+        if (a.dbg && tid == 0) { a.dbg[8 * tile + 0] = global_ns(); a.dbg[8 * tile + 7] = blockIdx.x; }
+        // ---- static data of the tile's ranks; ranks [tid * kOwn, (tid + 1) * kOwn) of the tile belong to this thread
+        //      for the staging (so that the scans below lay the lists out in rank order)
         long long ptr[kOwn];
-        uint32_t tot[kOwn], nin[kOwn], soff[kOwn], xoff[kOwn];
-        int32_t mine = 0, mine_x = 0;  // same-tile / other-tile list entries this thread wants to stage
-        unsigned undecided = 0;        // bit q: rank q of this thread is not decided yet
+        uint32_t tot[kOwn], nin[kOwn];
+        int32_t st[kOwn];
+        int32_t mine = 0, mine_x = 0, nvalid = 0, nx = 0;
+        unsigned valid_bits = 0;
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
-            const int i = tid + q * kFlowThreads;
-            const uint64_t r = uint64_t(t0) + uint64_t(i);
+            const uint64_t r = uint64_t(t0) + uint64_t(tid * kOwn + q);
             const bool valid = r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n);
-            ptr[q] = 0; tot[q] = 0; nin[q] = 0;
-            int32_t rem = 0;
+            ptr[q] = 0; tot[q] = 0; nin[q] = 0; st[q] = kDecided;
             if (valid) {
                 const uint32_t lc = a.lcnt[r];
                 ptr[q] = a.lptr[r]; tot[q] = lc & 0xFFFFu; nin[q] = lc >> 16;
-                undecided |= 1u << q;
-                rem = int32_t(a.cint[r]);
-                if (nin[q] != kUnpartitioned) { mine += int32_t(nin[q]); mine_x += int32_t(tot[q] - nin[q]); }
+                // the CURRENT value: tiles that are running have pushed into it already. Whatever happens to the word
+                // after this read arrives through the mailbox (and a notification about something this read has seen
+                // is recognised as such: PENDING already clear / DECIDED already set).
+                const uint32_t w = *(volatile const uint32_t*)(a.wext + r);
+                st[q] = int32_t(a.cint[r]) & kRemMask;
+                if (w & kOutFlag) st[q] |= kDecided;
+                else if (w != 0u) st[q] |= kPending;
+                const bool raw = nin[q] == kUnpartitioned;
+                if (raw) st[q] |= kSlow;
+                else { mine += int32_t(nin[q]); mine_x += int32_t(tot[q] - nin[q]); }
+                valid_bits |= 1u << q;
+                ++nvalid;
+                if (raw ? tot[q] > 0u : tot[q] > nin[q]) ++nx;
             }
-            s_rem[i] = rem;
-            s_hit[i] = 0;
         }
-        if (undecided) atomicAdd(&s_left, __popc(undecided));
         // shared-memory segments for the two halves of the lists: block-wide exclusive scans over the threads
         {
-            int32_t s = mine, sx = mine_x;
+            int32_t s = mine, sx = mine_x, nv = nvalid, nxx = nx;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const int32_t t = __shfl_up_sync(0xffffffffu, s, d);
                 const int32_t tx = __shfl_up_sync(0xffffffffu, sx, d);
                 if (lane >= d) { s += t; sx += tx; }
             }
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                nv += __shfl_down_sync(0xffffffffu, nv, d);
+                nxx += __shfl_down_sync(0xffffffffu, nxx, d);
+            }
+            if (lane == 0) { if (nv) atomicAdd(&s_ctr[0], nv); if (nxx) atomicAdd(&s_ctr[3], nxx); }
             if (lane == 31) { s_warp[0][warp] = s; s_warp[1][warp] = sx; }
             __syncthreads();
             if (warp < 2) {
@@ -403,129 +481,181 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             int32_t off = s_warp[0][warp] + (s - mine), offx = s_warp[1][warp] + (sx - mine_x);
 #pragma unroll
             for (int q = 0; q < kOwn; ++q) {
-                const bool part = ((undecided >> q) & 1u) && nin[q] != kUnpartitioned;
+                const int i = tid * kOwn + q;
+                const bool part = ((valid_bits >> q) & 1u) && !(st[q] & kSlow);
                 const int32_t want = part ? int32_t(nin[q]) : 0, wantx = part ? int32_t(tot[q] - nin[q]) : 0;
-                soff[q] = (want > 0 && off + want <= kListCap) ? uint32_t(off) : 0xFFFFFFFFu;
-                xoff[q] = (wantx > 0 && offx + wantx <= kExtCap) ? uint32_t(offx) : 0xFFFFFFFFu;
+                s_lptr[i] = uint16_t(off < 0xFFFF ? off : 0xFFFF);
+                s_xptr[i] = uint16_t(offx < 0xFFFF ? offx : 0xFFFF);
+                if (part && (off + want > kListCap || offx + wantx > kExtCap)) st[q] |= kSlow;   // and so is every rank after it
                 off += want; offx += wantx;
+                s_state[i] = st[q];
+                s_queue[i] = uint16_t(kEmpty);
+                s_xqueue[i] = uint16_t(kEmpty);
+            }
+            if (tid == kFlowThreads - 1) {
+                s_lptr[kTile] = uint16_t(off < 0xFFFF ? off : 0xFFFF);
+                s_xptr[kTile] = uint16_t(offx < 0xFFFF ? offx : 0xFFFF);
             }
         }
         // ---- stage the lists: same-tile entries as uint16 (offset in the tile | (multiplicity - 1) << 12), the
         //      others as they are
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
-            if (soff[q] != 0xFFFFFFFFu)
-                for (uint32_t e = 0; e < nin[q]; ++e) {
-                    const uint32_t x = a.lst[ptr[q] + e];
-                    s_list[soff[q] + e] = uint16_t(((x & rmask) - t0) | ((x >> a.order.kbits) << kTileLog));
-                }
-            if (xoff[q] != 0xFFFFFFFFu)
-                for (uint32_t e = nin[q]; e < tot[q]; ++e) s_ext[xoff[q] + (e - nin[q])] = a.lst[ptr[q] + e];
+            if (!((valid_bits >> q) & 1u) || (st[q] & kSlow)) continue;
+            const int i = tid * kOwn + q;
+            const uint32_t lo = s_lptr[i], xo = s_xptr[i];
+            for (uint32_t e = 0; e < nin[q]; ++e) {
+                const uint32_t x = a.lst[ptr[q] + e];
+                s_list[lo + e] = uint16_t(((x & rmask) - t0) | ((x >> a.order.kbits) << kTileLog));
+            }
+            for (uint32_t e = nin[q]; e < tot[q]; ++e) s_ext[xo + (e - nin[q])] = a.lst[ptr[q] + e];
         }
         __syncthreads();
-        // ---- the flow: no barrier inside. Every thread spins over its undecided ranks; a decision is applied at
-        //      once (same-tile targets in shared memory, the others with reductions on the global words), and a
-        //      thread that pushed into other tiles bumps their epoch words so that they look again.
         if (a.dbg && tid == 0) a.dbg[8 * tile + 1] = global_ns();
-        unsigned dbg_iter = 0, dbg_poll = 0;
-        bool dbg_first = true;
-        uint32_t ext[kOwn];
+        // ---- what is decided from the start: knocked out already / nothing to wait for
 #pragma unroll
-        for (int q = 0; q < kOwn; ++q) ext[q] = 1u;                    // 1: the global word has not been read yet
-        unsigned int seen = 0xFFFFFFFFu;                               // forces the first read
-        unsigned idle = 0, watch = 0;
-        while (*(volatile int32_t*)&s_left > 0) {
-            // one thread of the block watches the epoch word (with a back-off while the block is making no progress)
-            if (tid == 0 && (dbg_iter & 3u) == 0u) {
-                // (every 4096th look also forces a fresh read of the words, whatever the epoch says: a lost
-                // wake-up must cost microseconds, never the kernel)
-                const unsigned int e = ((*(volatile const unsigned int*)my_epoch << 1) | ((++watch >> 12) & 1u)) & 0x7FFFFFFFu;
-                if (e != *(volatile unsigned int*)&s_epoch) *(volatile unsigned int*)&s_epoch = e;
-            }
-            ++dbg_iter;
-            const unsigned int now = *(volatile unsigned int*)&s_epoch;
-            if (now != seen) {
-                ++dbg_poll;
-                // the epoch was read BEFORE these words: a push that lands after this poll bumps it again
-                seen = now;
-                __threadfence();
-#pragma unroll
-                for (int q = 0; q < kOwn; ++q)     // a word that has reached 0 has no outside coverer left and stays 0
-                    if (((undecided >> q) & 1u) && ext[q] != 0u) ext[q] = *(volatile uint32_t*)(a.wext + t0 + tid + q * kFlowThreads);
-            }
-            bool decided_any = false;
-            uint32_t wake[4];                      // tiles this thread pushed into during this pass
-            int nwake = 0;
-#pragma unroll
-            for (int q = 0; q < kOwn; ++q) {
-                if (!((undecided >> q) & 1u)) continue;
-                const int i = tid + q * kFlowThreads;
-                bool in;
-                if ((ext[q] & kOutFlag) || *(volatile uint8_t*)(s_hit + i)) in = false;
-                else if (ext[q] == 0u && *(volatile int32_t*)(s_rem + i) == 0) in = true;
-                else continue;
-                undecided &= ~(1u << q);
-                decided_any = true;
-                if (a.dbg && dbg_first) { dbg_first = false; atomicMin(a.dbg + 8 * tile + 2, global_ns()); }
-                // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a rejected one releases
-                // its later coverees
-                const bool raw = nin[q] == kUnpartitioned;
-                if (soff[q] != 0xFFFFFFFFu) {
-                    for (uint32_t e = 0; e < nin[q]; ++e) {
-                        const uint32_t y = s_list[soff[q] + e];
-                        if (in) *(volatile uint8_t*)(s_hit + (y & (kTile - 1))) = 1;
-                        else atomicSub(s_rem + (y & (kTile - 1)), int32_t(y >> kTileLog) + 1);
-                    }
-                } else {
-                    // list not staged (no room, or not partitioned): same-tile targets straight from the list
-                    const uint32_t cnt = raw ? tot[q] : nin[q];
-                    for (uint32_t e = 0; e < cnt; ++e) {
-                        const uint32_t x = a.lst[ptr[q] + e];
-                        const uint32_t rt = x & rmask;
-                        if ((rt >> kTileLog) != tile) continue;
-                        if (in) *(volatile uint8_t*)(s_hit + (rt - t0)) = 1;
-                        else atomicSub(s_rem + (rt - t0), int32_t(x >> a.order.kbits) + 1);
-                    }
-                }
-                const uint32_t first = raw ? 0u : nin[q];
-                for (uint32_t e = first; e < tot[q]; ++e) {
-                    const uint32_t x = xoff[q] != 0xFFFFFFFFu ? s_ext[xoff[q] + (e - first)] : a.lst[ptr[q] + e];
-                    const uint32_t rt = x & rmask;
-                    const uint32_t tt = rt >> kTileLog;
-                    if (raw && tt == tile) continue;
-                    if (in) atomicOr(a.wext + rt, kOutFlag);
-                    else atomicSub(a.wext + rt, (x >> a.order.kbits) + 1u);
-                    bool known = false;
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) known = known || (u < nwake && wake[u] == tt);
-                    if (!known) {
-                        if (nwake == 4) {          // rare: flush what is noted so far (its pushes are fenced first)
-                            __threadfence();
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) atomicAdd(a.epoch + wake[u], 1u);
-                            nwake = 0;
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) if (u == nwake) wake[u] = tt;
-                        ++nwake;
-                    }
-                }
-                a.res[t0 + i] = in ? 1 : 0;
-                atomicSub(&s_left, 1);
-            }
-            if (nwake) {                           // the pushes first, then the wake-ups
-                __threadfence();
-#pragma unroll
-                for (int u = 0; u < 4; ++u) if (u < nwake) atomicAdd(a.epoch + wake[u], 1u);
-            }
-            // a thread that is done with the tile meets the block at the barrier; thread 0 stays: it is the watcher
-            if (!undecided && tid != 0) { if (a.dbg) atomicMax(a.dbg + 8 * tile + 3, global_ns()); break; }
-            // no sleeping here: a waiting rank must react within one pass (the dependency chain of a row-major grid
-            // is tens of thousands of passes long); only a tile that has waited very long backs off
-            if (decided_any) idle = 0;
-            else if (++idle > 20000) __nanosleep(200);
+        for (int q = 0; q < kOwn; ++q) {
+            if (!((valid_bits >> q) & 1u)) continue;
+            if (st[q] & kDecided) push(uint32_t(tid * kOwn + q), 0u);
+            else if ((st[q] & (kRemMask | kPending)) == 0) push(uint32_t(tid * kOwn + q), 1u);
         }
-        if (a.dbg && tid == 0) { a.dbg[8 * tile + 4] = dbg_iter; a.dbg[8 * tile + 5] = dbg_poll; a.dbg[8 * tile + 6] = global_ns(); a.dbg[8 * tile + 7] = blockIdx.x; }
+        const int32_t total = *(volatile int32_t*)&s_ctr[0];
+        if (warp == 0) {
+            // ---- WATCH: the tile's mailbox, a window of 32 slots per look (a slot is written after it is reserved, so
+            //      the filled slots need not be a prefix: the window moves past its leading dealt-with slots)
+            const volatile uint16_t* box = a.mbox + (size_t(tile) << kTileLog);
+            int next = 0;
+            unsigned seen = 0;                 // bit l: slot next + l has been dealt with
+            unsigned long long looks = 0;
+            while (*(volatile int32_t*)&s_ctr[1] < total) {
+                const int k = next + lane;
+                const uint32_t x = k < kTile ? uint32_t(box[k]) : kEmpty;
+                const unsigned fresh = __ballot_sync(0xffffffffu, x != kEmpty) & ~seen;
+                if ((fresh >> lane) & 1u) {
+                    const uint32_t t = x & uint32_t(kTile - 1);
+                    if (x >> kTileLog) knock_out(t);
+                    else {
+                        const int32_t old = atomicAnd(s_state + t, ~kPending);
+                        if ((old & kPending) && (old & (kRemMask | kDecided)) == 0) push(t, 1u);
+                    }
+                }
+                seen |= fresh;
+                const int cnt = seen == 0xFFFFFFFFu ? 32 : __ffs(int(~seen)) - 1;
+                next += cnt;
+                seen = cnt == 32 ? 0u : seen >> cnt;
+                ++looks;
+            }
+            if (a.dbg && lane == 0) { a.dbg[8 * tile + 4] = looks; a.dbg[8 * tile + 5] = (unsigned long long)next; }
+        } else if (warp <= a.fast_warps) {
+            // ---- FAST: four ranks per warp at a time, 8 lanes each (lists are short, and what bounds the tile is how
+            //      many decided ranks are being applied at once: with one rank per warp the queue backs up and a rank
+            //      on the critical chain waits microseconds behind ranks that are not). The groups of a warp move in
+            //      lock step: look at the claimed slot, apply it if it is filled, claim the next.
+            const int grp = a.group;
+            const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
+            int32_t slot = 0;
+            if (sub == 0) slot = atomicAdd(&s_ctr[2], 1);
+            slot = __shfl_sync(0xffffffffu, slot, lead);
+            while (__any_sync(0xffffffffu, slot < total)) {
+                const uint32_t e = slot < total ? uint32_t(*(volatile uint16_t*)(s_queue + slot)) : kEmpty;
+                if (e != kEmpty) {
+                    const uint32_t v = e & uint32_t(kTile - 1);
+                    const bool in = (e >> kTileLog) != 0u;
+                    if (a.dbg && sub == 0) atomicMin(a.dbg + 8 * tile + 2, global_ns());
+                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 1] = uint32_t(global_ns() - trace_t0);
+                    bool has_ext;
+                    // (independent loads, issued together: every dependent shared-memory access is a step of the chain)
+                    const int32_t sv = *(volatile int32_t*)(s_state + v);
+                    const uint32_t b = s_lptr[v], end = s_lptr[v + 1], xb = s_xptr[v], xe = s_xptr[v + 1];
+                    if (!(sv & kSlow)) {
+                        for (uint32_t k = b + sub; k < end; k += grp) {
+                            const uint32_t y = s_list[k];
+                            // a selected vertex knocks out everything it covers (src/sampling.cpp:38,45); a rejected one
+                            // releases its later coverees
+                            if (in) knock_out(y & uint32_t(kTile - 1));
+                            else release(y & uint32_t(kTile - 1), int32_t(y >> kTileLog) + 1);
+                        }
+                        has_ext = xe > xb;
+                    } else {
+                        const uint32_t lc = a.lcnt[t0 + v];
+                        const long long p = a.lptr[t0 + v];
+                        const uint32_t all = lc & 0xFFFFu, same = lc >> 16;
+                        const bool raw = same == kUnpartitioned;
+                        const uint32_t cnt = raw ? all : same;
+                        for (uint32_t k = sub; k < cnt; k += grp) {
+                            const uint32_t x = a.lst[p + k];
+                            const uint32_t rt = x & rmask;
+                            if ((rt >> kTileLog) != tile) continue;
+                            if (in) knock_out(rt - t0);
+                            else release(rt - t0, int32_t(x >> a.order.kbits) + 1);
+                        }
+                        has_ext = raw ? all > 0u : all > same;
+                    }
+                    if (sub == 0) {
+                        a.res[t0 + v] = in ? 1 : 0;
+                        if (has_ext) {
+                            const int32_t xs = atomicAdd(&s_ctr[4], 1);
+                            *(volatile uint16_t*)(s_xqueue + xs) = uint16_t(e);
+                        }
+                        slot = atomicAdd(&s_ctr[2], 1);
+                    }
+                }
+                slot = __shfl_sync(0xffffffffu, slot, lead);
+            }
+        } else {
+            // ---- EXT: the other-tile half, with atomics that return: the lane that decides something about a rank of
+            //      another tile tells that tile. Same lock-step groups; two L2 round trips per pass.
+            const int grp = a.xgroup;
+            const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
+            const int32_t total_x = *(volatile int32_t*)&s_ctr[3];
+            int32_t slot = 0;
+            if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
+            slot = __shfl_sync(0xffffffffu, slot, lead);
+            while (__any_sync(0xffffffffu, slot < total_x)) {
+                const uint32_t e = slot < total_x ? uint32_t(*(volatile uint16_t*)(s_xqueue + slot)) : kEmpty;
+                // (sleeping: a spinning warp takes issue slots from the warps that walk the dependency chain)
+                if (!__any_sync(0xffffffffu, e != kEmpty)) { if (a.xsleep) __nanosleep(a.xsleep); continue; }
+                if (e != kEmpty) {
+                    const uint32_t v = e & uint32_t(kTile - 1);
+                    const bool in = (e >> kTileLog) != 0u;
+                    const bool slow = (*(volatile int32_t*)(s_state + v) & kSlow) != 0;
+                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 2] = uint32_t(global_ns() - trace_t0);
+                    uint32_t first, count;
+                    long long p = 0;
+                    bool raw = false;
+                    if (!slow) { first = s_xptr[v]; count = uint32_t(s_xptr[v + 1]) - first; }
+                    else {
+                        const uint32_t lc = a.lcnt[t0 + v];
+                        p = a.lptr[t0 + v];
+                        raw = (lc >> 16) == kUnpartitioned;
+                        first = raw ? 0u : (lc >> 16);
+                        count = (lc & 0xFFFFu) - first;
+                    }
+                    for (uint32_t k = sub; k < count; k += grp) {
+                        const uint32_t x = slow ? a.lst[p + first + k] : s_ext[first + k];
+                        const uint32_t rt = x & rmask;
+                        const uint32_t tt = rt >> kTileLog;
+                        if (raw && tt == tile) continue;
+                        bool tell;
+                        if (in) tell = !(atomicOr(a.wext + rt, kOutFlag) & kOutFlag);          // the first knock-out
+                        else {
+                            const uint32_t mult = (x >> a.order.kbits) + 1u;
+                            tell = atomicSub(a.wext + rt, mult) == mult;                         // the one that reaches 0
+                        }
+                        if (tell) {
+                            const unsigned int k2 = atomicAdd(a.epoch + tt, 1u);                 // the mailbox's fill count
+                            *(volatile uint16_t*)(a.mbox + (size_t(tt) << kTileLog) + k2) =
+                                uint16_t((rt & uint32_t(kTile - 1)) | (in ? uint32_t(kTile) : 0u));
+                        }
+                    }
+                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 3] = uint32_t(global_ns() - trace_t0);
+                    if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
+                }
+                slot = __shfl_sync(0xffffffffu, slot, lead);
+            }
+            if (a.dbg && lane == 0) atomicMax(a.dbg + 8 * tile + 3, global_ns());
+        }
+        if (a.dbg) { __syncthreads(); if (tid == 0) a.dbg[8 * tile + 6] = global_ns(); }
     }
 }
 
@@ -614,7 +744,12 @@ void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned lo
     if (n > 0) GMG_LAUNCH(c, degree_square_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, d_out);
 }
 
-constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint32_t) * kExtCap + sizeof(uint16_t) * kListCap + kTile;
+constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint32_t) * kExtCap + sizeof(uint16_t) * (kListCap + 2 * kPtrLen + 2 * kTile);
+
+static int env_int(const char* name, int fallback) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : fallback;
+}
 
 template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, uint64_t ranks, int32_t* flag) {
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
@@ -667,6 +802,15 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     const unsigned ntiles = unsigned((ranks + kTile - 1) >> kTileLog);
     DevBuf<unsigned int> epochs(c, int64_t(ntiles));
     epochs.zero();
+    DevBuf<uint16_t> mbox;
+    if (mode != GMG_SAMPLER_HASHED) {
+        mbox.alloc(c, int64_t(ntiles) << kTileLog);
+        GMG_CUDA(cudaMemsetAsync(mbox.p, 0xFF, sizeof(uint16_t) * (size_t(ntiles) << kTileLog), c->stream));
+    }
+    DevBuf<uint32_t> trace;
+    const char* trace_path = mode == GMG_SAMPLER_HASHED || n < 1000000 ? nullptr : getenv("GMG_SAMPLER_TRACE");
+    DevBuf<unsigned long long> trace_t0;
+    if (trace_path) { trace.alloc(c, 4 * int64_t(ranks)); trace.zero(); trace_t0.alloc(c, 1); }
     DevBuf<unsigned long long> dbg;
     const bool debug = getenv("GMG_SAMPLER_DEBUG") != nullptr && mode != GMG_SAMPLER_HASHED;
     if (debug) {
@@ -682,7 +826,9 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     SamplerArgs a{n, colptr, rowidx, len, radius, order, wext.p, cint.p, lptr.p, lcnt.p, lst.p, cursor.p,
                   reinterpret_cast<unsigned int*>(cursor.p + 2), ntiles, res.p,
                   reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, epochs.p,
-                  mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr};
+                  mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr, trace.p, trace_t0.p, env_int("GMG_FLOW_FAST", kFastWarps), env_int("GMG_FLOW_GROUP", kGroup),
+                  env_int("GMG_FLOW_XGROUP", kGroup), env_int("GMG_FLOW_XSLEEP", 64), mbox.p};
+    if (trace_path) GMG_LAUNCH(c, stamp_kernel, 1, 1, 0, trace_t0.p);
     if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, ranks, flag.p);
     else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, ranks, flag.p);
     // ascending compaction of the IN flags
@@ -695,6 +841,12 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     GMG_CUDA(cudaMemcpyAsync(&hflags, cursor.p + 3, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     sync(c);
     GMG_REQUIRE((hflags & 0xFFFFFFFFull) == 0, GMG_ERR_INVALID, "fastDiscSample: a vertex covers more than 65535 later vertices");
+    if (trace_path) {   // per-rank timestamps of the tile flow (diagnostic only)
+        std::vector<uint32_t> h(size_t(4) * ranks);
+        GMG_CUDA(cudaMemcpyAsync(h.data(), trace.p, sizeof(uint32_t) * h.size(), cudaMemcpyDeviceToHost, c->stream));
+        sync(c);
+        if (FILE* f = fopen(trace_path, "wb")) { fwrite(h.data(), sizeof(uint32_t), h.size() < 12000000 ? h.size() : 12000000, f); fclose(f); }
+    }
     if (debug) {        // timeline of the tile flow (diagnostic only)
         std::vector<unsigned long long> h(size_t(8) * ntiles);
         GMG_CUDA(cudaMemcpyAsync(h.data(), dbg.p, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost, c->stream));
@@ -710,11 +862,11 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
                 active += double(w[6] - w[2]); wait += double(w[2] - w[1]);
             }
             fprintf(stderr, "[gmg] sampler tile flow: n %d, %u tiles, %.3f ms; per tile: first decision -> done %.1f us, staged -> first decision %.1f us, "
-                            "%.0f spin iterations, %.0f polls\n", n, ntiles, double(t_end - t_begin) * 1e-6, active / ntiles * 1e-3,
+                            "%.0f mailbox looks, %.0f notifications\n", n, ntiles, double(t_end - t_begin) * 1e-6, active / ntiles * 1e-3,
                     wait / ntiles * 1e-3, double(iters) / ntiles, double(polls) / ntiles);
             for (unsigned t = 0; t < ntiles && t < 400; t += (t < 24 ? 1 : 47)) {
                 const unsigned long long* w = h.data() + size_t(8) * t;
-                fprintf(stderr, "[gmg]   tile %u block %llu: ticket %.1f staged %.1f first %.1f last-thread %.1f done %.1f us; iters %llu polls %llu\n", t, w[7],
+                fprintf(stderr, "[gmg]   tile %u block %llu: ticket %.1f staged %.1f first %.1f ext-done %.1f done %.1f us; looks %llu notifications %llu\n", t, w[7],
                         double(w[0] - t_begin) * 1e-3, double(w[1] - t_begin) * 1e-3, double(w[2] - t_begin) * 1e-3, double(w[3] - t_begin) * 1e-3,
                         double(w[6] - t_begin) * 1e-3, w[4], w[5]);
             }

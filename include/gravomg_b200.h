@@ -59,10 +59,11 @@ typedef enum {
 enum { GMG_BARYCENTRIC = 0, GMG_UNIFORM = 1, GMG_INVDIST = 2 };
 /* Sampler modes: the same greedy rule (src/sampling.cpp:22-50) under three precedence orders.
  *   EXACT     index order: the reference's sample set bit-for-bit.
- *   PARALLEL  the index-order sweep restarted in 2-4 contiguous super-tiles that are taken in a seeded hashed
- *             order: a different set, within 2 % of the reference on sample count and coverage radius (the
- *             north star's statistical criterion) also on index-coherent grids, where the reference's
- *             row-by-row sweep packs much more tightly than any order-independent rule.
+ *   PARALLEL  the index-order sweep restarted in 3 contiguous super-tiles that are swept concurrently (their
+ *             flow tiles are interleaved in the order; the seed is not used): a different set, within 2 % of the
+ *             reference on sample count and coverage radius (the north star's statistical criterion) also on
+ *             index-coherent grids, where the reference's row-by-row sweep packs much more tightly than any
+ *             order-independent rule; a third of the index order's dependency depth.
  *   HASHED    every vertex hashed: dependency depth O(log n); what the row-sharded build runs for both
  *             non-exact modes. Statistically equal to the reference on unordered inputs (point clouds,
  *             subdivision orders), 28 % fewer samples on a row-major grid. */

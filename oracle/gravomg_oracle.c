@@ -4,7 +4,7 @@
  * function cites the reference file:line it follows (paths relative to /root/reference).
  *
  * PARITY PINNING: the reference ships no tests, golden vectors or fixtures,
- * so this oracle is pinned by executing the reference itself: tests/test_oracle_vs_ref.py compares
+ * so this oracle is pinned by executing the reference itself: tests/test_oracle.py compares
  * every orc_* function bit-for-bit with ref_* (the unmodified reference sources compiled against
  * oracle/eigen_shim, oracle/_ref/libgravomg_ref.so), and tests/golden/ holds outputs of ref_*
  * generated in the build container by tests/golden/make_golden.py. The arithmetic order of 3-vector
