@@ -1,30 +1,27 @@
-// Galerkin coarse operator A_c = P^T A P as a two-pass (symbolic, then numeric) SpGEMM.
+// Galerkin coarse operator A_c = P^T A P as two sparse products, each sized by a counting pass and then computed:
+//     T   = P^T A      (m x n, by fine column k)      T(i,k)   = sum_l A(l,k) * P(l,i)
+//     A_c = T P        (m x m, by coarse column j)    A_c(i,j) = sum_k T(i,k) * P(k,j)
 // [not in reference: README.md:6 says only the P/R builders were kept; BASELINE.json asks for it.
 //  Semantics are those of Eigen's un-pruned sparse product: structural pattern, sorted indices.]
 //
-// A and A_c are compressed by OUTER index (column-major, like Eigen::SparseMatrix<double>); the
-// row-wise Gustavson formulation below only ever walks outer vectors, so it computes
-//     out(inner j, outer i) = sum_k sum_l P(k,i) * A(l,k) * P(l,j)
-// which is exactly (P^T A P)(j,i) with A(l,k) read from outer vector k. No symmetry of A is assumed.
+// A and A_c are compressed by OUTER index (column-major, like Eigen::SparseMatrix<double>); both products only
+// ever walk outer vectors of A (column k of T is a combination of the rows of P named by column k of A), so no
+// symmetry of A is assumed.
 //
-// One warp per coarse outer index i, in two steps that share the warp's shared memory:
-//   step 1  c(l) = sum_k P(k,i) * A(l,k)   R = P^T lists the fine k with P(k,i) stored (sorted ascending in shared
-//                                          memory); the products (k, q), q over A's outer vector k, are taken 32 at a
-//                                          time, one per lane, in (k, q) order
-//   step 2  out(j) = sum_l c(l) * P(l,j)   the distinct l sorted ascending, 32 per round, one per lane; entry t = 0, 1, 2
-//                                          of every row of P in turn
-// Grouping by l first means every row of P is expanded once per distinct l (~45 per coarse row) and not once per
-// (k, l) pair (~160). Keys are found with a shared-memory hash (atomicCAS on the key only). VALUES are accumulated
-// WITHOUT atomics: shared-memory atomicAdd(double) is a compare-and-swap loop on this architecture (ATOMS.CAST.SPIN
-// in the SASS; the first version spent 86 % of its time there). Instead the lanes of one group of 32 that hold the
-// same key find each other with __match_any_sync, the lowest lane adds the group's values in lane order and does a
-// plain read-modify-write of the slot -- distinct keys own distinct slots. The summation order is therefore FIXED
-// (products in (k, q) order, then l ascending; inside a group of 32 equal keys are summed first), the result is
-// reproducible bit for bit, and the CPU checker (oracle/solver_oracle.c) follows the same association.
-// Pass 1 (symbolic) runs both steps on keys only and counts distinct j, a scan sizes the result, pass 2 (numeric)
-// computes the values, sorts the keys and writes the outer vector. Rows that outgrow the warp's tables (more than
-// 64 rows of P per column, 192 distinct l or 96 distinct j) go to a block-wide single-table version of the plain
-// triple loop with atomics (not bit-reproducible; none on the BASELINE meshes).
+// ONE THREAD PER OUTER VECTOR. The rows here are tiny (a column of T sums ~21 products into ~8 entries, a column
+// of A_c ~130 products into ~19) and what costs is finding equal keys, not arithmetic: a warp per row spends ~400
+// lane-slots per product on hashing with atomics, matching lanes and sorting (the first two versions of this file),
+// a thread per row spends ~15 instructions per product on a PRIVATE open-addressed table. The tables live in shared
+// memory as [slot][thread], so whatever slot each lane probes, the 32 lanes of a warp hit 32 different banks.
+// No atomics anywhere, and the summation order is the plain sequential one: products in stored order of A's outer
+// vector, then of P's row, for T; fine rows k ascending (R = P^T has sorted rows) for A_c. The result is
+// reproducible bit for bit and the CPU checker (oracle/solver_oracle.c) is the same two loops.
+// Sizing: column k of T holds at most ub1(k) = sum over column k of A of the row lengths of P, column j of A_c at
+// most ub2(j) = sum over row j of R of the column counts of T. Both products write into slots of that size (scans
+// of ub1 / ub2), record the count they found, and A_c is then compacted into its final arrays (T is only ever
+// read through its slots). A thread whose table fills up (more than kCap1 / kCap2 distinct keys: dense rows of
+// deep levels or kNN operators) redoes its vector as a linear-search list directly in its slot -- same order,
+// same bits, just slow.
 // Algorithmic bytes: symbolic 12n + 4nnzA + 8nnzP + 4m; numeric 12n + 12nnzA + 24nnzP + 4m + 12nnzAc.
 #include "stages.h"
 
@@ -110,306 +107,212 @@ void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, i
     tr.mark("sort rows");
 }
 
+
 // ---- SpGEMM -------------------------------------------------------------------------------------
-struct GalerkinArgs {
-    int32_t m;
-    const int32_t* r_ptr; const int32_t* r_col; const double* r_val;      // R = P^T
+constexpr int kCap1 = 32, kThreads1 = 128;     // first product: slots per thread, threads per block
+constexpr int kCap2 = 64, kThreads2 = 64;      // second product
+
+// A thread's private accumulator: open addressing, linear probing, [slot][thread] in shared memory.
+template <int CAP, int THREADS>
+struct ThreadTable {
+    int32_t* keys;      // this thread's column of the block's key array (stride THREADS)
+    double* vals;
+    int32_t count;
+    __device__ __forceinline__ ThreadTable(unsigned char* smem, int tid)
+        : keys(reinterpret_cast<int32_t*>(smem + sizeof(double) * CAP * THREADS) + tid),
+          vals(reinterpret_cast<double*>(smem) + tid), count(0) {}
+    static constexpr size_t bytes() { return (sizeof(double) + sizeof(int32_t)) * size_t(CAP) * THREADS; }
+    __device__ __forceinline__ void clear() {
+#pragma unroll 8
+        for (int s = 0; s < CAP; ++s) keys[s * THREADS] = -1;
+        count = 0;
+    }
+    // acc[key] += v (the first product of a key is stored, not added to zero); false: the table is full
+    __device__ __forceinline__ bool add(int32_t key, double v) {
+        constexpr int kLog = CAP == 32 ? 5 : (CAP == 64 ? 6 : 7);
+        static_assert((1 << kLog) == CAP, "table sizes: 32, 64 or 128 slots");
+        uint32_t h = (uint32_t(key) * 0x9E3779B1u) >> (32 - kLog);
+        for (int probe = 0; probe < CAP; ++probe, h = (h + 1u) & uint32_t(CAP - 1)) {
+            const int32_t cur = keys[h * THREADS];
+            if (cur == key) { vals[h * THREADS] = vals[h * THREADS] + v; return true; }
+            if (cur < 0) { keys[h * THREADS] = key; vals[h * THREADS] = v; ++count; return true; }
+        }
+        return false;
+    }
+    // occupied slots to the front, in slot order
+    __device__ __forceinline__ void compact() {
+        int pos = 0;
+        for (int s = 0; s < CAP && pos < count; ++s) {
+            const int32_t key = keys[s * THREADS];
+            if (key < 0) continue;
+            if (pos != s) { keys[pos * THREADS] = key; vals[pos * THREADS] = vals[s * THREADS]; }
+            ++pos;
+        }
+    }
+    // the compacted entries ascending by key (insertion sort: ~20 entries that arrive nearly sorted)
+    __device__ __forceinline__ void sort() {
+        for (int i = 1; i < count; ++i) {
+            const int32_t key = keys[i * THREADS];
+            const double v = vals[i * THREADS];
+            int j = i - 1;
+            while (j >= 0 && keys[j * THREADS] > key) {
+                keys[(j + 1) * THREADS] = keys[j * THREADS];
+                vals[(j + 1) * THREADS] = vals[j * THREADS];
+                --j;
+            }
+            keys[(j + 1) * THREADS] = key;
+            vals[(j + 1) * THREADS] = v;
+        }
+    }
+};
+
+// The slow path of both products: the same accumulation as a linear-search list in global memory (the vector's own
+// slot, which holds at least as many entries as it has distinct keys).
+struct SlotList {
+    int32_t* idx; double* val; int32_t count;
+    __device__ __forceinline__ void add(int32_t key, double v) {
+        for (int32_t s = 0; s < count; ++s)
+            if (idx[s] == key) { val[s] = val[s] + v; return; }
+        idx[count] = key; val[count] = v; ++count;
+    }
+    __device__ __forceinline__ void sort() {
+        for (int32_t i = 1; i < count; ++i) {
+            const int32_t key = idx[i];
+            const double v = val[i];
+            int32_t j = i - 1;
+            while (j >= 0 && idx[j] > key) { idx[j + 1] = idx[j]; val[j + 1] = val[j]; --j; }
+            idx[j + 1] = key; val[j + 1] = v;
+        }
+    }
+};
+
+using Table1 = ThreadTable<kCap1, kThreads1>;
+using Table2 = ThreadTable<kCap2, kThreads2>;
+
+struct ProductArgs {
+    int32_t n, m;                                                         // fine vertices; outer vectors of A_c formed here
     const int32_t* a_ptr; const int32_t* a_idx; const double* a_val;      // A by outer vector
     const int32_t* p_ptr; const int32_t* p_col; const double* p_val;      // P rows
-    int32_t* out_count;        // symbolic: distinct inner indices of outer vector i
-    const int32_t* out_ptr;    // numeric: scan of out_count
-    int32_t* out_idx; double* out_val;
-    int32_t* flags;            // [1] overflow list tail, [2] hard overflow
-    int32_t* overflow;
+    const int32_t* r_ptr; const int32_t* r_col; const double* r_val;      // R = P^T (rows = the outer vectors formed here)
+    const uint8_t* needed;                                                // fine columns of T that R reads (null: all)
+    int32_t* ub1; const int32_t* t_ptr; int32_t* t_cnt; int32_t* t_idx; double* t_val;     // T in slots
+    int32_t* ub2; const int32_t* w_ptr; int32_t* w_cnt; int32_t* w_idx; double* w_val;     // A_c in slots
+    const int32_t* out_ptr; int32_t* out_idx; double* out_val;                              // A_c
+    int32_t* flags;                                                       // [0] vectors that took the slow path
 };
 
-template <bool NUMERIC, int THREADS, int SLOTS>
-__device__ __forceinline__ bool galerkin_row(const GalerkinArgs& a, int32_t i, int tid, int32_t* keys, double* vals,
-                                             int32_t* scount) {
-    for (int s = tid; s < SLOTS; s += THREADS) { keys[s] = -1; if (NUMERIC) vals[s] = 0.0; }
-    if (tid == 0) *scount = 0;
-    if (THREADS == 32) __syncwarp(); else __syncthreads();
-    const int32_t rb = __ldg(a.r_ptr + i), re = __ldg(a.r_ptr + i + 1);
-    // 8 lanes per fine row k (outer vectors of A hold ~7 entries), THREADS/8 rows in flight
-    constexpr int kSub = 8;
-    for (int32_t e = rb + tid / kSub; e < re; e += THREADS / kSub) {
-        const int32_t k = __ldg(a.r_col + e);
-        const double pki = NUMERIC ? __ldg(a.r_val + e) : 0.0;
-        const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
-        for (int32_t q = ab + tid % kSub; q < ae; q += kSub) {
+__global__ void __launch_bounds__(kBlock) mark_needed_kernel(int64_t nnz, const int32_t* __restrict__ r_col,
+                                                             uint8_t* __restrict__ needed) {
+    const int64_t e = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (e < nnz) needed[r_col[e]] = 1;
+}
+
+// ub1(k): products (= an upper bound on the entries) of column k of T
+__global__ void __launch_bounds__(kBlock) product1_bound_kernel(ProductArgs a) {
+    const int64_t k = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (k > a.n) return;
+    int32_t ub = 0;
+    if (k < a.n && (!a.needed || a.needed[k]))
+        for (int32_t q = __ldg(a.a_ptr + k); q < __ldg(a.a_ptr + k + 1); ++q) {
             const int32_t l = __ldg(a.a_idx + q);
-            const double w = NUMERIC ? pki * __ldg(a.a_val + q) : 0.0;
-            const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
-            for (int32_t t = pb; t < pe; ++t) {
-                const int32_t j = __ldg(a.p_col + t);
-                uint32_t h = (uint32_t(j) * 0x9E3779B1u) >> 7;
-                for (int probe = 0; probe < SLOTS; ++probe, ++h) {
-                    const int s = int(h & (SLOTS - 1));
-                    const int32_t prev = atomicCAS(keys + s, -1, j);
-                    if (prev == -1) atomicAdd(scount, 1);
-                    if (prev == -1 || prev == j) {
-                        if (NUMERIC) atomicAdd(vals + s, w * __ldg(a.p_val + t));
-                        break;
-                    }
-                }
-            }
+            ub += __ldg(a.p_ptr + l + 1) - __ldg(a.p_ptr + l);
         }
-    }
-    if (THREADS == 32) __syncwarp(); else __syncthreads();
-    const int32_t K = *scount;
-    if (K > SLOTS * 3 / 4) return false;
-    if (!NUMERIC) { if (tid == 0) a.out_count[i] = K; return true; }
-    const int32_t off = __ldg(a.out_ptr + i);
-    if constexpr (THREADS == 32) {
-        // compact the occupied slots to the front (in place: a slot only moves down and every chunk is
-        // read before it is written), then rank-sort the K survivors
-        int32_t base = 0;
-        for (int s0 = 0; s0 < SLOTS; s0 += 32) {
-            const int32_t key = keys[s0 + tid];
-            const double v = vals[s0 + tid];
-            const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
-            __syncwarp();
-            if (key >= 0) { const int pos = base + __popc(occ & ((1u << tid) - 1u)); keys[pos] = key; vals[pos] = v; }
-            base += __popc(occ);
-            __syncwarp();
-        }
-        for (int s = tid; s < K; s += 32) {
-            const int32_t key = keys[s];
-            int32_t rank = 0;
-            for (int s2 = 0; s2 < K; ++s2) rank += keys[s2] < key ? 1 : 0;
-            a.out_idx[off + rank] = key;
-            a.out_val[off + rank] = vals[s];
-        }
-        return true;
-    }
-    for (int s = tid; s < SLOTS; s += THREADS) {
-        const int32_t key = keys[s];
-        if (key < 0) continue;
-        int32_t rank = 0;
-        for (int s2 = 0; s2 < SLOTS; ++s2) { const int32_t k2 = keys[s2]; rank += (k2 >= 0 && k2 < key) ? 1 : 0; }
-        a.out_idx[off + rank] = key;
-        a.out_val[off + rank] = vals[s];
-    }
-    return true;
+    a.ub1[k] = ub;          // entry n = 0: the scan's total
 }
 
-// probe-insert `key` into an open-addressed table; returns the slot, or -1 when the table is full
-template <int SLOTS>
-__device__ __forceinline__ int hash_insert(int32_t* keys, int32_t key, int32_t* count) {
-    uint32_t h = (uint32_t(key) * 0x9E3779B1u) >> 7;
-    for (int probe = 0; probe < SLOTS; ++probe, ++h) {
-        const int s = int(h & (SLOTS - 1));
-        const int32_t prev = atomicCAS(keys + s, -1, key);
-        if (prev == -1) atomicAdd(count, 1);
-        if (prev == -1 || prev == key) return s;
+// T(:,k) = sum_l A(l,k) * P(l,:)
+__global__ void __launch_bounds__(kThreads1) product1_kernel(ProductArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int64_t k = int64_t(blockIdx.x) * kThreads1 + threadIdx.x;
+    if (k >= a.n) return;
+    const int32_t base = __ldg(a.t_ptr + k);
+    if (__ldg(a.t_ptr + k + 1) == base) { a.t_cnt[k] = 0; return; }
+    Table1 tab(smem, threadIdx.x);
+    tab.clear();
+    const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
+    bool ok = true;
+    for (int32_t q = ab; q < ae && ok; ++q) {
+        const int32_t l = __ldg(a.a_idx + q);
+        const double w = __ldg(a.a_val + q);
+        const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
+        for (int32_t t = pb; t < pe; ++t) ok = tab.add(__ldg(a.p_col + t), w * __ldg(a.p_val + t)) && ok;
     }
-    return -1;
+    int32_t* idx = a.t_idx + base;
+    double* val = a.t_val + base;
+    if (ok) {
+        tab.compact();
+        for (int32_t s = 0; s < tab.count; ++s) { idx[s] = tab.keys[s * kThreads1]; val[s] = tab.vals[s * kThreads1]; }
+        a.t_cnt[k] = tab.count;
+        return;
+    }
+    SlotList list{idx, val, 0};
+    for (int32_t q = ab; q < ae; ++q) {
+        const int32_t l = __ldg(a.a_idx + q);
+        const double w = __ldg(a.a_val + q);
+        for (int32_t t = __ldg(a.p_ptr + l); t < __ldg(a.p_ptr + l + 1); ++t) list.add(__ldg(a.p_col + t), w * __ldg(a.p_val + t));
+    }
+    a.t_cnt[k] = list.count;
+    atomicAdd(a.flags, 1);
 }
 
-constexpr int kGWarpSlots = 128;
-constexpr int kGFineSlots = 256;
-constexpr int kGBlockSlots = 2048;
-constexpr int kGMaxR = 64;            // rows of P per coarse column the warp path stages
-
-struct GalerkinWarpSmem {
-    int32_t fkeys[kGFineSlots];
-    int32_t keys[kGWarpSlots];
-    int32_t rk[kGMaxR];               // fine rows k of R's row i, ascending
-    int32_t rbase[kGMaxR + 1];        // exclusive scan of the lengths of A's outer vectors k
-    int32_t scount[2];                // distinct fine / coarse keys
-};
-struct GalerkinWarpVals {
-    double fvals[kGFineSlots];
-    double vals[kGWarpSlots];
-    double rp[kGMaxR];                // P(k, i)
-    double xch[32];                   // group_accumulate's exchange
-};
-
-// Add v to acc[slot] for every lane with valid == true; lanes holding the same key are summed first, in lane
-// order, by the lowest of them (see the header comment). The values travel through 32 doubles of shared memory so
-// that only the group leaders loop. All 32 lanes must call.
-__device__ __forceinline__ void group_accumulate(bool valid, int32_t key, int slot, double v, double* acc, double* xch, int lane) {
-    const unsigned grp = __match_any_sync(0xffffffffu, valid ? key : -1 - lane);
-    xch[lane] = v;
-    __syncwarp();
-    if (valid && (__ffs(grp) - 1) == lane) {
-        double partial = v;
-        for (unsigned rest = grp & (grp - 1); rest; rest &= rest - 1) partial = partial + xch[__ffs(rest) - 1];
-        acc[slot] = acc[slot] + partial;
-    }
-    __syncwarp();
+// ub2(j): products of column j of A_c
+__global__ void __launch_bounds__(kBlock) product2_bound_kernel(ProductArgs a) {
+    const int64_t j = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (j > a.m) return;
+    int32_t ub = 0;
+    if (j < a.m)
+        for (int32_t e = __ldg(a.r_ptr + j); e < __ldg(a.r_ptr + j + 1); ++e) ub += __ldg(a.t_cnt + __ldg(a.r_col + e));
+    a.ub2[j] = ub;
 }
 
-// Two-step row for ONE WARP (see the header comment).
-template <bool NUMERIC>
-__device__ __forceinline__ bool galerkin_row_two_step(const GalerkinArgs& a, int32_t i, int lane, GalerkinWarpSmem& sm,
-                                                      GalerkinWarpVals* sv) {
-    const int32_t rb = __ldg(a.r_ptr + i), re = __ldg(a.r_ptr + i + 1);
-    const int32_t nr = re - rb;
-    if (nr > kGMaxR) return false;
-    for (int s = lane; s < kGFineSlots; s += 32) { sm.fkeys[s] = -1; if (NUMERIC) sv->fvals[s] = 0.0; }
-    for (int s = lane; s < kGWarpSlots; s += 32) { sm.keys[s] = -1; if (NUMERIC) sv->vals[s] = 0.0; }
-    if (lane < 2) sm.scount[lane] = 0;
-    // ---- R's row: sorted by fine row (the transpose fills it in arrival order), with the scan of the lengths of
-    //      A's outer vectors, which numbers the products
-    {
-        int32_t k0 = 0x7fffffff, k1 = 0x7fffffff;
-        double p0 = 0.0, p1 = 0.0;
-        if (lane < nr) { k0 = __ldg(a.r_col + rb + lane); if (NUMERIC) p0 = __ldg(a.r_val + rb + lane); }
-        if (lane + 32 < nr) { k1 = __ldg(a.r_col + rb + lane + 32); if (NUMERIC) p1 = __ldg(a.r_val + rb + lane + 32); }
-        sm.rbase[lane] = k0; sm.rbase[lane + 32] = k1;        // scratch: the unsorted keys
-        __syncwarp();
-        int32_t rank0 = 0, rank1 = 0;
-        for (int32_t e = 0; e < nr; ++e) { const int32_t o = sm.rbase[e]; rank0 += o < k0 ? 1 : 0; rank1 += o < k1 ? 1 : 0; }
-        __syncwarp();
-        if (lane < nr) { sm.rk[rank0] = k0; if (NUMERIC) sv->rp[rank0] = p0; }
-        if (lane + 32 < nr) { sm.rk[rank1] = k1; if (NUMERIC) sv->rp[rank1] = p1; }
-        __syncwarp();
+// A_c(:,j) = sum_k T(:,k) * P(k,j), k ascending; written sorted into the column's slot
+__global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int64_t j = int64_t(blockIdx.x) * kThreads2 + threadIdx.x;
+    if (j >= a.m) return;
+    Table2 tab(smem, threadIdx.x);
+    tab.clear();
+    const int32_t rb = __ldg(a.r_ptr + j), re = __ldg(a.r_ptr + j + 1);
+    bool ok = true;
+    // (the column of T named by the NEXT entry of R is located while this one is consumed: the chain
+    //  r_col -> t_ptr -> entries is two dependent trips to memory per fine row otherwise)
+    int32_t nbase = 0, ncnt = 0;
+    double nw = 0.0;
+    if (rb < re) { const int32_t k = __ldg(a.r_col + rb); nbase = __ldg(a.t_ptr + k); ncnt = __ldg(a.t_cnt + k); nw = __ldg(a.r_val + rb); }
+    for (int32_t e = rb; e < re && ok; ++e) {
+        const int32_t base = nbase, cnt = ncnt;
+        const double w = nw;
+        if (e + 1 < re) { const int32_t k = __ldg(a.r_col + e + 1); nbase = __ldg(a.t_ptr + k); ncnt = __ldg(a.t_cnt + k); nw = __ldg(a.r_val + e + 1); }
+        for (int32_t s = 0; s < cnt; ++s) ok = tab.add(__ldg(a.t_idx + base + s), __ldg(a.t_val + base + s) * w) && ok;
     }
-    // ---- step 1: fine-keyed. A sub-step takes 4 rows k of R (8 lanes each) and entries [q0, q0 + 8) of A's outer
-    //      vectors k; lane = 8 * (k's place among the 4) + (q - q0).
-    bool full = false;
-    constexpr int kSub = 8;
-    for (int32_t e0 = 0; e0 < nr; e0 += 32 / kSub) {
-        const int32_t e = e0 + lane / kSub;
-        int32_t ab = 0, ae = 0;
-        double pki = 0.0;
-        if (e < nr) {
-            const int32_t k = sm.rk[e];
-            ab = __ldg(a.a_ptr + k); ae = __ldg(a.a_ptr + k + 1);
-            if (NUMERIC) pki = sv->rp[e];
-        }
-        const int32_t longest = __reduce_max_sync(0xffffffffu, ae - ab);
-        for (int32_t q0 = 0; q0 < longest; q0 += kSub) {
-            const int32_t q = ab + q0 + lane % kSub;
-            const bool valid = q < ae;
-            int32_t l = 0;
-            double w = 0.0;
-            int slot = -1;
-            if (valid) {
-                l = __ldg(a.a_idx + q);
-                if (NUMERIC) w = pki * __ldg(a.a_val + q);
-                slot = hash_insert<kGFineSlots>(sm.fkeys, l, sm.scount);
-                if (slot < 0) full = true;
-            }
-            if (NUMERIC) group_accumulate(valid && slot >= 0, l, slot, w, sv->fvals, sv->xch, lane);
-        }
+    int32_t* idx = a.w_idx + __ldg(a.w_ptr + j);
+    double* val = a.w_val + __ldg(a.w_ptr + j);
+    if (ok) {
+        tab.compact();
+        tab.sort();
+        for (int32_t s = 0; s < tab.count; ++s) { idx[s] = tab.keys[s * kThreads2]; val[s] = tab.vals[s * kThreads2]; }
+        a.w_cnt[j] = tab.count;
+        return;
     }
-    __syncwarp();
-    if (__any_sync(0xffffffffu, full) || sm.scount[0] > kGFineSlots * 3 / 4) return false;
-    // compact the occupied fine slots to the front (in place, chunk read before chunk written)
-    int32_t kf = 0;
-    for (int s0 = 0; s0 < kGFineSlots; s0 += 32) {
-        const int32_t key = sm.fkeys[s0 + lane];
-        const double v = NUMERIC ? sv->fvals[s0 + lane] : 0.0;
-        const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
-        __syncwarp();
-        if (key >= 0) { const int pos = kf + __popc(occ & ((1u << lane) - 1u)); sm.fkeys[pos] = key; if (NUMERIC) sv->fvals[pos] = v; }
-        kf += __popc(occ);
-        __syncwarp();
+    SlotList list{idx, val, 0};
+    for (int32_t e = rb; e < re; ++e) {
+        const int32_t k = __ldg(a.r_col + e);
+        const double w = __ldg(a.r_val + e);
+        const int32_t base = __ldg(a.t_ptr + k), cnt = __ldg(a.t_cnt + k);
+        for (int32_t s = 0; s < cnt; ++s) list.add(a.t_idx[base + s], a.t_val[base + s] * w);
     }
-    if (NUMERIC) {
-        // sort the distinct fine indices ascending (through registers: rank every entry, then write it back)
-        constexpr int kPer = kGFineSlots * 3 / 4 / 32;      // entries per lane
-        int32_t key[kPer], rank[kPer];
-        double val[kPer];
-#pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const int f = lane + 32 * u;
-            key[u] = f < kf ? sm.fkeys[f] : 0x7fffffff;
-            val[u] = f < kf ? sv->fvals[f] : 0.0;
-            rank[u] = 0;
-        }
-        for (int32_t f = 0; f < kf; ++f) {
-            const int32_t o = sm.fkeys[f];
-#pragma unroll
-            for (int u = 0; u < kPer; ++u) rank[u] += o < key[u] ? 1 : 0;
-        }
-        __syncwarp();
-#pragma unroll
-        for (int u = 0; u < kPer; ++u)
-            if (lane + 32 * u < kf) { sm.fkeys[rank[u]] = key[u]; sv->fvals[rank[u]] = val[u]; }
-        __syncwarp();
-    }
-    // ---- step 2: coarse-keyed, one lane per distinct fine index, entry t of every row of P in turn. The sorted
-    //      fine indices are dealt out INTERLEAVED (round r takes f = lane * rounds + r): neighbouring fine rows
-    //      share their coarse columns, and lanes of one sub-step that hold the same column are summed one by one.
-    const int32_t rounds = (kf + 31) / 32;
-    for (int32_t r = 0; r < rounds; ++r) {
-        const int32_t f = lane * rounds + r;
-        int32_t pb = 0, pe = 0;
-        double cl = 0.0;
-        if (f < kf) {
-            const int32_t l = sm.fkeys[f];
-            pb = __ldg(a.p_ptr + l); pe = __ldg(a.p_ptr + l + 1);
-            if (NUMERIC) cl = sv->fvals[f];
-        }
-        const int32_t longest = __reduce_max_sync(0xffffffffu, pe - pb);
-        for (int32_t t = 0; t < longest; ++t) {
-            const bool valid = pb + t < pe;
-            int32_t j = 0;
-            int slot = -1;
-            if (valid) {
-                j = __ldg(a.p_col + pb + t);
-                slot = hash_insert<kGWarpSlots>(sm.keys, j, sm.scount + 1);
-                if (slot < 0) full = true;
-            }
-            if (NUMERIC) {
-                const double v = valid ? cl * __ldg(a.p_val + pb + t) : 0.0;
-                group_accumulate(valid && slot >= 0, j, slot, v, sv->vals, sv->xch, lane);
-            }
-        }
-    }
-    __syncwarp();
-    const int32_t K = sm.scount[1];
-    if (__any_sync(0xffffffffu, full) || K > kGWarpSlots * 3 / 4) return false;
-    if (!NUMERIC) { if (lane == 0) a.out_count[i] = K; return true; }
-    const int32_t off = __ldg(a.out_ptr + i);
-    int32_t base = 0;
-    for (int s0 = 0; s0 < kGWarpSlots; s0 += 32) {
-        const int32_t key = sm.keys[s0 + lane];
-        const double v = sv->vals[s0 + lane];
-        const unsigned occ = __ballot_sync(0xffffffffu, key >= 0);
-        __syncwarp();
-        if (key >= 0) { const int pos = base + __popc(occ & ((1u << lane) - 1u)); sm.keys[pos] = key; sv->vals[pos] = v; }
-        base += __popc(occ);
-        __syncwarp();
-    }
-    for (int s = lane; s < K; s += 32) {
-        const int32_t key = sm.keys[s];
-        int32_t rank = 0;
-        for (int s2 = 0; s2 < K; ++s2) rank += sm.keys[s2] < key ? 1 : 0;
-        a.out_idx[off + rank] = key;
-        a.out_val[off + rank] = sv->vals[s];
-    }
-    return true;
+    list.sort();
+    a.w_cnt[j] = list.count;
+    atomicAdd(a.flags, 1);
 }
 
-template <bool NUMERIC>
-__global__ void __launch_bounds__(kBlock) galerkin_warp_kernel(GalerkinArgs a) {
-    __shared__ GalerkinWarpSmem sm[kBlock / 32];
-    __shared__ GalerkinWarpVals sv[NUMERIC ? kBlock / 32 : 1];
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t i = int64_t(blockIdx.x) * (kBlock / 32) + w;
-    if (i >= a.m) return;
-    if (!galerkin_row_two_step<NUMERIC>(a, int32_t(i), lane, sm[w], NUMERIC ? &sv[w] : nullptr)) {
-        // symbolic pass records the overflow; the numeric pass skips rows already on the list
-        if (!NUMERIC && lane == 0) { a.out_count[i] = 0; a.overflow[atomicAdd(a.flags + 1, 1)] = int32_t(i); }
-    }
-}
-
-template <bool NUMERIC>
-__global__ void __launch_bounds__(kBlock) galerkin_block_kernel(GalerkinArgs a, int32_t n_overflow) {
-    __shared__ int32_t keys[kGBlockSlots];
-    __shared__ double vals[NUMERIC ? kGBlockSlots : 1];
-    __shared__ int32_t scount;
-    for (int32_t o = blockIdx.x; o < n_overflow; o += gridDim.x) {
-        const int32_t i = a.overflow[o];
-        if (!galerkin_row<NUMERIC, kBlock, kGBlockSlots>(a, i, threadIdx.x, keys, vals, &scount)) {
-            if (threadIdx.x == 0) a.flags[2] = 1;
-        }
-        __syncthreads();
-    }
+// the slots of A_c into its final arrays: 8 lanes per column
+__global__ void __launch_bounds__(kBlock) compact_columns_kernel(ProductArgs a) {
+    const int64_t j = (int64_t(blockIdx.x) * kBlock + threadIdx.x) >> 3;
+    const int sub = threadIdx.x & 7;
+    if (j >= a.m) return;
+    const int32_t src = __ldg(a.w_ptr + j), dst = __ldg(a.out_ptr + j), cnt = __ldg(a.out_ptr + j + 1) - dst;
+    for (int32_t s = sub; s < cnt; s += 8) { a.out_idx[dst + s] = a.w_idx[src + s]; a.out_val[dst + s] = a.w_val[src + s]; }
 }
 
 void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_rowidx, const double* a_val,
@@ -428,43 +331,62 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     DeviceCsr& R = keep_R ? *keep_R : R_local;
     Trace tr(c, "galerkin");
     if (marks) cudaEventRecord(marks[0], c->stream);
-    // the warp kernel sorts R's rows itself while it stages them; a restriction that is KEPT is sorted once here
-    transpose_csr(c, P, R, c_lo, c_hi, keep_R != nullptr);
+    transpose_csr(c, P, R, c_lo, c_hi, true);       // sorted rows: k ascending is the summation order of A_c
     tr.mark("transpose");
     if (marks) cudaEventRecord(marks[1], c->stream);
-    DevBuf<int32_t> count(c, int64_t(m) + 1), flags(c, 4), overflow(c, m);
-    DevBuf<int64_t> total(c, 1);
-    count.zero(); flags.zero();
-    GalerkinArgs a{m, R.rowptr.p, R.colidx.p, R.val.p, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p,
-                   count.p, nullptr, nullptr, nullptr, flags.p, overflow.p};
-    const int grid = div_up(m, kBlock / 32);
-    // pass 1: symbolic
-    GMG_LAUNCH(c, galerkin_warp_kernel<false>, grid, kBlock, 0, a);
-    int32_t hf[4];
-    flags.download(hf, 4);
-    sync(c);
-    const int32_t n_over = hf[1];
-    if (getenv("GMG_TRACE")) fprintf(stderr, "[gmg] galerkin: %d outer vectors, %d to the block-wide table\n", m, n_over);
-    const int ogrid = n_over < 4 * c->sm_count ? n_over : 4 * c->sm_count;
-    if (n_over > 0) {
-        GMG_LAUNCH(c, galerkin_block_kernel<false>, ogrid, kBlock, 0, a, n_over);
-        flags.download(hf, 4);
-        sync(c);
-        GMG_REQUIRE(hf[2] == 0, GMG_ERR_INVALID, "galerkin: a coarse row has more than 1536 entries");
+    const bool all = c_lo == 0 && c_hi == P.cols;
+    DevBuf<uint8_t> needed;
+    if (!all) {
+        needed.alloc(c, n);
+        needed.zero();
+        if (R.nnz > 0) GMG_LAUNCH(c, mark_needed_kernel, div_up(R.nnz, kBlock), kBlock, 0, R.nnz, R.colidx.p, needed.p);
     }
-    exclusive_scan_i32(c, count.p, Ac.colptr.p, int64_t(m) + 1, total.p);
-    total.download(&Ac.nnz, 1);
+    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), t_cnt(c, n), flags(c, 1);
+    DevBuf<int32_t> ub2(c, int64_t(m) + 1), w_ptr(c, int64_t(m) + 1), w_cnt(c, int64_t(m) + 1);
+    DevBuf<int64_t> totals(c, 3);
+    flags.zero();
+    ProductArgs a{n, m, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p, R.rowptr.p, R.colidx.p, R.val.p,
+                  all ? nullptr : needed.p, ub1.p, t_ptr.p, t_cnt.p, nullptr, nullptr, ub2.p, w_ptr.p, w_cnt.p, nullptr, nullptr,
+                  nullptr, nullptr, nullptr, flags.p};
+    // ---- first product
+    int64_t h_total[3] = {0, 0, 0};
+    GMG_LAUNCH(c, product1_bound_kernel, div_up(int64_t(n) + 1, kBlock), kBlock, 0, a);
+    exclusive_scan_i32(c, ub1.p, t_ptr.p, int64_t(n) + 1, totals.p);
+    totals.download(h_total, 1);
     sync(c);
-    tr.mark("symbolic");
+    GMG_REQUIRE(h_total[0] < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: P^T A exceeds 32-bit indexing");
+    DevBuf<int32_t> t_idx(c, h_total[0]);
+    DevBuf<double> t_val(c, h_total[0]);
+    a.t_idx = t_idx.p; a.t_val = t_val.p;
+    GMG_CUDA(cudaFuncSetAttribute(product1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Table1::bytes())));
+    GMG_LAUNCH(c, product1_kernel, div_up(n, kThreads1), kThreads1, Table1::bytes(), a);
+    tr.mark("T = P^T A");
     if (marks) cudaEventRecord(marks[2], c->stream);
-    GMG_REQUIRE(Ac.nnz < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: A_c exceeds 32-bit indexing");
+    // ---- second product
+    GMG_LAUNCH(c, product2_bound_kernel, div_up(int64_t(m) + 1, kBlock), kBlock, 0, a);
+    exclusive_scan_i32(c, ub2.p, w_ptr.p, int64_t(m) + 1, totals.p + 1);
+    totals.download(h_total, 2);
+    sync(c);
+    GMG_REQUIRE(h_total[1] < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: the slots of A_c exceed 32-bit indexing");
+    DevBuf<int32_t> w_idx(c, h_total[1]);
+    DevBuf<double> w_val(c, h_total[1]);
+    a.w_idx = w_idx.p; a.w_val = w_val.p;
+    GMG_CUDA(cudaMemsetAsync(w_cnt.p + m, 0, sizeof(int32_t), c->stream));
+    GMG_CUDA(cudaFuncSetAttribute(product2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Table2::bytes())));
+    GMG_LAUNCH(c, product2_kernel, div_up(m, kThreads2), kThreads2, Table2::bytes(), a);
+    exclusive_scan_i32(c, w_cnt.p, Ac.colptr.p, int64_t(m) + 1, totals.p + 2);
+    totals.download(h_total, 3);
+    int32_t slow = 0;
+    flags.download(&slow, 1);
+    sync(c);
+    Ac.nnz = h_total[2];
+    if (getenv("GMG_TRACE")) fprintf(stderr, "[gmg] galerkin: n %d, %d outer vectors, %lld entries of T, %lld of A_c, %d vectors on the slow path\n",
+                                     n, m, (long long)h_total[0], (long long)Ac.nnz, slow);
     Ac.rowidx.alloc(c, Ac.nnz);
     Ac.val.alloc(c, Ac.nnz);
-    // pass 2: numeric
     a.out_ptr = Ac.colptr.p; a.out_idx = Ac.rowidx.p; a.out_val = Ac.val.p;
-    GMG_LAUNCH(c, galerkin_warp_kernel<true>, grid, kBlock, 0, a);
-    if (n_over > 0) GMG_LAUNCH(c, galerkin_block_kernel<true>, ogrid, kBlock, 0, a, n_over);
-    tr.mark("numeric");
+    GMG_LAUNCH(c, compact_columns_kernel, div_up(int64_t(m) * 8, kBlock), kBlock, 0, a);
+    tr.mark("A_c = T P");
     if (marks) cudaEventRecord(marks[3], c->stream);
 }
 

@@ -44,11 +44,11 @@ constexpr int kStage = 16;   // later-path targets a lane can stage in shared me
 //                         then (odd multiply, xorshift by ceil(k/2)) twice and a last odd multiply, all modulo 2^k;
 //                         every step is a bijection on k bits and the xorshift is its own inverse because twice the
 //                         shift is >= k. Dependency depth O(log n).
-//   GMG_SAMPLER_PARALLEL  the reference's index-order sweep restarted in `supers` (3) contiguous SUPER-TILES of
+//   GMG_SAMPLER_PARALLEL  the reference's index-order sweep restarted in `supers` (2) contiguous SUPER-TILES of
 //                         `ssize` vertices (a multiple of the flow tile) that are swept CONCURRENTLY: the flow tiles
 //                         of the super-tiles are interleaved in the order, rank = ((flow tile in its super-tile) *
 //                         supers + super-tile) * kTile + offset. Every super-tile starts at once (its first rows
-//                         precede the last rows of its neighbour), so the dependency depth is a third of the index
+//                         precede the last rows of its neighbour), so the dependency depth is half the index
 //                         order's; the packing is the reference's except along the seams (why: DESIGN.md section 4,
 //                         "sampler orders"). The seed is not used.
 struct Order {
@@ -58,6 +58,7 @@ struct Order {
     uint32_t kbits;                    // bits of a rank; ranks live in [0, 2^kbits)
 };
 constexpr int kOrderTileLog = 12;      // = kTileLog of the tile flow kernel
+constexpr int32_t kParallelMinVertices = 2000000;   // GMG_SAMPLER_PARALLEL: two concurrent sweeps from here on
 __host__ __device__ __forceinline__ uint32_t order_rank(const Order& o, uint32_t v) {
     if (o.supers) {
         const uint32_t sup = (v >= o.ssize ? 1u : 0u) + (v >= 2u * o.ssize ? 1u : 0u);
@@ -96,11 +97,16 @@ static Order make_order(int32_t n, uint64_t seed, int mode) {
         return o;
     }
     if (mode == GMG_SAMPLER_PARALLEL) {
+        // every additional sweep start costs samples (the packing of a sweep tightens over its first rows): measured
+        // on the noisy torus with tools/order_stats.py, two sweeps lose 2.3 % at 1 M vertices, 1.4 % at 2.5 M and
+        // 1.1 % at 10 M, three lose 3.2 % / 2.3 % at 1 M / 10 M. The north star allows 2 %: two sweeps from 2 M
+        // vertices on, the plain index order below that.
         constexpr int64_t tile = int64_t(1) << kOrderTileLog;
-        const int64_t third = ((int64_t(n) + 2) / 3 + tile - 1) / tile * tile;
-        o.ssize = uint32_t(third);
-        o.supers = uint32_t((int64_t(n) + third - 1) / third);          // 3, fewer for a small n
-        o.kbits = uint32_t(ceil_log2(third * int64_t(o.supers)));
+        const int64_t want = n >= kParallelMinVertices ? 2 : 1;
+        const int64_t part = ((int64_t(n) + want - 1) / want + tile - 1) / tile * tile;
+        o.ssize = uint32_t(part);
+        o.supers = uint32_t((int64_t(n) + part - 1) / part);
+        o.kbits = uint32_t(ceil_log2(part * int64_t(o.supers)));
         if (o.kbits == 0) o.kbits = 1;
         return o;
     }

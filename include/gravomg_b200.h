@@ -59,11 +59,12 @@ typedef enum {
 enum { GMG_BARYCENTRIC = 0, GMG_UNIFORM = 1, GMG_INVDIST = 2 };
 /* Sampler modes: the same greedy rule (src/sampling.cpp:22-50) under three precedence orders.
  *   EXACT     index order: the reference's sample set bit-for-bit.
- *   PARALLEL  the index-order sweep restarted in 3 contiguous super-tiles that are swept concurrently (their
+ *   PARALLEL  the index-order sweep restarted in 2 contiguous super-tiles that are swept concurrently (their
  *             flow tiles are interleaved in the order; the seed is not used): a different set, within 2 % of the
  *             reference on sample count and coverage radius (the north star's statistical criterion) also on
  *             index-coherent grids, where the reference's row-by-row sweep packs much more tightly than any
- *             order-independent rule; a third of the index order's dependency depth.
+ *             order-independent rule; half the index order's dependency depth. Below 2 M
+ *             vertices (where a second sweep start would cost more than 2 % of the samples) it is the index order.
  *   HASHED    every vertex hashed: dependency depth O(log n); what the row-sharded build runs for both
  *             non-exact modes. Statistically equal to the reference on unordered inputs (point clouds,
  *             subdivision orders), 28 % fewer samples on a row-major grid. */
@@ -201,7 +202,8 @@ typedef struct {
        0 edge lengths+radius, 1 sampling, 2 parents, 3 cluster CSR, 4 coarse edges, 5 coarse points,
        6 triangle fans, 7 prolongation rows, 8 Galerkin */
     double stage_ms[9];
-    /* stage 8 split: transpose R = P^T, symbolic pass, numeric pass (0 unless build_galerkin) */
+    /* stage 8 split: transpose R = P^T; first product T = P^T A (sizing pass + values); second product A_c = T P
+     * (sizing pass + values + compaction). 0 unless build_galerkin */
     double galerkin_ms[3];
 } gmg_level_info;
 
