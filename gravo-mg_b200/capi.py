@@ -165,6 +165,14 @@ class Context:
                                                      _p(edges, _i32p), C.byref(out)))
         return out.value
 
+    def morton_order(self, points):
+        """Permutation sorting the points along the Morton curve of their bounding cube (gmg_morton_order)."""
+        pts = _pts(points)
+        perm = np.empty(pts.shape[0], dtype=np.int32)
+        self.lib.gmg_morton_order.argtypes = [C.c_void_p, C.c_int64, _f64p, C.c_int64, _i32p]
+        self._check(self.lib.gmg_morton_order(self.h, pts.shape[0], _p(pts, _f64p), pts.shape[0], _p(perm, _i32p)))
+        return perm
+
     def fast_disc_sample(self, points, colptr, rowidx, radius, mode=SAMPLER_EXACT, seed=42):
         pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
         n = pts.shape[0]
@@ -345,6 +353,44 @@ class Input:
             ctx.lib.gmg_input_torus_operator.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_double]
             ctx._check(ctx.lib.gmg_input_torus_operator(ctx.h, h, nu, nv, float(mass_shift)))
         return self
+
+    @classmethod
+    def knn(cls, ctx, points, k=8):
+        """Exact kNN graph of a point cloud built on the device (gmg_input_from_knn): union-symmetrised + diagonal."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        pts = _pts(points)
+        h = C.c_void_p()
+        ctx.lib.gmg_input_from_knn.argtypes = [C.c_void_p, C.c_int64, _f64p, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]
+        ctx._check(ctx.lib.gmg_input_from_knn(ctx.h, pts.shape[0], _p(pts, _f64p), pts.shape[0], int(k), C.byref(h)))
+        self.h = h
+        self._sizes()
+        self.h2d_bytes = pts.nbytes
+        return self
+
+    @classmethod
+    def mesh(cls, ctx, points, faces, mass_shift=0.0):
+        """Triangle mesh -> adjacency + diagonal pattern and the cotangent Laplacian (+ mass_shift * lumped mass),
+        assembled on the device (gmg_input_from_mesh)."""
+        self = cls.__new__(cls)
+        self.ctx = ctx
+        pts = _pts(points)
+        F = np.ascontiguousarray(faces, dtype=np.int32)
+        h = C.c_void_p()
+        ctx.lib.gmg_input_from_mesh.argtypes = [C.c_void_p, C.c_int64, _f64p, C.c_int64, C.c_int64, _i32p, C.c_double,
+                                                C.POINTER(C.c_void_p)]
+        ctx._check(ctx.lib.gmg_input_from_mesh(ctx.h, pts.shape[0], _p(pts, _f64p), pts.shape[0], F.shape[0], _p(F, _i32p),
+                                               float(mass_shift), C.byref(h)))
+        self.h = h
+        self._sizes()
+        self.h2d_bytes = pts.nbytes + F.nbytes
+        return self
+
+    def _sizes(self):
+        n, nnz = C.c_int64(), C.c_int64()
+        self.ctx.lib.gmg_input_size.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        self.ctx.lib.gmg_input_size(self.h, C.byref(n), C.byref(nnz))
+        self.n, self.nnz = int(n.value), int(nnz.value)
 
     def fetch_operator(self):
         """A values (nnz) of an input that has them, copied back to the host."""

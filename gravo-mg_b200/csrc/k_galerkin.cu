@@ -195,7 +195,7 @@ struct ProductArgs {
     const int32_t* p_ptr; const int32_t* p_col; const double* p_val;      // P rows
     const int32_t* r_ptr; const int32_t* r_col; const double* r_val;      // R = P^T (rows = the outer vectors formed here)
     const uint8_t* needed;                                                // fine columns of T that R reads (null: all)
-    int32_t* ub1; const int32_t* t_ptr; int32_t* t_cnt; int32_t* t_idx; double* t_val;     // T in slots
+    int32_t* ub1; const int32_t* t_ptr; int2* t_loc; int32_t* t_idx; double* t_val;        // T: slots per block, (start, count) per column
     int32_t* ub2; const int32_t* w_ptr; int32_t* w_cnt; int32_t* w_idx; double* w_val;     // A_c in slots
     const int32_t* out_ptr; int32_t* out_idx; double* out_val;                              // A_c
     int32_t* flags;                                                       // [0] vectors that took the slow path
@@ -220,39 +220,104 @@ __global__ void __launch_bounds__(kBlock) product1_bound_kernel(ProductArgs a) {
     a.ub1[k] = ub;          // entry n = 0: the scan's total
 }
 
-// T(:,k) = sum_l A(l,k) * P(l,:)
+// exclusive scan of one int per thread over a block of THREADS threads (all threads must call)
+template <int THREADS>
+__device__ __forceinline__ int32_t block_scan_exclusive(int32_t v, int32_t* warp_sums) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    int32_t off = 0;
+#pragma unroll
+    for (int w = 0; w < THREADS / 32; ++w) off += w < wid ? warp_sums[w] : 0;
+    return off + incl - v;
+}
+
+// T(:,k) = sum_l A(l,k) * P(l,:). The loads are issued in BATCHES before anything consumes them (eight entries of A's
+// outer vector, then the eight row pointers of P, then the rows themselves): a thread that walks
+// a_idx -> p_ptr -> p_col one entry at a time pays three dependent trips to memory per entry, and with a 48 KB
+// table per block there are too few warps on an SM to hide that (ncu: 49 % of the stalls long-scoreboard at 23 %
+// occupancy). The columns of a block are then written DENSELY into the block's share of the slots (a block scan of
+// the counts), so that the second product reads full sectors.
 __global__ void __launch_bounds__(kThreads1) product1_kernel(ProductArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int32_t s_warp[kThreads1 / 32];
     const int64_t k = int64_t(blockIdx.x) * kThreads1 + threadIdx.x;
-    if (k >= a.n) return;
-    const int32_t base = __ldg(a.t_ptr + k);
-    if (__ldg(a.t_ptr + k + 1) == base) { a.t_cnt[k] = 0; return; }
+    int32_t ub = 0;
+    if (k < a.n) ub = __ldg(a.t_ptr + k + 1) - __ldg(a.t_ptr + k);
     Table1 tab(smem, threadIdx.x);
-    tab.clear();
-    const int32_t ab = __ldg(a.a_ptr + k), ae = __ldg(a.a_ptr + k + 1);
     bool ok = true;
-    for (int32_t q = ab; q < ae && ok; ++q) {
-        const int32_t l = __ldg(a.a_idx + q);
-        const double w = __ldg(a.a_val + q);
-        const int32_t pb = __ldg(a.p_ptr + l), pe = __ldg(a.p_ptr + l + 1);
-        for (int32_t t = pb; t < pe; ++t) ok = tab.add(__ldg(a.p_col + t), w * __ldg(a.p_val + t)) && ok;
+    int32_t ab = 0, ae = 0;
+    if (ub > 0) {
+        tab.clear();
+        ab = __ldg(a.a_ptr + k); ae = __ldg(a.a_ptr + k + 1);
+        constexpr int kB = 8, kRow = 3;
+        for (int32_t q0 = ab; q0 < ae && ok; q0 += kB) {
+            int32_t l[kB], pb[kB], pe[kB];
+            double w[kB];
+#pragma unroll
+            for (int u = 0; u < kB; ++u) {
+                const bool have = q0 + u < ae;
+                l[u] = have ? __ldg(a.a_idx + q0 + u) : -1;
+                w[u] = have ? __ldg(a.a_val + q0 + u) : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < kB; ++u) {
+                pb[u] = l[u] >= 0 ? __ldg(a.p_ptr + l[u]) : 0;
+                pe[u] = l[u] >= 0 ? __ldg(a.p_ptr + l[u] + 1) : 0;
+            }
+#pragma unroll
+            for (int half = 0; half < kB; half += kB / 2) {
+                int32_t col[kB / 2][kRow];
+                double val[kB / 2][kRow];
+#pragma unroll
+                for (int u = 0; u < kB / 2; ++u)
+#pragma unroll
+                    for (int t = 0; t < kRow; ++t) {
+                        const bool have = pb[half + u] + t < pe[half + u];
+                        col[u][t] = have ? __ldg(a.p_col + pb[half + u] + t) : -1;
+                        val[u][t] = have ? __ldg(a.p_val + pb[half + u] + t) : 0.0;
+                    }
+#pragma unroll
+                for (int u = 0; u < kB / 2; ++u) {
+#pragma unroll
+                    for (int t = 0; t < kRow; ++t)
+                        if (col[u][t] >= 0) ok = tab.add(col[u][t], w[half + u] * val[u][t]) && ok;
+                    for (int32_t t = pb[half + u] + kRow; t < pe[half + u]; ++t)        // rows of P beyond three entries
+                        ok = tab.add(__ldg(a.p_col + t), w[half + u] * __ldg(a.p_val + t)) && ok;
+                }
+            }
+        }
     }
-    int32_t* idx = a.t_idx + base;
-    double* val = a.t_val + base;
-    if (ok) {
+    // where this column goes: fast columns take what they hold, a column on the slow path its whole bound
+    const int32_t reserve = ub == 0 ? 0 : (ok ? tab.count : ub);
+    const int32_t off = block_scan_exclusive<kThreads1>(reserve, s_warp);
+    if (k >= a.n) return;
+    const int64_t k0 = int64_t(blockIdx.x) * kThreads1;
+    const int32_t start = __ldg(a.t_ptr + k0) + off;
+    int32_t* idx = a.t_idx + start;
+    double* val = a.t_val + start;
+    int32_t cnt = 0;
+    if (ub > 0 && ok) {
         tab.compact();
-        for (int32_t s = 0; s < tab.count; ++s) { idx[s] = tab.keys[s * kThreads1]; val[s] = tab.vals[s * kThreads1]; }
-        a.t_cnt[k] = tab.count;
-        return;
+        cnt = tab.count;
+        for (int32_t s = 0; s < cnt; ++s) { idx[s] = tab.keys[s * kThreads1]; val[s] = tab.vals[s * kThreads1]; }
+    } else if (ub > 0) {
+        SlotList list{idx, val, 0};
+        for (int32_t q = ab; q < ae; ++q) {
+            const int32_t l = __ldg(a.a_idx + q);
+            const double w = __ldg(a.a_val + q);
+            for (int32_t t = __ldg(a.p_ptr + l); t < __ldg(a.p_ptr + l + 1); ++t) list.add(__ldg(a.p_col + t), w * __ldg(a.p_val + t));
+        }
+        cnt = list.count;
+        atomicAdd(a.flags, 1);
     }
-    SlotList list{idx, val, 0};
-    for (int32_t q = ab; q < ae; ++q) {
-        const int32_t l = __ldg(a.a_idx + q);
-        const double w = __ldg(a.a_val + q);
-        for (int32_t t = __ldg(a.p_ptr + l); t < __ldg(a.p_ptr + l + 1); ++t) list.add(__ldg(a.p_col + t), w * __ldg(a.p_val + t));
-    }
-    a.t_cnt[k] = list.count;
-    atomicAdd(a.flags, 1);
+    a.t_loc[k] = make_int2(start, cnt);
 }
 
 // ub2(j): products of column j of A_c
@@ -261,11 +326,13 @@ __global__ void __launch_bounds__(kBlock) product2_bound_kernel(ProductArgs a) {
     if (j > a.m) return;
     int32_t ub = 0;
     if (j < a.m)
-        for (int32_t e = __ldg(a.r_ptr + j); e < __ldg(a.r_ptr + j + 1); ++e) ub += __ldg(a.t_cnt + __ldg(a.r_col + e));
+        for (int32_t e = __ldg(a.r_ptr + j); e < __ldg(a.r_ptr + j + 1); ++e) ub += __ldg(a.t_loc + __ldg(a.r_col + e)).y;
     a.ub2[j] = ub;
 }
 
-// A_c(:,j) = sum_k T(:,k) * P(k,j), k ascending; written sorted into the column's slot
+// A_c(:,j) = sum_k T(:,k) * P(k,j), k ascending; written sorted into the column's slot. Same batching: the first
+// eight entries of the NEXT column of T are in flight (and the location of the one after that) while the current
+// one is added up.
 __global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int64_t j = int64_t(blockIdx.x) * kThreads2 + threadIdx.x;
@@ -274,16 +341,38 @@ __global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
     tab.clear();
     const int32_t rb = __ldg(a.r_ptr + j), re = __ldg(a.r_ptr + j + 1);
     bool ok = true;
-    // (the column of T named by the NEXT entry of R is located while this one is consumed: the chain
-    //  r_col -> t_ptr -> entries is two dependent trips to memory per fine row otherwise)
-    int32_t nbase = 0, ncnt = 0;
-    double nw = 0.0;
-    if (rb < re) { const int32_t k = __ldg(a.r_col + rb); nbase = __ldg(a.t_ptr + k); ncnt = __ldg(a.t_cnt + k); nw = __ldg(a.r_val + rb); }
+    constexpr int kB = 8;
+    int32_t ni[kB];
+    double nv[kB];
+    int2 nloc = make_int2(0, 0), nnloc = make_int2(0, 0);
+    double nw = 0.0, nnw = 0.0;
+    if (rb < re) { nloc = __ldg(a.t_loc + __ldg(a.r_col + rb)); nw = __ldg(a.r_val + rb); }
+    if (rb + 1 < re) { nnloc = __ldg(a.t_loc + __ldg(a.r_col + rb + 1)); nnw = __ldg(a.r_val + rb + 1); }
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+        const bool have = u < nloc.y;
+        ni[u] = have ? __ldg(a.t_idx + nloc.x + u) : -1;
+        nv[u] = have ? __ldg(a.t_val + nloc.x + u) : 0.0;
+    }
     for (int32_t e = rb; e < re && ok; ++e) {
-        const int32_t base = nbase, cnt = ncnt;
+        int32_t ci[kB];
+        double cv[kB];
+#pragma unroll
+        for (int u = 0; u < kB; ++u) { ci[u] = ni[u]; cv[u] = nv[u]; }
+        const int2 loc = nloc;
         const double w = nw;
-        if (e + 1 < re) { const int32_t k = __ldg(a.r_col + e + 1); nbase = __ldg(a.t_ptr + k); ncnt = __ldg(a.t_cnt + k); nw = __ldg(a.r_val + e + 1); }
-        for (int32_t s = 0; s < cnt; ++s) ok = tab.add(__ldg(a.t_idx + base + s), __ldg(a.t_val + base + s) * w) && ok;
+        nloc = nnloc; nw = nnw;
+#pragma unroll
+        for (int u = 0; u < kB; ++u) {
+            const bool have = e + 1 < re && u < nloc.y;
+            ni[u] = have ? __ldg(a.t_idx + nloc.x + u) : -1;
+            nv[u] = have ? __ldg(a.t_val + nloc.x + u) : 0.0;
+        }
+        if (e + 2 < re) { nnloc = __ldg(a.t_loc + __ldg(a.r_col + e + 2)); nnw = __ldg(a.r_val + e + 2); }
+#pragma unroll
+        for (int u = 0; u < kB; ++u)
+            if (ci[u] >= 0) ok = tab.add(ci[u], cv[u] * w) && ok;
+        for (int32_t s = kB; s < loc.y; ++s) ok = tab.add(__ldg(a.t_idx + loc.x + s), __ldg(a.t_val + loc.x + s) * w) && ok;
     }
     int32_t* idx = a.w_idx + __ldg(a.w_ptr + j);
     double* val = a.w_val + __ldg(a.w_ptr + j);
@@ -296,10 +385,9 @@ __global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
     }
     SlotList list{idx, val, 0};
     for (int32_t e = rb; e < re; ++e) {
-        const int32_t k = __ldg(a.r_col + e);
+        const int2 loc = __ldg(a.t_loc + __ldg(a.r_col + e));
         const double w = __ldg(a.r_val + e);
-        const int32_t base = __ldg(a.t_ptr + k), cnt = __ldg(a.t_cnt + k);
-        for (int32_t s = 0; s < cnt; ++s) list.add(a.t_idx[base + s], a.t_val[base + s] * w);
+        for (int32_t s = 0; s < loc.y; ++s) list.add(a.t_idx[loc.x + s], a.t_val[loc.x + s] * w);
     }
     list.sort();
     a.w_cnt[j] = list.count;
@@ -341,12 +429,13 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
         needed.zero();
         if (R.nnz > 0) GMG_LAUNCH(c, mark_needed_kernel, div_up(R.nnz, kBlock), kBlock, 0, R.nnz, R.colidx.p, needed.p);
     }
-    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), t_cnt(c, n), flags(c, 1);
+    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), flags(c, 1);
+    DevBuf<int2> t_loc(c, n);
     DevBuf<int32_t> ub2(c, int64_t(m) + 1), w_ptr(c, int64_t(m) + 1), w_cnt(c, int64_t(m) + 1);
     DevBuf<int64_t> totals(c, 3);
     flags.zero();
     ProductArgs a{n, m, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p, R.rowptr.p, R.colidx.p, R.val.p,
-                  all ? nullptr : needed.p, ub1.p, t_ptr.p, t_cnt.p, nullptr, nullptr, ub2.p, w_ptr.p, w_cnt.p, nullptr, nullptr,
+                  all ? nullptr : needed.p, ub1.p, t_ptr.p, t_loc.p, nullptr, nullptr, ub2.p, w_ptr.p, w_cnt.p, nullptr, nullptr,
                   nullptr, nullptr, nullptr, flags.p};
     // ---- first product
     int64_t h_total[3] = {0, 0, 0};

@@ -172,6 +172,21 @@ int gmg_input_torus_operator(gmg_ctx* ctx, gmg_input* in, int32_t nu, int32_t nv
 int gmg_input_fetch(gmg_ctx* ctx, const gmg_input* in, int which, void* host_out);
 int gmg_input_size(const gmg_input* in, int64_t* n, int64_t* nnz);
 
+/* Level-0 graphs BUILT on the device from raw geometry [not in reference; SURVEY.md 8(f) rank 2: what the reference's
+ * driver gets from an external buildPointCloudLaplacian / mesh loader, test/main.cpp:68]. points: column-major n x 3,
+ * leading dimension ld, on the host.
+ *   gmg_input_from_knn   exact k nearest neighbours (1 <= k <= 32, ties by index) by grid hashing, union-symmetrised,
+ *                        plus the diagonal: the graph of config C4. No A values.
+ *   gmg_input_from_mesh  faces: nf x 3 int32 row-major. Pattern = mesh adjacency + diagonal, A = cotangent Laplacian
+ *                        + mass_shift * lumped mass (the system matrix of C1/C2/C3).
+ *   gmg_morton_order     perm_out[r] = index of the point of rank r along the Morton curve of the bounding cube
+ *                        (21 bits per axis, ties by index): the reordering that makes contiguous row blocks
+ *                        spatially compact before a row-sharded build. */
+int gmg_input_from_knn(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int32_t k, gmg_input** out);
+int gmg_input_from_mesh(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int64_t nf, const int32_t* faces,
+                        double mass_shift, gmg_input** out);
+int gmg_morton_order(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int32_t* perm_out);
+
 typedef struct {
     int32_t levels;          /* levels including the finest; levels-1 prolongations are built */
     double ratio;            /* radius = cbrt(ratio) * averageEdgeLength  (test/main.cpp:74) */
