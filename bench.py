@@ -45,6 +45,11 @@ def parse():
                          "build (the exact greedy order is a cross-rank dependency chain; SURVEY.md 8(e))")
     ap.add_argument("--galerkin", type=int, default=None, help="1: also A_c = P^T A P on every level (default: 1 for C3 and the torus family)")
     ap.add_argument("--vcycle", type=int, default=None, help="1 (with --galerkin 1): one V-cycle Poisson solve and an SpMV, timed")
+    ap.add_argument("--reorder", default="none", choices=["none", "morton"],
+                    help="C4: renumber the cloud along the Morton curve on the device (gmg_morton_order) before the graph is built")
+    ap.add_argument("--driver", default="native", choices=["native", "python"],
+                    help="N > 1: the build's phase loop in C++ with the library's own NCCL communicator (gmg_shard_build_nccl), "
+                         "or driven from Python through torch.distributed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-scale", type=float, default=None, help="size of the in-line CPU baseline sample (default: the workload itself, which also gives the parity check)")
     a = ap.parse_args()
@@ -86,8 +91,11 @@ def workload_name(a):
 
 def bench_config(a, world):
     """The `config` object; identical in the B200 arm and the reference arm."""
-    return {"workload": workload_name(a), "sampler": a.sampler, "galerkin": bool(a.galerkin), "vcycle": bool(a.vcycle),
-            "n_gpus": world}
+    cfg = {"workload": workload_name(a), "sampler": a.sampler, "galerkin": bool(a.galerkin), "vcycle": bool(a.vcycle),
+           "n_gpus": world}
+    if getattr(a, "reorder", "none") != "none":
+        cfg["reorder"] = a.reorder
+    return cfg
 
 
 # ---- clocks sampler (B200_PROFILING.md recipe) ---------------------------------------------------
@@ -368,6 +376,12 @@ def run_b200(a, rank, world, local_rank):
         # fetched back once, so that the timed steps, the end-to-end arm and the CPU arm all start from host arrays
         import scipy.sparse as sp
         V = meshgen.sphere_cloud(max(64, int(20_000_000 * a.scale)))
+        morton_ms = None
+        if a.reorder == "morton":
+            t0 = time.perf_counter()
+            perm = ctx.morton_order(V)
+            morton_ms = 1e3 * (time.perf_counter() - t0)
+            V = np.asfortranarray(V[perm])
         t0 = time.perf_counter()
         knn = Input.knn(ctx, V, 8)
         torch.cuda.synchronize()
@@ -378,7 +392,8 @@ def run_b200(a, rank, world, local_rank):
         cfg = dict(name="C4", V=V, A=A, levels=LEVELS["C4"])
         builder = {"what": "exact kNN (k=8) by grid hashing + union-symmetrisation on the device, host points in, "
                            "wall clock of the call including the H2D copy of the points", "ms": knn_ms,
-                   "points": int(V.shape[0]), "nnz": int(A.nnz), "Mpoints_per_s": V.shape[0] / (knn_ms * 1e-3) / 1e6}
+                   "points": int(V.shape[0]), "nnz": int(A.nnz), "Mpoints_per_s": V.shape[0] / (knn_ms * 1e-3) / 1e6,
+                   "reorder": a.reorder, "morton_order_ms": morton_ms}
     else:
         cfg = meshgen.make_config(a.workload, a.scale)
     V, A = cfg["V"], cfg["A"]
@@ -619,7 +634,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     import torch.distributed as dist
     from gravomg_b200 import capi
     from gravomg_b200.capi import Context, Input
-    from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
+    from gravomg_b200.sharded import NativeComm, ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
@@ -630,6 +645,7 @@ def run_b200_sharded(a, rank, world, local_rank):
     torch.cuda.set_stream(stream)         # a real stream shared by the library, the NCCL exchanges and the timing events
     ctx = Context(local_rank, stream.cuda_stream)
     comm = TorchComm() if world > 1 else None
+    native = NativeComm(ctx) if world > 1 and a.driver == "native" else None
     nu, nv = torus_dims(a.workload)
     n = nu * nv
     levels = 4
@@ -653,7 +669,7 @@ def run_b200_sharded(a, rank, world, local_rank):
 
     def build(which, profile=False):
         return ShardedHierarchy(ctx, which, levels, world, [rank], comm=comm, sampler_mode=mode, profile=profile,
-                                build_galerkin=galerkin)
+                                build_galerkin=galerkin, native=None if profile else native)
 
     for _ in range(a.warmup):
         build(inp).close()
@@ -770,7 +786,9 @@ def run_b200_sharded(a, rank, world, local_rank):
             "config": {**bench_config(a, world),
                        "l2": "256 MB flush write between timed steps; inputs exceed the 126 MB L2",
                        "multi_gpu": (f"row-sharded over {world} ranks: owned ranges of fine vertices, replicated level "
-                                     f"graph, {exchanges} NCCL all-gathers ({xbytes / 1e6:.1f} MB gathered per rank) per build")
+                                     f"graph, {exchanges} NCCL all-gathers ({xbytes / 1e6:.1f} MB gathered per rank) per build; phase loop "
+                                     + ("in C++ with the library's own communicator (gmg_shard_build_nccl)" if native is not None
+                                        else "driven from Python through torch.distributed"))
                        if world > 1 else "single GPU through the sharded driver (world 1)",
                        "verts_per_gpu": n // world,
                        "levels": [{k: i[k] for k in ("n", "nnz", "m", "nnz_c", "T", "nnz_ac", "sampler_rounds", "parent_rounds")}

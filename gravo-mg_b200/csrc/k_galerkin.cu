@@ -21,7 +21,8 @@
 // of ub1 / ub2), record the count they found, and A_c is then compacted into its final arrays (T is only ever
 // read through its slots). A thread whose table fills up (more than kCap1 / kCap2 distinct keys: dense rows of
 // deep levels or kNN operators) redoes its vector as a linear-search list directly in its slot -- same order,
-// same bits, just slow.
+// same bits, just slow. The second product runs with a small table first (occupancy) and redoes the
+// columns that outgrow it with a large one in a second kernel.
 // Algorithmic bytes: symbolic 12n + 4nnzA + 8nnzP + 4m; numeric 12n + 12nnzA + 24nnzP + 4m + 12nnzAc.
 #include "stages.h"
 
@@ -110,7 +111,8 @@ void transpose_csr(gmg_ctx* c, const DeviceCsr& P, DeviceCsr& R, int32_t c_lo, i
 
 // ---- SpGEMM -------------------------------------------------------------------------------------
 constexpr int kCap1 = 32, kThreads1 = 128;     // first product: slots per thread, threads per block
-constexpr int kCap2 = 64, kThreads2 = 64;      // second product
+constexpr int kCap2 = 32, kThreads2 = 128;     // second product, first pass
+constexpr int kCap2b = 128, kThreads2b = 32;   // second product, columns that outgrow the first table
 
 // A thread's private accumulator: open addressing, linear probing, [slot][thread] in shared memory.
 template <int CAP, int THREADS>
@@ -188,6 +190,7 @@ struct SlotList {
 
 using Table1 = ThreadTable<kCap1, kThreads1>;
 using Table2 = ThreadTable<kCap2, kThreads2>;
+using Table2b = ThreadTable<kCap2b, kThreads2b>;
 
 struct ProductArgs {
     int32_t n, m;                                                         // fine vertices; outer vectors of A_c formed here
@@ -198,7 +201,8 @@ struct ProductArgs {
     int32_t* ub1; const int32_t* t_ptr; int2* t_loc; int32_t* t_idx; double* t_val;        // T: slots per block, (start, count) per column
     int32_t* ub2; const int32_t* w_ptr; int32_t* w_cnt; int32_t* w_idx; double* w_val;     // A_c in slots
     const int32_t* out_ptr; int32_t* out_idx; double* out_val;                              // A_c
-    int32_t* flags;                                                       // [0] vectors that took the slow path
+    int32_t* flags;                                                       // [0] vectors that took the slow path, [1] queued for the second pass
+    int32_t* overflow;                                                    // columns of A_c queued for the second pass
 };
 
 __global__ void __launch_bounds__(kBlock) mark_needed_kernel(int64_t nnz, const int32_t* __restrict__ r_col,
@@ -332,12 +336,9 @@ __global__ void __launch_bounds__(kBlock) product2_bound_kernel(ProductArgs a) {
 
 // A_c(:,j) = sum_k T(:,k) * P(k,j), k ascending; written sorted into the column's slot. Same batching: the first
 // eight entries of the NEXT column of T are in flight (and the location of the one after that) while the current
-// one is added up.
-__global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    const int64_t j = int64_t(blockIdx.x) * kThreads2 + threadIdx.x;
-    if (j >= a.m) return;
-    Table2 tab(smem, threadIdx.x);
+// one is added up. false: the table is full.
+template <typename Table, int THREADS>
+__device__ __forceinline__ bool product2_column(const ProductArgs& a, int64_t j, Table& tab) {
     tab.clear();
     const int32_t rb = __ldg(a.r_ptr + j), re = __ldg(a.r_ptr + j + 1);
     bool ok = true;
@@ -374,24 +375,48 @@ __global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
             if (ci[u] >= 0) ok = tab.add(ci[u], cv[u] * w) && ok;
         for (int32_t s = kB; s < loc.y; ++s) ok = tab.add(__ldg(a.t_idx + loc.x + s), __ldg(a.t_val + loc.x + s) * w) && ok;
     }
+    if (!ok) return false;
     int32_t* idx = a.w_idx + __ldg(a.w_ptr + j);
     double* val = a.w_val + __ldg(a.w_ptr + j);
-    if (ok) {
-        tab.compact();
-        tab.sort();
-        for (int32_t s = 0; s < tab.count; ++s) { idx[s] = tab.keys[s * kThreads2]; val[s] = tab.vals[s * kThreads2]; }
-        a.w_cnt[j] = tab.count;
-        return;
+    tab.compact();
+    tab.sort();
+    for (int32_t s = 0; s < tab.count; ++s) { idx[s] = tab.keys[s * THREADS]; val[s] = tab.vals[s * THREADS]; }
+    a.w_cnt[j] = tab.count;
+    return true;
+}
+
+// first pass: a small table per thread, so that four blocks of 128 threads fit on an SM (the kernel waits on memory;
+// what hides that is warps). A column that outgrows it is queued for the second pass.
+__global__ void __launch_bounds__(kThreads2) product2_kernel(ProductArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int64_t j = int64_t(blockIdx.x) * kThreads2 + threadIdx.x;
+    if (j >= a.m) return;
+    Table2 tab(smem, threadIdx.x);
+    if (!product2_column<Table2, kThreads2>(a, j, tab)) {
+        a.w_cnt[j] = 0;
+        a.overflow[atomicAdd(a.flags + 1, 1)] = int32_t(j);
     }
-    SlotList list{idx, val, 0};
-    for (int32_t e = rb; e < re; ++e) {
-        const int2 loc = __ldg(a.t_loc + __ldg(a.r_col + e));
-        const double w = __ldg(a.r_val + e);
-        for (int32_t s = 0; s < loc.y; ++s) list.add(a.t_idx[loc.x + s], a.t_val[loc.x + s] * w);
+}
+// second pass over the queued columns: a large table, and the list in global memory behind it
+__global__ void __launch_bounds__(kThreads2b) product2_overflow_kernel(ProductArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int32_t queued = a.flags[1];
+    Table2b tab(smem, threadIdx.x);
+    for (int64_t o = int64_t(blockIdx.x) * kThreads2b + threadIdx.x; o < queued; o += int64_t(gridDim.x) * kThreads2b) {
+        const int64_t j = a.overflow[o];
+        if (product2_column<Table2b, kThreads2b>(a, j, tab)) continue;
+        int32_t* idx = a.w_idx + __ldg(a.w_ptr + j);
+        double* val = a.w_val + __ldg(a.w_ptr + j);
+        SlotList list{idx, val, 0};
+        for (int32_t e = __ldg(a.r_ptr + j); e < __ldg(a.r_ptr + j + 1); ++e) {
+            const int2 loc = __ldg(a.t_loc + __ldg(a.r_col + e));
+            const double w = __ldg(a.r_val + e);
+            for (int32_t s = 0; s < loc.y; ++s) list.add(a.t_idx[loc.x + s], a.t_val[loc.x + s] * w);
+        }
+        list.sort();
+        a.w_cnt[j] = list.count;
+        atomicAdd(a.flags, 1);
     }
-    list.sort();
-    a.w_cnt[j] = list.count;
-    atomicAdd(a.flags, 1);
 }
 
 // the slots of A_c into its final arrays: 8 lanes per column
@@ -429,14 +454,14 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
         needed.zero();
         if (R.nnz > 0) GMG_LAUNCH(c, mark_needed_kernel, div_up(R.nnz, kBlock), kBlock, 0, R.nnz, R.colidx.p, needed.p);
     }
-    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), flags(c, 1);
+    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), flags(c, 2), overflow(c, m);
     DevBuf<int2> t_loc(c, n);
     DevBuf<int32_t> ub2(c, int64_t(m) + 1), w_ptr(c, int64_t(m) + 1), w_cnt(c, int64_t(m) + 1);
     DevBuf<int64_t> totals(c, 3);
     flags.zero();
     ProductArgs a{n, m, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p, R.rowptr.p, R.colidx.p, R.val.p,
                   all ? nullptr : needed.p, ub1.p, t_ptr.p, t_loc.p, nullptr, nullptr, ub2.p, w_ptr.p, w_cnt.p, nullptr, nullptr,
-                  nullptr, nullptr, nullptr, flags.p};
+                  nullptr, nullptr, nullptr, flags.p, overflow.p};
     // ---- first product
     int64_t h_total[3] = {0, 0, 0};
     GMG_LAUNCH(c, product1_bound_kernel, div_up(int64_t(n) + 1, kBlock), kBlock, 0, a);
@@ -463,14 +488,16 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     GMG_CUDA(cudaMemsetAsync(w_cnt.p + m, 0, sizeof(int32_t), c->stream));
     GMG_CUDA(cudaFuncSetAttribute(product2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Table2::bytes())));
     GMG_LAUNCH(c, product2_kernel, div_up(m, kThreads2), kThreads2, Table2::bytes(), a);
+    GMG_CUDA(cudaFuncSetAttribute(product2_overflow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Table2b::bytes())));
+    GMG_LAUNCH(c, product2_overflow_kernel, 4 * c->sm_count, kThreads2b, Table2b::bytes(), a);
     exclusive_scan_i32(c, w_cnt.p, Ac.colptr.p, int64_t(m) + 1, totals.p + 2);
     totals.download(h_total, 3);
-    int32_t slow = 0;
-    flags.download(&slow, 1);
+    int32_t slow[2] = {0, 0};
+    flags.download(slow, 2);
     sync(c);
     Ac.nnz = h_total[2];
-    if (getenv("GMG_TRACE")) fprintf(stderr, "[gmg] galerkin: n %d, %d outer vectors, %lld entries of T, %lld of A_c, %d vectors on the slow path\n",
-                                     n, m, (long long)h_total[0], (long long)Ac.nnz, slow);
+    if (getenv("GMG_TRACE")) fprintf(stderr, "[gmg] galerkin: n %d, %d outer vectors, %lld entries of T, %lld of A_c, %d columns of A_c took the large table, %d vectors the list\n",
+                                     n, m, (long long)h_total[0], (long long)Ac.nnz, slow[1], slow[0]);
     Ac.rowidx.alloc(c, Ac.nnz);
     Ac.val.alloc(c, Ac.nnz);
     a.out_ptr = Ac.colptr.p; a.out_idx = Ac.rowidx.p; a.out_val = Ac.val.p;

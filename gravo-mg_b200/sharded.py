@@ -200,13 +200,52 @@ class ShardRank:
     __del__ = close
 
 
+class NativeComm:
+    """The library's own NCCL communicator (csrc/shard_nccl.cu): gmg_shard_build_nccl runs the whole driver loop in
+    C++ and issues ncclAllGather itself. The unique id travels through torch.distributed once, at set-up."""
+
+    def __init__(self, ctx, group=None):
+        import torch.distributed as dist
+        lib = ctx.lib
+        self.ctx = ctx
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        lib.gmg_nccl_unique_id.argtypes = [C.c_void_p]
+        lib.gmg_nccl_init.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        lib.gmg_nccl_destroy.argtypes = [C.c_void_p]
+        lib.gmg_nccl_destroy.restype = None
+        lib.gmg_shard_build_nccl.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int64)]
+        buf = C.create_string_buffer(128)
+        if self.rank == 0:
+            rc = lib.gmg_nccl_unique_id(buf)
+            if rc != 0:
+                raise GmgError(rc, "gmg_nccl_unique_id: libnccl.so.2 could not be opened")
+        box = [bytes(buf.raw) if self.rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=group)
+        self._id = C.create_string_buffer(box[0], 128)
+        h = C.c_void_p()
+        ctx._check(lib.gmg_nccl_init(ctx.h, self._id, self.rank, self.world, C.byref(h)))
+        self.h = h
+
+    def build(self, shard, build_galerkin):
+        stats = (C.c_int64 * 2)()
+        self.ctx._check(self.ctx.lib.gmg_shard_build_nccl(self.ctx.h, shard.h, self.h, 1 if build_galerkin else 0, stats))
+        return int(stats[0]), int(stats[1])
+
+    def close(self):
+        if getattr(self, "h", None) and getattr(self.ctx, "h", None):
+            self.ctx.lib.gmg_nccl_destroy(self.h)
+        self.h = None
+
+    __del__ = close
+
+
 class ShardedHierarchy:
     """Row-sharded build. `ranks` is the list of ranks THIS process runs: one (its torch.distributed rank)
     in production, all of them as virtual ranks with comm=None (loop-back on one GPU) in the tests."""
 
     def __init__(self, ctx, inp, levels, world, ranks, comm=None, ratio=8.0,
                  weighting=capi.BARYCENTRIC, sampler_mode=capi.SAMPLER_HASHED, seed=0, radius_policy=0,
-                 radius_override=None, device=None, profile=False, build_galerkin=False):
+                 radius_override=None, device=None, profile=False, build_galerkin=False, native=None):
         import torch
         self.torch = torch
         self.ctx, self.world, self.comm = ctx, world, comm
@@ -236,7 +275,14 @@ class ShardedHierarchy:
         self.profile = {} if profile else None          # name -> [event pairs]; see phase_ms()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        self._build()
+        if native is not None:                  # the C++ driver: one call, NCCL issued by the library itself
+            if len(ranks) != 1 or profile:
+                raise ValueError("the native driver runs one rank per process and has no per-phase profile")
+            ex, by = native.build(self.shards[0], self.build_galerkin)
+            self.exchanges, self.exchange_bytes = ex - getattr(native, "_seen_ex", 0), by - getattr(native, "_seen_by", 0)
+            native._seen_ex, native._seen_by = ex, by
+        else:
+            self._build()
         ev1.record()
         torch.cuda.synchronize()
         self.build_ms = ev0.elapsed_time(ev1)

@@ -337,6 +337,15 @@ int gmg_shard_buffer(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, i
 /* ROWS_ID, ROWS_VAL, P_COL, P_VAL have slices of different sizes (packed rows): the buffer is the final
  * row-major array itself and rank r owns elements [offsets[r], offsets[r + 1]) (world + 1 entries). */
 int gmg_shard_buffer_v(gmg_shard* s, int which, void** ptr, int32_t* elem_bytes, int64_t* offsets);
+/* The same driver loop in ONE call, exchanges as ncclAllGather on the context's stream (csrc/shard_nccl.cu). NCCL is
+ * opened at run time (libnccl.so.2), not linked. The communicator is the library's own: rank 0 asks for a unique id
+ * (128 bytes), the caller hands it to every rank by any means, every rank calls gmg_nccl_init.
+ * stats (optional, 2 entries): exchanges issued, bytes gathered (summed over the ranks' slices). */
+typedef struct gmg_nccl gmg_nccl;
+int gmg_nccl_unique_id(void* out128);
+int gmg_nccl_init(gmg_ctx* ctx, const void* id128, int rank, int world, gmg_nccl** out);
+void gmg_nccl_destroy(gmg_nccl* comm);
+int gmg_shard_build_nccl(gmg_ctx* ctx, gmg_shard* s, gmg_nccl* comm, int build_galerkin, int64_t* stats);
 int gmg_shard_num_levels(const gmg_shard* s);
 int gmg_shard_level_info(const gmg_shard* s, int level, gmg_level_info* out, int64_t* row_lo, int64_t* row_hi);
 /* array ids of gmg_hierarchy_array; replicated arrays are complete on every rank, the P arrays hold

@@ -18,7 +18,7 @@ sys.path.insert(0, ROOT)
 import torch
 import torch.distributed as dist
 from gravomg_b200 import capi, meshgen
-from gravomg_b200.sharded import ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
+from gravomg_b200.sharded import NativeComm, ShardedHierarchy, ShardedSolver, TorchComm, upload_sharded
 
 name = sys.argv[1] if len(sys.argv) > 1 else "C3"
 scale = float(sys.argv[2]) if len(sys.argv) > 2 else 0.05
@@ -32,9 +32,11 @@ cfg = meshgen.make_config(name, scale)
 V, A = cfg["V"], cfg["A"]
 inp = capi.Input(ctx, V, A.indptr, A.indices, None)
 bad = 0
-for mode in (capi.SAMPLER_HASHED, capi.SAMPLER_EXACT) if name != "C3" else (capi.SAMPLER_HASHED,):
+native = NativeComm(ctx)          # the library's own NCCL communicator: the C++ driver (gmg_shard_build_nccl)
+for mode, nat in [(m, d) for m in ((capi.SAMPLER_HASHED, capi.SAMPLER_EXACT) if name != "C3" else (capi.SAMPLER_HASHED,))
+                  for d in (None, native)]:
     single = capi.Hierarchy(ctx, inp, cfg["levels"], sampler_mode=mode, seed=3)
-    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=mode, seed=3)
+    sh = ShardedHierarchy(ctx, inp, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=mode, seed=3, native=nat)
     assert sh.same_stream
     assert sh.num_levels == single.num_levels
     for lvl in range(single.num_levels):
@@ -52,7 +54,7 @@ for mode in (capi.SAMPLER_HASHED, capi.SAMPLER_EXACT) if name != "C3" else (capi
                 and np.array_equal(sh.fetch(lvl, capi.H_P_VAL), w["pva"][b:e])):
             bad += 1
             print(f"rank {rank} mode {mode} level {lvl}: P rows [{lo},{hi}) differ", flush=True)
-    print(f"rank {rank}/{world} mode {mode}: {single.num_levels} levels, n={V.shape[0]}, exchanges {sh.exchanges}, "
+    print(f"rank {rank}/{world} mode {mode} driver {'c++/nccl' if nat else 'python/torch'}: {single.num_levels} levels, n={V.shape[0]}, exchanges {sh.exchanges}, "
           f"sharded {sh.build_ms:.2f} ms vs single {single.build_ms:.2f} ms, mismatches so far {bad}", flush=True)
     sh.close(); single.close()
 # Galerkin operators and the V-cycle, on an input uploaded slice by slice and completed over NVLink
@@ -65,7 +67,7 @@ if not (np.array_equal(pts_d, V) and np.array_equal(cp_d, A.indptr) and np.array
 print(f"rank {rank}: sharded upload copied {h2d / 1e6:.1f} MB of {(V.nbytes + A.indptr.nbytes + A.indices.nbytes + A.data.nbytes) / 1e6:.1f} MB from the host", flush=True)
 single = capi.Hierarchy(ctx, inp_a, cfg["levels"], sampler_mode=capi.SAMPLER_HASHED, seed=3, build_galerkin=True)
 sh = ShardedHierarchy(ctx, inp_a, cfg["levels"], world, [rank], comm=TorchComm(), sampler_mode=capi.SAMPLER_HASHED, seed=3,
-                      build_galerkin=True)
+                      build_galerkin=True, native=native)
 for lvl in range(single.num_levels):
     want, got = single.galerkin(lvl), sh.galerkin(lvl)
     if not (np.array_equal(got.indptr, want.indptr) and np.array_equal(got.indices, want.indices)
