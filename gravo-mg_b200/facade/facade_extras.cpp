@@ -112,4 +112,36 @@ std::vector<HierarchyLevel> buildHierarchy(const PointMatrix& points, const Edge
     return out;
 }
 
+namespace {
+EdgeMatrix graph_from_input(gmg_ctx* c, gmg_input* in, bool with_values) {
+    int64_t n = 0, nnz = 0;
+    must(gmg_input_size(in, &n, &nnz), c, "gmg_input_size");
+    std::vector<int> outer(size_t(n) + 1), inner(static_cast<size_t>(nnz));
+    std::vector<double> val(static_cast<size_t>(nnz), 1.0);
+    must(gmg_input_fetch(c, in, 1, outer.data()), c, "fetch colptr");
+    must(gmg_input_fetch(c, in, 2, inner.data()), c, "fetch rowidx");
+    if (with_values) must(gmg_input_fetch(c, in, 3, val.data()), c, "fetch values");
+    return sparse_from<EdgeMatrix>(Index(n), Index(n), outer, inner, val);
+}
+}  // namespace
+
+EdgeMatrix knnGraph(const PointMatrix& points, int k) {
+    gmg_ctx* c = nullptr;
+    must(gmg_create(0, nullptr, &c), nullptr, "gmg_create");
+    struct Ctx { gmg_ctx* c; ~Ctx() { gmg_destroy(c); } } guard{c};
+    InputHandle in;
+    must(gmg_input_from_knn(c, points.rows(), points.data(), points.rows(), k, &in.h), c, "gmg_input_from_knn");
+    return graph_from_input(c, in.h, false);
+}
+
+EdgeMatrix cotangentLaplacian(const PointMatrix& points, const std::vector<int>& faces, double mass_shift) {
+    gmg_ctx* c = nullptr;
+    must(gmg_create(0, nullptr, &c), nullptr, "gmg_create");
+    struct Ctx { gmg_ctx* c; ~Ctx() { gmg_destroy(c); } } guard{c};
+    InputHandle in;
+    must(gmg_input_from_mesh(c, points.rows(), points.data(), points.rows(), int64_t(faces.size() / 3), faces.data(), mass_shift,
+                             &in.h), c, "gmg_input_from_mesh");
+    return graph_from_input(c, in.h, true);
+}
+
 }  // namespace GravoMG

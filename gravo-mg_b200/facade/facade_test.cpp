@@ -91,6 +91,9 @@ int main(int argc, char** argv) {
         int64_t nl = int64_t(H.size());
         write_rec(out, &nl, 1);
         for (auto& lv : H) { write_rec(out, &lv.radius, 1); write_sparse(out, lv.P); write_sparse(out, lv.A_coarse); }
+        // the device kNN builder through the facade: written out for the test to compare with the host kd-tree graph
+        auto G = GravoMG::knnGraph(p0, 8);
+        write_sparse(out, G);
     } catch (const GravoMG::B200Error& e) {
         std::fprintf(stderr, "B200Error %d: %s\n", e.status(), e.what());
         return 1;

@@ -116,4 +116,12 @@ struct HierarchyLevel {
 std::vector<HierarchyLevel> buildHierarchy(const PointMatrix& points, const EdgeMatrix& A,
                                            const HierarchyOptions& options = {});
 
+// Level-0 graphs built on the device from raw geometry (gmg_input_from_knn / gmg_input_from_mesh; what the
+// reference's driver gets from an external buildPointCloudLaplacian or a mesh loader, test/main.cpp:68).
+// knnGraph: exact k nearest neighbours, union-symmetrised, plus the diagonal, all stored values 1.
+// cotangentLaplacian: faces is an nf x 3 row-major index array; adjacency + diagonal pattern, cotangent weights
+// + mass_shift * lumped mass.
+EdgeMatrix knnGraph(const PointMatrix& points, int k);
+EdgeMatrix cotangentLaplacian(const PointMatrix& points, const std::vector<int>& faces, double mass_shift = 0.0);
+
 }  // namespace GravoMG

@@ -79,3 +79,8 @@ def test_facade_program_matches_reference(tmp_path, ctx, name):
             Ac = h.galerkin(lvl)
             assert np.array_equal(_read(f, np.int32), Ac.indptr) and np.array_equal(_read(f, np.int32), Ac.indices)
             assert np.allclose(_read(f, np.float64), Ac.data, rtol=1e-12, atol=1e-12 * np.abs(Ac.data).max())
+        # GravoMG::knnGraph (gmg_input_from_knn through the facade) == the host kd-tree graph
+        from gravomg_b200 import meshgen
+        G = meshgen.knn_graph(np.asfortranarray(V), 8)
+        assert np.array_equal(_read(f, np.int32), G.indptr) and np.array_equal(_read(f, np.int32), G.indices)
+        assert np.array_equal(_read(f, np.float64), np.ones(G.nnz))
