@@ -434,13 +434,18 @@ def run_b200(a, rank, world, local_rank):
         return pin_out[key]
 
     def step_e2e():
-        i2 = Input(ctx, hV, hcp, hri, hav if a.galerkin else None)
+        # A's values are needed at the first Galerkin product only: they travel on the copy stream while the build runs
+        i2 = Input(ctx, hV, hcp, hri, hav if a.galerkin else None, defer_values=True)
         # every level's P (and A_c) leaves the device on the copy stream as soon as the level is complete, while the
         # next level builds; the step ends when the last copy has landed in the pinned result buffers
         def stream_out(lvl, info):
             nl, nzp, m, nzac = info["n"], info["nnz_p"], info["m"], info["nnz_ac"]
-            want = [(capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32), (capi.H_P_VAL, nzp, np.float64)]
-            if a.galerkin:
+            want = []
+            # with A_c the library calls twice per level: P as soon as it is complete (it travels while A_c is formed),
+            # A_c when the level is done
+            if info["p_ready_only"] or not a.galerkin:
+                want += [(capi.H_P_ROWPTR, nl + 1, np.int32), (capi.H_P_COLIDX, nzp, np.int32), (capi.H_P_VAL, nzp, np.float64)]
+            if a.galerkin and not info["p_ready_only"]:
                 want += [(capi.H_AC_COLPTR, m + 1, np.int32), (capi.H_AC_ROWIDX, nzac, np.int32), (capi.H_AC_VAL, nzac, np.float64)]
             return [(which, pinned_out((lvl, which), cnt, dt)[:cnt]) for which, cnt, dt in want]
         h = Hierarchy(ctx, i2, levels, sampler_mode=mode, build_galerkin=bool(a.galerkin), stream_out=stream_out)

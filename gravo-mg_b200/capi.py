@@ -24,6 +24,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgravomg_b200.so")
 
 BARYCENTRIC, UNIFORM, INVDIST = 0, 1, 2
+NESTED = 0x100          # OR-ed into a weighting (include/gravomg_b200.h GMG_NESTED)
+LEVEL_P_READY = 0x40000000
 SAMPLER_EXACT, SAMPLER_PARALLEL, SAMPLER_HASHED = 0, 1, 2
 
 STATUS_NAMES = {0: "GMG_OK", 1: "GMG_ERR_CUDA", 2: "GMG_ERR_INVALID", 3: "GMG_ERR_FALLBACK_RATIO",
@@ -165,6 +167,31 @@ class Context:
                                                      _p(edges, _i32p), C.byref(out)))
         return out.value
 
+    def fast_disc_sample_bounded(self, points, colptr, rowidx, radius, min_selection=0, max_selection=2 ** 62,
+                                 mode=SAMPLER_EXACT, seed=42):
+        """(selection, radius used): fastDiscSample with the min/max bounds of src/sampling.cpp:11-12."""
+        pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
+        n = pts.shape[0]
+        sel = np.empty(max(n, 1), dtype=np.int64)
+        m, used = C.c_int64(), C.c_double()
+        self.lib.gmg_fast_disc_sample_bounded.argtypes = [C.c_void_p, C.c_int64, _f64p, C.c_int64, _i32p, _i32p, C.c_double,
+                                                          C.c_int64, C.c_int64, C.c_int, C.c_uint64, _i64p,
+                                                          C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+        self._check(self.lib.gmg_fast_disc_sample_bounded(self.h, n, _p(pts, _f64p), n, _p(colptr, _i32p), _p(rowidx, _i32p),
+                                                          float(radius), int(min_selection), int(max_selection), int(mode),
+                                                          int(seed), _p(sel, _i64p), C.byref(m), C.byref(used)))
+        return sel[:m.value].copy(), used.value
+
+    def coarse_from_samples(self, points, samples):
+        """Nested mode: the coarse points are the samples' positions (gmg_coarse_from_samples)."""
+        pts = _pts(points)
+        s = np.ascontiguousarray(samples, dtype=np.int64)
+        out = np.empty((s.shape[0], 3), dtype=np.float64, order="F")
+        self.lib.gmg_coarse_from_samples.argtypes = [C.c_void_p, C.c_int64, _f64p, C.c_int64, C.c_int64, _i64p, _f64p, C.c_int64]
+        self._check(self.lib.gmg_coarse_from_samples(self.h, pts.shape[0], _p(pts, _f64p), pts.shape[0], s.shape[0],
+                                                     _p(s, _i64p), _p(out, _f64p), max(s.shape[0], 1)))
+        return out
+
     def morton_order(self, points):
         """Permutation sorting the points along the Morton curve of their bounding cube (gmg_morton_order)."""
         pts = _pts(points)
@@ -299,7 +326,9 @@ STAGE_NAMES = ["edge_lengths", "sampling", "parents", "cluster_csr", "coarse_edg
 class Input:
     """A level-0 problem resident in HBM (points + the pattern of A, optionally A's values)."""
 
-    def __init__(self, ctx, points, colptr, rowidx, a_val=None):
+    def __init__(self, ctx, points, colptr, rowidx, a_val=None, defer_values=False):
+        """defer_values: copy A's values on the copy stream after the call has returned (gmg_input_set_values_async);
+        a_val must then stay alive (and should be pinned) until a call that uses the values has returned."""
         self.ctx = ctx
         pts, colptr, rowidx = _pts(points), _i32(colptr), _i32(rowidx)
         self.n, self.nnz = pts.shape[0], rowidx.shape[0]
@@ -307,8 +336,12 @@ class Input:
         h = C.c_void_p()
         ctx._check(ctx.lib.gmg_input_create(ctx.h, C.c_int64(self.n), _p(pts, _f64p), C.c_int64(self.n),
                                             _p(colptr, _i32p), _p(rowidx, _i32p),
-                                            _p(a, _f64p) if a is not None else None, C.byref(h)))
+                                            _p(a, _f64p) if a is not None and not defer_values else None, C.byref(h)))
         self.h = h
+        if a is not None and defer_values:
+            self._values = a                      # keeps the host array alive
+            ctx.lib.gmg_input_set_values_async.argtypes = [C.c_void_p, C.c_void_p, _f64p]
+            ctx._check(ctx.lib.gmg_input_set_values_async(ctx.h, h, _p(a, _f64p)))
         self.h2d_bytes = pts.nbytes + colptr.nbytes + rowidx.nbytes + (a.nbytes if a is not None else 0)
 
     @classmethod
@@ -445,10 +478,16 @@ class Hierarchy:
             lib.gmg_hierarchy_fetch_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
 
             def on_level(_user, hptr, level):
+                # with build_galerkin the library calls twice per level: (level | LEVEL_P_READY) when P is complete,
+                # then the plain level when A_c is; stream_out sees info["p_ready_only"] = True on the first call
+                early = bool(level & LEVEL_P_READY)
+                level &= ~LEVEL_P_READY
                 li = LevelInfo()
                 if lib.gmg_hierarchy_level_info(hptr, level, C.byref(li)) != 0:
                     return
-                for which, out in stream_out(level, li.as_dict()):
+                info = li.as_dict()
+                info["p_ready_only"] = early
+                for which, out in stream_out(level, info):
                     if lib.gmg_hierarchy_fetch_async(ctx.h, hptr, level, which, out.ctypes.data_as(C.c_void_p)) == 0:
                         self.streamed_bytes += out.nbytes
             self._cb = LEVEL_CALLBACK(on_level)          # keep the trampoline alive for the duration of the build

@@ -222,6 +222,56 @@ int gmg_fast_disc_sample(gmg_ctx* c, int64_t n, const double* points, int64_t ld
     });
 }
 
+/* fastDiscSample with the selection bounds the reference marks as a todo (src/sampling.cpp:11-12) */
+int gmg_fast_disc_sample_bounded(gmg_ctx* c, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                                 const int32_t* rowidx, double radius, int64_t min_selection, int64_t max_selection, int mode,
+                                 uint64_t seed, int64_t* selection_out, int64_t* m_out, double* radius_used) {
+    return guarded(c, [&] {
+        int64_t nnz; check_sizes(n, colptr, nnz);
+        GMG_REQUIRE(min_selection >= 0 && max_selection >= 0 && selection_out && m_out, GMG_ERR_INVALID, "fastDiscSample: bad bounds");
+        auto d_cp = to_device(c, colptr, n + 1); auto d_ri = to_device(c, rowidx, nnz);
+        auto d_pts = points_to_device(c, points, n, ld);
+        DevBuf<double> d_len(c, nnz);
+        check_pattern(c, int32_t(n), d_cp.p, d_ri.p, true);
+        KernelTimer t(c);
+        edge_lengths(c, int32_t(n), d_cp.p, d_ri.p, d_pts.p, d_len.p);
+        DevBuf<int32_t> sel;
+        int32_t m = 0;
+        // too few samples: halve the radius and sample again (the lengths are computed once)
+        for (int pass = 0; pass < 64; ++pass) {
+            m = disc_sample(c, int32_t(n), d_cp.p, d_ri.p, d_len.p, radius, mode, seed, sel, nullptr);
+            if (m >= min_selection || m >= n) break;
+            radius = radius / 2;
+        }
+        // too many: the greedy loop would have stopped selecting = the head of the ascending selection
+        if (m > max_selection) m = int32_t(max_selection);
+        DevBuf<int64_t> wide(c, m);
+        widen_i32(c, sel.p, wide.p, m);
+        t.stop();
+        wide.download(selection_out, m);
+        sync(c);
+        *m_out = m;
+        if (radius_used) *radius_used = radius;
+    });
+}
+
+/* nested mode: the coarse points are the samples' positions */
+int gmg_coarse_from_samples(gmg_ctx* c, int64_t n, const double* points, int64_t ld, int64_t m, const int64_t* samples,
+                            double* out_points, int64_t out_ld) {
+    return guarded(c, [&] {
+        GMG_REQUIRE(n >= 0 && n < (int64_t(1) << 31) && m >= 0 && m <= n && points && out_points && ld >= n && out_ld >= m,
+                    GMG_ERR_INVALID, "coarseFromSamples: bad sizes");
+        auto d_pts = points_to_device(c, points, n, ld);
+        auto d_s = indices_to_device(c, samples, m, n, "coarseFromSamples: coarse_samples");
+        DevBuf<double> d_out(c, 3 * m);
+        KernelTimer t(c);
+        sample_points(c, int32_t(n), d_pts.p, int32_t(m), d_s.p, d_out.p);
+        t.stop();
+        points_to_host(c, d_out.p, m, out_points, out_ld);
+        sync(c);
+    });
+}
+
 int gmg_assign_parents(gmg_ctx* c, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
                        const int32_t* rowidx, int64_t m, const int64_t* samples, int64_t* parents_out) {
     return guarded(c, [&] {

@@ -69,6 +69,28 @@ int gmg_input_create(gmg_ctx* c, int64_t n, const double* points, int64_t ld, co
     });
 }
 
+/* The values of A for an input created without them, copied on the context's COPY stream while the compute stream
+ * goes on: a hierarchy build only needs them when it reaches the first Galerkin product, so a 10 M-vertex build
+ * overlaps their 560 MB with sampling, parents and the rows of P. A_val (nnz doubles, pinned for a real overlap) must
+ * stay valid until a call that uses the values (gmg_hierarchy_build with build_galerkin, gmg_solver_create, ...) has
+ * returned, or gmg_copy_sync has. */
+int gmg_input_set_values_async(gmg_ctx* c, gmg_input* in, const double* A_val) {
+    return guarded_h(c, [&] {
+        GMG_REQUIRE(in && A_val, GMG_ERR_STATE, "null input or values");
+        GMG_REQUIRE(!in->has_a, GMG_ERR_STATE, "the input already has A values");
+        if (!c->copy_stream) GMG_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        in->a_val.alloc(c, in->nnz);
+        // the block comes from the compute stream's pool: the copy stream may touch it once that stream got this far
+        if (!in->a_ready) GMG_CUDA(cudaEventCreateWithFlags(&in->a_ready, cudaEventDisableTiming));
+        GMG_CUDA(cudaEventRecord(in->a_ready, c->stream));
+        GMG_CUDA(cudaStreamWaitEvent(c->copy_stream, in->a_ready, 0));
+        if (in->nnz > 0)
+            GMG_CUDA(cudaMemcpyAsync(in->a_val.p, A_val, sizeof(double) * size_t(in->nnz), cudaMemcpyHostToDevice, c->copy_stream));
+        GMG_CUDA(cudaEventRecord(in->a_ready, c->copy_stream));
+        in->has_a = true;
+    });
+}
+
 /* An input whose arrays the CALLER fills on the device (row-sharded upload: each rank copies its own slice from
  * the host and the slices are all-gathered over NVLink instead of every rank pulling the whole mesh over PCIe).
  * gmg_input_commit checks the pattern once the arrays are complete. */
@@ -152,7 +174,8 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
 
         for (int lvl = 0; lvl + 1 < opt->levels; ++lvl) {
             if (n == 0) break;
-            std::unique_ptr<Level> L(new Level());
+            std::unique_ptr<Level> Lown(new Level());
+            Level* const L = Lown.get();       // (the level moves into the hierarchy before its Galerkin product)
             L->info.n = n; L->info.nnz = nnz;
             StageClock clk(c);
             status.begin(c);
@@ -200,7 +223,8 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             clk.mark();
             // stage 5: coarseFromMeanOfFineChildren
             L->coarse_pts.alloc(c, 3 * int64_t(m));
-            coarse_points(c, n, pts, colptr, rowidx, m, cl, L->coarse_pts.p);
+            if (opt->weighting & GMG_NESTED) sample_points(c, n, pts, m, L->samples.p, L->coarse_pts.p);
+            else coarse_points(c, n, pts, colptr, rowidx, m, cl, L->coarse_pts.p);
             clk.mark();
             // stage 6: constructVoronoiTriangles
             voronoi_triangles(c, m, L->coarse.nnz, L->coarse_pts.p, L->coarse.colptr.p, L->coarse.rowidx.p, L->coarse.val.p,
@@ -219,9 +243,14 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             status.raise_parents();
             status.raise_coarse();
             status.raise_prolong(n);
+            // P is complete on the device (the status fetch synchronised): with a Galerkin product still to come, let the
+            // caller start copying P out now, so that it travels while A_c is formed
+            h->levels.push_back(std::move(Lown));
+            if (opt->build_galerkin && opt->on_level) opt->on_level(opt->user, h.get(), (int(h->levels.size()) - 1) | GMG_LEVEL_P_READY);
             // stage 8: Galerkin coarse operator
             StageClock gclk(c);
             if (opt->build_galerkin) {
+                if (h->levels.size() == 1) await_values(c, in);        // level 0 reads the input's values (maybe still arriving)
                 for (int s = 0; s < 4; ++s) { cudaEvent_t e; GMG_CUDA(cudaEventCreate(&e)); gclk.ev.push_back(e); }
                 galerkin(c, a_n, a_colptr, a_rowidx, a_val, L->P, L->Ac, 0, -1, nullptr, gclk.ev.data());
                 L->info.nnz_ac = L->Ac.nnz;
@@ -235,7 +264,6 @@ int gmg_hierarchy_build(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy_opt
             n = m; nnz = L->coarse.nnz;
             pts = L->coarse_pts.p; colptr = L->coarse.colptr.p; rowidx = L->coarse.rowidx.p; val = L->coarse.val.p;
             if (opt->build_galerkin) { a_n = m; a_colptr = L->Ac.colptr.p; a_rowidx = L->Ac.rowidx.p; a_val = L->Ac.val.p; }
-            h->levels.push_back(std::move(L));
             // the level is complete on the device (the status fetch above synchronised): let the caller start
             // copying it out on the copy stream while the next level builds
             if (opt->on_level) opt->on_level(opt->user, h.get(), int(h->levels.size()) - 1);

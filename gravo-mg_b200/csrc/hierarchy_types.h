@@ -16,7 +16,14 @@ struct gmg_input {
     DevBuf<int32_t> colptr, rowidx;
     DevBuf<double> a_val;
     bool has_a = false;
+    // gmg_input_set_values_async: the values are still on their way on the copy stream until this event has passed
+    cudaEvent_t a_ready = nullptr;
+    ~gmg_input() { if (a_ready) cudaEventDestroy(a_ready); }
 };
+// Whoever reads in->a_val on the context's stream calls this first.
+inline void await_values(gmg_ctx* c, const gmg_input* in) {
+    if (in && in->a_ready) GMG_CUDA(cudaStreamWaitEvent(c->stream, in->a_ready, 0));
+}
 
 struct Level {
     gmg_level_info info{};

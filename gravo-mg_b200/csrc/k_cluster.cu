@@ -393,4 +393,16 @@ void coarse_points(gmg_ctx* c, int32_t n, const double* pts, const int32_t* colp
                out_pts);
 }
 
+// nested mode: the coarse points are the samples' own positions
+__global__ void __launch_bounds__(kBlock) sample_points_kernel(int32_t n, const double* __restrict__ pts, int32_t m,
+                                                               const int32_t* __restrict__ samples, double* __restrict__ out) {
+    const int64_t P = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (P >= m) return;
+    const int32_t f = samples[P];
+    out[P] = pts[f]; out[m + P] = pts[n + f]; out[2 * int64_t(m) + P] = pts[2 * int64_t(n) + f];
+}
+void sample_points(gmg_ctx* c, int32_t n, const double* pts, int32_t m, const int32_t* samples, double* out_pts) {
+    if (m > 0) GMG_LAUNCH(c, sample_points_kernel, div_up(m, kBlock), kBlock, 0, n, pts, m, samples, out_pts);
+}
+
 }  // namespace gmg

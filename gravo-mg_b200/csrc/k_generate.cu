@@ -163,6 +163,7 @@ int gmg_input_fetch(gmg_ctx* c, const gmg_input* in, int which, void* host_out) 
         GMG_REQUIRE(in && host_out, GMG_ERR_STATE, "null input");
         GMG_REQUIRE(which >= 0 && which <= 3, GMG_ERR_INVALID, "unknown input array");
         GMG_REQUIRE(which != 3 || in->has_a, GMG_ERR_STATE, "input has no A values");
+        if (which == 3) await_values(c, in);
         const void* src = which == 0 ? (const void*)in->pts.p : which == 1 ? (const void*)in->colptr.p
                         : which == 2 ? (const void*)in->rowidx.p : (const void*)in->a_val.p;
         const size_t bytes = which == 0 ? sizeof(double) * 3 * size_t(in->n)

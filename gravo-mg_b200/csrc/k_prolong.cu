@@ -36,6 +36,7 @@ struct ProlongArgs {
     const int32_t* fan_o2;
     const double* normal;
     int weighting;
+    int nested;            // GMG_NESTED: a fine point that coincides with its parent's coarse point gets the row (parent, 1.0)
     int32_t* row_cnt;      // n (+1 for the scan)
     int32_t* row_col;      // 3n scratch
     double* row_val;       // 3n scratch
@@ -117,6 +118,11 @@ __global__ void __launch_bounds__(kBlock, 4) prolong_rows_kernel(ProlongArgs a, 
     const V3 p = ld3(a.fp, a.n, f), pc = ld3(a.cp, a.m, c);
     const int32_t cb = __ldg(a.c_colptr + c), ce = __ldg(a.c_colptr + c + 1);
     int32_t ids[3]; double w[3];
+    // "Exact matches get a weight of 1.0 (if in nested mode)" -- the reference's todo at :291-292
+    if (a.nested && p.x == pc.x && p.y == pc.y && p.z == pc.z) {
+        ids[0] = c; w[0] = 1.0; emit_row(a, f, ids, w, 1);
+        return;
+    }
     if (cb == ce) {                                                                       // :295-299
         ids[0] = c; w[0] = 1.0; emit_row(a, f, ids, w, 1);
         return;
@@ -241,6 +247,8 @@ void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, cons
                   const int32_t* c_colptr, const int32_t* c_rowidx, const int32_t* parents, const Triangles& tr,
                   int weighting, DeviceCsr& P, gmg_prolongation_stats* stats, StageStatus* status, int32_t f_lo,
                   int32_t f_hi) {
+    const int nested = (weighting & GMG_NESTED) ? 1 : 0;
+    weighting &= ~GMG_NESTED;
     GMG_REQUIRE(weighting >= 0 && weighting <= 2, GMG_ERR_INVALID, "unknown weighting scheme");
     if (f_hi < 0) { f_lo = 0; f_hi = n; }
     const int32_t n_all = n;                       // fine vertices of the level (stride of the point arrays)
@@ -256,7 +264,7 @@ void prolongation(gmg_ctx* c, int32_t n, const double* fine_pts, int32_t m, cons
     int64_t* total = reinterpret_cast<int64_t*>(st->dev.p + StageStatus::kProlongNnz);
     P.rowptr.zero();
     ProlongArgs a{f_lo, f_hi, n_all, m, fine_pts, coarse_pts, c_colptr, c_rowidx, parents, tr.fan_ptr.p, tr.fan_tri.p, tr.fan_o1.p,
-                  tr.fan_o2.p, tr.normal.p, weighting, P.rowptr.p, row_col.p, row_val.p, dstats};
+                  tr.fan_o2.p, tr.normal.p, weighting, nested, P.rowptr.p, row_col.p, row_val.p, dstats};
     if (n > 0) {
         DevBuf<int32_t> fallback(c, n);
         int32_t* fallback_count = st->dev.p + StageStatus::kProlongFallback;      // zeroed with the status block

@@ -162,7 +162,7 @@ struct SamplerArgs {
     unsigned long long* dbg;     // GMG_SAMPLER_DEBUG: 8 words per tile (timeline of the tile flow), else null
     uint32_t* trace;             // GMG_SAMPLER_TRACE: 4 words per rank (ns since t0: queued, popped, ext popped, ext done), else null
     const unsigned long long* trace_t0;
-    int fast_warps, group, xgroup, xsleep;   // tile flow shape (defaults kFastWarps, kGroup, kGroup, 64; GMG_FLOW_* env for tuning)
+    int fast_warps, group, xgroup, xsleep, claim;   // tile flow shape (defaults kFastWarps, kGroup, kGroup, 64; GMG_FLOW_* env for tuning)
     uint16_t* mbox;              // [tiles * kTile] tile flow: mailbox of every tile (rank offset | knocked-out << kTileLog), 0xFFFF = empty
 };
 
@@ -559,10 +559,26 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             //      lock step: look at the claimed slot, apply it if it is filled, claim the next.
             const int grp = a.group;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
-            int32_t slot = 0;
-            if (sub == 0) slot = atomicAdd(&s_ctr[2], 1);
-            slot = __shfl_sync(0xffffffffu, slot, lead);
-            while (__any_sync(0xffffffffu, slot < total)) {
+            int32_t slot = total;
+            if (!a.claim) {
+                if (sub == 0) slot = atomicAdd(&s_ctr[2], 1);
+                slot = __shfl_sync(0xffffffffu, slot, lead);
+            }
+            for (;;) {
+                if (!__any_sync(0xffffffffu, slot < total)) {
+                    if (!a.claim) break;
+                    // the warp holds nothing: take what is queued (a warp that is busy holds no claim on future
+                    // slots, so a rank that has just been decided goes to whichever warp is idle)
+                    const int32_t head = *(volatile int32_t*)&s_ctr[2];
+                    if (head >= total) break;
+                    const int32_t avail = *(volatile int32_t*)&s_ctr[1] - head;
+                    if (avail <= 0) continue;
+                    const int32_t want = avail < 32 / grp ? avail : 32 / grp;
+                    int32_t h = 0;
+                    if (lane == 0) h = atomicAdd(&s_ctr[2], want);
+                    h = __shfl_sync(0xffffffffu, h, 0);
+                    slot = lane / grp < want ? h + lane / grp : total;
+                }
                 const uint32_t e = slot < total ? uint32_t(*(volatile uint16_t*)(s_queue + slot)) : kEmpty;
                 if (e != kEmpty) {
                     const uint32_t v = e & uint32_t(kTile - 1);
@@ -603,7 +619,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                             const int32_t xs = atomicAdd(&s_ctr[4], 1);
                             *(volatile uint16_t*)(s_xqueue + xs) = uint16_t(e);
                         }
-                        slot = atomicAdd(&s_ctr[2], 1);
+                        slot = a.claim ? total : atomicAdd(&s_ctr[2], 1);
                     }
                 }
                 slot = __shfl_sync(0xffffffffu, slot, lead);
@@ -614,10 +630,24 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             const int grp = a.xgroup;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
             const int32_t total_x = *(volatile int32_t*)&s_ctr[3];
-            int32_t slot = 0;
-            if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
-            slot = __shfl_sync(0xffffffffu, slot, lead);
-            while (__any_sync(0xffffffffu, slot < total_x)) {
+            int32_t slot = total_x;
+            if (!a.claim) {
+                if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
+                slot = __shfl_sync(0xffffffffu, slot, lead);
+            }
+            for (;;) {
+                if (!__any_sync(0xffffffffu, slot < total_x)) {
+                    if (!a.claim) break;
+                    const int32_t head = *(volatile int32_t*)&s_ctr[5];
+                    if (head >= total_x) break;
+                    const int32_t avail = *(volatile int32_t*)&s_ctr[4] - head;
+                    if (avail <= 0) { if (a.xsleep) __nanosleep(a.xsleep); continue; }
+                    const int32_t want = avail < 32 / grp ? avail : 32 / grp;
+                    int32_t h = 0;
+                    if (lane == 0) h = atomicAdd(&s_ctr[5], want);
+                    h = __shfl_sync(0xffffffffu, h, 0);
+                    slot = lane / grp < want ? h + lane / grp : total_x;
+                }
                 const uint32_t e = slot < total_x ? uint32_t(*(volatile uint16_t*)(s_xqueue + slot)) : kEmpty;
                 // (sleeping: a spinning warp takes issue slots from the warps that walk the dependency chain)
                 if (!__any_sync(0xffffffffu, e != kEmpty)) { if (a.xsleep) __nanosleep(a.xsleep); continue; }
@@ -655,7 +685,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                         }
                     }
                     if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 3] = uint32_t(global_ns() - trace_t0);
-                    if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
+                    if (sub == 0) slot = a.claim ? total_x : atomicAdd(&s_ctr[5], 1);
                 }
                 slot = __shfl_sync(0xffffffffu, slot, lead);
             }
@@ -833,7 +863,7 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
                   reinterpret_cast<unsigned int*>(cursor.p + 2), ntiles, res.p,
                   reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, epochs.p,
                   mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr, trace.p, trace_t0.p, env_int("GMG_FLOW_FAST", kFastWarps), env_int("GMG_FLOW_GROUP", kGroup),
-                  env_int("GMG_FLOW_XGROUP", kGroup), env_int("GMG_FLOW_XSLEEP", 64), mbox.p};
+                  env_int("GMG_FLOW_XGROUP", kGroup), env_int("GMG_FLOW_XSLEEP", 64), env_int("GMG_FLOW_CLAIM", 0), mbox.p};
     if (trace_path) GMG_LAUNCH(c, stamp_kernel, 1, 1, 0, trace_t0.p);
     if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, ranks, flag.p);
     else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, ranks, flag.p);

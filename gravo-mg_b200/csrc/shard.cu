@@ -176,6 +176,7 @@ int gmg_shard_create(gmg_ctx* c, int rank, int world, const gmg_input* in, const
         // level 0 is a VIEW of the input (which must outlive the shard): the whole graph, on every rank
         s->n = in->n; s->nnz = in->nnz;
         s->pts = in->pts.p; s->colptr = in->colptr.p; s->rowidx = in->rowidx.p;
+        await_values(c, in);
         s->a_n = in->n; s->a_colptr = in->colptr.p; s->a_rowidx = in->rowidx.p; s->a_val = in->has_a ? in->a_val.p : nullptr;
         *out = s.release();
     });
@@ -291,7 +292,8 @@ int gmg_shard_phase(gmg_ctx* c, gmg_shard* s, int phase, int64_t* io) {
                 s->xQ = DevBuf<int32_t>(); s->xt = DevBuf<double>();
                 // replicated cheap stages
                 L.coarse_pts.alloc(c, 3 * int64_t(s->m));
-                coarse_points(c, s->n, s->pts, s->colptr, s->rowidx, s->m, s->clusters, L.coarse_pts.p);
+                if (s->opt.weighting & GMG_NESTED) sample_points(c, s->n, s->pts, s->m, s->samples.p, L.coarse_pts.p);
+                else coarse_points(c, s->n, s->pts, s->colptr, s->rowidx, s->m, s->clusters, L.coarse_pts.p);
                 // Triangle fans: only what the owned rows of P read. A fan of c lists every triangle that contains c,
                 // and a triangle is enumerated at its smallest vertex, which is c or a neighbour of c.
                 DevBuf<uint8_t> need_c(c, int64_t(s->m) + 1), need_v0(c, int64_t(s->m) + 1);

@@ -116,6 +116,7 @@ int gmg_shard_solver_create(gmg_ctx* c, const gmg_shard* sh, const gmg_input* in
     *out = nullptr;
     return guarded_v(c, [&] {
         GMG_REQUIRE(sh && in && in->has_a, GMG_ERR_INVALID, "solver needs a shard and an input with A values");
+        await_values(c, in);
         GMG_REQUIRE(!sh->done.empty() && sh->done[0]->Ac.colptr.p, GMG_ERR_STATE, "shard was built without the Galerkin operator");
         std::unique_ptr<gmg_shard_solver> s(new gmg_shard_solver());
         s->ctx = c; s->rank = sh->rank; s->world = sh->world;

@@ -115,6 +115,7 @@ int gmg_solver_create(gmg_ctx* c, const gmg_input* in, const gmg_hierarchy* h, g
     *out = nullptr;
     return guarded_s(c, [&] {
         GMG_REQUIRE(in && h && in->has_a, GMG_ERR_INVALID, "solver needs an input with A values");
+        await_values(c, in);
         std::unique_ptr<gmg_solver> s(new gmg_solver());
         s->ctx = c;
         const size_t nl = h->levels.size();

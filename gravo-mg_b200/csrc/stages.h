@@ -114,6 +114,7 @@ void coarse_rows_range(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32
                        CoarseRows& out, int32_t* d_hard_overflow);
 void coarse_assemble(gmg_ctx* c, int32_t m, const int32_t* boff, const int32_t* cnt, const int32_t* sQ, const double* st,
                      DeviceCsc& out, int32_t* d_asym);
+void sample_points(gmg_ctx* c, int32_t n, const double* pts, int32_t m, const int32_t* samples, double* out_pts);   // nested mode
 void coarse_points(gmg_ctx* c, int32_t n, const double* pts, const int32_t* colptr, const int32_t* rowidx, int32_t m,
                    const Clusters& cl, double* out_pts);
 

@@ -74,7 +74,7 @@ std::vector<HierarchyLevel> buildHierarchy(const PointMatrix& points, const Edge
     must(gmg_input_create(c, points.rows(), points.data(), points.rows(), A.outerIndexPtr(), A.innerIndexPtr(),
                           o.galerkin ? A.valuePtr() : nullptr, &in.h), c, "gmg_input_create");
     gmg_hierarchy_options opt{};
-    opt.levels = o.levels; opt.ratio = o.ratio; opt.weighting = int(o.weighting);
+    opt.levels = o.levels; opt.ratio = o.ratio; opt.weighting = int(o.weighting) | (o.nested ? GMG_NESTED : 0);
     opt.sampler_mode = o.parallel_sampler ? GMG_SAMPLER_PARALLEL : GMG_SAMPLER_EXACT;
     opt.seed = 42; opt.radius_policy = 0; opt.radius_override = nullptr; opt.build_galerkin = o.galerkin ? 1 : 0;
     HierarchyHandle h;

@@ -109,6 +109,20 @@ std::vector<Index> fastDiscSample(const Eigen::MatrixXd& pos, const Eigen::Spars
     return sel;
 }
 
+std::vector<Index> fastDiscSample(const Eigen::MatrixXd& pos, const Eigen::SparseMatrix<double>& edge_matrix,
+                                  const double& radius, std::size_t min_selection, std::size_t max_selection) {
+    Compressed<EdgeMatrix> m(edge_matrix);
+    std::vector<Index> sel(size_t(std::max<Index>(pos.rows(), 1)));
+    int64_t count = 0;
+    const auto clamp = [](std::size_t v) { return int64_t(std::min<std::size_t>(v, std::size_t(1) << 62)); };
+    check(gmg_fast_disc_sample_bounded(context(), pos.rows(), pos.data(), pos.rows(), m.outer(), m.inner(), radius,
+                                       clamp(min_selection), clamp(max_selection), GMG_SAMPLER_EXACT, 0,
+                                       reinterpret_cast<int64_t*>(sel.data()), &count, nullptr),
+          "fastDiscSample");
+    sel.resize(size_t(count));
+    return sel;
+}
+
 std::vector<Index> assignParents(const Eigen::MatrixXd& fine_points, const EdgeMatrix& fine_edge_matrix,
                                  const std::vector<Index>& coarse_samples) {
     Compressed<EdgeMatrix> m(fine_edge_matrix);
@@ -183,6 +197,22 @@ ProlongationOperator constructProlongation(const PointMatrix& fine_points, const
                                            const EdgeMatrix& coarse_edge_matrix,
                                            const std::vector<Index>& fine_to_nearest_coarse,
                                            Weighting weighting_scheme) {
+    return constructProlongation(fine_points, coarse_points, coarse_edge_matrix, fine_to_nearest_coarse, weighting_scheme, false);
+}
+
+PointMatrix coarseFromSamples(const PointMatrix& fine_points, const std::vector<Index>& coarse_samples) {
+    PointMatrix out(Index(coarse_samples.size()), Index(3));
+    check(gmg_coarse_from_samples(context(), fine_points.rows(), fine_points.data(), fine_points.rows(),
+                                  int64_t(coarse_samples.size()), reinterpret_cast<const int64_t*>(coarse_samples.data()),
+                                  out.data(), std::max<Index>(out.rows(), 1)),
+          "coarseFromSamples");
+    return out;
+}
+
+ProlongationOperator constructProlongation(const PointMatrix& fine_points, const PointMatrix& coarse_points,
+                                           const EdgeMatrix& coarse_edge_matrix,
+                                           const std::vector<Index>& fine_to_nearest_coarse,
+                                           Weighting weighting_scheme, bool nested) {
     Compressed<EdgeMatrix> m(coarse_edge_matrix);
     const Index n = fine_points.rows(), mc = coarse_points.rows();
     std::vector<int> rowptr(size_t(n) + 1);
@@ -191,7 +221,7 @@ ProlongationOperator constructProlongation(const PointMatrix& fine_points, const
     check(gmg_construct_prolongation(context(), n, fine_points.data(), fine_points.rows(), mc, coarse_points.data(),
                                      std::max<Index>(coarse_points.rows(), 1), m.outer(), m.inner(), m.values(),
                                      reinterpret_cast<const int64_t*>(fine_to_nearest_coarse.data()),
-                                     int(weighting_scheme), rowptr.data(), &nnz, &stats),
+                                     int(weighting_scheme) | (nested ? GMG_NESTED : 0), rowptr.data(), &nnz, &stats),
           "constructProlongation");
     std::vector<int> colidx(static_cast<size_t>(nnz));
     std::vector<double> val(static_cast<size_t>(nnz));

@@ -64,6 +64,10 @@ std::pair<EdgeList, Eigen::VectorXd> extractEdges(const EdgeMatrix& matrix);
 // ---- sampling.h --------------------------------------------------------------------------------
 std::vector<Index> fastDiscSample(const Eigen::MatrixXd& pos, const Eigen::SparseMatrix<double>& edge_matrix,
                                   const double& radius);
+// the signature the reference leaves commented out (src/sampling.cpp:11-12): fewer than min_selection samples ->
+// the radius is halved and the sampling repeated; more than max_selection -> the loop stops selecting there
+std::vector<Index> fastDiscSample(const Eigen::MatrixXd& pos, const Eigen::SparseMatrix<double>& edge_matrix,
+                                  const double& radius, std::size_t min_selection, std::size_t max_selection);
 
 // ---- multigrid.h -------------------------------------------------------------------------------
 // Host-side helpers, kept for API completeness (the device path has its own copies).
@@ -93,6 +97,13 @@ ProlongationOperator constructProlongation(const PointMatrix& fine_points, const
                                            const EdgeMatrix& coarse_edge_matrix,
                                            const std::vector<Index>& fine_to_nearest_coarse,
                                            Weighting weighting_scheme);
+// nested mode (the reference's todo at src/multigrid.cpp:291-292): a fine point that coincides with its parent's
+// coarse point gets weight 1.0 on it; pair it with coarseFromSamples
+ProlongationOperator constructProlongation(const PointMatrix& fine_points, const PointMatrix& coarse_points,
+                                           const EdgeMatrix& coarse_edge_matrix,
+                                           const std::vector<Index>& fine_to_nearest_coarse,
+                                           Weighting weighting_scheme, bool nested);
+PointMatrix coarseFromSamples(const PointMatrix& fine_points, const std::vector<Index>& coarse_samples);
 
 PointMatrix projectedPoints(const ProlongationOperator& weights, const PointMatrix& coarse_points);
 
@@ -103,6 +114,7 @@ struct HierarchyOptions {
     Weighting weighting = Weighting::BARYCENTRIC;
     bool parallel_sampler = false;  // false: the reference's index-order greedy set, bit-exact
     bool galerkin = false;          // also A_c = P^T A P per level
+    bool nested = false;            // coarse points = sample positions, exact matches get weight 1.0
 };
 struct HierarchyLevel {
     std::vector<Index> samples, parents;

@@ -57,6 +57,11 @@ typedef enum {
 
 /* Weighting of include/gravomg/multigrid.h:12-16 */
 enum { GMG_BARYCENTRIC = 0, GMG_UNIFORM = 1, GMG_INVDIST = 2 };
+/* NESTED mode [the reference's todo at src/multigrid.cpp:291-292], OR-ed into a weighting: the coarse points of a level
+ * are the positions of its samples (gmg_coarse_from_samples; gmg_hierarchy_build / the sharded build do this themselves)
+ * instead of the means of their children, and a fine point that coincides with its parent's coarse point -- every
+ * sample, then -- gets the row (parent, 1.0), so that P restricted to the samples is the identity. */
+enum { GMG_NESTED = 0x100 };
 /* Sampler modes: the same greedy rule (src/sampling.cpp:22-50) under three precedence orders.
  *   EXACT     index order: the reference's sample set bit-for-bit.
  *   PARALLEL  the index-order sweep restarted in 2 contiguous super-tiles that are swept concurrently (their
@@ -99,6 +104,15 @@ int gmg_fast_disc_sample(gmg_ctx* ctx, int64_t n, const double* points, int64_t 
                          const int32_t* rowidx, double radius, int mode, uint64_t seed, int64_t* selection_out,
                          int64_t* m_out);
 
+/* The bounds the reference marks as a todo (src/sampling.cpp:11-12: min_selection = 0, max_selection = max) [semantics
+ * not in reference]: a radius that yields fewer than min_selection samples is halved and the sampling repeated until
+ * there are enough (or every vertex is selected); more than max_selection samples are cut to the first max_selection
+ * of the ascending selection (where the reference's loop would have stopped selecting). *radius_used (optional)
+ * receives the radius of the run that was kept. */
+int gmg_fast_disc_sample_bounded(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
+                                 const int32_t* rowidx, double radius, int64_t min_selection, int64_t max_selection, int mode,
+                                 uint64_t seed, int64_t* selection_out, int64_t* m_out, double* radius_used);
+
 int gmg_assign_parents(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
                        const int32_t* rowidx, int64_t m, const int64_t* samples, int64_t* parents_out);
 
@@ -132,6 +146,10 @@ int gmg_construct_prolongation(gmg_ctx* ctx, int64_t n, const double* fine_point
                                const int32_t* c_rowidx, const double* c_val, const int64_t* parents, int weighting,
                                int32_t* out_rowptr, int64_t* nnz_out, gmg_prolongation_stats* stats_out);
 
+/* nested mode: out (column-major m x 3, leading dimension out_ld) = the positions of the samples */
+int gmg_coarse_from_samples(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int64_t m, const int64_t* samples,
+                            double* out_points, int64_t out_ld);
+
 int gmg_projected_points(gmg_ctx* ctx, int64_t n, int64_t m, const int32_t* rowptr, const int32_t* colidx,
                          const double* val, const double* coarse_points, int64_t coarse_ld, double* out_points,
                          int64_t out_ld);
@@ -155,6 +173,10 @@ void gmg_input_destroy(gmg_input* in);
  * pulling the whole mesh over PCIe (gravo-mg_b200/sharded.py upload_sharded). gmg_input_device_ptr: 0 points
  * (f64[3n]: x | y | z), 1 colptr (int32[n+1]), 2 rowidx (int32[nnz]), 3 A values (f64[nnz]).
  * gmg_input_commit validates the completed arrays (same checks as gmg_input_create). */
+/* A values for an input created with A_val = NULL, copied on the context's copy stream while the compute stream goes
+ * on (a build needs them only at its first Galerkin product). A_val must stay valid (and should be pinned) until a call
+ * that uses the values has returned, or gmg_copy_sync has. */
+int gmg_input_set_values_async(gmg_ctx* ctx, gmg_input* in, const double* A_val);
 int gmg_input_create_device(gmg_ctx* ctx, int64_t n, int64_t nnz, int with_a, gmg_input** out);
 int gmg_input_device_ptr(gmg_input* in, int which, void** ptr);
 int gmg_input_commit(gmg_ctx* ctx, gmg_input* in);
@@ -203,6 +225,9 @@ typedef struct {
     void (*on_level)(void* user, gmg_hierarchy* h, int level);
     void* user;
 } gmg_hierarchy_options;
+/* With build_galerkin, on_level is called TWICE per level: first with (level | GMG_LEVEL_P_READY) as soon as P is
+ * complete (its three arrays may be fetched; A_c does not exist yet), then with the plain level once A_c is. */
+enum { GMG_LEVEL_P_READY = 0x40000000 };
 
 typedef struct {
     int64_t n, nnz;          /* fine side of this level */

@@ -113,6 +113,25 @@ int64_t orc_fast_disc_sample(int64_t n, const double* points, const int32_t* col
     return m;
 }
 
+/* The option the reference marks as a todo (src/sampling.cpp:11-12: "std::size_t min_selection = 0, std::size_t
+ * max_selection = max"), with the semantics the CUDA path implements [not in reference]:
+ *   max: the greedy loop stops selecting once max_selection vertices are selected = the first max_selection entries
+ *        of the ascending selection;
+ *   min: a radius that yields fewer than min_selection samples is halved and the sampling repeated, until there are
+ *        enough (or every vertex is selected). *radius_used receives the radius of the run that was kept. */
+int64_t orc_fast_disc_sample_bounded(int64_t n, const double* points, const int32_t* colptr, const int32_t* rowidx,
+                                     double radius, int64_t min_selection, int64_t max_selection, int64_t* selection_out,
+                                     double* radius_used) {
+    int64_t m = 0;
+    for (int pass = 0; pass < 64; ++pass) {
+        m = orc_fast_disc_sample(n, points, colptr, rowidx, radius, selection_out);
+        if (m >= min_selection || m >= n) break;
+        radius = radius / 2;
+    }
+    if (radius_used) *radius_used = radius;
+    return m > max_selection ? max_selection : m;
+}
+
 /* ---- binary min-heap of (distance, vertex), ordered like std::greater<pair<double,Index>> ---- */
 typedef struct { double d; int64_t v; } heap_item;
 typedef struct { heap_item* a; size_t n, cap; } heap;
@@ -415,12 +434,18 @@ int orc_construct_prolongation(int64_t n, const double* fp, int64_t m, const dou
     edge_map mp = {0, 0, 0, 0};
     int64_t fallback = 0;
     size_t cdcap = 0; double* cd_d = 0; int64_t* cd_i = 0;
+    /* nested mode [the reference's todo at :291-292, not in reference]: weighting | 0x100 -- a fine point that coincides
+     * with its parent's coarse point gets the row (parent, 1.0) */
+    const int nested = (weighting & 0x100) != 0;
+    weighting &= ~0x100;
     for (int64_t f = 0; f < n; ++f) {                                           /* :286 */
         int64_t c = parents[f];
         v3 p = pt(fp, n, f), pc = pt(cp, m, c);
         int32_t cb = c_colptr[c], ce = c_colptr[c + 1];
         int64_t ids[3]; double w[3];
-        if (cb == ce) {                                                         /* :295-299 */
+        if (nested && p.x == pc.x && p.y == pc.y && p.z == pc.z) {              /* :291-292 */
+            ids[0] = c; w[0] = 1.0; emit_row(&pb, f, ids, w, 1);
+        } else if (cb == ce) {                                                  /* :295-299 */
             ids[0] = c; w[0] = 1.0; emit_row(&pb, f, ids, w, 1);
         } else if (ce - cb == 1) {                                              /* :301-334 */
             int64_t q = c_rowidx[cb];

@@ -102,6 +102,18 @@ class Oracle:
                                         C.c_double(radius), _p(sel, _i64p))
         return sel[:m].copy()
 
+    def fast_disc_sample_bounded(self, points, colptr, rowidx, radius, min_selection, max_selection):
+        """(selection, radius used): the sampler with the min/max bounds the reference marks as a todo (orc only)."""
+        pts = fpoints(points); n = pts.shape[0]
+        colptr, rowidx, _ = self._csc(colptr, rowidx)
+        sel = np.empty(max(n, 1), dtype=np.int64)
+        used = C.c_double()
+        f = self.lib.orc_fast_disc_sample_bounded
+        f.restype = C.c_int64
+        m = f(C.c_int64(n), _p(pts, _f64p), _p(colptr, _i32p), _p(rowidx, _i32p), C.c_double(radius),
+              C.c_int64(min_selection), C.c_int64(max_selection), _p(sel, _i64p), C.byref(used))
+        return sel[:m].copy(), used.value
+
     def assign_parents(self, points, colptr, rowidx, samples):
         pts = fpoints(points); n = pts.shape[0]
         colptr, rowidx, _ = self._csc(colptr, rowidx)

@@ -15,7 +15,10 @@ def run_level(be, pts, cp, ri, val, radius=None, samples=None, weighting=0, rati
     m = len(out["sel"])
     out["par"] = be.assign_parents(pts, cp, ri, out["sel"])
     out["ccp"], out["cri"], out["cval"] = be.extract_coarse_edges(cp, ri, val, m, out["par"])
-    out["cpts"] = be.coarse_from_mean_of_fine_children(pts, cp, ri, out["par"], m)
+    if weighting & 0x100:       # nested mode: the coarse points are the samples themselves
+        out["cpts"] = np.asfortranarray(np.asarray(pts)[out["sel"]])
+    else:
+        out["cpts"] = be.coarse_from_mean_of_fine_children(pts, cp, ri, out["par"], m)
     out["tri"], out["nrm"], out["fptr"], out["fan"] = be.construct_voronoi_triangles(out["cpts"], out["ccp"], out["cri"], out["cval"])
     r = be.construct_prolongation(pts, out["cpts"], out["ccp"], out["cri"], out["cval"], out["par"], weighting)
     out["prp"], out["pci"], out["pva"] = r[0], r[1], r[2]

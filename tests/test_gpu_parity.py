@@ -149,3 +149,44 @@ def test_levels_streamed_out_during_the_build(ctx):
     # int64 outputs are converted on the way out and have no asynchronous path
     h.close(); inp.close()
     assert ctx.trim() >= 0
+
+
+def test_streaming_with_galerkin_and_deferred_values(ctx):
+    """With build_galerkin the level callback comes twice (P ready, then A_c ready), and A's values may be uploaded
+    on the copy stream after the input exists (gmg_input_set_values_async): same hierarchy as the plain calls."""
+    import torch
+    from gravomg_b200 import capi
+    cfg = meshgen.make_config("C3", 0.01)
+    V, A = cfg["V"], cfg["A"]
+    ref_inp = capi.Input(ctx, V, A.indptr, A.indices, A.data)
+    ref = capi.Hierarchy(ctx, ref_inp, cfg["levels"], build_galerkin=True)
+    pinned_a = torch.from_numpy(np.ascontiguousarray(A.data)).pin_memory().numpy()
+    inp = capi.Input(ctx, V, A.indptr, A.indices, pinned_a, defer_values=True)
+    got, calls = {}, []
+
+    def stream_out(level, info):
+        calls.append((level, info["p_ready_only"]))
+        if info["p_ready_only"]:
+            ids = [(capi.H_P_ROWPTR, info["n"] + 1, torch.int32), (capi.H_P_COLIDX, info["nnz_p"], torch.int32),
+                   (capi.H_P_VAL, info["nnz_p"], torch.float64)]
+        else:
+            assert info["nnz_ac"] > 0
+            ids = [(capi.H_AC_COLPTR, info["m"] + 1, torch.int32), (capi.H_AC_ROWIDX, info["nnz_ac"], torch.int32),
+                   (capi.H_AC_VAL, info["nnz_ac"], torch.float64)]
+        bufs = [(w, torch.empty(cnt, dtype=dt).pin_memory().numpy()) for w, cnt, dt in ids]
+        got.setdefault(level, []).extend(bufs)
+        return bufs
+
+    h = capi.Hierarchy(ctx, inp, cfg["levels"], build_galerkin=True, stream_out=stream_out)
+    ctx.copy_sync()
+    assert calls == [(l, e) for l in range(h.num_levels) for e in (True, False)]
+    for lvl, bufs in got.items():
+        assert len(bufs) == 6
+        for which, arr in bufs:
+            assert np.array_equal(arr, ref.fetch(lvl, which)), (lvl, which)
+    assert np.array_equal(inp.fetch_operator(), A.data)
+    # a solver on the deferred input
+    b = A @ np.ones(V.shape[0])
+    x, res = capi.Solver(ctx, inp, h).vcycle(b, cycles=2)
+    assert res[-1] < res[0]
+    h.close(); inp.close(); ref.close(); ref_inp.close()

@@ -125,3 +125,26 @@ def test_solver_oracle_matches_scipy(orc, name, scale):
     for _ in range(2):
         want = sp.linalg.spsolve_triangular(Lo, b - (As - Lo) @ want, lower=True)
     assert np.abs(got - want).max() <= 1e-10 * np.abs(want).max()
+
+
+def test_oracle_options_semantics(orc):
+    """The restatement of the two options the reference leaves as todo (selection bounds, nested mode): the
+    properties their definitions promise, on C1."""
+    cfg = meshgen.make_config("C1")
+    V, A = cfg["V"], cfg["A"]
+    val = orc.to_edge_distance_matrix(A.indptr, A.indices, V)
+    edges, _ = orc.extract_edges(A.indptr, A.indices, val)
+    radius = 2.0 * orc.average_edge_length(V, edges)
+    plain = orc.fast_disc_sample(V, A.indptr, A.indices, radius)
+    sel, used = orc.fast_disc_sample_bounded(V, A.indptr, A.indices, radius, 0, 50)
+    assert np.array_equal(sel, plain[:50]) and used == radius
+    sel, used = orc.fast_disc_sample_bounded(V, A.indptr, A.indices, radius, 2 * len(plain), 2 ** 62)
+    assert len(sel) >= 2 * len(plain) and used in (radius / 2, radius / 4, radius / 8)
+    assert np.array_equal(sel, orc.fast_disc_sample(V, A.indptr, A.indices, used))
+    nested = run_hierarchy(orc, V, A, cfg["levels"], weighting=0x100)[0]
+    s = nested["sel"]
+    assert np.array_equal(nested["cpts"], V[s])
+    assert np.all(np.diff(nested["prp"])[s] == 1) and np.all(nested["pva"][nested["prp"][s]] == 1.0)
+    assert np.array_equal(nested["pci"][nested["prp"][s]], np.arange(len(s)))
+    rows = np.add.reduceat(nested["pva"], nested["prp"][:-1])
+    assert np.abs(rows - 1.0).max() < 1e-12
