@@ -186,7 +186,8 @@ def test_streaming_with_galerkin_and_deferred_values(ctx):
             assert np.array_equal(arr, ref.fetch(lvl, which)), (lvl, which)
     assert np.array_equal(inp.fetch_operator(), A.data)
     # a solver on the deferred input
-    b = A @ np.ones(V.shape[0])
+    b = A @ (np.sin(3 * V[:, 0]) * np.cos(2 * V[:, 1]) + V[:, 2])
     x, res = capi.Solver(ctx, inp, h).vcycle(b, cycles=2)
-    assert res[-1] < res[0]
+    x_ref, res_ref = capi.Solver(ctx, ref_inp, ref).vcycle(b, cycles=2)
+    assert res[-1] < 0.2 * res[0] and np.array_equal(res, res_ref) and np.array_equal(x, x_ref)
     h.close(); inp.close(); ref.close(); ref_inp.close()
