@@ -182,6 +182,21 @@ __device__ __forceinline__ bool use_lane_flow(const SamplerArgs& a) {
     return same * 4ull < all;
 }
 
+// Which BUILD kernel runs is decided on the device too, from a probe of the graph (sampler_coherence_kernel: the share
+// of stored neighbours that sit in the vertex's own flow tile, over every 16th vertex): merging and partitioning the
+// lists (shared-memory hash per vertex) pays for itself only where the tile flow will run; for an incoherent order
+// (subdivision numbering, an unordered cloud, the hashed order) the raw single-walk build is twice as fast and the
+// per-lane flow does not care.
+// Measured (B200): icosphere in subdivision order (6 neighbours), raw 0.97 ms vs merged 1.26 ms of sampling at 2.6 M
+// vertices; kNN cloud (~9 neighbours, ~150 later paths that merge into ~40 entries), raw 2.1 ms vs merged 1.9 ms at
+// 2 M points. Hence the second condition: at most 8 neighbours on average.
+__device__ __forceinline__ bool use_raw_build(const SamplerArgs& a) {
+    const unsigned long long same = *(volatile unsigned long long*)(a.stats + 2);
+    const unsigned long long all = *(volatile unsigned long long*)(a.stats + 3);
+    const bool sparse = all * 2ull <= (unsigned long long)a.n;          // the probe visits n / 16 vertices
+    return (a.force_lane || same * 4ull < all) && sparse;
+}
+
 template <int MODE> __device__ __forceinline__ uint32_t rank_of(const SamplerArgs& a, int32_t v) {
     return MODE == GMG_SAMPLER_EXACT ? uint32_t(v) : order_rank(a.order, uint32_t(v));
 }
@@ -239,6 +254,10 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
     __shared__ uint32_t s_cnt[kBlock / kLanes][kMergeSlots];
     __shared__ int32_t s_used[kBlock / kLanes];        // occupied slots of the group's table (-1: overflowed)
     __shared__ int32_t s_same;
+    __shared__ int s_skip;
+    if (threadIdx.x == 0) s_skip = use_raw_build(a) ? 1 : 0;      // (one read per block: the words are shared by the grid)
+    __syncthreads();
+    if (s_skip) return;
     const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
     const int32_t i = int32_t(gid / kLanes);
     const int sub = threadIdx.x % kLanes;
@@ -344,6 +363,101 @@ __global__ void __launch_bounds__(kBlock) sampler_build_kernel(SamplerArgs a) {
         a.lcnt[ri] = uint32_t(group_total) | ((group_over ? kUnpartitioned : uint32_t(group_in)) << 16);
         a.cint[ri] = uint32_t(prev_in);
         a.wext[ri] = uint32_t(prev_ext);
+    }
+}
+
+// The probe behind use_raw_build: one thread per 16th vertex.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) sampler_coherence_kernel(SamplerArgs a) {
+    const int64_t i = (int64_t(blockIdx.x) * kBlock + threadIdx.x) * 16;
+    unsigned same = 0, all = 0;
+    if (i < a.n) {
+        const uint32_t ti = rank_of<MODE>(a, int32_t(i)) >> kTileLog;
+        for (int32_t k = __ldg(a.colptr + i); k < __ldg(a.colptr + i + 1); ++k) {
+            const int32_t j = __ldg(a.rowidx + k);
+            if (j == i) continue;
+            ++all;
+            same += (rank_of<MODE>(a, j) >> kTileLog) == ti ? 1u : 0u;
+        }
+    }
+    same = __reduce_add_sync(0xffffffffu, same);
+    all = __reduce_add_sync(0xffffffffu, all);
+    if ((threadIdx.x & 31) == 0 && all) { atomicAdd(a.stats + 2, (unsigned long long)same); atomicAdd(a.stats + 3, (unsigned long long)all); }
+}
+
+// The build for incoherent orders: ONE walk, later targets staged in a lane-private row of shared memory and written
+// as they are (one entry per path, flagged kUnpartitioned; every preceding path counts into the global word). A
+// vertex with a lane that outgrows its row walks again.
+template <int MODE>
+__global__ void __launch_bounds__(kBlock) sampler_build_raw_kernel(SamplerArgs a) {
+    static_assert(kBlock / kLanes == 32, "one warp scans the group totals");
+    __shared__ int32_t s_group[kBlock / kLanes];
+    __shared__ unsigned long long s_base;
+    __shared__ uint32_t s_stage[kBlock][kStage + 1];   // +1: conflict-free lane-private rows
+    __shared__ int s_skip;
+    if (threadIdx.x == 0) s_skip = use_raw_build(a) ? 0 : 1;
+    __syncthreads();
+    if (s_skip) return;
+    const int64_t gid = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int32_t i = int32_t(gid / kLanes);
+    const int sub = threadIdx.x % kLanes;
+    const int g = threadIdx.x / kLanes;
+    const bool active = i < a.n;
+    int32_t prev = 0, later = 0;
+    uint32_t ri = 0;
+    if (active) {
+        ri = rank_of<MODE>(a, i);
+        uint32_t* stage = s_stage[threadIdx.x];
+        for_each_covered(a, i, sub, [&](int32_t t) {
+            const uint32_t rt = rank_of<MODE>(a, t);
+            if (rt < ri) ++prev;
+            else { if (later < kStage) stage[later] = rt; ++later; }
+        });
+    }
+    const int lane = threadIdx.x & 31;
+    const unsigned gmask = 0xFFu << (lane & ~(kLanes - 1));
+    const bool group_over = (__ballot_sync(0xffffffffu, later > kStage) & gmask) != 0;
+#pragma unroll
+    for (int d = kLanes / 2; d > 0; d >>= 1) prev += __shfl_xor_sync(0xffffffffu, prev, d, kLanes);
+    int32_t incl = later;
+#pragma unroll
+    for (int d = 1; d < kLanes; d <<= 1) {
+        const int32_t t = __shfl_up_sync(0xffffffffu, incl, d, kLanes);
+        if (sub >= d) incl += t;
+    }
+    const int32_t group_total = __shfl_sync(0xffffffffu, incl, kLanes - 1, kLanes);
+    if (sub == 0) s_group[g] = group_total;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int32_t v = s_group[threadIdx.x];
+        int32_t sc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int32_t t = __shfl_up_sync(0xffffffffu, sc, d);
+            if (int(threadIdx.x) >= d) sc += t;
+        }
+        s_group[threadIdx.x] = sc - v;
+        if (threadIdx.x == 31) { s_base = atomicAdd(a.cursor, (unsigned long long)sc); if (sc) atomicAdd(a.stats + 1, (unsigned long long)sc); }
+    }
+    __syncthreads();
+    if (!active) return;
+    const long long start = (long long)s_base + s_group[g];
+    uint32_t* dst = a.lst + start + (incl - later);
+    if (!group_over) {
+        const uint32_t* stage = s_stage[threadIdx.x];
+        for (int32_t e = 0; e < later; ++e) dst[e] = stage[e];
+    } else {
+        for_each_covered(a, i, sub, [&](int32_t t) {
+            const uint32_t rt = rank_of<MODE>(a, t);
+            if (!(rt < ri)) *dst++ = rt;
+        });
+    }
+    if (sub == 0) {
+        if (group_total > 0xFFFF) a.flags[0] = 1;
+        a.lptr[ri] = start;
+        a.lcnt[ri] = uint32_t(group_total) | (kUnpartitioned << 16);
+        a.cint[ri] = 0u;
+        a.wext[ri] = uint32_t(prev);
     }
 }
 
@@ -697,7 +811,10 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
 
 template <int MODE>
 __global__ void __launch_bounds__(kBlock) sampler_merge_counts_kernel(SamplerArgs a) {
-    if (!use_lane_flow(a)) return;
+    __shared__ int s_skip;
+    if (threadIdx.x == 0) s_skip = (!use_lane_flow(a) || use_raw_build(a)) ? 1 : 0;     // (the raw build leaves nothing to merge)
+    __syncthreads();
+    if (s_skip) return;
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
     const uint64_t r = uint64_t(blockIdx.x) * kBlock + threadIdx.x;
     if (r < ranks && vertex_of<MODE>(a, uint32_t(r)) < uint32_t(a.n)) a.wext[r] += a.cint[r];
@@ -788,7 +905,10 @@ static int env_int(const char* name, int fallback) {
 }
 
 template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, uint64_t ranks, int32_t* flag) {
+    // probe, then both build kernels: the one the probe does not select returns at once (no host round trip)
+    GMG_LAUNCH(c, sampler_coherence_kernel<MODE>, div_up(div_up(int64_t(a.n), 16), kBlock), kBlock, 0, a);
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
+    GMG_LAUNCH(c, sampler_build_raw_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
     // both flow kernels are launched; the one the build's counts do not select returns at once
     GMG_CUDA(cudaFuncSetAttribute(sampler_flow_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFlowSmem)));
     int per_sm = 0;
@@ -815,8 +935,9 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     GMG_REQUIRE(mode == GMG_SAMPLER_EXACT || mode == GMG_SAMPLER_PARALLEL || mode == GMG_SAMPLER_HASHED, GMG_ERR_INVALID,
                 "unknown sampler mode");
     // bound on the later-path lists: every path has a mirror image, exactly one of the two is "later"
-    // [0] list cursor, [1] sum deg^2, [2] tickets (tile flow | lane flow), [3] flags | epoch, [4] same-tile entries, [5] all entries
-    DevBuf<unsigned long long> cursor(c, 6);
+    // [0] list cursor, [1] sum deg^2, [2] tickets (tile flow | lane flow), [3] flags | epoch, [4] same-tile entries, [5] all entries,
+    // [6] [7] the coherence probe (same-tile neighbours, neighbours)
+    DevBuf<unsigned long long> cursor(c, 8);
     cursor.zero();
     if (path_bound < 0) {
         degree_square_sum(c, n, colptr, cursor.p + 1);
