@@ -628,6 +628,29 @@ def run_b200(a, rank, world, local_rank):
             line["parity"] = {"skipped": "the CPU sample is a different size (--cpu-scale)"}
     if h_exact is not None:
         h_exact.close()
+    if a.workload == "C3" and a.scale == 1.0 and world == 1:
+        # the 1-GPU point of the N = 2, 4, 8 curve: the SAME workload family and code path as `bench.py --gpus N`
+        # (12.5 M-vertex torus per GPU through the row-sharded driver, hashed sampler, A_c on every level), so that
+        # scaling efficiency can be computed on one family: value(N) / (N * scale_anchor.value)
+        try:
+            from gravomg_b200.sharded import ShardedHierarchy
+            nu, nv = torus_dims(f"T{a.per_gpu_mverts:g}")
+            tin = Input.torus(ctx, nu, nv, mass_shift=1e-3)
+            t_ms = []
+            for s_ in range(5):
+                flush.fill_(s_)
+                torch.cuda.synchronize()
+                sh = ShardedHierarchy(ctx, tin, 4, 1, [0], comm=None, sampler_mode=capi.SAMPLER_HASHED, build_galerkin=True)
+                if s_ >= 2:
+                    t_ms.append(sh.build_ms)
+                sh.close()
+            tin.close()
+            t_mean = float(np.mean(t_ms))
+            line["scale_anchor"] = {"workload": f"noisy torus {nu}x{nv} ({nu * nv:,} verts, C5 family) through the row-sharded driver, "
+                                                f"world 1, hashed sampler, A_c on every level", "ms_per_step": t_mean,
+                                    "value": nu * nv / (t_mean * 1e-3) / 1e6, "unit": "Mverts/s", "steps": len(t_ms)}
+        except Exception as e:                                      # never lose the main line over the side measurement
+            line["scale_anchor"] = {"error": repr(e)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

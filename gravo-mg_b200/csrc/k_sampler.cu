@@ -162,7 +162,6 @@ struct SamplerArgs {
     unsigned long long* dbg;     // GMG_SAMPLER_DEBUG: 8 words per tile (timeline of the tile flow), else null
     uint32_t* trace;             // GMG_SAMPLER_TRACE: 4 words per rank (ns since t0: queued, popped, ext popped, ext done), else null
     const unsigned long long* trace_t0;
-    int fast_warps, group, xgroup, xsleep, claim;   // tile flow shape (defaults kFastWarps, kGroup, kGroup, 64; GMG_FLOW_* env for tuning)
     uint16_t* mbox;              // [tiles * kTile] tile flow: mailbox of every tile (rank offset | knocked-out << kTileLog), 0xFFFF = empty
 };
 
@@ -496,7 +495,10 @@ constexpr int kFastWarps = 16;                // warps 1 .. kFastWarps pop the t
 constexpr int kGroup = 8;                     // lanes that apply one rank's list
 constexpr int kPtrLen = kTile + 2;            // prefix arrays (kTile + 1 used; even length keeps 4-byte alignment)
 
-template <int MODE>
+// DBG: the instantiation with the timeline / per-rank trace instrumentation (GMG_SAMPLER_DEBUG, GMG_SAMPLER_TRACE); the
+// production one carries none of it -- the loops below are latency chains, every instruction in them counts (an
+// experimental extra mode in the pop loop once cost 10 % just by being compiled in).
+template <int MODE, bool DBG>
 __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerArgs a) {
     extern __shared__ unsigned char smem_raw[];
     int32_t* s_state = reinterpret_cast<int32_t*>(smem_raw);                     // kTile state words
@@ -514,9 +516,9 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rmask = a.order.kbits >= 32 ? 0xFFFFFFFFu : ((1u << a.order.kbits) - 1u);
     const uint64_t ranks = MODE == GMG_SAMPLER_EXACT ? uint64_t(a.n) : (uint64_t(1) << a.order.kbits);
-    const unsigned long long trace_t0 = a.trace ? *a.trace_t0 : 0ull;
+    const unsigned long long trace_t0 = (DBG && a.trace) ? *a.trace_t0 : 0ull;
     auto push = [&](uint32_t t, uint32_t in) {
-        if (a.trace) a.trace[4 * (size_t(s_tile) * kTile + t) + 0] = uint32_t(global_ns() - trace_t0);
+        if (DBG && a.trace) a.trace[4 * (size_t(s_tile) * kTile + t) + 0] = uint32_t(global_ns() - trace_t0);
         const int32_t slot = atomicAdd(&s_ctr[1], 1);
         *(volatile uint16_t*)(s_queue + slot) = uint16_t(t | (in << kTileLog));
     };
@@ -539,7 +541,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         const unsigned int tile = s_tile;
         if (tile >= a.tiles) break;
         const uint32_t t0 = tile << kTileLog;
-        if (a.dbg && tid == 0) { a.dbg[8 * tile + 0] = global_ns(); a.dbg[8 * tile + 7] = blockIdx.x; }
+        if (DBG && a.dbg && tid == 0) { a.dbg[8 * tile + 0] = global_ns(); a.dbg[8 * tile + 7] = blockIdx.x; }
         // ---- static data of the tile's ranks; ranks [tid * kOwn, (tid + 1) * kOwn) of the tile belong to this thread
         //      for the staging (so that the scans below lay the lists out in rank order)
         long long ptr[kOwn];
@@ -631,7 +633,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             for (uint32_t e = nin[q]; e < tot[q]; ++e) s_ext[xo + (e - nin[q])] = a.lst[ptr[q] + e];
         }
         __syncthreads();
-        if (a.dbg && tid == 0) a.dbg[8 * tile + 1] = global_ns();
+        if (DBG && a.dbg && tid == 0) a.dbg[8 * tile + 1] = global_ns();
         // ---- what is decided from the start: knocked out already / nothing to wait for
 #pragma unroll
         for (int q = 0; q < kOwn; ++q) {
@@ -665,40 +667,24 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                 seen = cnt == 32 ? 0u : seen >> cnt;
                 ++looks;
             }
-            if (a.dbg && lane == 0) { a.dbg[8 * tile + 4] = looks; a.dbg[8 * tile + 5] = (unsigned long long)next; }
-        } else if (warp <= a.fast_warps) {
+            if (DBG && a.dbg && lane == 0) { a.dbg[8 * tile + 4] = looks; a.dbg[8 * tile + 5] = (unsigned long long)next; }
+        } else if (warp <= kFastWarps) {
             // ---- FAST: four ranks per warp at a time, 8 lanes each (lists are short, and what bounds the tile is how
             //      many decided ranks are being applied at once: with one rank per warp the queue backs up and a rank
             //      on the critical chain waits microseconds behind ranks that are not). The groups of a warp move in
             //      lock step: look at the claimed slot, apply it if it is filled, claim the next.
-            const int grp = a.group;
+            constexpr int grp = kGroup;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
-            int32_t slot = total;
-            if (!a.claim) {
-                if (sub == 0) slot = atomicAdd(&s_ctr[2], 1);
-                slot = __shfl_sync(0xffffffffu, slot, lead);
-            }
-            for (;;) {
-                if (!__any_sync(0xffffffffu, slot < total)) {
-                    if (!a.claim) break;
-                    // the warp holds nothing: take what is queued (a warp that is busy holds no claim on future
-                    // slots, so a rank that has just been decided goes to whichever warp is idle)
-                    const int32_t head = *(volatile int32_t*)&s_ctr[2];
-                    if (head >= total) break;
-                    const int32_t avail = *(volatile int32_t*)&s_ctr[1] - head;
-                    if (avail <= 0) continue;
-                    const int32_t want = avail < 32 / grp ? avail : 32 / grp;
-                    int32_t h = 0;
-                    if (lane == 0) h = atomicAdd(&s_ctr[2], want);
-                    h = __shfl_sync(0xffffffffu, h, 0);
-                    slot = lane / grp < want ? h + lane / grp : total;
-                }
+            int32_t slot = 0;
+            if (sub == 0) slot = atomicAdd(&s_ctr[2], 1);
+            slot = __shfl_sync(0xffffffffu, slot, lead);
+            while (__any_sync(0xffffffffu, slot < total)) {
                 const uint32_t e = slot < total ? uint32_t(*(volatile uint16_t*)(s_queue + slot)) : kEmpty;
                 if (e != kEmpty) {
                     const uint32_t v = e & uint32_t(kTile - 1);
                     const bool in = (e >> kTileLog) != 0u;
-                    if (a.dbg && sub == 0) atomicMin(a.dbg + 8 * tile + 2, global_ns());
-                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 1] = uint32_t(global_ns() - trace_t0);
+                    if (DBG && a.dbg && sub == 0) atomicMin(a.dbg + 8 * tile + 2, global_ns());
+                    if (DBG && a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 1] = uint32_t(global_ns() - trace_t0);
                     bool has_ext;
                     // (independent loads, issued together: every dependent shared-memory access is a step of the chain)
                     const int32_t sv = *(volatile int32_t*)(s_state + v);
@@ -733,7 +719,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                             const int32_t xs = atomicAdd(&s_ctr[4], 1);
                             *(volatile uint16_t*)(s_xqueue + xs) = uint16_t(e);
                         }
-                        slot = a.claim ? total : atomicAdd(&s_ctr[2], 1);
+                        slot = atomicAdd(&s_ctr[2], 1);
                     }
                 }
                 slot = __shfl_sync(0xffffffffu, slot, lead);
@@ -741,35 +727,21 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         } else {
             // ---- EXT: the other-tile half, with atomics that return: the lane that decides something about a rank of
             //      another tile tells that tile. Same lock-step groups; two L2 round trips per pass.
-            const int grp = a.xgroup;
+            constexpr int grp = kGroup;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
             const int32_t total_x = *(volatile int32_t*)&s_ctr[3];
-            int32_t slot = total_x;
-            if (!a.claim) {
-                if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
-                slot = __shfl_sync(0xffffffffu, slot, lead);
-            }
-            for (;;) {
-                if (!__any_sync(0xffffffffu, slot < total_x)) {
-                    if (!a.claim) break;
-                    const int32_t head = *(volatile int32_t*)&s_ctr[5];
-                    if (head >= total_x) break;
-                    const int32_t avail = *(volatile int32_t*)&s_ctr[4] - head;
-                    if (avail <= 0) { if (a.xsleep) __nanosleep(a.xsleep); continue; }
-                    const int32_t want = avail < 32 / grp ? avail : 32 / grp;
-                    int32_t h = 0;
-                    if (lane == 0) h = atomicAdd(&s_ctr[5], want);
-                    h = __shfl_sync(0xffffffffu, h, 0);
-                    slot = lane / grp < want ? h + lane / grp : total_x;
-                }
+            int32_t slot = 0;
+            if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
+            slot = __shfl_sync(0xffffffffu, slot, lead);
+            while (__any_sync(0xffffffffu, slot < total_x)) {
                 const uint32_t e = slot < total_x ? uint32_t(*(volatile uint16_t*)(s_xqueue + slot)) : kEmpty;
                 // (sleeping: a spinning warp takes issue slots from the warps that walk the dependency chain)
-                if (!__any_sync(0xffffffffu, e != kEmpty)) { if (a.xsleep) __nanosleep(a.xsleep); continue; }
+                if (!__any_sync(0xffffffffu, e != kEmpty)) { __nanosleep(64); continue; }
                 if (e != kEmpty) {
                     const uint32_t v = e & uint32_t(kTile - 1);
                     const bool in = (e >> kTileLog) != 0u;
                     const bool slow = (*(volatile int32_t*)(s_state + v) & kSlow) != 0;
-                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 2] = uint32_t(global_ns() - trace_t0);
+                    if (DBG && a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 2] = uint32_t(global_ns() - trace_t0);
                     uint32_t first, count;
                     long long p = 0;
                     bool raw = false;
@@ -798,14 +770,14 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
                                 uint16_t((rt & uint32_t(kTile - 1)) | (in ? uint32_t(kTile) : 0u));
                         }
                     }
-                    if (a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 3] = uint32_t(global_ns() - trace_t0);
-                    if (sub == 0) slot = a.claim ? total_x : atomicAdd(&s_ctr[5], 1);
+                    if (DBG && a.trace && sub == 0) a.trace[4 * (size_t(t0) + v) + 3] = uint32_t(global_ns() - trace_t0);
+                    if (sub == 0) slot = atomicAdd(&s_ctr[5], 1);
                 }
                 slot = __shfl_sync(0xffffffffu, slot, lead);
             }
-            if (a.dbg && lane == 0) atomicMax(a.dbg + 8 * tile + 3, global_ns());
+            if (DBG && a.dbg && lane == 0) atomicMax(a.dbg + 8 * tile + 3, global_ns());
         }
-        if (a.dbg) { __syncthreads(); if (tid == 0) a.dbg[8 * tile + 6] = global_ns(); }
+        if (DBG && a.dbg) { __syncthreads(); if (tid == 0) a.dbg[8 * tile + 6] = global_ns(); }
     }
 }
 
@@ -899,24 +871,21 @@ void degree_square_sum(gmg_ctx* c, int32_t n, const int32_t* colptr, unsigned lo
 
 constexpr size_t kFlowSmem = sizeof(int32_t) * kTile + sizeof(uint32_t) * kExtCap + sizeof(uint16_t) * (kListCap + 2 * kPtrLen + 2 * kTile);
 
-static int env_int(const char* name, int fallback) {
-    const char* v = getenv(name);
-    return v && *v ? atoi(v) : fallback;
-}
-
 template <int MODE> static void run_sampler(gmg_ctx* c, SamplerArgs a, uint64_t ranks, int32_t* flag) {
     // probe, then both build kernels: the one the probe does not select returns at once (no host round trip)
     GMG_LAUNCH(c, sampler_coherence_kernel<MODE>, div_up(div_up(int64_t(a.n), 16), kBlock), kBlock, 0, a);
     GMG_LAUNCH(c, sampler_build_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
     GMG_LAUNCH(c, sampler_build_raw_kernel<MODE>, div_up(int64_t(a.n) * kLanes, kBlock), kBlock, 0, a);
     // both flow kernels are launched; the one the build's counts do not select returns at once
-    GMG_CUDA(cudaFuncSetAttribute(sampler_flow_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFlowSmem)));
+    const bool dbg = a.dbg != nullptr || a.trace != nullptr;
+    auto flow = dbg ? sampler_flow_kernel<MODE, true> : sampler_flow_kernel<MODE, false>;
+    GMG_CUDA(cudaFuncSetAttribute(flow, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFlowSmem)));
     int per_sm = 0;
-    GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_flow_kernel<MODE>, kFlowThreads, kFlowSmem));
+    GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, flow, kFlowThreads, kFlowSmem));
     GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "sampler flow kernel does not fit on an SM");
     int grid = per_sm * c->sm_count;
     if (grid > int(a.tiles)) grid = int(a.tiles);
-    if (!a.force_lane) GMG_LAUNCH(c, sampler_flow_kernel<MODE>, grid < 1 ? 1 : grid, kFlowThreads, kFlowSmem, a);
+    if (!a.force_lane) GMG_LAUNCH(c, flow, grid < 1 ? 1 : grid, kFlowThreads, kFlowSmem, a);
     GMG_LAUNCH(c, sampler_merge_counts_kernel<MODE>, div_up(int64_t(ranks), kBlock), kBlock, 0, a);
     GMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_lane_flow_kernel<MODE>, kBlock, 0));
     GMG_REQUIRE(per_sm > 0, GMG_ERR_CUDA, "sampler flow kernel does not fit on an SM");
@@ -983,8 +952,7 @@ int32_t disc_sample(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t*
     SamplerArgs a{n, colptr, rowidx, len, radius, order, wext.p, cint.p, lptr.p, lcnt.p, lst.p, cursor.p,
                   reinterpret_cast<unsigned int*>(cursor.p + 2), ntiles, res.p,
                   reinterpret_cast<int32_t*>(cursor.p + 3), cursor.p + 4, epochs.p,
-                  mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr, trace.p, trace_t0.p, env_int("GMG_FLOW_FAST", kFastWarps), env_int("GMG_FLOW_GROUP", kGroup),
-                  env_int("GMG_FLOW_XGROUP", kGroup), env_int("GMG_FLOW_XSLEEP", 64), env_int("GMG_FLOW_CLAIM", 0), mbox.p};
+                  mode == GMG_SAMPLER_HASHED ? 1 : 0, debug ? dbg.p : nullptr, trace.p, trace_t0.p, mbox.p};
     if (trace_path) GMG_LAUNCH(c, stamp_kernel, 1, 1, 0, trace_t0.p);
     if (mode == GMG_SAMPLER_EXACT) run_sampler<GMG_SAMPLER_EXACT>(c, a, ranks, flag.p);
     else run_sampler<GMG_SAMPLER_PARALLEL>(c, a, ranks, flag.p);
