@@ -194,6 +194,7 @@ using Table2b = ThreadTable<kCap2b, kThreads2b>;
 
 struct ProductArgs {
     int32_t n, m;                                                         // fine vertices; outer vectors of A_c formed here
+    int32_t k_lo, k_hi;                                                   // the window of fine columns of T that R reads (ub1, t_ptr are indexed from k_lo)
     const int32_t* a_ptr; const int32_t* a_idx; const double* a_val;      // A by outer vector
     const int32_t* p_ptr; const int32_t* p_col; const double* p_val;      // P rows
     const int32_t* r_ptr; const int32_t* r_col; const double* r_val;      // R = P^T (rows = the outer vectors formed here)
@@ -205,23 +206,29 @@ struct ProductArgs {
     int32_t* overflow;                                                    // columns of A_c queued for the second pass
 };
 
+// window[0] = smallest, window[1] = largest fine column R names
 __global__ void __launch_bounds__(kBlock) mark_needed_kernel(int64_t nnz, const int32_t* __restrict__ r_col,
-                                                             uint8_t* __restrict__ needed) {
+                                                             uint8_t* __restrict__ needed, int32_t* __restrict__ window) {
     const int64_t e = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (e < nnz) needed[r_col[e]] = 1;
+    int32_t lo = 0x7fffffff, hi = -1;
+    if (e < nnz) { const int32_t k = r_col[e]; needed[k] = 1; lo = k; hi = k; }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(window, lo); atomicMax(window + 1, hi); }
 }
 
 // ub1(k): products (= an upper bound on the entries) of column k of T
 __global__ void __launch_bounds__(kBlock) product1_bound_kernel(ProductArgs a) {
-    const int64_t k = int64_t(blockIdx.x) * kBlock + threadIdx.x;
-    if (k > a.n) return;
+    const int64_t w = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    const int64_t k = a.k_lo + w;
+    if (k > a.k_hi) return;
     int32_t ub = 0;
-    if (k < a.n && (!a.needed || a.needed[k]))
+    if (k < a.k_hi && (!a.needed || a.needed[k]))
         for (int32_t q = __ldg(a.a_ptr + k); q < __ldg(a.a_ptr + k + 1); ++q) {
             const int32_t l = __ldg(a.a_idx + q);
             ub += __ldg(a.p_ptr + l + 1) - __ldg(a.p_ptr + l);
         }
-    a.ub1[k] = ub;          // entry n = 0: the scan's total
+    a.ub1[w] = ub;          // the entry behind the window = 0: the scan's total
 }
 
 // exclusive scan of one int per thread over a block of THREADS threads (all threads must call)
@@ -251,9 +258,10 @@ __device__ __forceinline__ int32_t block_scan_exclusive(int32_t v, int32_t* warp
 __global__ void __launch_bounds__(kThreads1) product1_kernel(ProductArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int32_t s_warp[kThreads1 / 32];
-    const int64_t k = int64_t(blockIdx.x) * kThreads1 + threadIdx.x;
+    const int64_t w = int64_t(blockIdx.x) * kThreads1 + threadIdx.x;
+    const int64_t k = a.k_lo + w;
     int32_t ub = 0;
-    if (k < a.n) ub = __ldg(a.t_ptr + k + 1) - __ldg(a.t_ptr + k);
+    if (k < a.k_hi) ub = __ldg(a.t_ptr + w + 1) - __ldg(a.t_ptr + w);
     Table1 tab(smem, threadIdx.x);
     bool ok = true;
     int32_t ab = 0, ae = 0;
@@ -301,9 +309,9 @@ __global__ void __launch_bounds__(kThreads1) product1_kernel(ProductArgs a) {
     // where this column goes: fast columns take what they hold, a column on the slow path its whole bound
     const int32_t reserve = ub == 0 ? 0 : (ok ? tab.count : ub);
     const int32_t off = block_scan_exclusive<kThreads1>(reserve, s_warp);
-    if (k >= a.n) return;
-    const int64_t k0 = int64_t(blockIdx.x) * kThreads1;
-    const int32_t start = __ldg(a.t_ptr + k0) + off;
+    if (k >= a.k_hi) return;
+    const int64_t w0 = int64_t(blockIdx.x) * kThreads1;
+    const int32_t start = __ldg(a.t_ptr + w0) + off;
     int32_t* idx = a.t_idx + start;
     double* val = a.t_val + start;
     int32_t cnt = 0;
@@ -448,24 +456,35 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     tr.mark("transpose");
     if (marks) cudaEventRecord(marks[1], c->stream);
     const bool all = c_lo == 0 && c_hi == P.cols;
+    // The row-sharded build forms the outer vectors of one rank: T is only needed for the fine columns its rows of R
+    // name, which in a coherent numbering is a window around the rank's own range -- the bound, the scan and the first
+    // product run over that window, not over all n (at 8 ranks the passes over all n cost more than the product).
     DevBuf<uint8_t> needed;
+    int32_t k_lo = 0, k_hi = n;
     if (!all) {
         needed.alloc(c, n);
         needed.zero();
-        if (R.nnz > 0) GMG_LAUNCH(c, mark_needed_kernel, div_up(R.nnz, kBlock), kBlock, 0, R.nnz, R.colidx.p, needed.p);
+        DevBuf<int32_t> window(c, 2);
+        int32_t hw[2] = {0x7fffffff, -1};
+        window.upload(hw, 2);
+        if (R.nnz > 0) GMG_LAUNCH(c, mark_needed_kernel, div_up(R.nnz, kBlock), kBlock, 0, R.nnz, R.colidx.p, needed.p, window.p);
+        window.download(hw, 2);
+        sync(c);
+        if (hw[1] >= hw[0]) { k_lo = hw[0]; k_hi = hw[1] + 1; } else { k_lo = 0; k_hi = 0; }
     }
-    DevBuf<int32_t> ub1(c, int64_t(n) + 1), t_ptr(c, int64_t(n) + 1), flags(c, 2), overflow(c, m);
+    const int64_t kw = int64_t(k_hi) - k_lo;
+    DevBuf<int32_t> ub1(c, kw + 1), t_ptr(c, kw + 1), flags(c, 2), overflow(c, m);
     DevBuf<int2> t_loc(c, n);
     DevBuf<int32_t> ub2(c, int64_t(m) + 1), w_ptr(c, int64_t(m) + 1), w_cnt(c, int64_t(m) + 1);
     DevBuf<int64_t> totals(c, 3);
     flags.zero();
-    ProductArgs a{n, m, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p, R.rowptr.p, R.colidx.p, R.val.p,
+    ProductArgs a{n, m, k_lo, k_hi, a_colptr, a_rowidx, a_val, P.rowptr.p, P.colidx.p, P.val.p, R.rowptr.p, R.colidx.p, R.val.p,
                   all ? nullptr : needed.p, ub1.p, t_ptr.p, t_loc.p, nullptr, nullptr, ub2.p, w_ptr.p, w_cnt.p, nullptr, nullptr,
                   nullptr, nullptr, nullptr, flags.p, overflow.p};
     // ---- first product
     int64_t h_total[3] = {0, 0, 0};
-    GMG_LAUNCH(c, product1_bound_kernel, div_up(int64_t(n) + 1, kBlock), kBlock, 0, a);
-    exclusive_scan_i32(c, ub1.p, t_ptr.p, int64_t(n) + 1, totals.p);
+    GMG_LAUNCH(c, product1_bound_kernel, div_up(kw + 1, kBlock), kBlock, 0, a);
+    exclusive_scan_i32(c, ub1.p, t_ptr.p, kw + 1, totals.p);
     totals.download(h_total, 1);
     sync(c);
     GMG_REQUIRE(h_total[0] < (int64_t(1) << 31), GMG_ERR_INVALID, "galerkin: P^T A exceeds 32-bit indexing");
@@ -473,7 +492,7 @@ void galerkin(gmg_ctx* c, int32_t n, const int32_t* a_colptr, const int32_t* a_r
     DevBuf<double> t_val(c, h_total[0]);
     a.t_idx = t_idx.p; a.t_val = t_val.p;
     GMG_CUDA(cudaFuncSetAttribute(product1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Table1::bytes())));
-    GMG_LAUNCH(c, product1_kernel, div_up(n, kThreads1), kThreads1, Table1::bytes(), a);
+    if (kw > 0) GMG_LAUNCH(c, product1_kernel, div_up(kw, kThreads1), kThreads1, Table1::bytes(), a);
     tr.mark("T = P^T A");
     if (marks) cudaEventRecord(marks[2], c->stream);
     // ---- second product
