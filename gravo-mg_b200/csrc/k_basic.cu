@@ -288,10 +288,23 @@ __global__ void __launch_bounds__(kBlock) check_pattern_kernel(int32_t n, const 
     }
 }
 
+// colptr alone, before anything indexes rowidx with it: non-decreasing, starting at 0
+__global__ void __launch_bounds__(kBlock) check_colptr_kernel(int32_t n, const int32_t* __restrict__ colptr, int32_t* __restrict__ flag) {
+    const int64_t i = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (i < n && (colptr[i] > colptr[i + 1] || colptr[i] < 0)) *flag = 1;
+}
+
 void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric) {
     if (n == 0) return;
     DevBuf<int32_t> flags(c, 2);
     flags.zero();
+    {
+        GMG_LAUNCH(c, check_colptr_kernel, div_up(n, kBlock), kBlock, 0, n, colptr, flags.p);
+        int32_t bad = 0;
+        flags.download(&bad, 1);
+        sync(c);
+        GMG_REQUIRE(bad == 0, GMG_ERR_INVALID, "edge matrix: colptr must be non-decreasing");
+    }
     GMG_LAUNCH(c, check_pattern_kernel, div_up(int64_t(n) * kGroup, kBlock), kBlock, 0, n, colptr, rowidx, flags.p);
     int32_t h[2];
     flags.download(h, 2);

@@ -96,6 +96,7 @@ def test_cuda_matches_golden_fixtures(ctx, name):
 
 def test_edge_cases_and_errors(ctx, orc):
     import scipy.sparse as sp
+    from gravomg_b200 import capi
     from gravomg_b200.capi import GmgError
     V = np.asfortranarray(np.array([[0., 0, 0], [1, 0, 0], [5, 5, 5], [1.5, 0.2, 0]]))
     A = sp.csc_matrix(np.array([[1., 1, 0, 0], [1, 1, 0, 1], [0, 0, 1, 0], [0, 1, 0, 1]]))
@@ -121,6 +122,15 @@ def test_edge_cases_and_errors(ctx, orc):
     with pytest.raises(GmgError) as e:
         ctx.extract_coarse_edges(A.indptr, A.indices, val, 2, np.array([0, 1, 2, 1]))
     assert e.value.status == 2
+    # a column pointer that runs backwards is caught before any kernel indexes through it, and the context survives
+    bad_cp = A.indptr.copy(); bad_cp[2] = bad_cp[1] - 1
+    with pytest.raises(GmgError) as e:
+        ctx.fast_disc_sample(V, bad_cp, A.indices, 1.0)
+    assert e.value.status == 2
+    with pytest.raises(GmgError) as e:
+        capi.Input(ctx, V, bad_cp, A.indices, None)
+    assert e.value.status == 2
+    assert len(ctx.fast_disc_sample(V, A.indptr, A.indices, 0.6)) == len(w["sel"])
 
 
 def test_levels_streamed_out_during_the_build(ctx):
