@@ -191,6 +191,7 @@ int gmg_average_edge_length(gmg_ctx* c, int64_t n, const double* points, int64_t
         GMG_REQUIRE(n >= 0 && n_edges >= 0, GMG_ERR_INVALID, "negative size");
         auto d_pts = points_to_device(c, points, n, ld);
         auto d_e = to_device(c, edges, 2 * n_edges);
+        check_index_range(c, 2 * n_edges, d_e.p, n, "averageEdgeLength: edges");
         DevBuf<double> d_out(c, 1);
         KernelTimer t(c);
         average_edge_length_dev(c, int32_t(n), d_pts.p, n_edges, d_e.p, d_out.p);
@@ -432,6 +433,8 @@ int gmg_projected_points(gmg_ctx* c, int64_t n, int64_t m, const int32_t* rowptr
         const int64_t nnz = rowptr[n];
         auto d_rp = to_device(c, rowptr, n + 1); auto d_ci = to_device(c, colidx, nnz); auto d_va = to_device(c, val, nnz);
         auto d_cpts = points_to_device(c, coarse_points, m, coarse_ld);
+        check_outer_pointers(c, n, d_rp.p, "projectedPoints: weights");
+        check_index_range(c, nnz, d_ci.p, m, "projectedPoints: weights");
         DevBuf<double> d_out(c, 3 * n);
         KernelTimer t(c);
         projected_points_dev(c, int32_t(n), int32_t(m), d_rp.p, d_ci.p, d_va.p, d_cpts.p, d_out.p);

@@ -239,6 +239,9 @@ struct Trace {
 
 // Device-side exclusive scan of int32 counts (in place allowed); *total (device int64) receives the sum.
 void exclusive_scan_i32(gmg_ctx* c, const int32_t* in, int32_t* out, int64_t n, int64_t* d_total);
+// validation of caller-supplied index arrays that kernels use as addresses (throw GMG_ERR_INVALID)
+void check_index_range(gmg_ctx* c, int64_t count, const int32_t* idx, int64_t upper, const char* what);
+void check_outer_pointers(gmg_ctx* c, int64_t n, const int32_t* outer, const char* what);
 
 // ---- 3-vector arithmetic: same association order as the oracle ---------------------------------
 struct V3 { double x, y, z; };

@@ -294,6 +294,34 @@ __global__ void __launch_bounds__(kBlock) check_colptr_kernel(int32_t n, const i
     if (i < n && (colptr[i] > colptr[i + 1] || colptr[i] < 0)) *flag = 1;
 }
 
+// every idx[k] in [0, upper) -- for index arrays that arrive from the caller and are used as addresses
+__global__ void __launch_bounds__(kBlock) check_range_kernel(int64_t count, const int32_t* __restrict__ idx, int32_t upper,
+                                                             int32_t* __restrict__ flag) {
+    const int64_t k = int64_t(blockIdx.x) * kBlock + threadIdx.x;
+    if (k < count && (idx[k] < 0 || idx[k] >= upper)) *flag = 1;
+}
+void check_index_range(gmg_ctx* c, int64_t count, const int32_t* idx, int64_t upper, const char* what) {
+    if (count <= 0) return;
+    DevBuf<int32_t> flag(c, 1);
+    flag.zero();
+    GMG_LAUNCH(c, check_range_kernel, div_up(count, kBlock), kBlock, 0, count, idx, int32_t(upper), flag.p);
+    int32_t bad = 0;
+    flag.download(&bad, 1);
+    sync(c);
+    if (bad) throw Error{GMG_ERR_INVALID, std::string(what) + ": index out of range"};
+}
+// an outer-pointer array on the device: starts at 0 (checked on the host), non-decreasing
+void check_outer_pointers(gmg_ctx* c, int64_t n, const int32_t* outer, const char* what) {
+    if (n <= 0) return;
+    DevBuf<int32_t> flag(c, 1);
+    flag.zero();
+    GMG_LAUNCH(c, check_colptr_kernel, div_up(n, kBlock), kBlock, 0, int32_t(n), outer, flag.p);
+    int32_t bad = 0;
+    flag.download(&bad, 1);
+    sync(c);
+    if (bad) throw Error{GMG_ERR_INVALID, std::string(what) + ": outer pointers must be non-decreasing"};
+}
+
 void check_pattern(gmg_ctx* c, int32_t n, const int32_t* colptr, const int32_t* rowidx, bool need_symmetric) {
     if (n == 0) return;
     DevBuf<int32_t> flags(c, 2);

@@ -82,6 +82,8 @@ int gmg_spmv(gmg_ctx* c, int64_t n, int64_t n_inner, const int32_t* outer, const
         const int64_t nnz = outer[n];
         auto d_o = to_device(c, outer, n + 1); auto d_i = to_device(c, inner, nnz); auto d_v = to_device(c, val, nnz);
         auto d_x = to_device(c, x, n_inner);
+        check_outer_pointers(c, n, d_o.p, "spmv");
+        check_index_range(c, nnz, d_i.p, n_inner, "spmv");
         DevBuf<double> d_y(c, n);
         Timer t(c);
         spmv(c, int32_t(n), d_o.p, d_i.p, d_v.p, d_x.p, d_y.p, 1.0, nullptr);
@@ -98,6 +100,8 @@ int gmg_gauss_seidel(gmg_ctx* c, int64_t n, const int32_t* outer, const int32_t*
         const int64_t nnz = outer[n];
         auto d_o = to_device(c, outer, n + 1); auto d_i = to_device(c, inner, nnz); auto d_v = to_device(c, val, nnz);
         auto d_b = to_device(c, b, n); auto d_x = to_device(c, x, n);
+        check_outer_pointers(c, n, d_o.p, "gaussSeidel");
+        check_index_range(c, nnz, d_i.p, n, "gaussSeidel");
         Colouring col;
         colour_graph(c, int32_t(n), d_o.p, d_i.p, col);
         Timer t(c);

@@ -131,6 +131,17 @@ def test_edge_cases_and_errors(ctx, orc):
         capi.Input(ctx, V, bad_cp, A.indices, None)
     assert e.value.status == 2
     assert len(ctx.fast_disc_sample(V, A.indptr, A.indices, 0.6)) == len(w["sel"])
+    # index arrays the kernels use as addresses are range-checked at the boundary
+    with pytest.raises(GmgError) as e:
+        ctx.average_edge_length(V, np.array([[0, 1], [1, 7]], dtype=np.int32))
+    assert e.value.status == 2
+    with pytest.raises(GmgError) as e:
+        ctx.projected_points(w["prp"], np.where(w["pci"] == 0, 99, w["pci"]).astype(np.int32), w["pva"], w["cpts"])
+    assert e.value.status == 2
+    bad_inner = A.indices.copy(); bad_inner[3] = 9
+    with pytest.raises(GmgError) as e:
+        capi.spmv(ctx, A.indptr, bad_inner, A.data, np.ones(4))
+    assert e.value.status == 2
 
 
 def test_levels_streamed_out_during_the_build(ctx):
