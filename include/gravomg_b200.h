@@ -99,6 +99,18 @@ int gmg_extract_edges(gmg_ctx* ctx, int64_t n, const int32_t* colptr, const int3
 int gmg_average_edge_length(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, int64_t n_edges,
                             const int32_t* edges, double* out_mean);
 
+/* averageEdgeLength for callers that cannot allocate [no counterpart in the reference]:
+ * code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc. Everything is a
+ * DEVICE pointer on ctx's device: d_points n x 3 column-major packed (x | y | z, leading dimension n), d_edges
+ * n_edges x 2 column-major, d_out_mean one double. The call allocates nothing (no cudaMalloc / cudaFree / pool): its
+ * scratch -- one partial sum per 2048 edge rows -- is a fixed 512 KiB __device__ array inside the library, which every
+ * GPU that loads the library holds until exit. LIMIT: n_edges <= 134,217,728, more is GMG_ERR_INVALID. The work is
+ * queued on ctx's stream and not waited for. All calls on a device share the scratch: calls that overlap on the GPU
+ * (other streams, other contexts of the same device) race and must be serialised by the caller; consecutive calls
+ * need no clearing. Same summation tree as gmg_average_edge_length: identical bits. (csrc/k_noalloc.cu) */
+int gmg_average_edge_length_noalloc(gmg_ctx* ctx, int64_t n, const double* d_points, int64_t n_edges,
+                                    const int32_t* d_edges, double* d_out_mean);
+
 /* selection_out has room for n entries, ascending; *m_out receives the count */
 int gmg_fast_disc_sample(gmg_ctx* ctx, int64_t n, const double* points, int64_t ld, const int32_t* colptr,
                          const int32_t* rowidx, double radius, int mode, uint64_t seed, int64_t* selection_out,
