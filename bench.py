@@ -195,7 +195,7 @@ def measured_peak():
 
 
 # kernels of each stage (for roofline.traffic: DRAM bytes per launch from the committed ncu --set full capture)
-STAGE_KERNELS = {"edge_lengths": ["edge_length_kernel"], "sampling": ["sampler_build_kernel<0>", "sampler_flow_kernel<0>"],
+STAGE_KERNELS = {"edge_lengths": ["edge_length_kernel"], "sampling": ["sampler_coherence_kernel<0>", "sampler_build_kernel<0>", "sampler_build_raw_kernel<0>", "sampler_flow_kernel<0, 0>"],
                  "parents": ["parents_sweep_kernel", "parents_pred_kernel"], "coarse_edges": ["coarse_rows_warp_kernel"],
                  "prolongation_rows": ["prolong_rows_kernel"], "galerkin_product2": ["product2_kernel", "compact_columns_kernel"],
                  "galerkin_product1": ["product1_kernel"],
