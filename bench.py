@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--driver", default="native", choices=["native", "python"],
                     help="N > 1: the build's phase loop in C++ with the library's own NCCL communicator (gmg_shard_build_nccl), "
                          "or driven from Python through torch.distributed")
+    ap.add_argument("--sharded", action="store_true", help="N = 1: run the workload through the row-sharded driver (world 1), "
+                                                            "the 1-GPU point of an N > 1 curve (C4, torus family)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-scale", type=float, default=None, help="size of the in-line CPU baseline sample (default: the workload itself, which also gives the parity check)")
     a = ap.parse_args()
@@ -59,13 +61,18 @@ def parse():
         # (10 M-vertex torus, P and A_c at every level, one V-cycle). N > 1: the same family row-sharded, 12.5 M
         # vertices per GPU (N = 8 is the 100 M-vertex mesh of config C5).
         a.workload = "C3" if world == 1 else f"T{a.per_gpu_mverts * world:g}"
+    if world > 1 and a.workload not in ("C4",) and not a.workload.startswith("T"):
+        raise SystemExit("bench.py: with N > 1 the workload is the torus family (T<millions>, the default) or C4; "
+                         "C1-C3 are single-GPU configurations")
+    if (world > 1 or a.sharded) and a.workload == "C4":
+        a.reorder = "morton"        # the row-sharded build always renumbers a cloud (see run_b200_sharded)
     torus = a.workload == "C3" or a.workload.startswith("T")
     if a.galerkin is None:
         a.galerkin = 1 if torus else 0
     if a.vcycle is None:
         a.vcycle = 1 if (torus and a.galerkin) else 0
     if a.sampler is None:
-        a.sampler = "hashed" if (world > 1 or a.workload.startswith("T")) else "exact"
+        a.sampler = "hashed" if (world > 1 or a.sharded or a.workload.startswith("T")) else "exact"
     return a
 
 
@@ -674,13 +681,32 @@ def run_b200_sharded(a, rank, world, local_rank):
     ctx = Context(local_rank, stream.cuda_stream)
     comm = TorchComm() if world > 1 else None
     native = NativeComm(ctx) if world > 1 and a.driver == "native" else None
-    nu, nv = torus_dims(a.workload)
-    n = nu * nv
     levels = 4
     mode = {"exact": capi.SAMPLER_EXACT, "parallel": capi.SAMPLER_PARALLEL, "hashed": capi.SAMPLER_HASHED}[a.sampler]
     galerkin = bool(a.galerkin or a.vcycle)
-    # the whole mesh, resident on every rank (with its system matrix when A_c is asked for)
-    inp = Input.torus(ctx, nu, nv, mass_shift=1e-3 if galerkin else None)
+    builder = None
+    if a.workload == "C4":
+        # config C4 row-sharded: every rank builds the same kNN graph on its own device (deterministic: exact neighbours,
+        # ties by index) from the cloud renumbered along the Morton curve -- contiguous row ranges of an unordered cloud
+        # would have the whole cloud as their halo. A graph without values: P only, no A_c, no V-cycle.
+        from gravomg_b200 import meshgen
+        V = meshgen.sphere_cloud(max(64, int(20_000_000 * a.scale)))
+        t0 = time.perf_counter()
+        perm = ctx.morton_order(V)
+        t1 = time.perf_counter()
+        V = np.asfortranarray(V[perm])          # (host gather, not timed)
+        t2 = time.perf_counter()
+        inp = Input.knn(ctx, V, 8)
+        torch.cuda.synchronize()
+        builder = {"what": "Morton order + exact kNN (k=8) graph on the device, on every rank", "morton_order_ms": 1e3 * (t1 - t0),
+                   "knn_ms": 1e3 * (time.perf_counter() - t2), "points": int(inp.n), "nnz": int(inp.nnz)}
+        n = inp.n
+        del V
+    else:
+        nu, nv = torus_dims(a.workload)
+        n = nu * nv
+        # the whole mesh, resident on every rank (with its system matrix when A_c is asked for)
+        inp = Input.torus(ctx, nu, nv, mass_shift=1e-3 if galerkin else None)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -809,7 +835,8 @@ def run_b200_sharded(a, rank, world, local_rank):
     total_bytes = sum(sum(v for k, v in stage_bytes(i).items() if k != "galerkin" or galerkin) for i in infos)
     achieved = total_bytes / (ms * 1e-3) / 1e9
     line = {"metric": METRIC, "value": n / (ms * 1e-3) / 1e6, "unit": "Mverts/s", "n_gpus": world, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong" if a.workload == "C4" else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {**bench_config(a, world),
                        "l2": "256 MB flush write between timed steps; inputs exceed the 126 MB L2",
@@ -829,6 +856,8 @@ def run_b200_sharded(a, rank, world, local_rank):
                          "frac": achieved / world / peak, "traffic": None, "algorithmic_bytes": int(total_bytes)}}
     if vc is not None:
         line["vcycle"] = vc
+    if builder is not None:
+        line["input_builder"] = builder
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -841,7 +870,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
         run_reference(a, rank, world)
-    elif world > 1 or a.workload.startswith("T"):
+    elif world > 1 or a.workload.startswith("T") or (a.sharded and a.workload == "C4"):
         run_b200_sharded(a, rank, world, local_rank)
     else:
         run_b200(a, rank, world, local_rank)
