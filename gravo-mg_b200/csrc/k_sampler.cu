@@ -491,8 +491,15 @@ constexpr int32_t kPending = 1 << 20;         // the global word (other-tile pre
 constexpr int32_t kDecided = 1 << 21;         // queued as OUT, or not a vertex at all
 constexpr int32_t kSlow = 1 << 22;            // lists not staged (no room, or not partitioned): read from global memory
 constexpr uint32_t kEmpty = 0xFFFFu;          // queue / mailbox slot not written yet
-constexpr int kFastWarps = 16;                // warps 1 .. kFastWarps pop the tile's queue; warp 0 watches the mailbox
-constexpr int kGroup = 8;                     // lanes that apply one rank's list
+// Shape of a flow block (31 worker warps + the watcher). Measured on C3 level 0 (B200, bit-exact in every shape):
+// FAST x lanes per rank, EXT lanes per rank -> ms: 16x8,8 -> 24.8 (four ranks per fast warp in lock step: a group cannot
+// look at its slot while a sibling applies a list; the trace shows a median 450 ns between a rank being queued and being
+// popped); 24x32,8 -> 24.1; 26x32,8 -> 22.3 (one rank per fast warp: that wait drops to 290 ns, but 5 EXT warps are
+// about as few as the other-tile halves tolerate: their queue wait doubles to 2.7 us); 27x32,8 -> 22.9; 28x32,8 -> 24.6;
+// 20x32,8 -> 30.5; 26x32,4 -> 26.4; 24x16,8 -> 25.3.
+constexpr int kFastWarps = 26;                // warps 1 .. kFastWarps pop the tile's queue; warp 0 watches the mailbox
+constexpr int kGroup = 32;                    // lanes that apply one rank's same-tile list
+constexpr int kXGroup = 8;                    // lanes that apply one rank's other-tile list
 constexpr int kPtrLen = kTile + 2;            // prefix arrays (kTile + 1 used; even length keeps 4-byte alignment)
 
 // DBG: the instantiation with the timeline / per-rank trace instrumentation (GMG_SAMPLER_DEBUG, GMG_SAMPLER_TRACE); the
@@ -669,10 +676,8 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
             }
             if (DBG && a.dbg && lane == 0) { a.dbg[8 * tile + 4] = looks; a.dbg[8 * tile + 5] = (unsigned long long)next; }
         } else if (warp <= kFastWarps) {
-            // ---- FAST: four ranks per warp at a time, 8 lanes each (lists are short, and what bounds the tile is how
-            //      many decided ranks are being applied at once: with one rank per warp the queue backs up and a rank
-            //      on the critical chain waits microseconds behind ranks that are not). The groups of a warp move in
-            //      lock step: look at the claimed slot, apply it if it is filled, claim the next.
+            // ---- FAST: 32 / kGroup ranks per warp at a time, kGroup lanes each. The groups of a warp move in lock step:
+            //      look at the claimed slot, apply it if it is filled, claim the next (kGroup = 32: one rank per warp).
             constexpr int grp = kGroup;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
             int32_t slot = 0;
@@ -727,7 +732,7 @@ __global__ void __launch_bounds__(kFlowThreads, 1) sampler_flow_kernel(SamplerAr
         } else {
             // ---- EXT: the other-tile half, with atomics that return: the lane that decides something about a rank of
             //      another tile tells that tile. Same lock-step groups; two L2 round trips per pass.
-            constexpr int grp = kGroup;
+            constexpr int grp = kXGroup;
             const int lead = lane & ~(grp - 1), sub = lane & (grp - 1);
             const int32_t total_x = *(volatile int32_t*)&s_ctr[3];
             int32_t slot = 0;
