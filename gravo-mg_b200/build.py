@@ -84,7 +84,7 @@ def build_facade_test():
     cmd = ["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-I", os.path.join(FACADE_DIR, "include"),
            "-I", os.path.join(root, "oracle", "eigen_shim"), "-I", os.path.join(root, "include"),
            *srcs, "-L", LIBDIR, "-lgravomg_b200",
-           "-Wl,-rpath,$ORIGIN", "-o", FACADE_TEST]
+           "-pthread", "-Wl,-rpath,$ORIGIN", "-o", FACADE_TEST]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"facade build failed:\n{r.stdout}\n{r.stderr}")

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <thread>
 
 #include <gravomg/multigrid.h>
 #include <gravomg/sampling.h>
@@ -53,6 +54,29 @@ int main(int argc, char** argv) {
         GravoMG::EdgeMatrix L = Eigen::Map<const GravoMG::EdgeMatrix>(n, n, Index(rowidx.size()), colptr.data(), rowidx.data(), aval.data());
 #endif
         auto fine_edge_matrix = GravoMG::toEdgeDistanceMatrix(L, fine_points);
+        {   // the reference's functions are stateless: two threads at once must get what one thread gets
+            const double r0 = radii[0] > 0 ? radii[0] : 0.5;
+            auto run = [&](std::vector<Index>& par, GravoMG::EdgeMatrix& ce) {
+                auto s = GravoMG::fastDiscSample(fine_points, fine_edge_matrix, r0);
+                par = GravoMG::assignParents(fine_points, fine_edge_matrix, s);
+                ce = GravoMG::extractCoarseEdges(fine_points, fine_edge_matrix, s, par);
+            };
+            std::vector<Index> p0, p1, p2;
+            GravoMG::EdgeMatrix c0, c1, c2;
+            run(p0, c0);
+            std::thread ta([&] { run(p1, c1); }), tb([&] { run(p2, c2); });
+            ta.join(); tb.join();
+            auto same = [](const GravoMG::EdgeMatrix& x, const GravoMG::EdgeMatrix& y) {
+                if (x.rows() != y.rows() || x.nonZeros() != y.nonZeros()) return false;
+                for (Index k = 0; k < x.nonZeros(); ++k)
+                    if (x.innerIndexPtr()[k] != y.innerIndexPtr()[k] || x.valuePtr()[k] != y.valuePtr()[k]) return false;
+                return true;
+            };
+            if (p1 != p0 || p2 != p0 || !same(c1, c0) || !same(c2, c0)) {
+                std::fprintf(stderr, "facade: concurrent callers disagree with a single caller\n");
+                return 2;
+            }
+        }
         for (int lvl = 0; lvl + 1 < meta[1]; ++lvl) {
             auto [edge_pairs, edge_distances] = GravoMG::extractEdges(fine_edge_matrix);
             const double own_radius = std::cbrt(8.0) * GravoMG::averageEdgeLength(fine_points, edge_pairs);

@@ -6,30 +6,34 @@
 
 #include <algorithm>
 #include <cmath>
-#include <mutex>
+#include <atomic>
 
 #include "gravomg_b200.h"
 
 namespace GravoMG {
 namespace {
 
-int g_device = 0;
-gmg_ctx* g_ctx = nullptr;
-std::mutex g_mutex;
-
-struct CtxGuard { ~CtxGuard() { if (g_ctx) gmg_destroy(g_ctx); g_ctx = nullptr; } } g_guard;
+// One context (= one CUDA stream and its retained results) PER CALLING THREAD: the reference's functions are stateless
+// and may be called from several threads at once; here a call such as extractCoarseEdges is two C-ABI calls (compute,
+// then fetch of the retained result) on one context, so threads must not share one. Created on first use, destroyed
+// when the thread ends.
+std::atomic<int> g_device{0};
+struct ThreadContext {
+    gmg_ctx* c = nullptr;
+    ~ThreadContext() { if (c) gmg_destroy(c); }
+};
+thread_local ThreadContext t_ctx;
 
 gmg_ctx* context() {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    if (!g_ctx) {
-        const int rc = gmg_create(g_device, nullptr, &g_ctx);
+    if (!t_ctx.c) {
+        const int rc = gmg_create(g_device.load(), nullptr, &t_ctx.c);
         if (rc != GMG_OK) throw B200Error(rc, std::string("gmg_create: ") + gmg_last_error(nullptr));
     }
-    return g_ctx;
+    return t_ctx.c;
 }
 
 void check(int rc, const char* where) {
-    if (rc != GMG_OK) throw B200Error(rc, std::string(where) + ": " + gmg_last_error(g_ctx));
+    if (rc != GMG_OK) throw B200Error(rc, std::string(where) + ": " + gmg_last_error(t_ctx.c));
 }
 
 // compressed view of a column- or row-major Eigen sparse matrix (copy only when it is uncompressed)
@@ -56,7 +60,7 @@ Mat make_sparse(Index rows, Index cols, const std::vector<int>& outer, const std
 
 }  // namespace
 
-void setDevice(int device) { g_device = device; }
+void setDevice(int device) { g_device.store(device); }     // for contexts created from now on
 
 // reference src/utility.cpp:8-48: translate to the origin, scale by the longest axis, centre
 void scaleMesh(Eigen::MatrixXd& V, const Eigen::MatrixXi&, double scaleRatio) {
@@ -154,7 +158,7 @@ Eigen::SparseMatrix<double> extractCoarseEdges(const PointMatrix& fine_points, c
           "extractCoarseEdges");
     std::vector<int> rowidx(static_cast<size_t>(nnz));
     std::vector<double> val(static_cast<size_t>(nnz));
-    check(gmg_fetch_sparse(g_ctx, rowidx.data(), val.data()), "extractCoarseEdges");
+    check(gmg_fetch_sparse(context(), rowidx.data(), val.data()), "extractCoarseEdges");
     return make_sparse<EdgeMatrix>(mc, mc, colptr, rowidx, val);
 }
 
@@ -182,7 +186,7 @@ std::pair<std::vector<TriangleWithNormal>, std::vector<std::vector<size_t>>> con
           "constructVoronoiTriangles");
     std::vector<int64_t> tri(static_cast<size_t>(3 * T)), fan(static_cast<size_t>(3 * T));
     std::vector<double> nrm(static_cast<size_t>(3 * T));
-    check(gmg_fetch_triangles(g_ctx, tri.data(), nrm.data(), fan.data()), "constructVoronoiTriangles");
+    check(gmg_fetch_triangles(context(), tri.data(), nrm.data(), fan.data()), "constructVoronoiTriangles");
     std::pair<std::vector<TriangleWithNormal>, std::vector<std::vector<size_t>>> out;
     out.first.reserve(size_t(T));
     for (int64_t t = 0; t < T; ++t)
@@ -225,7 +229,7 @@ ProlongationOperator constructProlongation(const PointMatrix& fine_points, const
           "constructProlongation");
     std::vector<int> colidx(static_cast<size_t>(nnz));
     std::vector<double> val(static_cast<size_t>(nnz));
-    check(gmg_fetch_sparse(g_ctx, colidx.data(), val.data()), "constructProlongation");
+    check(gmg_fetch_sparse(context(), colidx.data(), val.data()), "constructProlongation");
     return make_sparse<ProlongationOperator>(n, mc, rowptr, colidx, val);
 }
 
